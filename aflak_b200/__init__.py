@@ -1,0 +1,626 @@
+"""aflak_b200 -- thin ctypes driver over libaflak_b200.so (the C ABI in include/aflak_b200.h).
+
+The product is the shared library: hand-written sm_100a kernels behind a C ABI that mirrors aflak's
+`cake::Transform` / `IOValue` operator registry.  This module only exists so that tests, bench.py and
+examples can call that ABI from Python; it contains no compute and no fallback.  If the library is missing
+the import fails loudly (build it with `python -m aflak_b200.build`).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libaflak_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "aflak_b200.h")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: the CUDA extension is not built. Run `python -m aflak_b200.build` "
+        "(nvcc, sm_100a). There is no CPU fallback."
+    )
+
+lib = C.CDLL(LIB_PATH)
+
+# ---- status / type enums (include/aflak_b200.h) -------------------------------------------------------
+OK, ERR_IO, ERR_RAWLOADER, ERR_FITS, ERR_UNEXPECTED_INPUT, ERR_SHAPE, ERR_CUDA, ERR_PANIC, ERR_ARGUMENT = range(9)
+(T_INTEGER, T_FLOAT, T_FLOAT2, T_FLOAT3, T_FLOAT3X3, T_STR, T_BOOL, T_FITS, T_IMAGE, T_MAP2DTO3DCOORDS, T_ROI, T_PATHS,
+ T_TONECURVE) = range(13)
+SUM_COMPENSATED, SUM_SEQUENTIAL = 0, 1
+EPI_SUM, EPI_MEAN, EPI_MEAN_RATIO, EPI_EW = 0, 1, 2, 3
+
+
+class afk_result(C.Structure):
+    _fields_ = [("status", C.c_int), ("value", C.c_void_p), ("message", C.c_void_p)]
+
+
+class afk_input_slot(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("type_id", C.c_int), ("default_value", C.c_void_p)]
+
+
+PLAIN_FUNCTION = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_void_p), C.c_size_t, C.POINTER(afk_result), C.c_size_t)
+
+
+class afk_transform_desc(C.Structure):
+    _fields_ = [
+        ("name", C.c_char_p), ("kind", C.c_char_p), ("description", C.c_char_p),
+        ("major", C.c_uint8), ("minor", C.c_uint8), ("patch", C.c_uint8),
+        ("n_inputs", C.c_size_t), ("inputs", C.POINTER(afk_input_slot)),
+        ("n_outputs", C.c_size_t), ("outputs", C.POINTER(C.c_int)),
+        ("f", PLAIN_FUNCTION),
+    ]
+
+
+class afk_colormap_chain(C.Structure):
+    _fields_ = [("logscale_a", C.c_float), ("logscale_vmin", C.c_float), ("logscale_vmax", C.c_float),
+                ("normalize_min", C.c_float), ("normalize_max", C.c_float),
+                ("tone_table", C.POINTER(C.c_float)), ("tone_len", C.c_size_t)]
+
+
+def _sig(name, restype, *argtypes):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = list(argtypes)
+    return fn
+
+
+_P = C.c_void_p
+_i64p = C.POINTER(C.c_int64)
+_fp = C.POINTER(C.c_float)
+_u8p = C.POINTER(C.c_uint8)
+
+_sig("afk_last_error", C.c_char_p)
+_sig("afk_abi_version", C.c_int)
+_sig("afk_device_count", C.c_int)
+_sig("afk_set_device", C.c_int, C.c_int)
+_sig("afk_set_stream", C.c_int, _P)
+_sig("afk_get_stream", _P)
+_sig("afk_synchronize", C.c_int)
+_sig("afk_launch_count", C.c_uint64)
+_sig("afk_type_name", C.c_char_p, C.c_int)
+_sig("afk_type_from_name", C.c_int, C.c_char_p)
+_sig("afk_type_convertible", C.c_int, C.c_int, C.c_int)
+_sig("afk_type_editable", C.c_int, C.c_int)
+_sig("afk_image_upload", _P, _P, C.c_int, _i64p)
+_sig("afk_image_alloc", _P, C.c_int, _i64p)
+_sig("afk_image_wrap_device", _P, _P, C.c_int, _i64p)
+_sig("afk_image_synthetic", _P, C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int)
+_sig("afk_image_retain", None, _P)
+_sig("afk_image_release", None, _P)
+_sig("afk_image_ndim", C.c_int, _P)
+_sig("afk_image_shape", _i64p, _P)
+_sig("afk_image_len", C.c_int64, _P)
+_sig("afk_image_device_ptr", _P, _P)
+_sig("afk_image_device", C.c_int, _P)
+_sig("afk_image_download", C.c_int, _P, _P)
+_sig("afk_image_unit", C.c_char_p, _P)
+_sig("afk_image_set_unit", C.c_int, _P, C.c_char_p)
+_sig("afk_image_homogeneous", C.c_int, _P)
+_sig("afk_image_tag", C.c_char_p, _P)
+_sig("afk_image_set_tag", C.c_int, _P, C.c_char_p)
+_sig("afk_image_has_meta", C.c_int, _P)
+_sig("afk_image_set_axis", C.c_int, _P, C.c_int, C.c_char_p, C.c_char_p)
+_sig("afk_image_axis_name", C.c_char_p, _P, C.c_int)
+_sig("afk_image_axis_unit", C.c_char_p, _P, C.c_int)
+_sig("afk_value_integer", _P, C.c_int64)
+_sig("afk_value_float", _P, C.c_float)
+_sig("afk_value_float2", _P, _fp)
+_sig("afk_value_float3", _P, _fp)
+_sig("afk_value_float3x3", _P, _fp)
+_sig("afk_value_str", _P, C.c_char_p)
+_sig("afk_value_bool", _P, C.c_int)
+_sig("afk_value_image", _P, _P)
+_sig("afk_value_tone_curve", _P, _fp, C.c_size_t, _fp, C.c_size_t)
+_sig("afk_value_default_for", _P, C.c_int)
+_sig("afk_value_retain", None, _P)
+_sig("afk_value_release", None, _P)
+_sig("afk_value_type", C.c_int, _P)
+_sig("afk_value_get_integer", C.c_int, _P, _i64p)
+_sig("afk_value_get_float", C.c_int, _P, _fp)
+_sig("afk_value_get_floats", C.c_int, _P, _fp, C.c_size_t)
+_sig("afk_value_get_bool", C.c_int, _P, C.POINTER(C.c_int))
+_sig("afk_value_get_str", C.c_char_p, _P)
+_sig("afk_value_get_image", _P, _P)
+_sig("afk_value_convert", _P, _P, C.c_int)
+_sig("afk_value_eq", C.c_int, _P, _P)
+_sig("afk_result_clear", None, C.POINTER(afk_result))
+_sig("afk_result_display", _P, C.POINTER(afk_result))
+_sig("afk_free", None, _P)
+_sig("afk_transform_count", C.c_size_t)
+_sig("afk_transform_at", C.POINTER(afk_transform_desc), C.c_size_t)
+_sig("afk_get_transform", C.POINTER(afk_transform_desc), C.c_char_p)
+_sig("afk_transform_call", C.c_int, C.POINTER(afk_transform_desc), C.POINTER(C.c_void_p), C.c_size_t, C.POINTER(afk_result), C.c_size_t)
+_sig("afk_set_sum_mode", C.c_int, C.c_int)
+_sig("afk_get_sum_mode", C.c_int)
+_sig("afk_fused_average_ratio", C.c_int, _P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p))
+_sig("afk_fused_equivalent_width", C.c_int, _P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+     C.c_float, C.c_float, C.c_int, C.POINTER(C.c_void_p), _fp)
+_sig("afk_lut_linear", _P, _fp, _u8p, C.c_size_t)
+_sig("afk_lut_builtin", _P, C.c_char_p)
+_sig("afk_lut_builtin_count", C.c_size_t)
+_sig("afk_lut_builtin_name", C.c_char_p, C.c_size_t)
+_sig("afk_lut_release", None, _P)
+_sig("afk_lut_set_lims", None, _P, C.c_float, C.c_float, C.c_float)
+_sig("afk_lut_lims", None, _P, _fp)
+_sig("afk_lut_set_gradient", C.c_int, _P, _fp, _u8p, C.c_size_t)
+_sig("afk_lut_color_at", None, _P, C.c_float, _u8p)
+_sig("afk_lut_color_at_bounds", None, _P, C.c_float, C.c_float, C.c_float, _u8p)
+_sig("afk_lut_table", None, _P, _u8p)
+_sig("afk_lut_bounds", C.c_size_t, _P, _fp, _u8p, _fp, _u8p, C.c_size_t)
+_sig("afk_image_vmin_vmax", C.c_int, _P, _fp, _fp)
+_sig("afk_colormap", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int, C.POINTER(afk_colormap_chain), _P)
+_sig("afk_colormap_host", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int, C.POINTER(afk_colormap_chain), _P)
+_sig("afk_colormap_rgb_host", C.c_int, _P, C.POINTER(C.c_void_p), _fp, _fp, C.c_int, C.c_int, _P)
+_sig("afk_k_reduce", C.c_int, _P, C.c_int64, C.c_int64, C.c_int, _i64p, _i64p, C.c_int, _fp, C.c_int, _P)
+_sig("afk_profile_reduce", C.c_int, C.c_int)
+_sig("afk_profile_reduce_read", C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64))
+_sig("afk_ipc_export", C.c_int, _P, _u8p)
+_sig("afk_ipc_open", _P, _u8p)
+_sig("afk_ipc_close", C.c_int, _P)
+_sig("afk_graph_new", _P)
+_sig("afk_graph_free", None, _P)
+_sig("afk_graph_add_transform", C.c_int64, _P, C.c_char_p)
+_sig("afk_graph_add_constant", C.c_int64, _P, _P)
+_sig("afk_graph_set_constant", C.c_int, _P, C.c_int64, _P)
+_sig("afk_graph_connect", C.c_int, _P, C.c_int64, C.c_size_t, C.c_int64, C.c_size_t)
+_sig("afk_graph_disconnect", C.c_int, _P, C.c_int64, C.c_size_t)
+_sig("afk_graph_compute", C.c_int, _P, C.c_int64, C.c_size_t, C.POINTER(afk_result))
+_sig("afk_graph_calls", C.c_uint64, _P)
+_sig("afk_graph_set_fusion", None, _P, C.c_int)
+
+
+class AflakError(Exception):
+    """An `Err(IOErr)` (or a reference panic) coming back through the ABI."""
+
+    def __init__(self, status, message):
+        super().__init__(f"[{status}] {message}")
+        self.status = status
+        self.message = message
+
+
+def _check(status):
+    if status != OK:
+        raise AflakError(status, lib.afk_last_error().decode())
+
+
+def device_count():
+    return lib.afk_device_count()
+
+
+def set_device(i):
+    _check(lib.afk_set_device(i))
+
+
+def synchronize():
+    _check(lib.afk_synchronize())
+
+
+def set_stream(ptr):
+    _check(lib.afk_set_stream(C.c_void_p(ptr) if ptr else None))
+
+
+def launch_count():
+    return int(lib.afk_launch_count())
+
+
+def set_sum_mode(mode):
+    _check(lib.afk_set_sum_mode(mode))
+
+
+def type_name(t):
+    return lib.afk_type_name(t).decode()
+
+
+# ---- Image: device-resident WcsArray handle -------------------------------------------------------------
+class Image:
+    def __init__(self, handle, owned=True):
+        if not handle:
+            raise AflakError(ERR_CUDA, lib.afk_last_error().decode())
+        self._h = C.c_void_p(handle)
+        self._owned = owned
+
+    @classmethod
+    def upload(cls, array):
+        a = np.ascontiguousarray(array, dtype=np.float32)
+        shape = (C.c_int64 * max(a.ndim, 1))(*a.shape)
+        img = cls(lib.afk_image_upload(a.ctypes.data_as(_P), a.ndim, shape))
+        synchronize()  # `a` may be a temporary
+        return img
+
+    @classmethod
+    def synthetic(cls, seed, nz, ny, nx, y0=0, rows=None, pathology=False):
+        rows = ny - y0 if rows is None else rows
+        return cls(lib.afk_image_synthetic(seed, nz, ny, nx, y0, rows, int(pathology)))
+
+    @classmethod
+    def wrap_device(cls, ptr, shape):
+        sh = (C.c_int64 * max(len(shape), 1))(*shape)
+        return cls(lib.afk_image_wrap_device(C.c_void_p(ptr), len(shape), sh))
+
+    @classmethod
+    def alloc(cls, shape):
+        sh = (C.c_int64 * max(len(shape), 1))(*shape)
+        return cls(lib.afk_image_alloc(len(shape), sh))
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def shape(self):
+        n = lib.afk_image_ndim(self._h)
+        p = lib.afk_image_shape(self._h)
+        return tuple(int(p[i]) for i in range(n))
+
+    @property
+    def device_ptr(self):
+        return lib.afk_image_device_ptr(self._h)
+
+    @property
+    def unit(self):
+        return lib.afk_image_unit(self._h).decode()
+
+    @unit.setter
+    def unit(self, u):
+        lib.afk_image_set_unit(self._h, u.encode() if u else None)
+
+    @property
+    def tag(self):
+        t = lib.afk_image_tag(self._h)
+        return None if t is None else t.decode()
+
+    @tag.setter
+    def tag(self, t):
+        lib.afk_image_set_tag(self._h, None if t is None else t.encode())
+
+    @property
+    def has_meta(self):
+        return bool(lib.afk_image_has_meta(self._h))
+
+    @property
+    def homogeneous(self):
+        return bool(lib.afk_image_homogeneous(self._h))
+
+    def set_axis(self, i, name, unit):
+        lib.afk_image_set_axis(self._h, i, None if name is None else name.encode(), (unit or "").encode())
+
+    def axis(self, i):
+        return lib.afk_image_axis_name(self._h, i).decode(), lib.afk_image_axis_unit(self._h, i).decode()
+
+    def download(self):
+        out = np.empty(self.shape, dtype=np.float32)
+        _check(lib.afk_image_download(self._h, out.ctypes.data_as(_P)))
+        return out
+
+    def vmin_vmax(self):
+        a, b = C.c_float(), C.c_float()
+        _check(lib.afk_image_vmin_vmax(self._h, C.byref(a), C.byref(b)))
+        return np.float32(a.value), np.float32(b.value)
+
+    def __del__(self):
+        if getattr(self, "_owned", False) and self._h:
+            lib.afk_image_release(self._h)
+            self._h = None
+
+
+class ToneCurve:
+    """ToneCurveState: `arr` table + control points (imgui_tone_curve/src/lib.rs:10-48)."""
+
+    def __init__(self, arr=None, cp=((0.0, 0.0), (1.0, 1.0))):
+        self.arr = np.arange(256, dtype=np.float32) if arr is None else np.ascontiguousarray(arr, dtype=np.float32)
+        self.cp = np.ascontiguousarray(cp, dtype=np.float32).reshape(-1, 2)
+
+
+def _to_value(x):
+    """Python object -> new afk_value* (caller releases)."""
+    if isinstance(x, Image):
+        return lib.afk_value_image(x.handle)
+    if isinstance(x, bool):
+        return lib.afk_value_bool(int(x))
+    if isinstance(x, (int, np.integer)):
+        return lib.afk_value_integer(int(x))
+    if isinstance(x, (float, np.floating)):
+        return lib.afk_value_float(float(x))
+    if isinstance(x, str):
+        return lib.afk_value_str(x.encode())
+    if isinstance(x, ToneCurve):
+        return lib.afk_value_tone_curve(x.arr.ctypes.data_as(_fp), x.arr.size, x.cp.ctypes.data_as(_fp), x.cp.shape[0])
+    if isinstance(x, (tuple, list, np.ndarray)):
+        a = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+        ctor = {2: lib.afk_value_float2, 3: lib.afk_value_float3, 9: lib.afk_value_float3x3}.get(a.size)
+        if ctor is None:
+            raise TypeError("float tuples must have 2, 3 or 9 entries")
+        return ctor(a.ctypes.data_as(_fp))
+    raise TypeError(f"cannot convert {type(x)} to an IOValue")
+
+
+def _from_value(v):
+    """afk_value* (borrowed) -> Python object. Images get their own reference."""
+    t = lib.afk_value_type(v)
+    if t == T_INTEGER:
+        o = C.c_int64()
+        lib.afk_value_get_integer(v, C.byref(o))
+        return int(o.value)
+    if t == T_FLOAT:
+        o = C.c_float()
+        lib.afk_value_get_float(v, C.byref(o))
+        return np.float32(o.value)
+    if t in (T_FLOAT2, T_FLOAT3, T_FLOAT3X3):
+        buf = (C.c_float * 9)()
+        n = lib.afk_value_get_floats(v, buf, 9)
+        return np.array(buf[:n], dtype=np.float32)
+    if t == T_BOOL:
+        o = C.c_int()
+        lib.afk_value_get_bool(v, C.byref(o))
+        return bool(o.value)
+    if t == T_STR:
+        return lib.afk_value_get_str(v).decode()
+    if t == T_IMAGE:
+        h = lib.afk_value_get_image(v)
+        lib.afk_image_retain(h)
+        return Image(h)
+    if t == T_TONECURVE:
+        buf = (C.c_float * 4096)()
+        n = lib.afk_value_get_floats(v, buf, 4096)
+        return ToneCurve(np.array(buf[:n], dtype=np.float32))
+    return None
+
+
+class Transform:
+    """View of one registry entry (Algorithm::Function, aflak_cake/src/transform.rs:33-48)."""
+
+    def __init__(self, desc_ptr):
+        self._d = desc_ptr
+        d = desc_ptr.contents
+        self.name = d.name.decode()
+        self.kind = d.kind.decode()
+        self.description = d.description.decode()
+        self.version = (d.major, d.minor, d.patch)
+        self.inputs = []
+        for i in range(d.n_inputs):
+            s = d.inputs[i]
+            default = _from_value(C.c_void_p(s.default_value)) if s.default_value else None
+            self.inputs.append((s.name.decode(), type_name(s.type_id), default))
+        self.outputs = [type_name(d.outputs[i]) for i in range(d.n_outputs)]
+
+    def call_results(self, *args):
+        """Feed + call; returns one entry per output: a Python value, or an AflakError instance."""
+        d = self._d.contents
+        vals = [None if a is None else _to_value(a) for a in args]
+        arr = (C.c_void_p * max(len(vals), 1))(*[C.c_void_p(v) if v else None for v in vals])
+        res = (afk_result * max(d.n_outputs, 1))()
+        try:
+            lib.afk_transform_call(self._d, arr, len(vals), res, d.n_outputs)
+            out = []
+            for i in range(d.n_outputs):
+                r = res[i]
+                if r.status == OK and r.value:
+                    out.append(_from_value(C.c_void_p(r.value)))
+                else:
+                    msg = C.cast(r.message, C.c_char_p).value.decode() if r.message else lib.afk_last_error().decode()
+                    out.append(AflakError(r.status if r.status != OK else ERR_PANIC, msg))
+            return out
+        finally:
+            for i in range(d.n_outputs):
+                lib.afk_result_clear(C.byref(res[i]))
+            for v in vals:
+                if v:
+                    lib.afk_value_release(C.c_void_p(v))
+
+    def __call__(self, *args):
+        out = self.call_results(*args)
+        for o in out:
+            if isinstance(o, AflakError):
+                raise o
+        return out[0] if len(out) == 1 else tuple(out)
+
+
+def get_transform(name):
+    """NamedAlgorithms::get_transform (aflak_primitives/src/lib.rs:749-758)."""
+    p = lib.afk_get_transform(name.encode())
+    return Transform(p) if p else None
+
+
+def transformations():
+    return [Transform(lib.afk_transform_at(i)) for i in range(lib.afk_transform_count())]
+
+
+def call(name, *args):
+    t = get_transform(name)
+    if t is None:
+        raise KeyError(name)
+    return t(*args)
+
+
+# ---- fused paths --------------------------------------------------------------------------------------------
+def fused_average_ratio(cube, s0, e0, s1, e1):
+    out = C.c_void_p()
+    _check(lib.afk_fused_average_ratio(cube.handle, s0, e0, s1, e1, C.byref(out)))
+    return Image(out.value)
+
+
+def fused_equivalent_width(cube, on, off1, off2, fl, vmax, is_emission, want_minmax=False):
+    out = C.c_void_p()
+    mm = (C.c_float * 2)()
+    _check(lib.afk_fused_equivalent_width(cube.handle, on[0], on[1], off1[0], off1[1], off2[0], off2[1], fl, vmax,
+                                          int(is_emission), C.byref(out), mm if want_minmax else None))
+    img = Image(out.value)
+    return (img, (np.float32(mm[0]), np.float32(mm[1]))) if want_minmax else img
+
+
+def k_reduce(cube_ptr, nz, n2, windows, epilogue, out_ptr, params=None, sum_mode=SUM_COMPENSATED):
+    """Raw kernel layer: device pointers in, launch on this thread's stream."""
+    n = len(windows)
+    st = (C.c_int64 * n)(*[w[0] for w in windows])
+    en = (C.c_int64 * n)(*[w[1] for w in windows])
+    pr = (C.c_float * 5)(*(list(params) + [0.0] * 5)[:5]) if params is not None else None
+    _check(lib.afk_k_reduce(C.c_void_p(cube_ptr), nz, n2, n, st, en, epilogue, pr, sum_mode, C.c_void_p(out_ptr)))
+
+
+def profile_reduce(enable):
+    lib.afk_profile_reduce(int(enable))
+
+
+def profile_reduce_read():
+    ms, n = C.c_double(), C.c_uint64()
+    _check(lib.afk_profile_reduce_read(C.byref(ms), C.byref(n)))
+    return ms.value, int(n.value)
+
+
+# ---- display path ---------------------------------------------------------------------------------------------
+class Lut:
+    """ColorLUT (aflak_plot/src/imshow/lut.rs)."""
+
+    def __init__(self, gradient):
+        if isinstance(gradient, str):
+            self._h = C.c_void_p(lib.afk_lut_builtin(gradient.encode()))
+        else:
+            v = np.array([np.float32(s[0]) for s in gradient], dtype=np.float32)
+            c = np.ascontiguousarray([s[1] for s in gradient], dtype=np.uint8).reshape(-1, 3)
+            self._h = C.c_void_p(lib.afk_lut_linear(v.ctypes.data_as(_fp), c.ctypes.data_as(_u8p), v.size))
+        if not self._h:
+            raise AflakError(ERR_UNEXPECTED_INPUT, lib.afk_last_error().decode())
+
+    @staticmethod
+    def builtin_names():
+        return [lib.afk_lut_builtin_name(i).decode() for i in range(lib.afk_lut_builtin_count())]
+
+    @property
+    def handle(self):
+        return self._h
+
+    def set_lims(self, mn, mid, mx):
+        lib.afk_lut_set_lims(self._h, mn, mid, mx)
+
+    def lims(self):
+        out = (C.c_float * 3)()
+        lib.afk_lut_lims(self._h, out)
+        return tuple(np.float32(x) for x in out)
+
+    def set_gradient(self, gradient):
+        v = np.array([np.float32(s[0]) for s in gradient], dtype=np.float32)
+        c = np.ascontiguousarray([s[1] for s in gradient], dtype=np.uint8).reshape(-1, 3)
+        lib.afk_lut_set_gradient(self._h, v.ctypes.data_as(_fp), c.ctypes.data_as(_u8p), v.size)
+
+    def color_at(self, point):
+        rgb = (C.c_uint8 * 3)()
+        lib.afk_lut_color_at(self._h, point, rgb)
+        return [int(x) for x in rgb]
+
+    def color_at_bounds(self, point, vmin, vmax):
+        rgb = (C.c_uint8 * 3)()
+        lib.afk_lut_color_at_bounds(self._h, point, vmin, vmax, rgb)
+        return [int(x) for x in rgb]
+
+    def table(self):
+        out = np.empty((65536, 3), dtype=np.uint8)
+        lib.afk_lut_table(self._h, out.ctypes.data_as(_u8p))
+        return out
+
+    def bounds(self):
+        cap = 32
+        v1 = (C.c_float * cap)()
+        v2 = (C.c_float * cap)()
+        c1 = (C.c_uint8 * (3 * cap))()
+        c2 = (C.c_uint8 * (3 * cap))()
+        n = lib.afk_lut_bounds(self._h, v1, c1, v2, c2, cap)
+        return [((float(v1[i]), tuple(c1[3 * i:3 * i + 3])), (float(v2[i]), tuple(c2[3 * i:3 * i + 3]))) for i in range(n)]
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.afk_lut_release(self._h)
+            self._h = None
+
+
+def _chain_struct(chain):
+    if chain is None:
+        return None, None
+    table = np.ascontiguousarray(chain["tone_table"], dtype=np.float32)
+    st = afk_colormap_chain(chain["logscale_a"], chain["logscale_vmin"], chain["logscale_vmax"], chain["normalize_min"],
+                            chain["normalize_max"], table.ctypes.data_as(_fp), table.size)
+    return st, table
+
+
+def colormap(img, lut, vmin=float("nan"), vmax=float("nan"), flip_y=True, channels=4, chain=None):
+    """make_raw_image (aflak_plot/src/imshow/image.rs:20-49) -> host uint8 array [ny, nx, channels]."""
+    ny, nx = img.shape
+    out = np.empty((ny, nx, channels), dtype=np.uint8)
+    st, keep = _chain_struct(chain)
+    _check(lib.afk_colormap_host(img.handle, lut.handle, vmin, vmax, int(flip_y), channels, C.byref(st) if st else None,
+                                 out.ctypes.data_as(_P)))
+    del keep
+    return out
+
+
+def colormap_device(img, lut, vmin, vmax, out_ptr, flip_y=True, channels=4, chain=None):
+    st, keep = _chain_struct(chain)
+    _check(lib.afk_colormap(img.handle, lut.handle, vmin, vmax, int(flip_y), channels, C.byref(st) if st else None,
+                            C.c_void_p(out_ptr)))
+    del keep
+
+
+def colormap_rgb(img, luts, vmin3, vmax3, flip_y=True, channels=3):
+    _, ny, nx = img.shape
+    out = np.empty((ny, nx, channels), dtype=np.uint8)
+    hs = (C.c_void_p * 3)(*[l.handle for l in luts])
+    a = (C.c_float * 3)(*vmin3)
+    b = (C.c_float * 3)(*vmax3)
+    _check(lib.afk_colormap_rgb_host(img.handle, hs, a, b, int(flip_y), channels, out.ctypes.data_as(_P)))
+    return out
+
+
+# ---- mini evaluator ---------------------------------------------------------------------------------------------
+class Graph:
+    """DST + Cache (aflak_cake/src/dst, cache.rs): device handles are what is cached."""
+
+    def __init__(self):
+        self._h = C.c_void_p(lib.afk_graph_new())
+
+    def add_transform(self, name):
+        i = lib.afk_graph_add_transform(self._h, name.encode())
+        if i < 0:
+            raise AflakError(ERR_UNEXPECTED_INPUT, lib.afk_last_error().decode())
+        return int(i)
+
+    def add_constant(self, x):
+        v = _to_value(x)
+        try:
+            return int(lib.afk_graph_add_constant(self._h, C.c_void_p(v)))
+        finally:
+            lib.afk_value_release(C.c_void_p(v))
+
+    def set_constant(self, t_idx, x):
+        v = _to_value(x)
+        try:
+            _check(lib.afk_graph_set_constant(self._h, t_idx, C.c_void_p(v)))
+        finally:
+            lib.afk_value_release(C.c_void_p(v))
+
+    def connect(self, from_t, out_i, to_t, in_i):
+        _check(lib.afk_graph_connect(self._h, from_t, out_i, to_t, in_i))
+
+    def disconnect(self, to_t, in_i):
+        _check(lib.afk_graph_disconnect(self._h, to_t, in_i))
+
+    def compute(self, t_idx, out_i=0):
+        r = afk_result()
+        st = lib.afk_graph_compute(self._h, t_idx, out_i, C.byref(r))
+        try:
+            if st != OK:
+                msg = C.cast(r.message, C.c_char_p).value.decode() if r.message else lib.afk_last_error().decode()
+                raise AflakError(st, msg)
+            return _from_value(C.c_void_p(r.value))
+        finally:
+            lib.afk_result_clear(C.byref(r))
+
+    @property
+    def calls(self):
+        return int(lib.afk_graph_calls(self._h))
+
+    def set_fusion(self, enable):
+        lib.afk_graph_set_fusion(self._h, int(enable))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.afk_graph_free(self._h)
+            self._h = None

@@ -1,0 +1,150 @@
+// host.h -- internal declarations of the C++ host layer behind include/aflak_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/aflak_b200.h"
+#include "kernels.h"
+
+namespace afk {
+
+// ---- errors ----------------------------------------------------------------------------------------
+struct Error {
+    afk_status status = AFK_OK;
+    std::string message;
+    explicit operator bool() const { return status != AFK_OK; }
+};
+inline Error ok() { return Error{}; }
+Error make_error(afk_status st, const std::string &msg);
+Error cuda_error(cudaError_t e, const char *what);
+std::string fmt(const char *f, ...) __attribute__((format(printf, 1, 2)));
+void set_last_error(const std::string &msg);
+afk_status fail(const Error &e); // records the message for afk_last_error(), returns the status
+
+#define AFK_CUDA(call)                                        \
+    do {                                                      \
+        cudaError_t e__ = (call);                             \
+        if (e__ != cudaSuccess) return cuda_error(e__, #call); \
+    } while (0)
+
+// ---- per-thread execution context -----------------------------------------------------------------
+struct StreamScratch {
+    ReduceWorkspace ws{nullptr, 0, nullptr, 0};
+};
+
+struct ThreadCtx {
+    int device = -1;
+    cudaStream_t own[16] = {};
+    cudaStream_t external = nullptr;
+    std::map<std::pair<int, cudaStream_t>, StreamScratch> scratch;
+    int sum_mode = SUM_COMPENSATED;
+    bool profile = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    uint64_t prof_launches = 0;
+    std::string last_error;
+};
+ThreadCtx &tls();
+// make sure a device is current and return the stream operators on this thread use
+Error current_stream(cudaStream_t *out, int *device);
+int sm_count(int device);
+cudaEvent_t event_get();
+void event_put(cudaEvent_t e);
+
+// ---- images ----------------------------------------------------------------------------------------
+struct AxisMeta {
+    bool has_name = false;
+    std::string name;
+    std::string unit; // "" == Unit::None
+    bool operator==(const AxisMeta &o) const { return has_name == o.has_name && name == o.name && unit == o.unit; }
+};
+
+struct ImageMeta { // host-side part of WcsArray (unit.rs:190-242); the WCS transform itself is an opaque blob
+    bool has_unit = false;
+    std::string unit;
+    bool homogeneous = true;
+    bool has_tag = false;
+    std::string tag;
+    bool has_meta = false;
+    AxisMeta axes[4];
+    std::vector<double> wcs; // opaque: CRVAL/CRPIX/CDELT per kept axis, copied or trimmed by make_slice
+    bool meta_equal(const ImageMeta &o) const;
+};
+
+} // namespace afk
+
+struct afk_image {
+    std::atomic<int> rc{1};
+    float *ptr = nullptr;
+    size_t bytes = 0;
+    bool owned = true;
+    bool ipc_peer = false;
+    afk_image *parent = nullptr; // a view keeps its parent alive
+    int device = 0;
+    int ndim = 0;
+    int64_t shape[AFK_MAX_NDIM] = {0, 0, 0, 0};
+    cudaStream_t stream = nullptr; // producer stream
+    cudaEvent_t ready = nullptr;   // recorded after the producing kernel
+    std::mutex mu;
+    std::vector<cudaEvent_t> readers; // last reads from other streams, waited on before the memory is freed
+    afk::ImageMeta meta;
+
+    int64_t len() const {
+        int64_t n = 1;
+        for (int i = 0; i < ndim; ++i) n *= shape[i];
+        return n;
+    }
+    int64_t frame_len() const { // product of all but the first axis
+        int64_t n = 1;
+        for (int i = 1; i < ndim; ++i) n *= shape[i];
+        return n;
+    }
+};
+
+struct afk_value {
+    std::atomic<int> rc{1};
+    afk_type type = AFK_T_INTEGER;
+    int64_t i = 0;
+    float f[9] = {0};
+    bool b = false;
+    std::string s;
+    afk_image *img = nullptr;
+    std::vector<float> arr; // ToneCurve arr
+    std::vector<float> cp;  // ToneCurve control points (x,y pairs)
+};
+
+namespace afk {
+
+// allocate an output image on the calling thread's stream
+Error image_new(int ndim, const int64_t *shape, afk_image **out);
+// order `stream` after the producer of img (no-op on the same stream)
+Error image_wait(const afk_image *img, cudaStream_t stream);
+// note that `stream` has enqueued a read of img
+void image_note_read(const afk_image *img, cudaStream_t stream);
+// mark img as produced on stream
+Error image_mark_ready(afk_image *img, cudaStream_t stream);
+
+// get (growing if needed) the reduce workspace of (device, stream)
+Error reduce_workspace(const ReducePlan &plan, int device, cudaStream_t stream, ReduceWorkspace *ws);
+
+// small zero-initialised device scratch, stream ordered
+Error scratch_u32(cudaStream_t s, size_t n, unsigned **out);
+void scratch_free(cudaStream_t s, void *p);
+
+// ---- operators on handles (ops.cpp) -----------------------------------------------------------------
+Error op_reduce(const afk_image *cube, int nwin, const int64_t *starts, const int64_t *ends, int epilogue,
+                const float *params, float ew_sign, bool want_minmax, afk_image **out, float *minmax);
+Error op_map(int op, const afk_image *u, const afk_image *v, float a, float b, float c, int flag0, int flag1, afk_image **out);
+Error op_min_max(const afk_image *img, float *mn, float *mx, bool *any);
+
+// unit algebra (unit.rs:39-163, 454-495)
+std::string unit_mul(bool has_a, const std::string &a, bool has_b, const std::string &b, bool *has_out);
+std::string unit_div(bool has_a, const std::string &a, bool has_b, const std::string &b, bool *has_out);
+
+void registry_init();
+
+} // namespace afk

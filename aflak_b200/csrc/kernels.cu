@@ -1,0 +1,840 @@
+// kernels.cu -- hand-written sm_100a kernels for aflak's data-parallel hot path.
+//
+// Every kernel here is HBM-bound streaming work (<= 2 flop/B): coalesced 16-byte lanes, enough independent
+// loads in flight per thread to cover DRAM latency, grids sized from the SM count, no tensor cores.
+// Rounding contract: every step the reference rounds to f32 is an explicit __f*_rn intrinsic here (the file
+// is also compiled with -fmad=false), so elementwise results are bit-identical to the Rust code.
+// Reference citations are relative to /root/reference/src/.
+#include "kernels.h"
+
+#include <atomic>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace afk {
+
+static std::atomic<uint64_t> g_launches{0};
+uint64_t launch_count() { return g_launches.load(); }
+#define AFK_COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
+
+// ----------------------------------------------------------------------------------------------------
+// load helpers: streaming 16-byte loads that do not allocate in L1 (every voxel is touched once)
+// ----------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ld_stream(const float4 *p) {
+    float4 r;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+        : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+        : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float ld_stream(const float *p) {
+    float r;
+    asm("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ double2 ld_cg(const double2 *p) {
+    double2 r;
+    asm volatile("ld.global.cg.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    return r;
+}
+
+template <int VEC> struct Lane;
+template <> struct Lane<4> {
+    using T = float4;
+    static __device__ __forceinline__ void unpack(const float4 &v, float (&x)[4]) {
+        x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w;
+    }
+    static __device__ __forceinline__ void store(float *p, const float (&x)[4]) {
+        *reinterpret_cast<float4 *>(p) = make_float4(x[0], x[1], x[2], x[3]);
+    }
+};
+template <> struct Lane<1> {
+    using T = float;
+    static __device__ __forceinline__ void unpack(const float &v, float (&x)[1]) { x[0] = v; }
+    static __device__ __forceinline__ void store(float *p, const float (&x)[1]) { *p = x[0]; }
+};
+
+// ----------------------------------------------------------------------------------------------------
+// K1/K2: axis-0 windowed reduction, stream-K decomposition
+//
+// Work is the flattened space (pixel tile p, concatenated window frame r): units = ntiles * ktot.  CTA g owns
+// the contiguous unit range [g*q, (g+1)*q): every CTA streams the same number of tile-frames, so all SMs
+// finish together whatever the cube shape (1024x1024x3840 or 74x74x4563).  A tile whose frames are owned by
+// one CTA is finished in registers; a tile split between CTAs goes through f64 partials in scratch and the
+// last CTA to arrive (per-tile counter) combines them in CTA order -> deterministic, no float atomics.
+//
+// Per pixel: compensated (Kahan) f32 accumulation in k order, plus the plain f32 sum `p` that carries
+// NaN/Inf exactly like the reference's sequential sum (ndarray 0.12.1 sum_axis; lib.rs:1324-1330).
+// ----------------------------------------------------------------------------------------------------
+struct ReduceKArgs {
+    const float *cube;
+    int64_t n2;
+    int nwin;
+    int64_t start[kMaxWindows];
+    int64_t woff[kMaxWindows + 1]; // prefix sum of window lengths; woff[nwin] == ktot
+    float cnt[kMaxWindows];        // window length as the f32 the reference builds by repeated +1.0
+    int64_t ktot, units, q, ntiles;
+    int epilogue;
+    float pa, pb, pfl, pmax, psign;
+    float *out;
+    unsigned *minmax;
+    double2 *partials;
+    unsigned *counters;
+};
+
+template <bool COMP> struct Acc {
+    float s, c, p;
+};
+
+template <bool COMP> __device__ __forceinline__ void acc_init(Acc<COMP> &a) {
+    // -0.0 is the additive identity for every x including -0.0 (0.0 + -0.0 would give +0.0)
+    a.s = -0.0f;
+    a.c = 0.0f;
+    a.p = -0.0f;
+}
+
+template <bool COMP> __device__ __forceinline__ void acc_add(Acc<COMP> &a, float x) {
+    a.p = __fadd_rn(a.p, x);
+    if (COMP) {
+        float y = __fsub_rn(x, a.c);
+        float t = __fadd_rn(a.s, y);
+        a.c = __fsub_rn(__fsub_rn(t, a.s), y);
+        a.s = t;
+    }
+}
+
+template <bool COMP> __device__ __forceinline__ double acc_value(const Acc<COMP> &a) {
+    return COMP ? ((double)a.s - (double)a.c) : (double)a.p;
+}
+
+__device__ __forceinline__ float finalize_sum(double d, float p) {
+    // non-finite plain sum: the reference's own f32 sum is NaN/Inf here -> reproduce it
+    float r = (float)d;
+    if (!(fabsf(p) <= FLT_MAX)) r = p;
+    return r;
+}
+
+template <int VEC, bool COMP, int U>
+__device__ __forceinline__ void acc_batch(const char *&ptr, size_t stride, Acc<COMP> (&acc)[VEC]) {
+    using V = typename Lane<VEC>::T;
+    V x[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) x[j] = ld_stream(reinterpret_cast<const V *>(ptr + (size_t)j * stride));
+    ptr += (size_t)U * stride;
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+        float e[VEC];
+        Lane<VEC>::unpack(x[j], e);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) acc_add<COMP>(acc[i], e[i]);
+    }
+}
+
+// frames [ka, kb) of one pixel lane, strictly in k order
+template <int VEC, bool COMP>
+__device__ __forceinline__ void accumulate(const float *lane_base, int64_t n2, int64_t ka, int64_t kb,
+                                           Acc<COMP> (&acc)[VEC]) {
+    const size_t stride = (size_t)n2 * sizeof(float);
+    const char *ptr = reinterpret_cast<const char *>(lane_base) + (size_t)ka * stride;
+    int64_t n = kb - ka;
+    for (; n >= 8; n -= 8) acc_batch<VEC, COMP, 8>(ptr, stride, acc);
+    if (n >= 4) { acc_batch<VEC, COMP, 4>(ptr, stride, acc); n -= 4; }
+    if (n >= 2) { acc_batch<VEC, COMP, 2>(ptr, stride, acc); n -= 2; }
+    if (n >= 1) { acc_batch<VEC, COMP, 1>(ptr, stride, acc); }
+}
+
+__device__ __forceinline__ unsigned f32_key(float f) {
+    unsigned b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ inline float key_f32(unsigned k) {
+    unsigned b = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+#endif
+}
+float minmax_decode_min(unsigned inv_key) { return key_f32(~inv_key); }
+float minmax_decode_max(unsigned key) { return key_f32(key); }
+
+// Block-wide min/max of non-NaN values -> 3 atomics per CTA. result = {~key(min), key(max), any}
+__device__ __forceinline__ void block_minmax_flush(float mn, float mx, bool any, unsigned *result) {
+    __shared__ unsigned s_mn[32], s_mx[32], s_any[32];
+    unsigned kmn = any ? ~f32_key(mn) : 0u, kmx = any ? f32_key(mx) : 0u, a = any ? 1u : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+        kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+        a |= __shfl_xor_sync(0xffffffffu, a, o);
+    }
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+    if (l == 0) { s_mn[w] = kmn; s_mx[w] = kmx; s_any[w] = a; }
+    __syncthreads();
+    if (w == 0) {
+        kmn = l < nw ? s_mn[l] : 0u;
+        kmx = l < nw ? s_mx[l] : 0u;
+        a = l < nw ? s_any[l] : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+            kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+            a |= __shfl_xor_sync(0xffffffffu, a, o);
+        }
+        if (l == 0 && a) {
+            atomicMax(result + 0, kmn);
+            atomicMax(result + 1, kmx);
+            atomicMax(result + 2, 1u);
+        }
+    }
+}
+
+// create_equivalent_width, lib.rs:1584-1596: four separately rounded steps then the `> max` select
+__device__ __forceinline__ float ew_value(float off, float on, float fl, float mx, float sign) {
+    float t = __fsub_rn(off, on);
+    t = __fmul_rn(t, fl);
+    t = __fdiv_rn(t, off);
+    t = __fmul_rn(t, sign);
+    return (t > mx) ? 0.0f : t;
+}
+
+template <int NW>
+__device__ __forceinline__ float reduce_epilogue(const ReduceKArgs &a, const float (&S)[NW]) {
+    switch (a.epilogue) {
+    case EPI_SUM: return S[0];
+    case EPI_MEAN: return __fdiv_rn(S[0], a.cnt[0]);
+    case EPI_MEAN_RATIO: {
+        if (NW < 2) return 0.0f;
+        float m0 = __fdiv_rn(S[0], a.cnt[0]);
+        float m1 = __fdiv_rn(S[NW > 1 ? 1 : 0], a.cnt[1]);
+        return __fdiv_rn(m0, m1); // &WcsArray / &WcsArray, unit.rs:863-880
+    }
+    case EPI_EW: {
+        if (NW < 3) return 0.0f;
+        float on = __fdiv_rn(S[0], a.cnt[0]);
+        float off1 = __fdiv_rn(S[NW > 1 ? 1 : 0], a.cnt[1]);
+        float off2 = __fdiv_rn(S[NW > 2 ? 2 : 0], a.cnt[2]);
+        // linear_composition(u=off1, v=off2, a, b), lib.rs:1288-1297
+        float off = __fadd_rn(__fmul_rn(off1, a.pa), __fmul_rn(off2, a.pb));
+        return ew_value(off, on, a.pfl, a.pmax, a.psign);
+    }
+    }
+    return 0.0f;
+}
+
+template <int VEC, bool COMP, int NW>
+__global__ void __launch_bounds__(kReduceBlock, kReduceCtasPerSm) reduce_kernel(const ReduceKArgs a) {
+    constexpr int64_t TILE = (int64_t)kReduceBlock * VEC;
+    const int tid = threadIdx.x;
+    const int64_t g = blockIdx.x;
+    int64_t u = g * a.q;
+    const int64_t uend = min(u + a.q, a.units);
+    const int64_t p_first = u / a.ktot;
+    __shared__ int s_last;
+
+    float mm_min = __int_as_float(0x7f800000), mm_max = __int_as_float(0xff800000);
+    bool mm_any = false;
+
+    while (u < uend) {
+        const int64_t p = u / a.ktot;
+        const int64_t tile_u0 = p * a.ktot;
+        const int64_t r = u - tile_u0;
+        const int64_t seg_end = min(uend, tile_u0 + a.ktot);
+        const int64_t r_end = r + (seg_end - u);
+        const bool full = (r == 0) && (r_end == a.ktot);
+        const int64_t px = p * TILE + (int64_t)tid * VEC;
+        const bool active = px < a.n2;
+        const float *lane_base = a.cube + px;
+        const int slot = (p == p_first) ? 0 : 1;
+
+        float S[NW][VEC];
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
+            const int64_t lo = max(r, a.woff[w]), hi = min(r_end, a.woff[w + 1]);
+            if (w < a.nwin && lo < hi) {
+                Acc<COMP> acc[VEC];
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) acc_init<COMP>(acc[i]);
+                if (active)
+                    accumulate<VEC, COMP>(lane_base, a.n2, a.start[w] + (lo - a.woff[w]), a.start[w] + (hi - a.woff[w]), acc);
+                if (full) {
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) S[w][i] = finalize_sum(acc_value<COMP>(acc[i]), acc[i].p);
+                } else if (active) {
+                    double2 *dst = a.partials + (((size_t)g * 2 + slot) * a.nwin + w) * TILE + (size_t)tid * VEC;
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) dst[i] = make_double2(acc_value<COMP>(acc[i]), (double)acc[i].p);
+                }
+            }
+        }
+
+        if (!full) {
+            // publish partials, then count arrivals on this tile; the last CTA to arrive combines
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) {
+                const int64_t g_lo = tile_u0 / a.q, g_hi = (tile_u0 + a.ktot - 1) / a.q;
+                const unsigned expect = (unsigned)(g_hi - g_lo + 1);
+                const unsigned prev = atomicAdd(a.counters + p, 1u);
+                const int last = (prev == expect - 1);
+                if (last) a.counters[p] = 0u; // self-reset for the next launch
+                s_last = last;
+            }
+            __syncthreads();
+            const bool last = s_last != 0;
+            if (!last) {
+                u = seg_end;
+                continue;
+            }
+            __threadfence();
+            const int64_t g_lo = tile_u0 / a.q, g_hi = (tile_u0 + a.ktot - 1) / a.q;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                if (w < a.nwin) {
+                    double d[VEC];
+                    float pl[VEC];
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) { d[i] = -0.0; pl[i] = -0.0f; }
+                    for (int64_t gg = g_lo; gg <= g_hi; ++gg) {
+                        const int64_t cs = max(gg * a.q, tile_u0) - tile_u0;
+                        const int64_t ce = min((gg + 1) * a.q, tile_u0 + a.ktot) - tile_u0;
+                        if (max(cs, a.woff[w]) < min(ce, a.woff[w + 1])) {
+                            const int sl = ((gg * a.q) / a.ktot == p) ? 0 : 1;
+                            if (active) {
+                                const double2 *src = a.partials + (((size_t)gg * 2 + sl) * a.nwin + w) * TILE + (size_t)tid * VEC;
+                                double2 v[VEC];
+#pragma unroll
+                                for (int i = 0; i < VEC; ++i) v[i] = ld_cg(src + i);
+#pragma unroll
+                                for (int i = 0; i < VEC; ++i) {
+                                    d[i] += v[i].x;
+                                    pl[i] = __fadd_rn(pl[i], (float)v[i].y);
+                                }
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) S[w][i] = finalize_sum(d[i], pl[i]);
+                }
+            }
+        }
+
+        if (active) {
+            float o[VEC];
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) {
+                float t[NW];
+#pragma unroll
+                for (int w = 0; w < NW; ++w) t[w] = S[w][i];
+                o[i] = reduce_epilogue<NW>(a, t);
+                if (o[i] == o[i]) { // Rust f32::min/max ignore a NaN operand (lib.rs:186-195)
+                    mm_min = fminf(mm_min, o[i]);
+                    mm_max = fmaxf(mm_max, o[i]);
+                    mm_any = true;
+                }
+            }
+            Lane<VEC>::store(a.out + px, o);
+        }
+        u = seg_end;
+    }
+    if (a.minmax) block_minmax_flush(mm_min, mm_max, mm_any, a.minmax);
+}
+
+static float count_as_f32(int64_t n) {
+    // ndarray 0.12.1 mean_axis builds the divisor by n-1 additions of 1.0f32; exact up to 2^24
+    if (n <= (1 << 24)) return (float)n;
+    float c = 1.0f;
+    for (int64_t i = 1; i < n; ++i) c = c + 1.0f;
+    return c;
+}
+
+ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
+    ReducePlan pl{};
+    const bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0) &&
+                         ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
+    pl.vec = aligned ? 4 : 1;
+    const int64_t tile = (int64_t)kReduceBlock * pl.vec;
+    pl.ntiles = (a.n2 + tile - 1) / tile;
+    pl.ktot = 0;
+    for (int w = 0; w < a.nwin; ++w) pl.ktot += a.end[w] - a.start[w];
+    pl.units = pl.ntiles * pl.ktot;
+    const int64_t G = (int64_t)sm_count * kReduceCtasPerSm;
+    if (a.mode == SUM_SEQUENTIAL) {
+        pl.q = pl.ktot * ((pl.ntiles + G - 1) / G); // whole tiles only: never split a pixel's sum
+    } else {
+        int64_t q = (pl.units + G - 1) / G;
+        const int64_t qmin = pl.ktot < 8 ? pl.ktot : 8; // keep at least one 8-frame load batch per CTA
+        pl.q = q < qmin ? qmin : q;
+    }
+    if (pl.q < 1) pl.q = 1;
+    pl.grid = (int)((pl.units + pl.q - 1) / pl.q);
+    pl.partial_bytes = (size_t)pl.grid * 2 * a.nwin * tile * sizeof(double2);
+    pl.n_counters = (size_t)pl.ntiles;
+    return pl;
+}
+
+template <int VEC, bool COMP>
+static cudaError_t reduce_dispatch_nw(const ReduceKArgs &k, int grid, cudaStream_t s) {
+    switch (k.nwin) {
+    case 1: reduce_kernel<VEC, COMP, 1><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 2: reduce_kernel<VEC, COMP, 2><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 3: reduce_kernel<VEC, COMP, 3><<<grid, kReduceBlock, 0, s>>>(k); break;
+    default: return cudaErrorInvalidValue;
+    }
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const ReduceWorkspace &ws, cudaStream_t s) {
+    if (a.nwin < 1 || a.nwin > kMaxWindows || pl.grid < 1) return cudaErrorInvalidValue;
+    if (ws.partial_bytes < pl.partial_bytes || ws.n_counters < pl.n_counters) return cudaErrorInvalidValue;
+    ReduceKArgs k{};
+    k.cube = a.cube;
+    k.n2 = a.n2;
+    k.nwin = a.nwin;
+    k.woff[0] = 0;
+    for (int w = 0; w < a.nwin; ++w) {
+        k.start[w] = a.start[w];
+        k.woff[w + 1] = k.woff[w] + (a.end[w] - a.start[w]);
+        k.cnt[w] = count_as_f32(a.end[w] - a.start[w]);
+    }
+    for (int w = a.nwin; w < kMaxWindows; ++w) k.woff[w + 1] = k.woff[a.nwin];
+    k.ktot = pl.ktot;
+    k.units = pl.units;
+    k.q = pl.q;
+    k.ntiles = pl.ntiles;
+    k.epilogue = a.epilogue;
+    k.pa = a.p[0];
+    k.pb = a.p[1];
+    k.pfl = a.p[2];
+    k.pmax = a.p[3];
+    k.psign = a.ew_sign;
+    k.out = a.out;
+    k.minmax = a.minmax;
+    k.partials = static_cast<double2 *>(ws.partials);
+    k.counters = ws.counters;
+    const bool comp = a.mode != SUM_SEQUENTIAL;
+    if (pl.vec == 4) return comp ? reduce_dispatch_nw<4, true>(k, pl.grid, s) : reduce_dispatch_nw<4, false>(k, pl.grid, s);
+    return comp ? reduce_dispatch_nw<1, true>(k, pl.grid, s) : reduce_dispatch_nw<1, false>(k, pl.grid, s);
+}
+
+// ----------------------------------------------------------------------------------------------------
+// K3: fused elementwise operators -- one HBM pass, float4 lanes, grid-stride
+// ----------------------------------------------------------------------------------------------------
+struct MapK {
+    float a, b, c, ln_a;
+    int flag0, flag1;
+};
+
+template <int OP> __device__ __forceinline__ float map_one(float u, float v, const MapK &k) {
+    if (OP == MAP_LINCOMP) return __fadd_rn(__fmul_rn(u, k.a), __fmul_rn(v, k.b));
+    if (OP == MAP_RATIO) return __fdiv_rn(u, v);
+    if (OP == MAP_MULTIPLIER) return __fmul_rn(powf(u, k.a), powf(v, k.b));
+    if (OP == MAP_EW) return ew_value(u, v, k.a, k.b, k.c);
+    if (OP == MAP_EMISSION_LINE) {
+        float t = __fsub_rn(u, v);
+        t = __fmul_rn(t, k.a);
+        t = __fmul_rn(t, k.c);
+        return (t > k.b) ? 0.0f : t;
+    }
+    if (OP == MAP_LOGSCALE) {
+        float d = __fdiv_rn(__fsub_rn(u, k.b), __fsub_rn(k.c, k.b));
+        float t = __fadd_rn(__fmul_rn(k.a, d), 1.0f);
+        return __fdiv_rn(logf(t), k.ln_a);
+    }
+    if (OP == MAP_LOG10) return log10f(u);
+    if (OP == MAP_NEGATION) return -u;
+    if (OP == MAP_NORMALIZE) return __fdiv_rn(__fsub_rn(u, k.a), __fsub_rn(k.b, k.a));
+    if (OP == MAP_CLIP) return ((k.flag0 && u >= k.a) || (k.flag1 && u <= k.b)) ? __int_as_float(0x7fc00000) : u;
+    if (OP == MAP_REPLACE_NAN) return (u != u) ? k.a : u;
+    return u;
+}
+
+template <int OP, bool BINARY>
+__global__ void __launch_bounds__(256) map_kernel(const float *__restrict__ u, const float *__restrict__ v,
+                                                   float *__restrict__ out, int64_t n, int vec_ok, MapK k) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t n4 = n >> 2;
+        const float4 *u4 = reinterpret_cast<const float4 *>(u);
+        const float4 *v4 = reinterpret_cast<const float4 *>(v);
+        float4 *o4 = reinterpret_cast<float4 *>(out);
+        for (int64_t i = tid; i < n4; i += nthreads) {
+            float4 x = ld_stream(u4 + i);
+            float4 y = BINARY ? ld_stream(v4 + i) : make_float4(0, 0, 0, 0);
+            float4 r;
+            r.x = map_one<OP>(x.x, y.x, k);
+            r.y = map_one<OP>(x.y, y.y, k);
+            r.z = map_one<OP>(x.z, y.z, k);
+            r.w = map_one<OP>(x.w, y.w, k);
+            o4[i] = r;
+        }
+        done = n4 << 2;
+    }
+    for (int64_t i = done + tid; i < n; i += nthreads) out[i] = map_one<OP>(u[i], BINARY ? v[i] : 0.0f, k);
+}
+
+static int grid_for(int64_t work_items, int block, int sm_count, int ctas_per_sm) {
+    int64_t need = (work_items + block - 1) / block;
+    int64_t cap = (int64_t)sm_count * ctas_per_sm;
+    if (need < 1) need = 1;
+    return (int)(need < cap ? need : cap);
+}
+
+template <int OP, bool BINARY> static void map_go(const MapArgs &a, const MapK &k, int vec_ok, int grid, cudaStream_t s) {
+    map_kernel<OP, BINARY><<<grid, 256, 0, s>>>(a.u, a.v, a.out, a.n, vec_ok, k);
+}
+
+cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s) {
+    if (a.n <= 0) return cudaSuccess;
+    MapK k{a.a, a.b, a.c, 0.0f, a.flag0, a.flag1};
+    if (a.op == MAP_LOGSCALE) k.ln_a = logf(a.a); // a.ln(): host libm, same call the reference makes
+    auto al = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    const int vec_ok = al(a.u) && al(a.out) && (a.v == nullptr || al(a.v));
+    const int grid = grid_for(vec_ok ? (a.n + 3) / 4 : a.n, 256, sm_count, 8);
+    switch (a.op) {
+    case MAP_LINCOMP: map_go<MAP_LINCOMP, true>(a, k, vec_ok, grid, s); break;
+    case MAP_RATIO: map_go<MAP_RATIO, true>(a, k, vec_ok, grid, s); break;
+    case MAP_MULTIPLIER: map_go<MAP_MULTIPLIER, true>(a, k, vec_ok, grid, s); break;
+    case MAP_EW: map_go<MAP_EW, true>(a, k, vec_ok, grid, s); break;
+    case MAP_EMISSION_LINE: map_go<MAP_EMISSION_LINE, true>(a, k, vec_ok, grid, s); break;
+    case MAP_LOGSCALE: map_go<MAP_LOGSCALE, false>(a, k, vec_ok, grid, s); break;
+    case MAP_LOG10: map_go<MAP_LOG10, false>(a, k, vec_ok, grid, s); break;
+    case MAP_NEGATION: map_go<MAP_NEGATION, false>(a, k, vec_ok, grid, s); break;
+    case MAP_NORMALIZE: map_go<MAP_NORMALIZE, false>(a, k, vec_ok, grid, s); break;
+    case MAP_CLIP: map_go<MAP_CLIP, false>(a, k, vec_ok, grid, s); break;
+    case MAP_REPLACE_NAN: map_go<MAP_REPLACE_NAN, false>(a, k, vec_ok, grid, s); break;
+    default: return cudaErrorInvalidValue;
+    }
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+// apply_tone_curve, lib.rs:1858-1871.  Rust `as usize`: truncate, saturate, NaN -> 0.
+__device__ __forceinline__ float tone_one(float v, const float *table, int table_len, float ts, unsigned &oob) {
+    float t = __fdiv_rn(__fmul_rn(v, ts), 65535.0f);
+    unsigned key;
+    if (!(t > 0.0f)) key = 0u;                    // NaN, negatives, zero
+    else if (t >= 4294967296.0f) key = 0xFFFFFFFFu; // saturate
+    else key = (unsigned)t;                         // cvt.rzi
+    if (key >= (unsigned)table_len) { // the reference panics (index out of bounds); flag it, stay in bounds
+        oob = 1u;
+        key = (unsigned)table_len - 1u;
+    }
+    return __fdiv_rn(__fmul_rn(65535.0f, table[key]), ts);
+}
+
+__global__ void __launch_bounds__(256) tone_kernel(const float *__restrict__ img, int64_t n, const float *__restrict__ table,
+                                                    int table_len, float *__restrict__ out, unsigned *oob_flag, int vec_ok) {
+    extern __shared__ float s_table[];
+    for (int i = threadIdx.x; i < table_len; i += blockDim.x) s_table[i] = table[i];
+    __syncthreads();
+    const float ts = (float)(table_len - 1);
+    unsigned oob = 0u;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t n4 = n >> 2;
+        const float4 *i4 = reinterpret_cast<const float4 *>(img);
+        float4 *o4 = reinterpret_cast<float4 *>(out);
+        for (int64_t i = tid; i < n4; i += nthreads) {
+            float4 x = ld_stream(i4 + i), r;
+            r.x = tone_one(x.x, s_table, table_len, ts, oob);
+            r.y = tone_one(x.y, s_table, table_len, ts, oob);
+            r.z = tone_one(x.z, s_table, table_len, ts, oob);
+            r.w = tone_one(x.w, s_table, table_len, ts, oob);
+            o4[i] = r;
+        }
+        done = n4 << 2;
+    }
+    for (int64_t i = done + tid; i < n; i += nthreads) out[i] = tone_one(img[i], s_table, table_len, ts, oob);
+    if (oob) atomicMax(oob_flag, 1u);
+}
+
+cudaError_t tone_curve_launch(const float *img, int64_t n, const float *table_dev, int table_len, float *out,
+                              unsigned *oob_flag, int sm_count, cudaStream_t s) {
+    if (table_len < 1 || table_len > kMaxToneTable) return cudaErrorInvalidValue;
+    if (n <= 0) return cudaSuccess;
+    auto al = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    const int vec_ok = al(img) && al(out);
+    const int grid = grid_for(vec_ok ? (n + 3) / 4 : n, 256, sm_count, 8);
+    tone_kernel<<<grid, 256, (size_t)table_len * sizeof(float), s>>>(img, n, table_dev, table_len, out, oob_flag, vec_ok);
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+// ----------------------------------------------------------------------------------------------------
+// K4: min/max ignoring NaN (image_min_max lib.rs:180-197; lims::get_vmin/get_vmax lims.rs:7-35)
+// ----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) minmax_kernel(const float *__restrict__ img, int64_t n, unsigned *result, int vec_ok) {
+    // running values start at +-Inf so that +-Inf inputs are seen; the FLT_MAX init of image_min_max is applied
+    // by the host when it decodes the result
+    float mn = __int_as_float(0x7f800000), mx = __int_as_float(0xff800000);
+    bool any = false;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t n4 = n >> 2;
+        const float4 *i4 = reinterpret_cast<const float4 *>(img);
+        for (int64_t i = tid; i < n4; i += nthreads) {
+            float4 x = ld_stream(i4 + i);
+            float e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (e[j] == e[j]) { mn = fminf(mn, e[j]); mx = fmaxf(mx, e[j]); any = true; }
+        }
+        done = n4 << 2;
+    }
+    for (int64_t i = done + tid; i < n; i += nthreads) {
+        float e = img[i];
+        if (e == e) { mn = fminf(mn, e); mx = fmaxf(mx, e); any = true; }
+    }
+    block_minmax_flush(mn, mx, any, result);
+}
+
+cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_count, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    const int vec_ok = (reinterpret_cast<uintptr_t>(img) & 15u) == 0;
+    const int grid = grid_for(vec_ok ? (n + 3) / 4 : n, 256 * 4, sm_count, 8);
+    minmax_kernel<<<grid, 256, 0, s>>>(img, n, result, vec_ok);
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+// ----------------------------------------------------------------------------------------------------
+// K6: down_sampling = decimation (lib.rs:1894-1962): out[z][j][i] = img[z][j*n][i*n]
+// ----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) downsample_kernel(const float *__restrict__ img, int64_t ny, int64_t nx, int64_t n,
+                                                          float *__restrict__ out, int64_t oy, int64_t ox, int64_t total) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t x = i % ox, t = i / ox, y = t % oy, z = t / oy;
+        out[i] = img[(z * ny + y * n) * nx + x * n];
+    }
+}
+
+cudaError_t downsample_launch(const float *img, int64_t c, int64_t ny, int64_t nx, int64_t n, float *out, int64_t oy,
+                              int64_t ox, cudaStream_t s) {
+    const int64_t total = c * oy * ox;
+    if (total <= 0) return cudaSuccess;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    downsample_kernel<<<(int)blocks, 256, 0, s>>>(img, ny, nx, n, out, oy, ox, total);
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+// ----------------------------------------------------------------------------------------------------
+// K5: colour mapping (aflak_plot/src/imshow/lut.rs:132-160, image.rs:20-84, util.rs:3-14)
+// ----------------------------------------------------------------------------------------------------
+struct CmapK {
+    float vmin[3], vmax[3], l0[3], l1[3], l2[3];
+    int chain;
+    float ls_a, ls_min, ls_max, ls_lna, nm_min, nm_max;
+    int tone_len;
+};
+
+// mtf, lut.rs:152-160
+__device__ __forceinline__ float mtf(float m, float x) {
+    if (x >= 1.0f) return 1.0f;
+    if (x <= 0.0f) return 0.0f;
+    float num = __fmul_rn(__fsub_rn(m, 1.0f), x);
+    float den = __fsub_rn(__fmul_rn(__fsub_rn(__fmul_rn(2.0f, m), 1.0f), x), m);
+    return __fdiv_rn(num, den);
+}
+
+// color_at_bounds + color_at (index part), lut.rs:132-149
+__device__ __forceinline__ unsigned lut_index(float val, float vmin, float vmax, float l0, float l1, float l2) {
+    float p = val;
+    if (p < vmin) p = vmin;       // util::clamp: NaN fails both comparisons and passes through
+    else if (p > vmax) p = vmax;
+    float x = __fdiv_rn(__fsub_rn(p, vmin), __fsub_rn(vmax, vmin));
+    float c = __fdiv_rn(__fsub_rn(x, l0), __fsub_rn(l2, l0));
+    float i = __fmul_rn(mtf(l1, c), 65535.0f);
+    if (i < 0.0f) i = 0.0f;
+    unsigned idx;
+    if (!(i > 0.0f)) idx = 0u; // NaN as usize == 0
+    else if (i >= 65535.0f) idx = 65535u;
+    else idx = (unsigned)i;
+    return idx;
+}
+
+__device__ __forceinline__ float chain_one(float v, const CmapK &k, const float *s_tone, unsigned &oob) {
+    // convert_to_logscale (lib.rs:1598-1611) -> normalize_image (lib.rs:269-273) -> apply_tone_curve (lib.rs:1858-1871)
+    float d = __fdiv_rn(__fsub_rn(v, k.ls_min), __fsub_rn(k.ls_max, k.ls_min));
+    float t = __fdiv_rn(logf(__fadd_rn(__fmul_rn(k.ls_a, d), 1.0f)), k.ls_lna);
+    t = __fdiv_rn(__fsub_rn(t, k.nm_min), __fsub_rn(k.nm_max, k.nm_min));
+    return tone_one(t, s_tone, k.tone_len, (float)(k.tone_len - 1), oob);
+}
+
+template <bool RGB3, bool CHAIN, int CH>
+__global__ void __launch_bounds__(256) colormap_kernel(const float *__restrict__ img, int64_t ny, int64_t nx,
+                                                        const uint32_t *__restrict__ lut, const float *__restrict__ tone,
+                                                        int flip_y, int vec_ok, uint8_t *__restrict__ out, unsigned *oob_flag, CmapK k) {
+    extern __shared__ float s_tone[];
+    if (CHAIN) {
+        for (int i = threadIdx.x; i < k.tone_len; i += blockDim.x) s_tone[i] = tone[i];
+        __syncthreads();
+    }
+    unsigned oob = 0u;
+    const int64_t n2 = ny * nx;
+    const int64_t groups_per_row = (nx + 3) >> 2;
+    const int64_t total = ny * groups_per_row;
+    const bool row_vec = vec_ok != 0;
+    for (int64_t gi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t y = gi / groups_per_row, x0 = (gi - y * groups_per_row) << 2;
+        const int64_t ys = flip_y ? (ny - 1 - y) : y;
+        const int cnt = (int)min((int64_t)4, nx - x0);
+        uint32_t px[4];
+#pragma unroll
+        for (int c = 0; c < (RGB3 ? 3 : 1); ++c) {
+            const float *src = img + (size_t)c * n2 + ys * nx + x0;
+            float v[4];
+            if (row_vec) {
+                float4 t = ld_stream(reinterpret_cast<const float4 *>(src));
+                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] = j < cnt ? src[j] : 0.0f;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float val = v[j];
+                if (CHAIN) val = chain_one(val, k, s_tone, oob);
+                const unsigned idx = lut_index(val, k.vmin[c], k.vmax[c], k.l0[c], k.l1[c], k.l2[c]);
+                const uint32_t e = __ldg(lut + (size_t)c * 65536 + idx);
+                if (RGB3) {
+                    // make_raw_image_rgb (image.rs:66-72): channel c takes component c of its own table
+                    const uint32_t comp = (e >> (8 * c)) & 0xFFu;
+                    px[j] = (c == 0 ? 0xFF000000u : px[j]) | (comp << (8 * c));
+                } else {
+                    px[j] = e;
+                }
+            }
+        }
+        uint8_t *dst = out + (size_t)(y * nx + x0) * CH;
+        if (CH == 4) {
+            if (row_vec) {
+                *reinterpret_cast<uint4 *>(dst) = make_uint4(px[0], px[1], px[2], px[3]);
+            } else {
+                for (int j = 0; j < cnt; ++j) {
+                    dst[4 * j + 0] = px[j] & 0xFF; dst[4 * j + 1] = (px[j] >> 8) & 0xFF;
+                    dst[4 * j + 2] = (px[j] >> 16) & 0xFF; dst[4 * j + 3] = 0xFF;
+                }
+            }
+        } else {
+            if (row_vec) {
+                // 4 px = 12 bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+                const uint32_t a0 = px[0] & 0xFFFFFFu, a1 = px[1] & 0xFFFFFFu, a2 = px[2] & 0xFFFFFFu, a3 = px[3] & 0xFFFFFFu;
+                uint32_t *d32 = reinterpret_cast<uint32_t *>(dst);
+                d32[0] = a0 | (a1 << 24);
+                d32[1] = (a1 >> 8) | (a2 << 16);
+                d32[2] = (a2 >> 16) | (a3 << 8);
+            } else {
+                for (int j = 0; j < cnt; ++j) {
+                    dst[3 * j + 0] = px[j] & 0xFF; dst[3 * j + 1] = (px[j] >> 8) & 0xFF; dst[3 * j + 2] = (px[j] >> 16) & 0xFF;
+                }
+            }
+        }
+    }
+    if (CHAIN && oob) atomicMax(oob_flag, 1u);
+}
+
+cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s) {
+    if (a.ny <= 0 || a.nx <= 0) return cudaSuccess;
+    if (a.channels != 3 && a.channels != 4) return cudaErrorInvalidValue;
+    if (a.chain && (a.rgb3 || a.tone_len < 1 || a.tone_len > kMaxToneTable)) return cudaErrorInvalidValue;
+    CmapK k{};
+    for (int c = 0; c < 3; ++c) {
+        k.vmin[c] = a.vmin[c]; k.vmax[c] = a.vmax[c];
+        k.l0[c] = a.lims[c][0]; k.l1[c] = a.lims[c][1]; k.l2[c] = a.lims[c][2];
+    }
+    k.chain = a.chain;
+    k.ls_a = a.ls_a; k.ls_min = a.ls_min; k.ls_max = a.ls_max; k.ls_lna = logf(a.ls_a);
+    k.nm_min = a.nm_min; k.nm_max = a.nm_max;
+    k.tone_len = a.tone_len;
+    const int64_t groups = a.ny * ((a.nx + 3) / 4);
+    const int grid = grid_for(groups, 256, sm_count, 8);
+    const int vec_ok = (a.nx % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.img) & 15u) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
+    const size_t smem = a.chain ? (size_t)a.tone_len * sizeof(float) : 0;
+#define AFK_CMAP(R, C, CH) colormap_kernel<R, C, CH><<<grid, 256, smem, s>>>(a.img, a.ny, a.nx, a.lut, a.tone_table, a.flip_y, vec_ok, a.out, a.oob_flag, k)
+    if (a.rgb3) {
+        if (a.channels == 4) AFK_CMAP(true, false, 4); else AFK_CMAP(true, false, 3);
+    } else if (a.chain) {
+        if (a.channels == 4) AFK_CMAP(false, true, 4); else AFK_CMAP(false, true, 3);
+    } else {
+        if (a.channels == 4) AFK_CMAP(false, false, 4); else AFK_CMAP(false, false, 3);
+    }
+#undef AFK_CMAP
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+// ----------------------------------------------------------------------------------------------------
+// Synthetic cube generator: bit-identical to oracle/aflak_oracle.c orc_gen_voxel (only + - * / in f32)
+// ----------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__device__ __forceinline__ float gen_voxel(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t k, int64_t y, int64_t x,
+                                           int pathology) {
+    const uint64_t idx = ((uint64_t)k * (uint64_t)ny + (uint64_t)y) * (uint64_t)nx + (uint64_t)x;
+    const uint64_t h = mix64(seed + idx);
+    const float u1 = __fmul_rn(__uint2float_rn((uint32_t)(h >> 40)), 5.9604644775390625e-08f);
+    const float u2 = __fmul_rn(__uint2float_rn((uint32_t)((h >> 16) & 0xFFFFFFu)), 5.9604644775390625e-08f);
+    const float ph = __fmul_rn(__uint2float_rn((uint32_t)((uint64_t)(x * 3 + y * 5) & 255u)), 0.00390625f);
+    const float fnz = __ll2float_rn(nz);
+    float k0 = __fsub_rn(ph, 0.5f);
+    k0 = __fmul_rn(k0, 0.125f);
+    k0 = __fadd_rn(k0, 0.5f);
+    k0 = __fmul_rn(k0, fnz);
+    float sigma = __fadd_rn(__fmul_rn(fnz, 0.0078125f), 2.0f);
+    float d = __fdiv_rn(__fsub_rn(__ll2float_rn(k), k0), sigma);
+    float dd = __fadd_rn(__fmul_rn(d, d), 1.0f);
+    float line = __fdiv_rn(2.0f, dd);
+    float cont = __fadd_rn(__fmul_rn(0.1f, u1), 1.0f);
+    float noise = __fmul_rn(__fsub_rn(u2, 0.5f), 0.05f);
+    float v = __fadd_rn(__fadd_rn(cont, line), noise);
+    if (pathology) {
+        const uint32_t r = (uint32_t)(h & 0xFFFFu);
+        if (r < 16u) v = __int_as_float(0x7fc00000);
+        else if (r < 24u) v = __int_as_float(0x7f800000);
+        else if (r < 32u) v = __int_as_float(0xff800000);
+        else if (r < 48u) v = 0.0f;
+        else if (r < 64u) v = -v;
+        else if (r < 80u) v = 1e-40f;
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(256) gen_cube_kernel(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t y0, int64_t rows,
+                                                        int pathology, float *__restrict__ out, int64_t total) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t x = i % nx, t = i / nx, r = t % rows, k = t / rows;
+        out[i] = gen_voxel(seed, nz, ny, nx, k, y0 + r, x, pathology);
+    }
+}
+
+cudaError_t gen_cube_launch(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t y0, int64_t rows, int pathology,
+                            float *out, cudaStream_t s) {
+    const int64_t total = nz * rows * nx;
+    if (total <= 0) return cudaSuccess;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    gen_cube_kernel<<<(int)blocks, 256, 0, s>>>(seed, nz, ny, nx, y0, rows, pathology, out, total);
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+} // namespace afk

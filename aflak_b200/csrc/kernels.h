@@ -1,0 +1,131 @@
+// kernels.h -- internal C++ interface between the host layer (host.cpp) and the
+// sm_100a kernels (kernels.cu).  Device pointers + a stream in, no ownership.
+// Not part of the public ABI (that is include/aflak_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace afk {
+
+// ---- axis-0 windowed reduction (K1/K2 of DESIGN.md) -------------------------
+constexpr int kMaxWindows = 3;
+constexpr int kReduceBlock = 256;   // threads per CTA
+constexpr int kReduceCtasPerSm = 4; // resident CTAs per SM the launch is sized for
+
+enum ReduceEpilogue : int {
+    EPI_SUM = 0,        // out = S0                                   (integral, lib.rs:1324)
+    EPI_MEAN = 1,       // out = S0 / n0                              (average,  lib.rs:1328)
+    EPI_MEAN_RATIO = 2, // out = (S0/n0) / (S1/n1)                    (average, average, ratio: BASELINE C3)
+    EPI_EW = 3,         // on=S0/n0 off1=S1/n1 off2=S2/n2; off=a*off1+b*off2; EW(off,on,fl,max,sign)  (templates.rs:143-463)
+};
+
+enum SumMode : int {
+    SUM_COMPENSATED = 0, // Kahan per thread, f64 combine of split-K partials (<= 1e-5 of the f64 oracle)
+    SUM_SEQUENTIAL = 1,  // plain left-to-right f32 in k order, never split: bit-exact with ndarray sum_axis
+};
+
+struct ReduceArgs {
+    const float *cube; // [nz][n2] frames, n2 contiguous
+    int64_t n2;        // pixels per frame == frame stride in elements
+    int nwin;
+    int64_t start[kMaxWindows];
+    int64_t end[kMaxWindows]; // exclusive
+    int epilogue;
+    int mode;
+    float p[4];        // EPI_EW: a, b, fl, max ; sign in ew_sign
+    float ew_sign;     // -1 emission, +1 absorption
+    float *out;        // [n2] (may be a peer-mapped pointer)
+    unsigned *minmax;  // optional: {~key(min), key(max), any-non-NaN} accumulated with atomicMax, or nullptr
+};
+
+struct ReduceWorkspace {
+    void *partials;       // device scratch, >= reduce_workspace_bytes()
+    size_t partial_bytes;
+    unsigned *counters;   // device, zero-initialised, >= reduce_counter_count() entries, self-resetting
+    size_t n_counters;
+};
+
+struct ReducePlan {
+    int vec;             // 4 (float4 lanes) or 1
+    int64_t ntiles;
+    int64_t ktot;
+    int64_t units;       // ntiles * ktot
+    int64_t q;           // units per CTA
+    int grid;
+    size_t partial_bytes;
+    size_t n_counters;
+};
+
+ReducePlan reduce_plan(const ReduceArgs &a, int sm_count);
+cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &plan, const ReduceWorkspace &ws, cudaStream_t s);
+
+// ---- elementwise (K3) --------------------------------------------------------
+enum MapOp : int {
+    MAP_LINCOMP = 0,    // out = fl(fl(u*a) + fl(v*b))                     lib.rs:1288-1297
+    MAP_RATIO = 1,      // out = u / v                                      unit.rs:863-880
+    MAP_MULTIPLIER = 2, // out = powf(u,a) * powf(v,b)                      lib.rs:1619-1638
+    MAP_EW = 3,         // out = EW(off=u, on=v, fl=a, max=b, sign=c)       lib.rs:1584-1596
+    MAP_LOGSCALE = 4,   // out = ln(a*((u-b)/(c-b))+1)/ln(a)                lib.rs:1598-1611
+    MAP_LOG10 = 5,      // out = log10(u)                                   lib.rs:1613-1617
+    MAP_NEGATION = 6,   // out = -u                                         lib.rs:1640-1645
+    MAP_NORMALIZE = 7,  // out = (u - a) / (b - a)                          lib.rs:269-273
+    MAP_CLIP = 8,       // NaN where (ceil && u >= a) || (floor && u <= b)  lib.rs:1258-1274
+    MAP_REPLACE_NAN = 9,// u is NaN ? a : u                                 lib.rs:1276-1286
+    MAP_EMISSION_LINE = 10, // like EW without the division                 lib.rs run_create_emission_line_map
+};
+
+struct MapArgs {
+    int op;
+    const float *u;
+    const float *v; // nullptr for unary ops
+    float a, b, c;
+    int flag0, flag1;
+    int64_t n;
+    float *out;
+};
+cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s);
+
+// apply_tone_curve (lib.rs:1858-1871). table_len <= kMaxToneTable. *oob_flag is set to 1 when an index
+// exceeds the table (the reference panics there); the store is clamped so memory stays safe.
+constexpr int kMaxToneTable = 4096;
+cudaError_t tone_curve_launch(const float *img, int64_t n, const float *table_dev, int table_len, float *out,
+                              unsigned *oob_flag, int sm_count, cudaStream_t s);
+
+// ---- min/max (K4) -------------------------------------------------------------
+// result[0] = ~key(min), result[1] = key(max), result[2] = number-of-non-NaN > 0 ; all via atomicMax, zero-init.
+cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_count, cudaStream_t s);
+float minmax_decode_min(unsigned inv_key);
+float minmax_decode_max(unsigned key);
+
+// ---- gather (K6) ----------------------------------------------------------------
+cudaError_t downsample_launch(const float *img, int64_t c, int64_t ny, int64_t nx, int64_t n, float *out, int64_t oy,
+                              int64_t ox, cudaStream_t s);
+
+// ---- colour mapping (K5) -------------------------------------------------------
+struct ColormapArgs {
+    const float *img;     // [ny][nx], or [3][ny][nx] when rgb3
+    int64_t ny, nx;
+    const uint32_t *lut;  // 65536 entries (or 3 x 65536 when rgb3), packed r | g<<8 | b<<16 | 0xFF<<24
+    float vmin[3], vmax[3];
+    float lims[3][3];     // (min, mid, max) per channel table
+    int rgb3;             // make_raw_image_rgb (image.rs:51-84)
+    int flip_y;           // coerce_to_array_view2 (image.rs:123-129)
+    int channels;         // 3 = packed RGB8 (reference ClientFormat::U8U8U8), 4 = RGBA8
+    // optional fused upstream chain (BASELINE C4): logscale -> normalize -> tone curve, applied per pixel before the LUT
+    int chain;            // 0 none, 1 logscale(a, lmin, lmax) -> normalize(nmin, nmax) -> tone(table)
+    float ls_a, ls_min, ls_max, nm_min, nm_max;
+    const float *tone_table;
+    int tone_len;
+    unsigned *oob_flag;
+    uint8_t *out;         // [ny][nx][channels]
+};
+cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s);
+
+// ---- synthetic generator (same arithmetic as oracle/aflak_oracle.c orc_gen_voxel) ----
+cudaError_t gen_cube_launch(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t y0, int64_t rows, int pathology,
+                            float *out, cudaStream_t s);
+
+// number of kernel launches issued by this library since load (bench.py's gpu_launches)
+uint64_t launch_count();
+
+} // namespace afk

@@ -1,0 +1,277 @@
+/*
+ * aflak_b200.h -- C ABI of the B200-native replacement for aflak's data-parallel hot path.
+ *
+ * This is the drop-in boundary: the entry points below are what a Rust `-sys` crate inside
+ * aflak_primitives would bind.  Plain pointers and sizes only.
+ * Reference citations are relative to /root/reference/src/.
+ *
+ *   value model      mirrors `enum IOValue`               aflak_primitives/src/lib.rs:66-83
+ *   errors           mirror  `enum IOErr`                 aflak_primitives/src/lib.rs:109-130
+ *   registry         mirrors `TRANSFORMATIONS` + `cake::Transform` / `Algorithm::Function`
+ *                                                         aflak_primitives/src/lib.rs:141-758, aflak_cake/src/transform.rs:33-78
+ *   call             mirrors `TransformCaller::{feed,call}` aflak_cake/src/transform.rs:324-397
+ *   display          mirrors `ColorLUT` + `make_raw_image` aflak_plot/src/imshow/lut.rs, image.rs:20-84
+ *   evaluator+cache  mirrors `DST::compute` + `Cache`     aflak_cake/src/dst/compute.rs:153-274, cache.rs:18-148
+ *
+ * Threading: every entry point is re-entrant.  Each calling thread gets its own CUDA stream per device; image
+ * handles carry a ready-event so chained operators on different threads never need a host sync.
+ * Errors never abort: reference panics ("Unexpected argument!", index out of bounds) come back as AFK_ERR_PANIC.
+ * There is no CPU fallback: without a CUDA device every compute entry point returns AFK_ERR_CUDA.
+ */
+#ifndef AFLAK_B200_H
+#define AFLAK_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AFK_ABI_VERSION 1
+
+/* ---- status: IOErr variants (lib.rs:109-116) + two conditions the reference expresses as panics/CUDA ---- */
+typedef enum afk_status {
+    AFK_OK = 0,
+    AFK_ERR_IO = 1,               /* IOErr::IoError */
+    AFK_ERR_RAWLOADER = 2,        /* IOErr::RawLoaderError */
+    AFK_ERR_FITS = 3,             /* IOErr::FITSErr */
+    AFK_ERR_UNEXPECTED_INPUT = 4, /* IOErr::UnexpectedInput(String); message wording as precond.rs */
+    AFK_ERR_SHAPE = 5,            /* IOErr::ShapeError */
+    AFK_ERR_CUDA = 6,             /* surfaced to cake as UnexpectedInput("CUDA: ...") */
+    AFK_ERR_PANIC = 7,            /* the reference would panic here (cake_fn! "Unexpected argument!", OOB index) */
+    AFK_ERR_ARGUMENT = 8          /* cake ArgumentError::ConversionError (transform.rs:348-361) */
+} afk_status;
+
+/* Message of the last failing call on this thread (valid until the next call on the same thread). */
+const char *afk_last_error(void);
+int afk_abi_version(void);
+/* number of CUDA devices visible; 0 means every compute entry point will fail with AFK_ERR_CUDA */
+int afk_device_count(void);
+int afk_set_device(int device);
+/* Use an external stream (e.g. the caller's torch stream) for this thread on the current device; NULL restores
+ * the thread's own stream. */
+int afk_set_stream(void *cuda_stream);
+void *afk_get_stream(void);
+int afk_synchronize(void);
+/* kernels launched by this library since load (all threads) */
+uint64_t afk_launch_count(void);
+
+/* ---- type ids: the IOValue variant names (variant_name/src/lib.rs:24-29) ---- */
+typedef enum afk_type {
+    AFK_T_INTEGER = 0,
+    AFK_T_FLOAT = 1,
+    AFK_T_FLOAT2 = 2,
+    AFK_T_FLOAT3 = 3,
+    AFK_T_FLOAT3X3 = 4,
+    AFK_T_STR = 5,
+    AFK_T_BOOL = 6,
+    AFK_T_FITS = 7,
+    AFK_T_IMAGE = 8,
+    AFK_T_MAP2DTO3DCOORDS = 9,
+    AFK_T_ROI = 10,
+    AFK_T_PATHS = 11,
+    AFK_T_TONECURVE = 12,
+    AFK_T_COUNT = 13
+} afk_type;
+const char *afk_type_name(afk_type t);          /* "Integer", "Float", ... */
+int afk_type_from_name(const char *name);       /* -1 when unknown */
+/* ConvertibleVariants::convertible (aflak_cake/src/lib.rs:100-112; table lib.rs:795-823) */
+int afk_type_convertible(afk_type from, afk_type into);
+/* EditableVariants (lib.rs:778-793) */
+int afk_type_editable(afk_type t);
+
+/* ---- images: device-resident WcsArray (unit.rs:203-208) ---- */
+typedef struct afk_image afk_image;
+#define AFK_MAX_NDIM 4
+
+/* Upload a host array (C order, shape[0] slowest: [NAXISn..NAXIS1], fits.rs:42-49) to the current device.
+ * The copy is asynchronous when `host` is pinned; the returned handle has refcount 1. */
+afk_image *afk_image_upload(const float *host, int ndim, const int64_t *shape);
+/* Uninitialised device image. */
+afk_image *afk_image_alloc(int ndim, const int64_t *shape);
+/* Wrap device memory owned by the caller (e.g. a torch tensor); never freed by the library. */
+afk_image *afk_image_wrap_device(float *device_ptr, int ndim, const int64_t *shape);
+/* Fill with the synthetic cube generator (DESIGN.md "Synthetic inputs"): rows [y0,y0+rows) of a [nz,ny,nx] cube. */
+afk_image *afk_image_synthetic(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t y0, int64_t rows, int pathology);
+void afk_image_retain(afk_image *img);   /* Clone of an Arc: O(1) */
+void afk_image_release(afk_image *img);  /* last release frees stream-ordered */
+int afk_image_ndim(const afk_image *img);
+const int64_t *afk_image_shape(const afk_image *img);
+int64_t afk_image_len(const afk_image *img);
+float *afk_image_device_ptr(const afk_image *img);
+int afk_image_device(const afk_image *img);
+/* Blocking read-back (UI tooltips, FITS export): waits for the producer, copies to host. */
+int afk_image_download(const afk_image *img, float *host);
+/* metadata carried on the host side (unit.rs:190-242) */
+const char *afk_image_unit(const afk_image *img);       /* "" == Unit::None */
+int afk_image_set_unit(afk_image *img, const char *unit);
+int afk_image_homogeneous(const afk_image *img);
+const char *afk_image_tag(const afk_image *img);        /* NULL == visualization: None */
+int afk_image_set_tag(afk_image *img, const char *tag);
+int afk_image_has_meta(const afk_image *img);
+/* axis i of MetaWcsArray.axes (FITS order: axis 0 = NAXIS1): name/unit, "" when absent */
+int afk_image_set_axis(afk_image *img, int axis, const char *name, const char *unit);
+const char *afk_image_axis_name(const afk_image *img, int axis);
+const char *afk_image_axis_unit(const afk_image *img, int axis);
+
+/* ---- values: IOValue (lib.rs:66-83), refcounted like the Arc<T> the cake cache stores ---- */
+typedef struct afk_value afk_value;
+afk_value *afk_value_integer(int64_t v);
+afk_value *afk_value_float(float v);
+afk_value *afk_value_float2(const float v[2]);
+afk_value *afk_value_float3(const float v[3]);
+afk_value *afk_value_float3x3(const float v[9]);
+afk_value *afk_value_str(const char *s);
+afk_value *afk_value_bool(int b);
+afk_value *afk_value_image(afk_image *img); /* retains img */
+/* ToneCurveState: only `arr` is read by operators (imgui_tone_curve/src/lib.rs:10-48); cp = n_cp (x,y) pairs */
+afk_value *afk_value_tone_curve(const float *arr, size_t n, const float *cp_xy, size_t n_cp);
+/* DefaultFor::default_for (lib.rs:760-776); NULL for types without a default (Image, Fits, Map2dTo3dCoords) */
+afk_value *afk_value_default_for(afk_type t);
+void afk_value_retain(afk_value *v);
+void afk_value_release(afk_value *v);
+afk_type afk_value_type(const afk_value *v);
+int afk_value_get_integer(const afk_value *v, int64_t *out);
+int afk_value_get_float(const afk_value *v, float *out);
+int afk_value_get_floats(const afk_value *v, float *out, size_t cap); /* Float2/3/3x3/ToneCurve arr; returns count */
+int afk_value_get_bool(const afk_value *v, int *out);
+const char *afk_value_get_str(const afk_value *v);
+afk_image *afk_value_get_image(const afk_value *v); /* borrowed */
+/* ConvertibleVariants::convert (aflak_cake/src/lib.rs:86-98): Integer->Float (`as f32`), Float->Integer (round) */
+afk_value *afk_value_convert(const afk_value *v, afk_type into);
+/* PartialEq for IOValue (lib.rs:85-104); images compare shape, unit, tag and device contents */
+int afk_value_eq(const afk_value *a, const afk_value *b);
+
+/* ---- registry: TRANSFORMATIONS (lib.rs:141-747) ---- */
+typedef struct afk_result {
+    afk_status status;  /* Result<IOValue, IOErr> discriminant */
+    afk_value *value;   /* Ok(v): refcount 1, owned by the caller */
+    char *message;      /* Err(e): e's payload string (malloc'ed; free with afk_result_clear) */
+} afk_result;
+void afk_result_clear(afk_result *r);
+/* Display for IOErr (lib.rs:118-130): "Unexpected input! ..." etc.  Returns a malloc'ed string. */
+char *afk_result_display(const afk_result *r);
+void afk_free(void *p);
+
+/* PlainFunction = fn(Vec<Bow<T>>) -> Vec<Result<T,E>> (transform.rs:78): one result per declared output. */
+typedef afk_status (*afk_plain_function)(const afk_value *const *inputs, size_t n_inputs, afk_result *outputs, size_t n_outputs);
+
+typedef struct afk_input_slot { /* TransformInputSlot (transform.rs:64-70) */
+    const char *name;
+    afk_type type_id;
+    const afk_value *default_value; /* NULL when the slot has no default */
+} afk_input_slot;
+
+typedef struct afk_transform_desc { /* Algorithm::Function (transform.rs:33-48) */
+    const char *name;        /* FnTransformId */
+    const char *kind;
+    const char *description;
+    uint8_t major, minor, patch;
+    size_t n_inputs;
+    const afk_input_slot *inputs;
+    size_t n_outputs;
+    const afk_type *outputs;
+    afk_plain_function f;
+} afk_transform_desc;
+
+size_t afk_transform_count(void);
+const afk_transform_desc *afk_transform_at(size_t i);
+/* NamedAlgorithms::get_transform (lib.rs:749-758) */
+const afk_transform_desc *afk_get_transform(const char *name);
+/* TransformCaller feed + call (transform.rs:324-397): type-check each argument against the slot, convert
+ * Integer<->Float where the table allows, then call f.  NULL inputs[i] takes the slot default. */
+afk_status afk_transform_call(const afk_transform_desc *t, const afk_value *const *inputs, size_t n_inputs,
+                              afk_result *outputs, size_t n_outputs);
+
+/* Reduction arithmetic: 0 = compensated (default; <=1e-5 of the f64 sum), 1 = sequential (bit-exact with the
+ * reference's left-to-right f32 sum; slower on small images because it cannot split the spectral axis). */
+int afk_set_sum_mode(int mode);
+int afk_get_sum_mode(void);
+
+/* ---- fused paths the evaluator substitutes for recognised sub-graphs (unfused operators remain the parity
+ *      reference).  Inputs are borrowed, outputs have refcount 1. ---- */
+/* average(cube,s0,e0) / average(cube,s1,e1)  -- BASELINE config 3 */
+afk_status afk_fused_average_ratio(const afk_image *cube, int64_t s0, int64_t e0, int64_t s1, int64_t e1, afk_image **out);
+/* equivalent-width template (src/templates.rs:143-463): three averages -> ratio_from_bands ->
+ * linear_composition -> create_equivalent_width; minmax (may be NULL) receives image_min_max of the result */
+afk_status afk_fused_equivalent_width(const afk_image *cube, int64_t on_s, int64_t on_e, int64_t off1_s, int64_t off1_e,
+                                      int64_t off2_s, int64_t off2_e, float fl, float max, int is_emission,
+                                      afk_image **out, float minmax[2]);
+
+/* ---- display path: ColorLUT (lut.rs) + make_raw_image (image.rs:20-84) ---- */
+typedef struct afk_lut afk_lut;
+afk_lut *afk_lut_linear(const float *stop_values, const uint8_t *stop_rgb, size_t n_stops); /* ColorLUT::linear */
+afk_lut *afk_lut_builtin(const char *name); /* BuiltinLUT::name(): "Grey", "Flame", "HeatMap_Inv", ... */
+size_t afk_lut_builtin_count(void);
+const char *afk_lut_builtin_name(size_t i);
+void afk_lut_release(afk_lut *lut);
+void afk_lut_set_lims(afk_lut *lut, float min, float mid, float max); /* set_lims (lut.rs:232-236) */
+void afk_lut_lims(const afk_lut *lut, float out[3]);
+int afk_lut_set_gradient(afk_lut *lut, const float *stop_values, const uint8_t *stop_rgb, size_t n_stops);
+void afk_lut_color_at(const afk_lut *lut, float point, uint8_t rgb[3]);                       /* lut.rs:137-149 */
+void afk_lut_color_at_bounds(const afk_lut *lut, float point, float vmin, float vmax, uint8_t rgb[3]);
+/* copy of the 65536x3 table (host) */
+void afk_lut_table(const afk_lut *lut, uint8_t *out_rgb);
+/* bounds() iterator (lut.rs:196-200): writes up to cap pairs, returns the number of pairs */
+size_t afk_lut_bounds(const afk_lut *lut, float *v1, uint8_t *c1, float *v2, uint8_t *c2, size_t cap);
+
+/* lims::get_vmin / get_vmax (aflak_plot/src/lims.rs:7-35): NaN-skipping, NaN when every pixel is NaN */
+afk_status afk_image_vmin_vmax(const afk_image *img, float *vmin, float *vmax);
+
+typedef struct afk_colormap_chain { /* optional fused upstream chain (BASELINE config 4) */
+    float logscale_a, logscale_vmin, logscale_vmax; /* convert_to_logscale */
+    float normalize_min, normalize_max;             /* normalize_image */
+    const float *tone_table;                        /* apply_tone_curve (host pointer) */
+    size_t tone_len;
+} afk_colormap_chain;
+
+/* make_raw_image on the vertically flipped image.  vmin/vmax NaN -> computed with afk_image_vmin_vmax.
+ * channels: 3 = packed RGB8 (the reference's ClientFormat::U8U8U8), 4 = RGBA8 (A=255).
+ * out_device: device buffer of ny*nx*channels bytes (headless stand-in for the GL texture). */
+afk_status afk_colormap(const afk_image *img, const afk_lut *lut, float vmin, float vmax, int flip_y, int channels,
+                        const afk_colormap_chain *chain, uint8_t *out_device);
+/* same, result copied to host memory */
+afk_status afk_colormap_host(const afk_image *img, const afk_lut *lut, float vmin, float vmax, int flip_y, int channels,
+                             const afk_colormap_chain *chain, uint8_t *out_host);
+/* make_raw_image_rgb (image.rs:51-84): img is [3,ny,nx], one LUT and one (vmin,vmax) per channel */
+afk_status afk_colormap_rgb_host(const afk_image *img, const afk_lut *const lut[3], const float vmin[3], const float vmax[3],
+                                 int flip_y, int channels, uint8_t *out_host);
+
+/* ---- raw kernel layer: device pointers + the thread's stream, no handles (bench.py, multi-GPU bands) ---- */
+/* epilogue: 0 sum, 1 mean, 2 mean0/mean1, 3 EW(params = a,b,fl,max,sign). `out` may be a peer-mapped pointer. */
+afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends,
+                        int epilogue, const float *params, int sum_mode, float *out);
+/* CUDA-event timing of reduce-kernel launches on this thread: enable, run, then read (sum of ms, launches). */
+int afk_profile_reduce(int enable);
+int afk_profile_reduce_read(double *total_ms, uint64_t *launches);
+
+/* CUDA IPC helpers for the fused gather (one process per GPU): export this image's allocation, open a peer's. */
+int afk_ipc_export(const afk_image *img, uint8_t handle[64]);
+float *afk_ipc_open(const uint8_t handle[64]);
+int afk_ipc_close(float *peer_ptr);
+
+/* ---- mini evaluator with a device-handle cache: DST::compute + Cache (dst/compute.rs:153-274, cache.rs) ---- */
+typedef struct afk_graph afk_graph;
+afk_graph *afk_graph_new(void);
+void afk_graph_free(afk_graph *g);
+/* add_transform / add_constant: returns the node index (t_idx) or -1 */
+int64_t afk_graph_add_transform(afk_graph *g, const char *name);
+int64_t afk_graph_add_constant(afk_graph *g, const afk_value *v);
+/* replace a constant's value (node_editor::update_constant_node): bumps updated_on */
+int afk_graph_set_constant(afk_graph *g, int64_t t_idx, const afk_value *v);
+/* connect(Output(t_idx,out_i) -> Input(t_idx,in_i)); type-checked (dst/build.rs:45-88) */
+afk_status afk_graph_connect(afk_graph *g, int64_t from_t, size_t out_i, int64_t to_t, size_t in_i);
+afk_status afk_graph_disconnect(afk_graph *g, int64_t to_t, size_t in_i);
+/* compute Output(t_idx,out_i) with memoisation: a node is recomputed iff its cached time < updated_on of the
+ * node or any ancestor (cache.rs:130-136, dst/mod.rs:65-73).  Result value refcount +1 for the caller. */
+afk_status afk_graph_compute(afk_graph *g, int64_t t_idx, size_t out_i, afk_result *out);
+/* number of operator calls actually executed (cache misses) since creation */
+uint64_t afk_graph_calls(const afk_graph *g);
+/* enable/disable substitution of fused kernels for recognised sub-graphs (default on) */
+void afk_graph_set_fusion(afk_graph *g, int enable);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AFLAK_B200_H */
