@@ -220,11 +220,13 @@ class Image:
         self._owned = owned
 
     @classmethod
-    def upload(cls, array):
+    def upload(cls, array, sync=True):
+        """sync=False: asynchronous copy from a pinned array the caller keeps alive until the stream has drained."""
         a = np.ascontiguousarray(array, dtype=np.float32)
         shape = (C.c_int64 * max(a.ndim, 1))(*a.shape)
         img = cls(lib.afk_image_upload(a.ctypes.data_as(_P), a.ndim, shape))
-        synchronize()  # `a` may be a temporary
+        if sync:
+            synchronize()  # `a` may be a temporary
         return img
 
     @classmethod
@@ -287,8 +289,10 @@ class Image:
     def axis(self, i):
         return lib.afk_image_axis_name(self._h, i).decode(), lib.afk_image_axis_unit(self._h, i).decode()
 
-    def download(self):
-        out = np.empty(self.shape, dtype=np.float32)
+    def download(self, out=None):
+        if out is None:
+            out = np.empty(self.shape, dtype=np.float32)
+        assert out.dtype == np.float32 and out.flags.c_contiguous and out.size == int(np.prod(self.shape, dtype=np.int64))
         _check(lib.afk_image_download(self._h, out.ctypes.data_as(_P)))
         return out
 

@@ -1,0 +1,57 @@
+"""Shared helpers for the parity tests."""
+import numpy as np
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def assert_bit_equal(got, want, what=""):
+    """Tier A: bit-exact, except that -0.0/+0.0 and NaN payloads are compared by value."""
+    got = np.asarray(got, dtype=np.float32)
+    want = np.asarray(want, dtype=np.float32)
+    assert got.shape == want.shape, f"{what}: shape {got.shape} != {want.shape}"
+    gn, wn = np.isnan(got), np.isnan(want)
+    assert np.array_equal(gn, wn), f"{what}: NaN positions differ ({gn.sum()} vs {wn.sum()})"
+    ok = (got == want) | gn
+    if not ok.all():
+        i = np.argwhere(~ok)[0]
+        raise AssertionError(f"{what}: {(~ok).sum()} mismatches, first at {tuple(i)}: got {got[tuple(i)]!r} want {want[tuple(i)]!r}")
+
+
+def ulp_diff(got, want):
+    """Distance in units in the last place between two f32 arrays (same-sign finite values)."""
+    g = bits(got).astype(np.int64)
+    w = bits(want).astype(np.int64)
+    g = np.where(g & 0x80000000, 0x80000000 - g, g)
+    w = np.where(w & 0x80000000, 0x80000000 - w, w)
+    return np.abs(g - w)
+
+
+def assert_ulp(got, want, max_ulp, what=""):
+    """Tier B: within max_ulp of the f32 step-exact oracle; NaN/Inf positions must match exactly."""
+    got = np.asarray(got, dtype=np.float32)
+    want = np.asarray(want, dtype=np.float32)
+    assert got.shape == want.shape
+    assert np.array_equal(np.isnan(got), np.isnan(want)), f"{what}: NaN positions differ"
+    inf = np.isinf(want)
+    assert np.array_equal(got[inf], want[inf]), f"{what}: Inf positions differ"
+    fin = np.isfinite(want) & np.isfinite(got)
+    assert np.array_equal(np.isfinite(got), np.isfinite(want)), f"{what}: finite positions differ"
+    d = ulp_diff(got[fin], want[fin])
+    assert d.size == 0 or d.max() <= max_ulp, f"{what}: max ulp diff {d.max()} > {max_ulp}"
+
+
+def assert_reduction(got, sum64, abs64, what="", divisor=1.0):
+    """Tier C: |gpu - o64| <= 1e-5*|o64|  or  <= 4*2^-24*sum|x|; NaN/Inf positions exact."""
+    got = np.asarray(got, dtype=np.float32).astype(np.float64)
+    o = sum64 / divisor
+    a = abs64 / divisor
+    assert got.shape == o.shape, f"{what}: shape {got.shape} != {o.shape}"
+    assert np.array_equal(np.isnan(got), np.isnan(o)), f"{what}: NaN positions differ"
+    inf = np.isinf(o)
+    assert np.array_equal(got[inf], o[inf]), f"{what}: Inf positions differ"
+    fin = np.isfinite(o)
+    err = np.abs(got[fin] - o[fin])
+    ok = (err <= 1e-5 * np.abs(o[fin])) | (err <= 4 * 2.0 ** -24 * a[fin])
+    assert ok.all(), f"{what}: {(~ok).sum()} pixels outside tolerance, worst rel err {np.max(err / np.maximum(np.abs(o[fin]), 1e-300))}"
