@@ -3,7 +3,7 @@
 The product is the shared library: hand-written sm_100a kernels behind a C ABI that mirrors aflak's
 `cake::Transform` / `IOValue` operator registry.  This module only exists so that tests, bench.py and
 examples can call that ABI from Python; it contains no compute and no fallback.  If the library is missing
-the import fails loudly (build it with `python -m aflak_b200.build`).
+the import builds it with nvcc (aflak_b200/build.py) and fails loudly when that is impossible.
 """
 import ctypes as C
 import os
@@ -14,11 +14,18 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libaflak_b200.so")
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "aflak_b200.h")
 
-if not os.path.exists(LIB_PATH):
+# Build on first import (or when the sources changed): nvcc for sm_100a, in-tree.  A failed build is a failed import --
+# there is no other implementation to fall back to.
+from . import build as _build  # noqa: E402
+
+try:
+    _build.build()
+except Exception as exc:  # nvcc missing or a compile error
     raise ImportError(
-        f"{LIB_PATH} not found: the CUDA extension is not built. Run `python -m aflak_b200.build` "
-        "(nvcc, sm_100a). There is no CPU fallback."
-    )
+        f"{LIB_PATH} could not be built ({exc}). The CUDA extension is the product; there is no CPU fallback."
+    ) from exc
+if not os.path.exists(LIB_PATH):
+    raise ImportError(f"{LIB_PATH} not found: the CUDA extension is not built. There is no CPU fallback.")
 
 lib = C.CDLL(LIB_PATH)
 
@@ -157,6 +164,15 @@ _sig("afk_profile_reduce_read", C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_ui
 _sig("afk_ipc_export", C.c_int, _P, _u8p)
 _sig("afk_ipc_open", _P, _u8p)
 _sig("afk_ipc_close", C.c_int, _P)
+_sig("afk_shard_band", C.c_int, C.c_int64, C.c_int, C.c_int, _i64p, _i64p)
+_sig("afk_gather_create", _P, C.c_int, C.c_int, C.c_int64, C.c_int64, _u8p)
+_sig("afk_gather_connect", C.c_int, _P, _u8p)
+_sig("afk_gather_band", C.c_int, _P, C.c_int, _i64p, _i64p)
+_sig("afk_gather_reduce", C.c_int, _P, _P, C.c_int64, C.c_int, _i64p, _i64p, C.c_int, _fp, C.c_int)
+_sig("afk_gather_wait", C.c_int, _P, C.POINTER(C.c_void_p), C.c_double)
+_sig("afk_gather_check", C.c_int, _P)
+_sig("afk_gather_result_image", _P, _P)
+_sig("afk_gather_destroy", None, _P)
 _sig("afk_graph_new", _P)
 _sig("afk_graph_free", None, _P)
 _sig("afk_graph_add_transform", C.c_int64, _P, C.c_char_p)
@@ -469,6 +485,67 @@ def profile_reduce_read():
     ms, n = C.c_double(), C.c_uint64()
     _check(lib.afk_profile_reduce_read(C.byref(ms), C.byref(n)))
     return ms.value, int(n.value)
+
+
+# ---- spatial sharding + fused gather (one process per GPU) ----------------------------------------------------
+def shard_band(ny, world, rank):
+    """y-band [y0, y0+rows) of `rank`: pure host arithmetic, usable without a GPU."""
+    y0, rows = C.c_int64(), C.c_int64()
+    _check(lib.afk_shard_band(ny, world, rank, C.byref(y0), C.byref(rows)))
+    return int(y0.value), int(rows.value)
+
+
+class Gather:
+    """Fused gather of the 2-D result bands across the ranks of one box (include/aflak_b200.h, afk_gather_*).
+
+    `exchange(handle_bytes) -> list of every rank's handle bytes` is supplied by the host side's process group
+    (e.g. torch.distributed.all_gather_object); only 64 bytes per rank cross it, once.
+    """
+
+    def __init__(self, world, rank, ny_total, nx, exchange=None):
+        h = (C.c_uint8 * 64)()
+        self._h = C.c_void_p(lib.afk_gather_create(world, rank, ny_total, nx, h))
+        if not self._h:
+            raise AflakError(ERR_CUDA, lib.afk_last_error().decode())
+        self.world, self.rank, self.ny, self.nx = world, rank, ny_total, nx
+        if world > 1:
+            if exchange is None:
+                raise ValueError("world > 1 needs an exchange function")
+            allh = exchange(bytes(h))
+            buf = (C.c_uint8 * (64 * world)).from_buffer_copy(b"".join(allh))
+            _check(lib.afk_gather_connect(self._h, buf))
+
+    def band(self, rank=None):
+        y0, rows = C.c_int64(), C.c_int64()
+        lib.afk_gather_band(self._h, self.rank if rank is None else rank, C.byref(y0), C.byref(rows))
+        return int(y0.value), int(rows.value)
+
+    def reduce(self, band_cube_ptr, nz, windows, epilogue, params=None, sum_mode=SUM_COMPENSATED):
+        n = len(windows)
+        st = (C.c_int64 * n)(*[w[0] for w in windows])
+        en = (C.c_int64 * n)(*[w[1] for w in windows])
+        pr = (C.c_float * 5)(*(list(params) + [0.0] * 5)[:5]) if params is not None else None
+        _check(lib.afk_gather_reduce(self._h, C.c_void_p(band_cube_ptr), nz, n, st, en, epilogue, pr, sum_mode))
+
+    def wait(self, timeout_s=5.0):
+        """Enqueue the wait on this thread's stream; returns the device pointer of the full [ny, nx] image."""
+        p = C.c_void_p()
+        _check(lib.afk_gather_wait(self._h, C.byref(p), timeout_s))
+        return p.value
+
+    def check(self):
+        _check(lib.afk_gather_check(self._h))
+
+    def result_image(self):
+        return Image(lib.afk_gather_result_image(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.afk_gather_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
 
 
 # ---- display path ---------------------------------------------------------------------------------------------

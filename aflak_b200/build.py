@@ -1,7 +1,11 @@
 """Build libaflak_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).
 
-    python -m aflak_b200.build [--force]
+    python aflak_b200/build.py [--force] [-v]
+
+Staleness is decided by a content hash of the sources (kept next to the library in libaflak_b200.so.stamp), not by
+mtimes: the built library travels to the GPU box inside a snapshot whose mtimes are arbitrary.
 """
+import hashlib
 import os
 import subprocess
 import sys
@@ -9,7 +13,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libaflak_b200.so")
-SOURCES = ["kernels.cu", "runtime.cpp", "ops.cpp", "display.cpp", "graph.cpp"]
+STAMP = LIB + ".stamp"
+SOURCES = ["kernels.cu", "runtime.cpp", "ops.cpp", "display.cpp", "graph.cpp", "shard.cpp"]
 HEADERS = ["kernels.h", "host.h", os.path.join("..", "..", "include", "aflak_b200.h")]
 
 NVCC_FLAGS = [
@@ -24,18 +29,27 @@ NVCC_FLAGS = [
 
 
 def _nvcc():
-    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
-        if cand and (os.path.isabs(cand) and os.path.exists(cand) or not os.path.isabs(cand)):
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
             return cand
     return "nvcc"
 
 
+def source_hash():
+    h = hashlib.sha256()
+    h.update(" ".join(NVCC_FLAGS).encode())
+    for rel in SOURCES + HEADERS:
+        with open(os.path.join(CSRC, rel), "rb") as f:
+            h.update(rel.encode())
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def needs_build():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(STAMP):
         return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
-    return any(os.path.getmtime(d) > t for d in deps)
+    with open(STAMP) as f:
+        return f.read().strip() != source_hash()
 
 
 def build(force=False, verbose=False):
@@ -46,6 +60,8 @@ def build(force=False, verbose=False):
     env.pop("CXX", None)
     cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     subprocess.check_call(cmd, env=env)
+    with open(STAMP, "w") as f:
+        f.write(source_hash() + "\n")
     return LIB
 
 

@@ -77,10 +77,16 @@ struct ReduceKArgs {
     int64_t ktot, units, q, ntiles;
     int epilogue;
     float pa, pb, pfl, pmax, psign;
-    float *out;
+    float *out[kMaxPeers]; // nout destinations of the result (own buffer and/or peer-mapped buffers)
+    int nout;
     unsigned *minmax;
     double2 *partials;
     unsigned *counters;
+    // fused gather: when every CTA has stored its pixels, the last one writes `epoch` to each sig[i]
+    unsigned *done;            // grid-wide arrival counter (self-resetting), or nullptr
+    unsigned *sig[kMaxPeers];  // nsig flag words, typically one in every peer's flag array
+    int nsig;
+    unsigned epoch;
 };
 
 template <bool COMP> struct Acc {
@@ -336,11 +342,53 @@ __global__ void __launch_bounds__(kReduceBlock, kReduceCtasPerSm) reduce_kernel(
                     mm_any = true;
                 }
             }
-            Lane<VEC>::store(a.out + px, o);
+#pragma unroll 1
+            for (int d = 0; d < a.nout; ++d) Lane<VEC>::store(a.out[d] + px, o);
         }
         u = seg_end;
     }
     if (a.minmax) block_minmax_flush(mm_min, mm_max, mm_any, a.minmax);
+    if (a.done) {
+        // Fused gather epilogue: make this CTA's (peer) stores visible system-wide, count the arrival; the last CTA
+        // of the grid publishes the epoch to every destination's flag word with release semantics.
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned prev = atomicAdd(a.done, 1u);
+            if (prev == gridDim.x - 1) {
+                *a.done = 0u; // self-reset for the next launch
+                __threadfence_system();
+                for (int d = 0; d < a.nsig; ++d)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.sig[d]), "r"(a.epoch) : "memory");
+            }
+        }
+    }
+}
+
+// Stream-ordered wait of the fused gather: lane i spins until flags[i] >= epoch (epochs are monotonic), with a
+// clock bound so a lost peer turns into an error word instead of a hung GPU.
+__global__ void gather_wait_kernel(const unsigned *flags, int n, unsigned epoch, long long max_cycles, unsigned *err) {
+    const int i = threadIdx.x;
+    if (i >= n) return;
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
+        if ((int)(v - epoch) >= 0) break;
+        if (clock64() - t0 > max_cycles) {
+            atomicMax(err, 1u + (unsigned)i);
+            break;
+        }
+        __nanosleep(200);
+    }
+}
+
+cudaError_t gather_wait_launch(const unsigned *flags, int n, unsigned epoch, double timeout_s, unsigned *err, cudaStream_t s) {
+    if (n < 1 || n > 32) return cudaErrorInvalidValue;
+    const long long cycles = (long long)(timeout_s * 1.9e9);
+    gather_wait_kernel<<<1, 32, 0, s>>>(flags, n, epoch, cycles, err);
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
 }
 
 static float count_as_f32(int64_t n) {
@@ -353,8 +401,9 @@ static float count_as_f32(int64_t n) {
 
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     ReducePlan pl{};
-    const bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0) &&
-                         ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
+    bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
+    for (int d = 0; d < a.n_extra_out; ++d) aligned = aligned && ((reinterpret_cast<uintptr_t>(a.extra_out[d]) & 15u) == 0);
     pl.vec = aligned ? 4 : 1;
     const int64_t tile = (int64_t)kReduceBlock * pl.vec;
     pl.ntiles = (a.n2 + tile - 1) / tile;
@@ -412,7 +461,14 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
     k.pfl = a.p[2];
     k.pmax = a.p[3];
     k.psign = a.ew_sign;
-    k.out = a.out;
+    if (a.n_extra_out < 0 || a.n_extra_out > kMaxPeers - 1 || a.n_signal < 0 || a.n_signal > kMaxPeers) return cudaErrorInvalidValue;
+    k.out[0] = a.out;
+    for (int d = 0; d < a.n_extra_out; ++d) k.out[1 + d] = a.extra_out[d];
+    k.nout = 1 + a.n_extra_out;
+    k.done = a.n_signal > 0 ? a.done : nullptr;
+    for (int d = 0; d < a.n_signal; ++d) k.sig[d] = a.signal[d];
+    k.nsig = a.n_signal;
+    k.epoch = a.epoch;
     k.minmax = a.minmax;
     k.partials = static_cast<double2 *>(ws.partials);
     k.counters = ws.counters;

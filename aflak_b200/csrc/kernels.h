@@ -9,6 +9,7 @@ namespace afk {
 
 // ---- axis-0 windowed reduction (K1/K2 of DESIGN.md) -------------------------
 constexpr int kMaxWindows = 3;
+constexpr int kMaxPeers = 8;        // GPUs of one box (NVSwitch domain) a result band can be written to
 constexpr int kReduceBlock = 256;   // threads per CTA
 constexpr int kReduceCtasPerSm = 4; // resident CTAs per SM the launch is sized for
 
@@ -36,6 +37,14 @@ struct ReduceArgs {
     float ew_sign;     // -1 emission, +1 absorption
     float *out;        // [n2] (may be a peer-mapped pointer)
     unsigned *minmax;  // optional: {~key(min), key(max), any-non-NaN} accumulated with atomicMax, or nullptr
+    // fused gather: the same result is also stored to n_extra_out more buffers (peer-mapped over NVLink),
+    // and when the whole grid has stored, `epoch` is written to each signal word (release, system scope).
+    int n_extra_out;
+    float *extra_out[kMaxPeers - 1];
+    int n_signal;
+    unsigned *signal[kMaxPeers];
+    unsigned *done;    // device counter, zero-initialised, self-resetting; required when n_signal > 0
+    unsigned epoch;
 };
 
 struct ReduceWorkspace {
@@ -58,6 +67,9 @@ struct ReducePlan {
 
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count);
 cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &plan, const ReduceWorkspace &ws, cudaStream_t s);
+
+// stream-ordered wait until flags[i] >= epoch for i < n (n <= 32); *err gets 1+i of a flag that timed out
+cudaError_t gather_wait_launch(const unsigned *flags, int n, unsigned epoch, double timeout_s, unsigned *err, cudaStream_t s);
 
 // ---- elementwise (K3) --------------------------------------------------------
 enum MapOp : int {

@@ -1,0 +1,211 @@
+// shard.cpp -- spatial sharding of a cube across the GPUs of one box, and the fused gather of the 2-D result.
+//
+// The reference has no distribution at all (single process, rayon).  Every output pixel of the hot path
+// depends only on its own spaxel, so a cube [nz, ny, nx] shards into contiguous y-bands, one per GPU, with no
+// data-path collective; the only exchange is the gather of the [ny, nx] result.  That gather is fused
+// into the reduction kernel: each rank's kernel stores its result band straight into every rank's copy of the full
+// image through CUDA-IPC peer mappings (NVLink 5 / NVSwitch) and the last CTA publishes an epoch flag; consumers wait
+// on the flags with a one-warp kernel in stream order.  No NCCL on the data path; the host side's process group
+// (torch.distributed) only carries the 64-byte IPC handles once at start-up.
+#include <cstring>
+
+#include "host.h"
+
+struct afk_gather {
+    int world = 1, rank = 0, device = 0;
+    int64_t ny = 0, nx = 0;
+    int64_t y0[afk::kMaxPeers] = {0}, rows[afk::kMaxPeers] = {0};
+    size_t slot_floats = 0;         // one full image, padded to 256 B
+    char *local = nullptr;          // cudaMalloc'ed: [slot 0][slot 1][flags: kMaxPeers u32][done u32][err u32]
+    char *peer[afk::kMaxPeers] = {nullptr};
+    bool connected = false;
+    unsigned epoch = 0;
+    size_t bytes = 0;
+    float *slot(int r, unsigned e) const { return reinterpret_cast<float *>(peer[r]) + (size_t)(e & 1u) * slot_floats; }
+    unsigned *flags(int r) const { return reinterpret_cast<unsigned *>(peer[r] + 2 * slot_floats * sizeof(float)); }
+    unsigned *done() const { return flags(rank) + afk::kMaxPeers; }
+    unsigned *err() const { return flags(rank) + afk::kMaxPeers + 1; }
+};
+
+using namespace afk;
+
+extern "C" {
+
+// Band of rank `rank`: rows split as evenly as possible, the first (ny % world) ranks get one more row.
+int afk_shard_band(int64_t ny, int world, int rank, int64_t *y0, int64_t *rows) {
+    if (world < 1 || rank < 0 || rank >= world || ny < 0 || !y0 || !rows) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "bad arguments to afk_shard_band"));
+    const int64_t base = ny / world, rem = ny % world;
+    *y0 = rank * base + (rank < rem ? rank : rem);
+    *rows = base + (rank < rem ? 1 : 0);
+    return AFK_OK;
+}
+
+afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx, uint8_t handle_out[64]) {
+    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || ny_total < 0 || nx < 0 || !handle_out) {
+        fail(make_error(AFK_ERR_UNEXPECTED_INPUT, fmt("afk_gather_create: world must be 1..%d and 0 <= rank < world", kMaxPeers)));
+        return nullptr;
+    }
+    cudaStream_t s;
+    int dev;
+    if (fail(current_stream(&s, &dev)) != AFK_OK) return nullptr;
+    afk_gather *g = new afk_gather();
+    g->world = world;
+    g->rank = rank;
+    g->device = dev;
+    g->ny = ny_total;
+    g->nx = nx;
+    for (int r = 0; r < world; ++r) afk_shard_band(ny_total, world, r, &g->y0[r], &g->rows[r]);
+    size_t fl = (size_t)ny_total * (size_t)nx;
+    g->slot_floats = (fl + 63) / 64 * 64;
+    g->bytes = 2 * g->slot_floats * sizeof(float) + (kMaxPeers + 8) * sizeof(unsigned);
+    void *p = nullptr;
+    // cudaMalloc, not the stream-ordered pool: pool memory cannot be exported with cudaIpcGetMemHandle
+    cudaError_t ce = cudaMalloc(&p, g->bytes);
+    if (ce == cudaSuccess) ce = cudaMemset(p, 0, g->bytes);
+    cudaIpcMemHandle_t h;
+    if (ce == cudaSuccess) ce = cudaIpcGetMemHandle(&h, p);
+    if (ce != cudaSuccess) {
+        fail(cuda_error(ce, "afk_gather_create"));
+        if (p) cudaFree(p);
+        delete g;
+        return nullptr;
+    }
+    g->local = static_cast<char *>(p);
+    g->peer[rank] = g->local;
+    memcpy(handle_out, &h, 64);
+    if (world == 1) g->connected = true;
+    return g;
+}
+
+int afk_gather_connect(afk_gather *g, const uint8_t *handles) {
+    if (!g || !handles) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_gather_connect"));
+    cudaStream_t s;
+    if (Error e = current_stream(&s, nullptr)) return fail(e);
+    for (int r = 0; r < g->world; ++r) {
+        if (r == g->rank || g->peer[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + (size_t)r * 64, 64);
+        void *p = nullptr;
+        cudaError_t ce = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (ce != cudaSuccess) return fail(cuda_error(ce, "cudaIpcOpenMemHandle (peer result buffer)"));
+        g->peer[r] = static_cast<char *>(p);
+    }
+    g->connected = true;
+    return AFK_OK;
+}
+
+int afk_gather_band(const afk_gather *g, int rank, int64_t *y0, int64_t *rows) {
+    if (!g || rank < 0 || rank >= g->world) return AFK_ERR_UNEXPECTED_INPUT;
+    if (y0) *y0 = g->y0[rank];
+    if (rows) *rows = g->rows[rank];
+    return AFK_OK;
+}
+
+// One step on this rank: reduce the band cube [nz, rows(rank), nx] and store the result band into every rank's full
+// image (slot = epoch parity), then signal.  Stream-ordered; no host synchronisation.
+afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, int nwin, const int64_t *starts, const int64_t *ends,
+                             int epilogue, const float *params, int sum_mode) {
+    if (!g || !band_cube || !starts || !ends) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_gather_reduce"));
+    if (!g->connected) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_connect has not been called"));
+    if (nwin < 1 || nwin > kMaxWindows) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, fmt("between 1 and %d windows are supported, got %d", kMaxWindows, nwin)));
+    const int need = epilogue == EPI_EW ? 3 : (epilogue == EPI_MEAN_RATIO ? 2 : 1);
+    if (epilogue < EPI_SUM || epilogue > EPI_EW || nwin != need) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "epilogue and window count do not match"));
+    cudaStream_t s;
+    int dev;
+    if (Error e = current_stream(&s, &dev)) return fail(e);
+    if (dev != g->device) return fail(make_error(AFK_ERR_CUDA, "CUDA: gather belongs to another device"));
+    const unsigned epoch = ++g->epoch;
+    const int64_t band_off = g->y0[g->rank] * g->nx;
+    ReduceArgs a{};
+    a.cube = band_cube;
+    a.n2 = g->rows[g->rank] * g->nx;
+    a.nwin = nwin;
+    for (int w = 0; w < nwin; ++w) {
+        if (starts[w] < 0 || !(starts[w] < ends[w]) || ends[w] > nz)
+            return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, fmt("Expected 0 <= start < end <= %lld, but got %lld, %lld", (long long)nz, (long long)starts[w], (long long)ends[w])));
+        a.start[w] = starts[w];
+        a.end[w] = ends[w];
+    }
+    a.epilogue = epilogue;
+    a.mode = sum_mode;
+    for (int i = 0; i < 4; ++i) a.p[i] = params ? params[i] : 0.0f;
+    a.ew_sign = params ? params[4] : 1.0f;
+    a.out = g->slot(g->rank, epoch) + band_off;
+    int k = 0;
+    for (int r = 0; r < g->world; ++r)
+        if (r != g->rank) a.extra_out[k++] = g->slot(r, epoch) + band_off;
+    a.n_extra_out = k;
+    for (int r = 0; r < g->world; ++r) a.signal[r] = g->flags(r) + g->rank; // my word in rank r's flag array
+    a.n_signal = g->world;
+    a.done = g->done();
+    a.epoch = epoch;
+    if (a.n2 <= 0) {
+        // an empty band still has to signal: launch a 1-frame plan is impossible, so set the flags from the host side
+        for (int r = 0; r < g->world; ++r) {
+            cudaError_t ce = cudaMemcpyAsync(a.signal[r], &g->epoch, sizeof(unsigned), cudaMemcpyHostToDevice, s);
+            if (ce != cudaSuccess) return fail(cuda_error(ce, "signal of an empty band"));
+        }
+        return AFK_OK;
+    }
+    ReducePlan plan = reduce_plan(a, sm_count(dev));
+    ReduceWorkspace ws;
+    if (Error e = reduce_workspace(plan, dev, s, &ws)) return fail(e);
+    ThreadCtx &c = tls();
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (c.profile) {
+        cudaEventCreate(&e0);
+        cudaEventCreate(&e1);
+        cudaEventRecord(e0, s);
+    }
+    cudaError_t ce = reduce_launch(a, plan, ws, s);
+    if (c.profile) {
+        cudaEventRecord(e1, s);
+        c.prof_events.emplace_back(e0, e1);
+        c.prof_launches += 1;
+    }
+    if (ce != cudaSuccess) return fail(cuda_error(ce, "reduce_kernel launch (fused gather)"));
+    return AFK_OK;
+}
+
+// Enqueue the wait for the current epoch's bands of all ranks; *result = this rank's full image [ny, nx] of that epoch.
+afk_status afk_gather_wait(afk_gather *g, float **result, double timeout_s) {
+    if (!g) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_gather_wait"));
+    cudaStream_t s;
+    if (Error e = current_stream(&s, nullptr)) return fail(e);
+    if (timeout_s <= 0) timeout_s = 5.0;
+    cudaError_t ce = gather_wait_launch(g->flags(g->rank), g->world, g->epoch, timeout_s, g->err(), s);
+    if (ce != cudaSuccess) return fail(cuda_error(ce, "gather_wait_kernel launch"));
+    if (result) *result = g->slot(g->rank, g->epoch);
+    return AFK_OK;
+}
+
+// Host-synchronising check: 0 when no wait has timed out, else AFK_ERR_CUDA naming the rank whose band never arrived.
+afk_status afk_gather_check(afk_gather *g) {
+    if (!g) return AFK_ERR_UNEXPECTED_INPUT;
+    cudaStream_t s;
+    if (Error e = current_stream(&s, nullptr)) return fail(e);
+    unsigned h = 0;
+    cudaError_t ce = cudaMemcpyAsync(&h, g->err(), sizeof h, cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) return fail(cuda_error(ce, "afk_gather_check"));
+    if (h) return fail(make_error(AFK_ERR_CUDA, fmt("CUDA: fused gather timed out waiting for the band of rank %u", h - 1)));
+    return AFK_OK;
+}
+
+afk_image *afk_gather_result_image(afk_gather *g) {
+    if (!g) return nullptr;
+    int64_t shape[2] = {g->ny, g->nx};
+    return afk_image_wrap_device(g->slot(g->rank, g->epoch), 2, shape);
+}
+
+void afk_gather_destroy(afk_gather *g) {
+    if (!g) return;
+    cudaDeviceSynchronize();
+    for (int r = 0; r < g->world; ++r)
+        if (r != g->rank && g->peer[r]) cudaIpcCloseMemHandle(g->peer[r]);
+    if (g->local) cudaFree(g->local);
+    cudaGetLastError();
+    delete g;
+}
+
+} // extern "C"

@@ -251,6 +251,31 @@ int afk_ipc_export(const afk_image *img, uint8_t handle[64]);
 float *afk_ipc_open(const uint8_t handle[64]);
 int afk_ipc_close(float *peer_ptr);
 
+/* ---- spatial sharding across the GPUs of one box + fused gather of the 2-D result (one process per GPU).
+ *      The reference has no distributed path (single process, rayon: aflak_cake/src/dst/compute.rs:152-224); this is
+ *      the B200 form of "large cubes shard by spatial tiles, the only NVLink traffic is the gather of the 2-D result".
+ *      Protocol: every rank calls afk_gather_create, the 64-byte handles are exchanged by the host's process group
+ *      (world*64 bytes, rank-major), every rank calls afk_gather_connect; then per step afk_gather_reduce (the reduce
+ *      kernel stores its band into every rank's full image through peer mappings and publishes an epoch flag) and
+ *      afk_gather_wait (stream-ordered one-warp wait for all bands).  Results alternate between two slots, so step
+ *      n+1 never overwrites an image a peer may still be reading from step n. ---- */
+typedef struct afk_gather afk_gather;
+/* y-band [y0, y0+rows) of `rank`: rows split evenly, the first ny % world ranks get one extra row */
+int afk_shard_band(int64_t ny, int world, int rank, int64_t *y0, int64_t *rows);
+afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx, uint8_t handle_out[64]);
+int afk_gather_connect(afk_gather *g, const uint8_t *handles);
+int afk_gather_band(const afk_gather *g, int rank, int64_t *y0, int64_t *rows);
+/* band_cube: device pointer to this rank's [nz, rows, nx] band; epilogue/params/sum_mode as afk_k_reduce */
+afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, int nwin, const int64_t *starts,
+                             const int64_t *ends, int epilogue, const float *params, int sum_mode);
+/* *result = device pointer to this rank's copy of the full [ny_total, nx] image, valid once the stream reaches it */
+afk_status afk_gather_wait(afk_gather *g, float **result, double timeout_s);
+/* host-synchronising: AFK_ERR_CUDA if a wait timed out (a peer's band never arrived) */
+afk_status afk_gather_check(afk_gather *g);
+/* the current full image as a borrowed (non-owning) Image handle, for further operators (LUT, min/max, ...) */
+afk_image *afk_gather_result_image(afk_gather *g);
+void afk_gather_destroy(afk_gather *g);
+
 /* ---- mini evaluator with a device-handle cache: DST::compute + Cache (dst/compute.rs:153-274, cache.rs) ---- */
 typedef struct afk_graph afk_graph;
 afk_graph *afk_graph_new(void);

@@ -15,10 +15,7 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def afk():
     """The product: ctypes view of libaflak_b200.so (built on demand, never a fallback)."""
-    from aflak_b200 import build as _build
-
-    _build.build()
-    import aflak_b200
+    import aflak_b200  # builds libaflak_b200.so with nvcc when missing or stale; raises if that fails
 
     return aflak_b200
 

@@ -1,0 +1,164 @@
+"""CPU: pin the oracle (oracle/, the parity checker) against the committed fixtures of tests/golden/.
+
+  lut_golden.json   the reference's own value-asserting unit tests (aflak_plot/src/imshow/lut.rs:292-343)
+  kat.json          hand-derived known answers for operators the reference never asserts values for
+  test_fits_*       a crop of the reference's data fixture with numpy-f64 check sums
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from util import assert_bit_equal
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    with open(os.path.join(GOLD, name)) as f:
+        return json.load(f)
+
+
+def grad(g):
+    return [(s[0], tuple(s[1])) for s in g]
+
+
+def test_lut_color_at_golden(orc):
+    for case in load("lut_golden.json")["color_at"]:
+        table = orc.lut_build(grad(case["gradient"]), tuple(case.get("table_lims", case["lims"])))
+        for point, rgb in case["cases"]:
+            assert orc.color_at(table, point, tuple(case["lims"])) == rgb, (point, rgb)
+
+
+def test_lut_bounds_golden(orc):
+    b = load("lut_golden.json")["bounds"]
+    got = orc.lut_bounds(grad(b["gradient"]), tuple(b["lims"]))
+    want = [((p[0][0], tuple(p[0][1])), (p[1][0], tuple(p[1][1]))) for p in b["pairs"]]
+    assert got == want
+
+
+def test_lut_builtin_tables_are_monotone_in_grey(orc):
+    t = orc.lut_build("Grey")
+    assert t.shape == (65536, 3)
+    assert np.all(np.diff(t[:, 0].astype(np.int32)) >= 0)
+    assert tuple(t[0]) == (0, 0, 0) and tuple(t[-1]) == (255, 255, 255)
+    assert tuple(t[32767]) == (127, 127, 127)  # truncating `as u8`: 255 * 0.49999 = 127.49 -> 127
+
+
+def test_integral_ramp_kat(orc):
+    k = load("kat.json")
+    for c in k["integral_ramp"]:
+        nz = c["nz"]
+        cube = np.broadcast_to(np.arange(nz, dtype=np.float32)[:, None, None], (nz, 3, 5)).copy()
+        out = orc.integral(cube, c["a"], c["b"])
+        assert np.all(out == np.float32(c["value"]))
+        avg = orc.average(cube, c["a"], c["b"])
+        assert np.all(avg == np.float32(np.float32(c["value"]) / np.float32(c["b"] - c["a"])))
+    for c in k["middle_width"]:
+        assert orc.middle_width(c["a"], c["b"]) == (c["middle"], c["width"])
+
+
+def test_elementwise_kat(orc):
+    k = load("kat.json")
+    for c in k["equivalent_width"]:
+        out = orc.equivalent_width(np.array([c["off"]], np.float32), np.array([c["on"]], np.float32), c["fl"], c["max"], c["emission"])
+        assert out[0] == np.float32(c["value"]), c
+    r = k["ratio_from_bands"]
+    r2, r1 = orc.ratio_from_bands(r["z"], r["z1"], r["z2"])
+    assert (np.float32(r2), np.float32(r1)) == (np.float32(r["off_ratio_2"]), np.float32(r["off_ratio_1"]))
+    for c in k["linear_composition"]:
+        out = orc.linear_composition(np.array([c["u"]], np.float32), np.array([c["v"]], np.float32), c["a"], c["b"])
+        assert out[0] == np.float32(c["out"])
+    for c in k["logscale"]:
+        out = orc.convert_to_logscale(np.array([c["v"]], np.float32), c["a"], c["vmin"], c["vmax"])
+        assert out[0] == np.float32(c["out"])
+    table = orc.tone_curve_default()
+    assert table.size == 256 and table[255] == 255.0
+    for c in k["tone_curve_default"]:
+        out = orc.apply_tone_curve(np.array([c["v"]], np.float32), table)
+        assert out[0] == np.float32(c["out"]), c
+    mn, mx = orc.image_min_max(np.zeros((0,), np.float32))
+    assert (float(mn), float(mx)) == (k["image_min_max_empty"]["min"], k["image_min_max_empty"]["max"])
+
+
+def test_down_sampling_kat(orc):
+    d = load("kat.json")["down_sampling"]
+    img = np.arange(np.prod(d["shape"]), dtype=np.float32).reshape(d["shape"])
+    out = orc.down_sampling(img, d["n"])
+    assert list(out.shape) == d["out_shape"]
+    want = np.array([img[y, x] for y, x in d["picks"]], np.float32).reshape(d["out_shape"])
+    assert_bit_equal(out, want)
+    cube = np.arange(2 * 4 * 5, dtype=np.float32).reshape(2, 4, 5)
+    out3 = orc.down_sampling(cube, 3)
+    assert out3.shape == (2, 2, 2)
+    assert_bit_equal(out3, cube[:, ::3, ::3])
+
+
+def test_error_strings(orc):
+    e = load("kat.json")["errors"]
+    cube = np.zeros((10, 2, 2), np.float32)
+    cases = [(lambda: orc.integral(cube, -1, 5), e["start_negative"]), (lambda: orc.integral(cube, 2, -3), e["end_negative"]),
+             (lambda: orc.integral(cube, 5, 3), e["start_ge_end"]), (lambda: orc.average(cube, 0, 11), e["end_too_large_nz10"]),
+             (lambda: orc.slice_one_frame(cube, 10), e["frame_too_large_nz10"]),
+             (lambda: orc.down_sampling(cube[0], 0), e["down_sampling_n0"]),
+             (lambda: orc.ratio_from_bands(3.0, 5.0, 9.0), e["ratio_from_bands_order"])]
+    for fn, msg in cases:
+        with pytest.raises(orc.OracleError) as ei:
+            fn()
+        assert ei.value.msg == msg
+
+
+def test_real_cube_crop(orc):
+    """The reference's data fixture (crop): the f32 sequential oracle vs numpy f64 sums, and bit-exact slicing."""
+    crop = np.load(os.path.join(GOLD, "test_fits_crop.npy"))
+    facts = load("test_fits_facts.json")
+    assert crop.shape == (200, 12, 12) and crop.dtype == np.float32
+    want = np.array(facts["crop_sum_f64_40_160"])
+    got = orc.integral(crop, 40, 160).astype(np.float64)
+    np.testing.assert_allclose(got, want, rtol=2e-5, atol=1e-4)  # the reference's own f32 error: ~n * 2^-24 relative
+    s64, a64 = orc.sum_f64(crop, 40, 160)
+    np.testing.assert_allclose(s64, want, rtol=1e-12)
+    assert_bit_equal(orc.slice_one_frame(crop, 100), np.array(facts["crop_frame_100"], np.float32))
+
+
+def test_sequential_sum_order(orc):
+    """ndarray 0.12.1 sum_axis: strictly left-to-right f32 per pixel -- differs from pairwise/f64 on purpose."""
+    col = np.array([1e8, 1.0, -1e8, 1.0], np.float32).reshape(4, 1, 1)
+    assert orc.integral(col, 0, 4)[0, 0] == np.float32(1.0)  # (1e8 + 1) rounds to 1e8; then -1e8 -> 0; + 1 -> 1
+    s64, _ = orc.sum_f64(col, 0, 4)
+    assert s64[0, 0] == 2.0
+
+
+def test_average_count_is_f32_division(orc):
+    cube = np.full((3, 1, 1), 0.1, np.float32)
+    s = np.float32(np.float32(np.float32(0.1) + np.float32(0.1)) + np.float32(0.1))
+    assert orc.average(cube, 0, 3)[0, 0] == np.float32(s / np.float32(3.0))
+
+
+def test_generator_is_deterministic_and_shardable(orc):
+    full = orc.gen_cube(7, 9, 10, 6)
+    band = orc.gen_cube(7, 9, 10, 6, y0=4, rows=3)
+    assert_bit_equal(band, full[:, 4:7, :])
+    assert np.all(full > 0)
+    p = orc.gen_cube(7, 64, 32, 32, pathology=True)
+    assert np.isnan(p).any() and np.isinf(p).any()
+
+
+def test_get_vmin_vmax_skip_nan(orc):
+    a = np.array([np.nan, 3.0, -2.0, np.nan, 7.0], np.float32)
+    assert orc.get_vmin(a) == np.float32(-2.0) and orc.get_vmax(a) == np.float32(7.0)
+    assert np.isnan(orc.get_vmin(np.array([np.nan, np.nan], np.float32)))
+    mn, mx = orc.image_min_max(np.array([np.nan, np.inf, -1.0], np.float32))
+    assert mn == np.float32(-1.0) and np.isinf(mx)
+
+
+def test_make_raw_image_flip_and_nan(orc):
+    img = np.array([[0.0, 1.0], [np.nan, 0.5]], np.float32)
+    table = orc.lut_build("Grey")
+    out = orc.make_raw_image(img, 0.0, 1.0, table, channels=3)
+    # output row 0 is input row 1 (vertical flip, image.rs:123-129); NaN -> index 0 -> lut[0]
+    assert out[0, 0].tolist() == [0, 0, 0] and out[0, 1].tolist() == [127, 127, 127]
+    assert out[1, 0].tolist() == [0, 0, 0] and out[1, 1].tolist() == [255, 255, 255]
+    rgba = orc.make_raw_image(img, 0.0, 1.0, table, channels=4)
+    assert np.all(rgba[..., 3] == 255) and np.array_equal(rgba[..., :3], out)
