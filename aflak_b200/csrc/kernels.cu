@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace afk {
@@ -138,14 +139,15 @@ __device__ __forceinline__ void acc_batch(const char *&ptr, size_t stride, Acc<C
 }
 
 // frames [ka, kb) of one pixel lane, strictly in k order
-template <int VEC, bool COMP>
+template <int VEC, bool COMP, int U>
 __device__ __forceinline__ void accumulate(const float *lane_base, int64_t n2, int64_t ka, int64_t kb,
                                            Acc<COMP> (&acc)[VEC]) {
     const size_t stride = (size_t)n2 * sizeof(float);
     const char *ptr = reinterpret_cast<const char *>(lane_base) + (size_t)ka * stride;
     int64_t n = kb - ka;
-    for (; n >= 8; n -= 8) acc_batch<VEC, COMP, 8>(ptr, stride, acc);
-    if (n >= 4) { acc_batch<VEC, COMP, 4>(ptr, stride, acc); n -= 4; }
+    for (; n >= U; n -= U) acc_batch<VEC, COMP, U>(ptr, stride, acc);
+    if (U > 8 && n >= 8) { acc_batch<VEC, COMP, 8>(ptr, stride, acc); n -= 8; }
+    if (U > 4 && n >= 4) { acc_batch<VEC, COMP, 4>(ptr, stride, acc); n -= 4; }
     if (n >= 2) { acc_batch<VEC, COMP, 2>(ptr, stride, acc); n -= 2; }
     if (n >= 1) { acc_batch<VEC, COMP, 1>(ptr, stride, acc); }
 }
@@ -231,8 +233,8 @@ __device__ __forceinline__ float reduce_epilogue(const ReduceKArgs &a, const flo
     return 0.0f;
 }
 
-template <int VEC, bool COMP, int NW>
-__global__ void __launch_bounds__(kReduceBlock, kReduceCtasPerSm) reduce_kernel(const ReduceKArgs a) {
+template <int VEC, bool COMP, int NW, int U, int MINB>
+__global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const ReduceKArgs a) {
     constexpr int64_t TILE = (int64_t)kReduceBlock * VEC;
     const int tid = threadIdx.x;
     const int64_t g = blockIdx.x;
@@ -265,7 +267,7 @@ __global__ void __launch_bounds__(kReduceBlock, kReduceCtasPerSm) reduce_kernel(
 #pragma unroll
                 for (int i = 0; i < VEC; ++i) acc_init<COMP>(acc[i]);
                 if (active)
-                    accumulate<VEC, COMP>(lane_base, a.n2, a.start[w] + (lo - a.woff[w]), a.start[w] + (hi - a.woff[w]), acc);
+                    accumulate<VEC, COMP, U>(lane_base, a.n2, a.start[w] + (lo - a.woff[w]), a.start[w] + (hi - a.woff[w]), acc);
                 if (full) {
 #pragma unroll
                     for (int i = 0; i < VEC; ++i) S[w][i] = finalize_sum(acc_value<COMP>(acc[i]), acc[i].p);
@@ -399,6 +401,7 @@ static float count_as_f32(int64_t n) {
     return c;
 }
 
+int reduce_tune_ctas();
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     ReducePlan pl{};
     bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0) &&
@@ -410,7 +413,7 @@ ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     pl.ktot = 0;
     for (int w = 0; w < a.nwin; ++w) pl.ktot += a.end[w] - a.start[w];
     pl.units = pl.ntiles * pl.ktot;
-    const int64_t G = (int64_t)sm_count * kReduceCtasPerSm;
+    const int64_t G = (int64_t)sm_count * reduce_tune_ctas();
     if (a.mode == SUM_SEQUENTIAL) {
         pl.q = pl.ktot * ((pl.ntiles + G - 1) / G); // whole tiles only: never split a pixel's sum
     } else {
@@ -425,16 +428,35 @@ ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     return pl;
 }
 
-template <int VEC, bool COMP>
+// Tuning knobs, read once (AFK_REDUCE_UNROLL = 8|16 independent 16-byte loads per thread, AFK_REDUCE_CTAS = 2|3|4
+// resident CTAs per SM).  Measured on B200, ALMA-shape cube (profiles/r1_reduce_tuning_sweep.txt): (8,3) 7.10 TB/s,
+// (16,3) 7.08, (8,2) 7.01, (16,2) 7.00, (8,4) 6.72 (64 registers: spills + serialised loads), (4,4) 5.62.
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+int reduce_tune_unroll() { static int u = env_int("AFK_REDUCE_UNROLL", 8); return u == 16 ? 16 : 8; }
+int reduce_tune_ctas() { static int c = env_int("AFK_REDUCE_CTAS", kReduceCtasPerSm); return (c == 2 || c == 4) ? c : 3; }
+
+template <int VEC, bool COMP, int U, int MINB>
 static cudaError_t reduce_dispatch_nw(const ReduceKArgs &k, int grid, cudaStream_t s) {
     switch (k.nwin) {
-    case 1: reduce_kernel<VEC, COMP, 1><<<grid, kReduceBlock, 0, s>>>(k); break;
-    case 2: reduce_kernel<VEC, COMP, 2><<<grid, kReduceBlock, 0, s>>>(k); break;
-    case 3: reduce_kernel<VEC, COMP, 3><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 1: reduce_kernel<VEC, COMP, 1, U, MINB><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 2: reduce_kernel<VEC, COMP, 2, U, MINB><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 3: reduce_kernel<VEC, COMP, 3, U, MINB><<<grid, kReduceBlock, 0, s>>>(k); break;
     default: return cudaErrorInvalidValue;
     }
     AFK_COUNT_LAUNCH();
     return cudaGetLastError();
+}
+
+template <int VEC, bool COMP>
+static cudaError_t reduce_dispatch_tune(const ReduceKArgs &k, int grid, cudaStream_t s) {
+    const int u = reduce_tune_unroll(), c = reduce_tune_ctas();
+#define AFK_TUNE(U_, C_) if (u == U_ && c == C_) return reduce_dispatch_nw<VEC, COMP, U_, C_>(k, grid, s)
+    AFK_TUNE(8, 4); AFK_TUNE(8, 2); AFK_TUNE(16, 2); AFK_TUNE(16, 3);
+#undef AFK_TUNE
+    return reduce_dispatch_nw<VEC, COMP, 8, 3>(k, grid, s);
 }
 
 cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const ReduceWorkspace &ws, cudaStream_t s) {
@@ -473,8 +495,8 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
     k.partials = static_cast<double2 *>(ws.partials);
     k.counters = ws.counters;
     const bool comp = a.mode != SUM_SEQUENTIAL;
-    if (pl.vec == 4) return comp ? reduce_dispatch_nw<4, true>(k, pl.grid, s) : reduce_dispatch_nw<4, false>(k, pl.grid, s);
-    return comp ? reduce_dispatch_nw<1, true>(k, pl.grid, s) : reduce_dispatch_nw<1, false>(k, pl.grid, s);
+    if (pl.vec == 4) return comp ? reduce_dispatch_tune<4, true>(k, pl.grid, s) : reduce_dispatch_tune<4, false>(k, pl.grid, s);
+    return comp ? reduce_dispatch_tune<1, true>(k, pl.grid, s) : reduce_dispatch_tune<1, false>(k, pl.grid, s);
 }
 
 // ----------------------------------------------------------------------------------------------------

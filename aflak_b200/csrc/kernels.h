@@ -11,7 +11,7 @@ namespace afk {
 constexpr int kMaxWindows = 3;
 constexpr int kMaxPeers = 8;        // GPUs of one box (NVSwitch domain) a result band can be written to
 constexpr int kReduceBlock = 256;   // threads per CTA
-constexpr int kReduceCtasPerSm = 4; // resident CTAs per SM the launch is sized for
+constexpr int kReduceCtasPerSm = 3; // resident CTAs per SM the launch is sized for (<= 85 registers per thread)
 
 enum ReduceEpilogue : int {
     EPI_SUM = 0,        // out = S0                                   (integral, lib.rs:1324)

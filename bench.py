@@ -395,11 +395,18 @@ def run_e2e(args, afk, torch, dist, nz, ny, nx, rank, world, dev):
     res_t = torch.empty((rows, nx), dtype=torch.float32, pin_memory=True)
     g, c_cube, avg, ratio = build_c3_graph(afk, nz)
 
+    phases = []
+
     def step():
+        t0 = time.perf_counter()
         img = afk.Image.upload(host, sync=False)  # pinned cudaMemcpyAsync, stream-ordered
+        t1 = time.perf_counter()
         g.set_constant(c_cube, img)
         res = g.compute(ratio)                    # fused average/average/ratio kernel on the same stream
+        t2 = time.perf_counter()
         res.download(out=res_t.numpy())           # blocks until the 2-D result is on the host
+        t3 = time.perf_counter()
+        phases.append((t1 - t0, t2 - t1, t3 - t2))
 
     # wire the graph once with a real image so the edges type-check (Image -> average.image)
     img0 = afk.Image.upload(host, sync=True)
@@ -419,6 +426,7 @@ def run_e2e(args, afk, torch, dist, nz, ny, nx, rank, world, dev):
         step()
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / n_steps
+    ph = np.array(phases[-n_steps:]).mean(0) * 1e3
     tt = torch.tensor([dt], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -447,6 +455,7 @@ def run_e2e(args, afk, torch, dist, nz, ny, nx, rank, world, dev):
     return {"value": sbytes * world / dt / 1e9, "unit": UNIT, "h2d_bytes_per_step": nz * rows * nx * 4 * world,
             "d2h_bytes_per_step": rows * nx * 4 * world, "ms_per_step": dt * 1e3, "steps": n_steps,
             "cube_per_gpu": [nz, rows, nx],
+            "host_call_ms": {"upload_enqueue": float(ph[0]), "graph_compute_enqueue": float(ph[1]), "download_wait": float(ph[2])},
             "path": "pinned host cube -> afk_image_upload -> graph(average, average, ratio; fused) -> afk_image_download",
             "resident_cube": {"value": sbytes / dt_int / 1e9, "unit": UNIT, "ms_per_step": dt_int * 1e3, "steps": n_int,
                               "h2d_bytes_per_step": 8, "d2h_bytes_per_step": rows * nx * 4,

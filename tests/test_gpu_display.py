@@ -1,0 +1,145 @@
+"""GPU parity: the aflak_plot colour-mapping path (f32 image -> RGB8 / RGBA8 bytes), byte-exact.
+
+Reference: aflak_plot/src/imshow/lut.rs:132-194 (color_at_bounds, color_at, mtf, table build), image.rs:20-84
+(make_raw_image, make_raw_image_rgb), image.rs:123-129 (vertical flip), lims.rs:7-35,108-124 (get_vmin/get_vmax),
+util.rs:3-14 (clamp).  Every output byte must equal the oracle's (integer/byte work: bit-exact).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def lognormal(shape, seed, nan_frac=0.0):
+    rng = np.random.default_rng(seed)
+    img = np.exp(rng.standard_normal(shape)).astype(np.float32)
+    if nan_frac:
+        img[rng.random(shape) < nan_frac] = np.nan
+    return img
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (37, 53), (1, 1), (5, 1024), (300, 7)])
+@pytest.mark.parametrize("gradient", ["Flame", "Grey", "HeatMap_Inv", "GreyClip"])
+@pytest.mark.parametrize("channels", [3, 4])
+def test_make_raw_image_bytes(gpu, orc, shape, gradient, channels):
+    img = lognormal(shape, 21, nan_frac=0.01)
+    d = gpu.Image.upload(img)
+    lut = gpu.Lut(gradient)
+    table = orc.lut_build(gradient)
+    vmin, vmax = orc.get_vmin(img), orc.get_vmax(img)
+    got = gpu.colormap(d, lut, channels=channels)  # vmin/vmax computed on the device (Image::new, image.rs:143-194)
+    want = orc.make_raw_image(img, vmin, vmax, table, channels=channels)
+    assert np.array_equal(got, want), f"{(got != want).sum()} bytes differ"
+    gmn, gmx = d.vmin_vmax()
+    assert (gmn, gmx) == (vmin, vmax)
+
+
+@pytest.mark.parametrize("lims", [(0.0, 0.5, 1.0), (0.2, 0.3, 0.9), (0.0, 0.1, 0.5), (0.4, 0.9, 0.6)])
+def test_lims_and_midtone_transfer(gpu, orc, lims):
+    img = lognormal((96, 100), 22, nan_frac=0.001)
+    img[0, :4] = [np.inf, -np.inf, 0.0, -1.0]
+    d = gpu.Image.upload(img)
+    lut = gpu.Lut("Flame")
+    lut.set_lims(*lims)
+    eff = lut.lims()  # set_min/set_max clamp against each other (lut.rs:202-236)
+    table = orc.lut_build("Flame")  # built with the default lims
+    for vmin, vmax in [(0.1, 5.0), (1.0, 1.0), (2.0, 0.5)]:
+        got = gpu.colormap(d, lut, vmin=vmin, vmax=vmax, channels=3)
+        want = orc.make_raw_image(img, vmin, vmax, table, lims=eff, channels=3)
+        assert np.array_equal(got, want), (lims, vmin, vmax, int((got != want).sum()))
+
+
+def test_flip_and_nan_colour(gpu, orc):
+    img = np.array([[0.0, 1.0], [np.nan, 0.5]], np.float32)
+    d = gpu.Image.upload(img)
+    lut = gpu.Lut("Grey")
+    out = gpu.colormap(d, lut, vmin=0.0, vmax=1.0, channels=3)
+    # row 0 of the output is the last input row (image.rs:128); NaN -> index 0 -> lut[0]
+    assert out[0, 0].tolist() == [0, 0, 0] and out[0, 1].tolist() == [127, 127, 127]
+    assert out[1, 0].tolist() == [0, 0, 0] and out[1, 1].tolist() == [255, 255, 255]
+    noflip = gpu.colormap(d, lut, vmin=0.0, vmax=1.0, channels=3, flip_y=False)
+    assert np.array_equal(noflip, out[::-1])
+    rgba = gpu.colormap(d, lut, vmin=0.0, vmax=1.0, channels=4)
+    assert np.all(rgba[..., 3] == 255) and np.array_equal(rgba[..., :3], out)
+
+
+def test_all_nan_image_is_an_error(gpu):
+    d = gpu.Image.upload(np.full((4, 4), np.nan, np.float32))
+    mn, mx = d.vmin_vmax()
+    assert np.isnan(mn) and np.isnan(mx)  # lims.rs:108-124
+    with pytest.raises(gpu.AflakError) as ei:
+        gpu.colormap(d, gpu.Lut("Grey"))
+    assert "vmin, vmax not set" in ei.value.message  # image.rs:46-48
+
+
+def test_custom_gradient_golden_through_the_kernel(gpu):
+    """The reference's golden colours (lut.rs:292-343) reproduced by the device kernel, one pixel each."""
+    lut = gpu.Lut([(0.0, (0, 0, 255)), (0.5, (255, 255, 255)), (1.0, (255, 0, 0))])
+    pts = np.array([[0.0, 1.0, 0.5, 0.25]], np.float32)
+    out = gpu.colormap(gpu.Image.upload(pts), lut, vmin=0.0, vmax=1.0, channels=3, flip_y=False)
+    assert out[0].tolist() == [[0, 0, 255], [255, 0, 0], [254, 254, 255], [127, 127, 255]]
+    lut2 = gpu.Lut([(0.0, (0, 0, 0)), (1.0, (255, 255, 255))])
+    lut2.set_lims(0.2, 0.5, 0.9)
+    pts = np.array([[0.0, 0.1, 0.2, 0.55, 0.9, 0.95, 1.0]], np.float32)
+    out = gpu.colormap(gpu.Image.upload(pts), lut2, vmin=0.0, vmax=1.0, channels=3, flip_y=False)
+    assert out[0, :, 0].tolist() == [0, 0, 0, 127, 255, 255, 255]
+
+
+def test_make_raw_image_rgb(gpu, orc):
+    """3-channel image, one LUT and one (vmin, vmax) per channel (image.rs:51-84)."""
+    rng = np.random.default_rng(23)
+    img = rng.random((3, 45, 52)).astype(np.float32)
+    img[1, 3, 3] = np.nan
+    names = ["Red", "Green", "Blue"]
+    luts = [gpu.Lut(n) for n in names]
+    luts[1].set_lims(0.1, 0.4, 0.8)
+    tables = np.stack([orc.lut_build(n) for n in names])
+    lims3 = [l.lims() for l in luts]
+    vmin3, vmax3 = [0.0, 0.1, 0.2], [1.0, 0.9, 0.7]
+    for ch in (3, 4):
+        got = gpu.colormap_rgb(gpu.Image.upload(img), luts, vmin3, vmax3, channels=ch)
+        want = orc.make_raw_image_rgb(img, vmin3, vmax3, tables, lims3, channels=ch)
+        assert np.array_equal(got, want), int((got != want).sum())
+
+
+def test_fused_chain_matches_unfused_operators(gpu, orc):
+    """BASELINE config 4 chain: logscale -> rescale to 0..65535 -> tone curve -> colour LUT, fused into the colour-map
+    kernel, against the same chain run operator by operator on the device and against the oracle."""
+    img = lognormal((128, 160), 24)
+    d = gpu.Image.upload(img)
+    vmin, vmax = gpu.call("image_min_max", d)
+    a = 1000.0
+    tone = orc.create_curve([(0.0, 0.0), (0.4, 0.7), (1.0, 1.0)])
+    lut = gpu.Lut("Flame")
+    lut.set_lims(0.05, 0.4, 0.95)
+    # unfused on the device: three operators materialise f32 images, then the plain colour map
+    ls = gpu.call("convert_to_logscale", d, a, float(vmin), float(vmax))
+    lmax = np.float32(np.log(np.float32(a) + np.float32(1.0)) / np.log(np.float32(a)))
+    nmin, nmax = 0.0, float(lmax / np.float32(65535.0))  # normalize_image so that the result spans 0..65535
+    nm = gpu.call("normalize_image", ls, nmin, nmax)
+    tc = gpu.call("apply_tone_curve", nm, gpu.ToneCurve(tone))
+    unfused = gpu.colormap(tc, lut, vmin=0.0, vmax=65535.0, channels=4)
+    chain = {"logscale_a": a, "logscale_vmin": float(vmin), "logscale_vmax": float(vmax), "normalize_min": nmin,
+             "normalize_max": nmax, "tone_table": tone}
+    fused = gpu.colormap(d, lut, vmin=0.0, vmax=65535.0, channels=4, chain=chain)
+    assert np.array_equal(fused, unfused), int((fused != unfused).sum())
+    # oracle: same chain on the CPU; libm's logf may differ from CUDA's in the last bit, which can move a pixel by one
+    # table entry -> allow a channel difference of at most 1 on at most 0.1 % of the pixels
+    o = orc.convert_to_logscale(img, a, vmin, vmax)
+    o = ((o - np.float32(nmin)) / (np.float32(nmax) - np.float32(nmin))).astype(np.float32)
+    o = orc.apply_tone_curve(o, tone)
+    want = orc.make_raw_image(o, 0.0, 65535.0, orc.lut_build("Flame"), lims=lut.lims(), channels=4)
+    diff = np.abs(fused.astype(np.int32) - want.astype(np.int32))
+    assert diff.max() <= 2 and (diff.max(axis=2) > 0).mean() < 1e-3, (diff.max(), (diff.max(axis=2) > 0).mean())
+
+
+def test_colormap_device_buffer(gpu, orc):
+    """The headless stand-in for the GL texture: bytes written to a caller-provided device buffer."""
+    img = lognormal((40, 64), 25)
+    d = gpu.Image.upload(img)
+    out = gpu.Image.alloc((40, 64))  # 40*64*4 bytes = RGBA8
+    lut = gpu.Lut("Yellowy")
+    gpu.colormap_device(d, lut, 0.2, 4.0, out.device_ptr, channels=4)
+    rgba = out.download().view(np.uint8).reshape(40, 64, 4)
+    want = orc.make_raw_image(img, 0.2, 4.0, orc.lut_build("Yellowy"), channels=4)
+    assert np.array_equal(rgba, want)
