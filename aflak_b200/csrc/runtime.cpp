@@ -1,5 +1,6 @@
 // runtime.cpp -- execution context, device-resident image handles and the IOValue model.
 // Reference citations are relative to /root/reference/src/.
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -9,6 +10,8 @@
 #include "host.h"
 
 namespace afk {
+
+bool trace_enabled();
 
 // ---- errors ------------------------------------------------------------------------------------------
 std::string fmt(const char *f, ...) {
@@ -49,6 +52,12 @@ afk_status fail(const Error &e) {
 static std::mutex g_dev_mu;
 static int g_sm_count[16] = {0};
 static bool g_pool_configured[16] = {false};
+// Cubes get a memory pool of their own.  In the default pool the small stream-ordered allocations of the operators
+// (2-D results, split-K partials, flags) carve pieces out of a freed 16 GB block, and the next cube upload then makes
+// the driver stitch a new 16 GB virtual range together page by page: measured 100-500 ms per cudaMallocAsync on B200
+// (profiles/r1_e2e_alloc_trace.txt) against 0.01 ms for an exact-fit reuse.
+static cudaMemPool_t g_big_pool[16] = {nullptr};
+constexpr size_t kBigAllocBytes = (size_t)32 << 20;
 
 int sm_count(int device) {
     if (device < 0 || device >= 16) return 148;
@@ -68,6 +77,13 @@ static Error configure_pool(int device) {
         AFK_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
         uint64_t threshold = UINT64_MAX; // keep freed blocks cached: chained DAG nodes reuse them without cudaMalloc
         AFK_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold));
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        AFK_CUDA(cudaMemPoolCreate(&g_big_pool[device], &props));
+        AFK_CUDA(cudaMemPoolSetAttribute(g_big_pool[device], cudaMemPoolAttrReleaseThreshold, &threshold));
         g_pool_configured[device] = true;
     }
     return ok();
@@ -189,7 +205,24 @@ Error image_new(int ndim, const int64_t *shape, afk_image **out) {
     img->stream = s;
     img->bytes = (size_t)img->len() * sizeof(float);
     void *p = nullptr;
-    cudaError_t ce = cudaMallocAsync(&p, img->bytes ? img->bytes : 16, s);
+    if (trace_enabled() && img->bytes >= ((size_t)64 << 20)) {
+        cudaMemPool_t pool, cur;
+        uint64_t reserved = 0, used = 0, thr = 0;
+        cudaDeviceGetDefaultMemPool(&pool, dev);
+        cudaDeviceGetMemPool(&cur, dev);
+        if (g_big_pool[dev]) pool = g_big_pool[dev];
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved);
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used);
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        fprintf(stderr, "[afk] pool reserved %llu MiB used %llu MiB threshold %llx default==current %d\n",
+                (unsigned long long)(reserved >> 20), (unsigned long long)(used >> 20), (unsigned long long)thr, pool == cur);
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    cudaError_t ce = (img->bytes >= kBigAllocBytes && g_big_pool[dev]) ? cudaMallocFromPoolAsync(&p, img->bytes, g_big_pool[dev], s)
+                                                                       : cudaMallocAsync(&p, img->bytes ? img->bytes : 16, s);
+    if (trace_enabled() && img->bytes >= ((size_t)64 << 20))
+        fprintf(stderr, "[afk] cudaMallocAsync(%zu MiB) took %.2f ms\n", img->bytes >> 20,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     if (ce != cudaSuccess) {
         delete img;
         return cuda_error(ce, "cudaMallocAsync(image)");
@@ -231,6 +264,11 @@ Error image_mark_ready(afk_image *img, cudaStream_t stream) {
     return ok();
 }
 
+bool trace_enabled() {
+    static const bool on = getenv("AFK_TRACE") != nullptr;
+    return on;
+}
+
 static void image_destroy(afk_image *img) {
     if (img->parent) {
         afk_image_release(img->parent);
@@ -241,10 +279,14 @@ static void image_destroy(afk_image *img) {
         cudaGetDevice(&prev);
         cudaSetDevice(img->device);
         for (cudaEvent_t e : img->readers) cudaStreamWaitEvent(img->stream, e, 0);
+        const auto t0 = std::chrono::steady_clock::now();
         if (cudaFreeAsync(img->ptr, img->stream) != cudaSuccess) {
             cudaGetLastError();
             cudaFree(img->ptr);
         }
+        if (trace_enabled() && img->bytes >= ((size_t)64 << 20))
+            fprintf(stderr, "[afk] cudaFreeAsync(%zu MiB) took %.2f ms\n", img->bytes >> 20,
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
         if (prev >= 0 && prev != img->device) cudaSetDevice(prev);
     }
     for (cudaEvent_t e : img->readers) event_put(e);
@@ -362,6 +404,7 @@ afk_image *afk_image_upload(const float *host, int ndim, const int64_t *shape) {
     const size_t chunk = (size_t)256 << 20;
     const char *src = reinterpret_cast<const char *>(host);
     char *dst = reinterpret_cast<char *>(img->ptr);
+    const auto t0 = std::chrono::steady_clock::now();
     for (size_t off = 0; off < img->bytes; off += chunk) {
         size_t n = img->bytes - off < chunk ? img->bytes - off : chunk;
         cudaError_t ce = cudaMemcpyAsync(dst + off, src + off, n, cudaMemcpyHostToDevice, s);
@@ -371,6 +414,9 @@ afk_image *afk_image_upload(const float *host, int ndim, const int64_t *shape) {
             return nullptr;
         }
     }
+    if (trace_enabled() && img->bytes >= ((size_t)64 << 20))
+        fprintf(stderr, "[afk] H2D enqueue of %zu MiB took %.2f ms\n", img->bytes >> 20,
+                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     if (fail(image_mark_ready(img, s)) != AFK_OK) {
         afk_image_release(img);
         return nullptr;
