@@ -233,15 +233,21 @@ __device__ __forceinline__ float reduce_epilogue(const ReduceKArgs &a, const flo
     return 0.0f;
 }
 
-template <int VEC, bool COMP, int NW, int U, int MINB>
+template <int VEC, bool COMP, int NW, int U, int MINB, int KG>
 __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const ReduceKArgs a) {
-    constexpr int64_t TILE = (int64_t)kReduceBlock * VEC;
+    // KG k-groups of LANES threads share one pixel tile: group kg accumulates its own contiguous share of the segment's
+    // frames, the groups are then combined through shared memory in group order (second level of the split-K; used for
+    // small images, where there are far fewer pixel lanes than threads on the chip).  KG == 8: one warp per group.
+    constexpr int LANES = kReduceBlock / KG;
+    constexpr int64_t TILE = (int64_t)LANES * VEC;
     const int tid = threadIdx.x;
+    const int lane = tid % LANES, kg = tid / LANES;
     const int64_t g = blockIdx.x;
     int64_t u = g * a.q;
     const int64_t uend = min(u + a.q, a.units);
     const int64_t p_first = u / a.ktot;
     __shared__ int s_last;
+    __shared__ double2 s_comb[KG > 1 ? KG : 1][KG > 1 ? LANES * VEC : 1];
 
     float mm_min = __int_as_float(0x7f800000), mm_max = __int_as_float(0xff800000);
     bool mm_any = false;
@@ -253,8 +259,9 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
         const int64_t seg_end = min(uend, tile_u0 + a.ktot);
         const int64_t r_end = r + (seg_end - u);
         const bool full = (r == 0) && (r_end == a.ktot);
-        const int64_t px = p * TILE + (int64_t)tid * VEC;
-        const bool active = px < a.n2;
+        const int64_t px = p * TILE + (int64_t)lane * VEC;
+        const bool in_image = px < a.n2;
+        const bool active = in_image && kg == 0; // the threads that own the tile's pixels after the group combine
         const float *lane_base = a.cube + px;
         const int slot = (p == p_first) ? 0 : 1;
 
@@ -266,15 +273,44 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
                 Acc<COMP> acc[VEC];
 #pragma unroll
                 for (int i = 0; i < VEC; ++i) acc_init<COMP>(acc[i]);
-                if (active)
-                    accumulate<VEC, COMP, U>(lane_base, a.n2, a.start[w] + (lo - a.woff[w]), a.start[w] + (hi - a.woff[w]), acc);
+                int64_t klo = lo, khi = hi;
+                if (KG > 1) {
+                    const int64_t c = (hi - lo + KG - 1) / KG;
+                    klo = lo + (int64_t)kg * c;
+                    khi = min(hi, klo + c);
+                }
+                if (in_image && klo < khi)
+                    accumulate<VEC, COMP, U>(lane_base, a.n2, a.start[w] + (klo - a.woff[w]), a.start[w] + (khi - a.woff[w]), acc);
+                double dv[VEC];
+                float pv[VEC];
+#pragma unroll
+                for (int i = 0; i < VEC; ++i) { dv[i] = acc_value<COMP>(acc[i]); pv[i] = acc[i].p; }
+                if (KG > 1) {
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) s_comb[kg][lane * VEC + i] = make_double2(dv[i], (double)pv[i]);
+                    __syncthreads();
+                    if (kg == 0) {
+#pragma unroll
+                        for (int i = 0; i < VEC; ++i) { dv[i] = -0.0; pv[i] = -0.0f; }
+#pragma unroll 2
+                        for (int j = 0; j < KG; ++j) {
+#pragma unroll
+                            for (int i = 0; i < VEC; ++i) {
+                                const double2 v = s_comb[j][lane * VEC + i];
+                                dv[i] += v.x;
+                                pv[i] = __fadd_rn(pv[i], (float)v.y);
+                            }
+                        }
+                    }
+                    __syncthreads(); // s_comb is reused by the next window
+                }
                 if (full) {
 #pragma unroll
-                    for (int i = 0; i < VEC; ++i) S[w][i] = finalize_sum(acc_value<COMP>(acc[i]), acc[i].p);
+                    for (int i = 0; i < VEC; ++i) S[w][i] = finalize_sum(dv[i], pv[i]);
                 } else if (active) {
-                    double2 *dst = a.partials + (((size_t)g * 2 + slot) * a.nwin + w) * TILE + (size_t)tid * VEC;
+                    double2 *dst = a.partials + (((size_t)g * 2 + slot) * a.nwin + w) * TILE + (size_t)lane * VEC;
 #pragma unroll
-                    for (int i = 0; i < VEC; ++i) dst[i] = make_double2(acc_value<COMP>(acc[i]), (double)acc[i].p);
+                    for (int i = 0; i < VEC; ++i) dst[i] = make_double2(dv[i], (double)pv[i]);
                 }
             }
         }
@@ -306,13 +342,14 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
                     float pl[VEC];
 #pragma unroll
                     for (int i = 0; i < VEC; ++i) { d[i] = -0.0; pl[i] = -0.0f; }
-                    for (int64_t gg = g_lo; gg <= g_hi; ++gg) {
+                    // group kg takes the contributing CTAs g_lo+kg, g_lo+kg+KG, ... (all of them when KG == 1)
+                    for (int64_t gg = g_lo + kg; gg <= g_hi; gg += KG) {
                         const int64_t cs = max(gg * a.q, tile_u0) - tile_u0;
                         const int64_t ce = min((gg + 1) * a.q, tile_u0 + a.ktot) - tile_u0;
                         if (max(cs, a.woff[w]) < min(ce, a.woff[w + 1])) {
                             const int sl = ((gg * a.q) / a.ktot == p) ? 0 : 1;
-                            if (active) {
-                                const double2 *src = a.partials + (((size_t)gg * 2 + sl) * a.nwin + w) * TILE + (size_t)tid * VEC;
+                            if (in_image) {
+                                const double2 *src = a.partials + (((size_t)gg * 2 + sl) * a.nwin + w) * TILE + (size_t)lane * VEC;
                                 double2 v[VEC];
 #pragma unroll
                                 for (int i = 0; i < VEC; ++i) v[i] = ld_cg(src + i);
@@ -323,6 +360,25 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
                                 }
                             }
                         }
+                    }
+                    if (KG > 1) {
+#pragma unroll
+                        for (int i = 0; i < VEC; ++i) s_comb[kg][lane * VEC + i] = make_double2(d[i], (double)pl[i]);
+                        __syncthreads();
+                        if (kg == 0) {
+#pragma unroll
+                            for (int i = 0; i < VEC; ++i) { d[i] = -0.0; pl[i] = -0.0f; }
+#pragma unroll 2
+                            for (int j = 0; j < KG; ++j) {
+#pragma unroll
+                                for (int i = 0; i < VEC; ++i) {
+                                    const double2 v = s_comb[j][lane * VEC + i];
+                                    d[i] += v.x;
+                                    pl[i] = __fadd_rn(pl[i], (float)v.y);
+                                }
+                            }
+                        }
+                        __syncthreads();
                     }
 #pragma unroll
                     for (int i = 0; i < VEC; ++i) S[w][i] = finalize_sum(d[i], pl[i]);
@@ -402,24 +458,34 @@ static float count_as_f32(int64_t n) {
 }
 
 int reduce_tune_ctas();
+int reduce_tune_kg();
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     ReducePlan pl{};
     bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0) &&
                    ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
     for (int d = 0; d < a.n_extra_out; ++d) aligned = aligned && ((reinterpret_cast<uintptr_t>(a.extra_out[d]) & 15u) == 0);
     pl.vec = aligned ? 4 : 1;
-    const int64_t tile = (int64_t)kReduceBlock * pl.vec;
+    int64_t G = (int64_t)sm_count * reduce_tune_ctas();
+    // Small images (fewer pixel tiles than half the CTAs of a full wave, e.g. MaNGA 74x74): split the spectral axis
+    // inside the CTA as well -- 8 k-groups of one warp each per 32-lane tile.  Never in sequential mode.
+    const int64_t tiles_kg1 = (a.n2 + (int64_t)kReduceBlock * pl.vec - 1) / ((int64_t)kReduceBlock * pl.vec);
+    pl.kg = (a.mode != SUM_SEQUENTIAL && tiles_kg1 * 2 < G && reduce_tune_kg()) ? kReduceKGroups : 1;
+    if (pl.kg > 1) G = (int64_t)sm_count * kReduceKgCtasPerSm; // that variant is compiled for 2 resident CTAs per SM
+    const int64_t tile = (int64_t)(kReduceBlock / pl.kg) * pl.vec;
     pl.ntiles = (a.n2 + tile - 1) / tile;
     pl.ktot = 0;
     for (int w = 0; w < a.nwin; ++w) pl.ktot += a.end[w] - a.start[w];
     pl.units = pl.ntiles * pl.ktot;
-    const int64_t G = (int64_t)sm_count * reduce_tune_ctas();
     if (a.mode == SUM_SEQUENTIAL) {
         pl.q = pl.ktot * ((pl.ntiles + G - 1) / G); // whole tiles only: never split a pixel's sum
     } else {
         int64_t q = (pl.units + G - 1) / G;
-        const int64_t qmin = pl.ktot < 8 ? pl.ktot : 8; // keep at least one 8-frame load batch per CTA
+        const int64_t want = pl.kg > 1 ? 4 * pl.kg : 8; // at least a few frames per k-group / one 8-frame batch per CTA
+        const int64_t qmin = pl.ktot < want ? pl.ktot : want;
         pl.q = q < qmin ? qmin : q;
+        // a tile with little work (template-sized windows on a small image) is not worth a cross-CTA split: the
+        // partials round trip and the arrival counter cost more than the frames
+        if (pl.kg > 1 && pl.q < pl.ktot && pl.ktot <= 32 * pl.kg) pl.q = pl.ktot;
     }
     if (pl.q < 1) pl.q = 1;
     pl.grid = (int)((pl.units + pl.q - 1) / pl.q);
@@ -437,13 +503,14 @@ static int env_int(const char *name, int dflt) {
 }
 int reduce_tune_unroll() { static int u = env_int("AFK_REDUCE_UNROLL", 8); return u == 16 ? 16 : 8; }
 int reduce_tune_ctas() { static int c = env_int("AFK_REDUCE_CTAS", kReduceCtasPerSm); return (c == 2 || c == 4) ? c : 3; }
+int reduce_tune_kg() { static int k = env_int("AFK_REDUCE_KGROUPS", 1); return k != 0; } // 0 disables the in-CTA k split
 
-template <int VEC, bool COMP, int U, int MINB>
+template <int VEC, bool COMP, int U, int MINB, int KG = 1>
 static cudaError_t reduce_dispatch_nw(const ReduceKArgs &k, int grid, cudaStream_t s) {
     switch (k.nwin) {
-    case 1: reduce_kernel<VEC, COMP, 1, U, MINB><<<grid, kReduceBlock, 0, s>>>(k); break;
-    case 2: reduce_kernel<VEC, COMP, 2, U, MINB><<<grid, kReduceBlock, 0, s>>>(k); break;
-    case 3: reduce_kernel<VEC, COMP, 3, U, MINB><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 1: reduce_kernel<VEC, COMP, 1, U, MINB, KG><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 2: reduce_kernel<VEC, COMP, 2, U, MINB, KG><<<grid, kReduceBlock, 0, s>>>(k); break;
+    case 3: reduce_kernel<VEC, COMP, 3, U, MINB, KG><<<grid, kReduceBlock, 0, s>>>(k); break;
     default: return cudaErrorInvalidValue;
     }
     AFK_COUNT_LAUNCH();
@@ -451,7 +518,8 @@ static cudaError_t reduce_dispatch_nw(const ReduceKArgs &k, int grid, cudaStream
 }
 
 template <int VEC, bool COMP>
-static cudaError_t reduce_dispatch_tune(const ReduceKArgs &k, int grid, cudaStream_t s) {
+static cudaError_t reduce_dispatch_tune(const ReduceKArgs &k, int grid, int kg, cudaStream_t s) {
+    if (kg > 1) return reduce_dispatch_nw<VEC, COMP, 8, kReduceKgCtasPerSm, kReduceKGroups>(k, grid, s);
     const int u = reduce_tune_unroll(), c = reduce_tune_ctas();
 #define AFK_TUNE(U_, C_) if (u == U_ && c == C_) return reduce_dispatch_nw<VEC, COMP, U_, C_>(k, grid, s)
     AFK_TUNE(8, 4); AFK_TUNE(8, 2); AFK_TUNE(16, 2); AFK_TUNE(16, 3);
@@ -495,8 +563,9 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
     k.partials = static_cast<double2 *>(ws.partials);
     k.counters = ws.counters;
     const bool comp = a.mode != SUM_SEQUENTIAL;
-    if (pl.vec == 4) return comp ? reduce_dispatch_tune<4, true>(k, pl.grid, s) : reduce_dispatch_tune<4, false>(k, pl.grid, s);
-    return comp ? reduce_dispatch_tune<1, true>(k, pl.grid, s) : reduce_dispatch_tune<1, false>(k, pl.grid, s);
+    if (!comp && pl.kg != 1) return cudaErrorInvalidValue;
+    if (pl.vec == 4) return comp ? reduce_dispatch_tune<4, true>(k, pl.grid, pl.kg, s) : reduce_dispatch_tune<4, false>(k, pl.grid, 1, s);
+    return comp ? reduce_dispatch_tune<1, true>(k, pl.grid, pl.kg, s) : reduce_dispatch_tune<1, false>(k, pl.grid, 1, s);
 }
 
 // ----------------------------------------------------------------------------------------------------

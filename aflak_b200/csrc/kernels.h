@@ -9,6 +9,8 @@ namespace afk {
 
 // ---- axis-0 windowed reduction (K1/K2 of DESIGN.md) -------------------------
 constexpr int kMaxWindows = 3;
+constexpr int kReduceKGroups = 8;   // k-groups (one warp each) per CTA in the small-image variant of the reduce kernel
+constexpr int kReduceKgCtasPerSm = 2; // resident CTAs per SM of that variant (<= 128 registers: no spills)
 constexpr int kMaxPeers = 8;        // GPUs of one box (NVSwitch domain) a result band can be written to
 constexpr int kReduceBlock = 256;   // threads per CTA
 constexpr int kReduceCtasPerSm = 3; // resident CTAs per SM the launch is sized for (<= 85 registers per thread)
@@ -56,6 +58,7 @@ struct ReduceWorkspace {
 
 struct ReducePlan {
     int vec;             // 4 (float4 lanes) or 1
+    int kg;              // k-groups per CTA: 1, or kReduceKGroups for small images (tile = 256/kg lanes)
     int64_t ntiles;
     int64_t ktot;
     int64_t units;       // ntiles * ktot
