@@ -107,6 +107,8 @@ _sig("afk_image_tag", C.c_char_p, _P)
 _sig("afk_image_set_tag", C.c_int, _P, C.c_char_p)
 _sig("afk_image_has_meta", C.c_int, _P)
 _sig("afk_image_set_axis", C.c_int, _P, C.c_int, C.c_char_p, C.c_char_p)
+_sig("afk_image_set_wcs_axis", C.c_int, _P, C.c_int, C.c_double, C.c_double, C.c_double)
+_sig("afk_image_pix2world", C.c_int, _P, C.c_int, C.c_float, C.POINTER(C.c_float))
 _sig("afk_image_axis_name", C.c_char_p, _P, C.c_int)
 _sig("afk_image_axis_unit", C.c_char_p, _P, C.c_int)
 _sig("afk_value_integer", _P, C.c_int64)
@@ -301,6 +303,13 @@ class Image:
 
     def set_axis(self, i, name, unit):
         lib.afk_image_set_axis(self._h, i, None if name is None else name.encode(), (unit or "").encode())
+
+    def set_wcs_axis(self, i, crval, crpix, cdelt):
+        lib.afk_image_set_wcs_axis(self._h, i, crval, crpix, cdelt)
+
+    def pix2world(self, axis, pixel):
+        w = C.c_float()
+        return w.value if lib.afk_image_pix2world(self._h, axis, pixel, C.byref(w)) else None
 
     def axis(self, i):
         return lib.afk_image_axis_name(self._h, i).decode(), lib.afk_image_axis_unit(self._h, i).decode()

@@ -1,0 +1,574 @@
+// axis0.cu -- the other per-spaxel reductions along the spectral axis: variance / stddev, the
+// max/min fold, argmax/argmin wavelength maps, centrobaric wavelength (with and without per-pixel masks) and the
+// per-pixel median.  Same access pattern as the integral (kernels.cu): a thread owns 4 consecutive spaxels and
+// streams frames with 8 independent 16-byte loads in flight; every voxel is read from HBM exactly once.
+//
+// Decomposition: grid = (pixel tiles of 256*VEC spaxels) x (ksplit chunks of the spectral range).  ksplit == 1
+// (any image with >= 2 waves of tiles) finishes in registers.  Small images split the spectral range so the chip
+// is filled; the per-chunk states go through scratch and a second tiny kernel merges them in chunk order
+// (deterministic).  Operators whose reference arithmetic is order dependent and not mergeable bit-exactly
+// (Welford, sequential sums) are never split in SUM_SEQUENTIAL mode.
+//
+// Reference citations are relative to /root/reference/src/.
+#include "kernels.h"
+
+#include <cfloat>
+#include <cstdint>
+
+namespace afk {
+
+__device__ __forceinline__ float4 a0_ld(const float4 *p) {
+    float4 r;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float a0_ld(const float *p) {
+    float r;
+    asm("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
+template <int VEC> struct A0Lane;
+template <> struct A0Lane<4> {
+    using T = float4;
+    static __device__ __forceinline__ void unpack(const float4 &v, float (&x)[4]) { x[0] = v.x; x[1] = v.y; x[2] = v.z; x[3] = v.w; }
+};
+template <> struct A0Lane<1> {
+    using T = float;
+    static __device__ __forceinline__ void unpack(const float &v, float (&x)[1]) { x[0] = v; }
+};
+
+struct Axis0K {
+    const float *cube;
+    int64_t n2, nz;
+    int64_t start, end; // frames [start, end)
+    int64_t chunk;      // frames per k-chunk
+    int ksplit;
+    int is_min;
+    int64_t r1, r2;     // index offsets of the two arg maps
+    int out2_kind;      // 0 none, 1 max/min fold, 2 second arg map (offset r2)
+    int sqrt_out;       // stddev
+    int use_wcs;
+    double crval, crpix, cdelt;
+    const float *mask_lo, *mask_hi;
+    float *out, *out2;
+    void *partials;     // State[ksplit][n2]
+    unsigned *flag;     // set to 1 where the reference would panic (mask range outside the cube)
+};
+
+// pix2world on one axis: linear WCS evaluated in f64, returned as f32 (fitrs WCS, unit.rs:335-342); without WCS
+// the reference falls back to the pixel index itself
+__device__ __forceinline__ float a0_world(const Axis0K &a, float pix) {
+    if (!a.use_wcs) return pix;
+    const double p1 = __dadd_rn((double)pix, __dsub_rn(1.0, a.crpix));
+    return (float)__dadd_rn(a.crval, __dmul_rn(a.cdelt, p1));
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// functors: State is a POD; init / step (frame k, strictly increasing) / merge (later chunk into earlier) / finish
+// ---------------------------------------------------------------------------------------------------------------
+
+// ndarray 0.12.1 var_axis(Axis(0), ddof = 1.0): Welford per pixel in f32, mul_add for m2 (lib.rs:1332-1338)
+struct VarSeq {
+    struct State { float mean, m2; };
+    static constexpr bool kMergeable = false;
+    static constexpr bool kNeedsFirst = false;
+    static __device__ __forceinline__ void init(State &s, const Axis0K &, int64_t, float) { s.mean = 0.0f; s.m2 = 0.0f; }
+    static __device__ __forceinline__ void step(State &s, float x, int64_t k, float wk, const Axis0K &a) {
+        (void)wk;
+        const float count = (float)(k - a.start + 1); // built by repeated +1.0 in the reference: exact below 2^24
+        const float delta = __fsub_rn(x, s.mean);
+        s.mean = __fadd_rn(s.mean, __fdiv_rn(delta, count));
+        s.m2 = __fmaf_rn(__fsub_rn(x, s.mean), delta, s.m2);
+    }
+    static __device__ __forceinline__ void merge(State &, const State &, const Axis0K &) {}
+    static __device__ __forceinline__ void finish(const State &s, const Axis0K &a, int64_t px) {
+        const float dof = __fsub_rn((float)(a.end - a.start), 1.0f);
+        float v = __fdiv_rn(s.m2, dof);
+        if (a.sqrt_out) v = __fsqrt_rn(v);
+        a.out[px] = v;
+    }
+};
+
+// default mode: f64 sums of d = x - c and d*d with c = the pixel's first frame (shifted data: no cancellation blow-up),
+// mergeable by addition; agrees with the two-pass f64 variance to ~1e-12
+struct VarComp {
+    struct State { double s1, s2; float c; };
+    static constexpr bool kMergeable = true;
+    static constexpr bool kNeedsFirst = true;
+    static __device__ __forceinline__ void init(State &s, const Axis0K &, int64_t, float first) { s.s1 = 0.0; s.s2 = 0.0; s.c = first; }
+    static __device__ __forceinline__ void step(State &s, float x, int64_t, float, const Axis0K &) {
+        const double d = (double)x - (double)s.c;
+        s.s1 += d;
+        s.s2 = fma(d, d, s.s2);
+    }
+    static __device__ __forceinline__ void merge(State &s, const State &o, const Axis0K &) { s.s1 += o.s1; s.s2 += o.s2; }
+    static __device__ __forceinline__ void finish(const State &s, const Axis0K &a, int64_t px) {
+        const double n = (double)(a.end - a.start);
+        double v = (s.s2 - s.s1 * s.s1 / n) / (n - 1.0);
+        if (v < 0.0) v = 0.0; // rounding of a constant spectrum
+        if (a.sqrt_out) v = sqrt(v);
+        a.out[px] = (float)v;
+    }
+};
+
+// run_create_argmap (lib.rs:1400-1460) and run_minmax (lib.rs:1374-1398) in one pass.
+// Arg map: strict comparison from +-Inf, first extreme wins, NaN never wins, nothing won -> 0.0.
+// Fold: acc = (acc > y) ? acc : y from -Inf (max) / (acc < y) ? acc : y from +Inf (min): a NaN frame replaces the
+// accumulator and the next frame replaces the NaN, so the fold restarts after every NaN.
+struct ArgFold {
+    struct State { float value; int idx; float fold; int reset; };
+    static constexpr bool kMergeable = true;
+    static constexpr bool kNeedsFirst = false;
+    static __device__ __forceinline__ void init(State &s, const Axis0K &a, int64_t, float) {
+        s.value = a.is_min ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+        s.idx = -1;
+        s.fold = s.value;
+        s.reset = 0;
+    }
+    static __device__ __forceinline__ void step(State &s, float x, int64_t k, float, const Axis0K &a) {
+        if (a.is_min ? (x < s.value) : (x > s.value)) { s.value = x; s.idx = (int)(k - a.start); }
+        if (x != x) s.reset = 1;
+        s.fold = (a.is_min ? (s.fold < x) : (s.fold > x)) ? s.fold : x;
+    }
+    static __device__ __forceinline__ void merge(State &s, const State &o, const Axis0K &a) {
+        if (o.idx >= 0 && (a.is_min ? (o.value < s.value) : (o.value > s.value))) { s.value = o.value; s.idx = o.idx; }
+        if (o.reset) { s.fold = o.fold; s.reset = 1; }
+        else s.fold = (a.is_min ? (s.fold < o.fold) : (s.fold > o.fold)) ? s.fold : o.fold;
+    }
+    static __device__ __forceinline__ void finish(const State &s, const Axis0K &a, int64_t px) {
+        // out = pix2world(trypix, ((k + start) as i64 + range) as f32), or that index itself (lib.rs:1437-1447)
+        a.out[px] = s.idx < 0 ? 0.0f : a0_world(a, (float)(a.start + s.idx + a.r1));
+        if (a.out2_kind == 1) a.out2[px] = s.fold;
+        else if (a.out2_kind == 2) a.out2[px] = s.idx < 0 ? 0.0f : a0_world(a, (float)(a.start + s.idx + a.r2));
+    }
+};
+
+// run_centroid (lib.rs:1466-1527): flux_sum = sum f, waveimg = sum fl(f * w_k), out = waveimg / flux_sum; all f32,
+// sequential from 0.0
+struct CentroidSeq {
+    struct State { float f, w; };
+    static constexpr bool kMergeable = false;
+    static constexpr bool kNeedsFirst = false;
+    static __device__ __forceinline__ void init(State &s, const Axis0K &, int64_t, float) { s.f = 0.0f; s.w = 0.0f; }
+    static __device__ __forceinline__ void step(State &s, float x, int64_t, float wk, const Axis0K &) {
+        s.f = __fadd_rn(s.f, x);
+        s.w = __fadd_rn(s.w, __fmul_rn(x, wk));
+    }
+    static __device__ __forceinline__ void merge(State &, const State &, const Axis0K &) {}
+    static __device__ __forceinline__ void finish(const State &s, const Axis0K &a, int64_t px) { a.out[px] = __fdiv_rn(s.w, s.f); }
+};
+
+// default mode: the product f*w_k is rounded to f32 like the reference, the two sums are accumulated in f64
+struct CentroidComp {
+    struct State { double f, w; };
+    static constexpr bool kMergeable = true;
+    static constexpr bool kNeedsFirst = false;
+    static __device__ __forceinline__ void init(State &s, const Axis0K &, int64_t, float) { s.f = 0.0; s.w = 0.0; }
+    static __device__ __forceinline__ void step(State &s, float x, int64_t, float wk, const Axis0K &) {
+        s.f += (double)x;
+        s.w += (double)x * (double)wk;
+    }
+    static __device__ __forceinline__ void merge(State &s, const State &o, const Axis0K &) { s.f += o.f; s.w += o.w; }
+    static __device__ __forceinline__ void finish(const State &s, const Axis0K &a, int64_t px) { a.out[px] = (float)(s.w / s.f); }
+};
+
+template <class F, int VEC, int U, bool WAVE>
+__device__ __forceinline__ void a0_batch(const char *&ptr, size_t stride, int64_t &k, typename F::State (&st)[VEC], const Axis0K &a) {
+    using V = typename A0Lane<VEC>::T;
+    V x[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) x[j] = a0_ld(reinterpret_cast<const V *>(ptr + (size_t)j * stride));
+    ptr += (size_t)U * stride;
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+        float e[VEC];
+        A0Lane<VEC>::unpack(x[j], e);
+        const float wk = WAVE ? a0_world(a, (float)(k + j)) : 0.0f;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) F::step(st[i], e[i], k + j, wk, a);
+    }
+    k += U;
+}
+
+template <class F, int VEC, int U, bool WAVE>
+__global__ void __launch_bounds__(256, 2) axis0_kernel(const Axis0K a) {
+    const int64_t px = ((int64_t)blockIdx.x * 256 + threadIdx.x) * VEC;
+    if (px >= a.n2) return;
+    const int kc = blockIdx.y;
+    int64_t k = a.start + (int64_t)kc * a.chunk;
+    const int64_t kend = min(a.end, k + a.chunk);
+    typename F::State st[VEC];
+    {
+        float first[VEC];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) first[i] = 0.0f;
+        if (F::kNeedsFirst) {
+            typename A0Lane<VEC>::T v = a0_ld(reinterpret_cast<const typename A0Lane<VEC>::T *>(a.cube + a.start * a.n2 + px));
+            A0Lane<VEC>::unpack(v, first);
+        }
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) F::init(st[i], a, px + i, first[i]);
+    }
+    const size_t stride = (size_t)a.n2 * sizeof(float);
+    const char *ptr = reinterpret_cast<const char *>(a.cube + px) + (size_t)k * stride;
+    while (kend - k >= U) a0_batch<F, VEC, U, WAVE>(ptr, stride, k, st, a);
+    if (U > 4 && kend - k >= 4) a0_batch<F, VEC, 4, WAVE>(ptr, stride, k, st, a);
+    if (U > 2 && kend - k >= 2) a0_batch<F, VEC, 2, WAVE>(ptr, stride, k, st, a);
+    while (kend - k >= 1) a0_batch<F, VEC, 1, WAVE>(ptr, stride, k, st, a);
+    if (a.ksplit == 1) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) F::finish(st[i], a, px + i);
+    } else {
+        typename F::State *dst = static_cast<typename F::State *>(a.partials) + (size_t)kc * a.n2 + px;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) dst[i] = st[i];
+    }
+}
+
+template <class F> __global__ void __launch_bounds__(256) axis0_merge_kernel(const Axis0K a) {
+    const int64_t px = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (px >= a.n2) return;
+    const typename F::State *src = static_cast<const typename F::State *>(a.partials) + px;
+    typename F::State st = src[0];
+    for (int c = 1; c < a.ksplit; ++c) F::merge(st, src[(size_t)c * a.n2], a);
+    F::finish(st, a, px);
+}
+
+// run_centroid_with_mask (lib.rs:1529-1582): per-pixel range [start_mask as usize, end_mask as usize), sequential f32
+// sums, wavelength from pix2world(2, k).  slice_axis panics when start > end or end > nz: flagged, never read.
+template <bool COMP> __global__ void __launch_bounds__(256) centroid_mask_kernel(const Axis0K a) {
+    const int64_t px = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (px >= a.n2) return;
+    auto as_usize = [](float f) -> int64_t { // Rust `as usize`: truncate, saturate, NaN -> 0
+        if (!(f > 0.0f)) return 0;
+        if (f >= 9.2233720368547758e18f) return INT64_MAX;
+        return (int64_t)f;
+    };
+    const int64_t lo = as_usize(a.mask_lo[px]), hi = as_usize(a.mask_hi[px]);
+    if (lo > hi || hi > a.nz) {
+        atomicMax(a.flag, 1u);
+        a.out[px] = 0.0f;
+        return;
+    }
+    const float *p = a.cube + px;
+    if (COMP) {
+        double f = 0.0, w = 0.0;
+        for (int64_t k = lo; k < hi; ++k) {
+            const float x = a0_ld(p + k * a.n2);
+            f += (double)x;
+            w += (double)x * (double)a0_world(a, (float)k);
+        }
+        a.out[px] = (float)(w / f);
+    } else {
+        float f = 0.0f, w = 0.0f;
+        for (int64_t k = lo; k < hi; ++k) {
+            const float x = a0_ld(p + k * a.n2);
+            f = __fadd_rn(f, x);
+            w = __fadd_rn(w, __fmul_rn(x, a0_world(a, (float)k)));
+        }
+        a.out[px] = __fdiv_rn(w, f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// run_median (lib.rs:1340-1372): per-pixel median of n = end - start frames; n odd -> middle element, n even ->
+// fl((v[n/2] + v[n/2-1]) / 2).  The reference sorts with partial_cmp().unwrap(): it panics if any value is NaN.
+//
+// One CTA owns P consecutive spaxels.  Their n x P values are staged once into shared memory with cp.async
+// (thousands of 4-byte copies in flight per CTA, no registers held), transposed on the way in to [P][npad] so that a
+// spaxel's spectrum is contiguous (npad = n rounded up to 32/P mod 32 words: the staging stores and the select loads are
+// both bank-conflict free).  Each spaxel is then solved by one warp with a 4-pass radix select (8-bit digits,
+// warp-aggregated shared-memory histogram) over order-preserving integer keys.  HBM traffic is exactly one read of
+// the sub-cube.
+// ---------------------------------------------------------------------------------------------------------------
+struct MedianK {
+    const float *cube;
+    int64_t n2;
+    int64_t start, n;
+    int P;          // spaxels per CTA: power of two <= 32
+    int npad;       // words per staged spectrum
+    float *out;
+    unsigned *flag; // 1: NaN present (reference panics)
+};
+
+__device__ __forceinline__ unsigned med_key(float f) {
+    const unsigned b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float med_unkey(unsigned k) {
+    const unsigned b = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
+    return __uint_as_float(b);
+}
+
+// One radix-select digit step shared by both median kernels: given the 256-bin histogram of the candidates' current
+// digit, find the bin holding rank kth (0-based among the candidates), return it and make kth relative to that bin.
+__device__ __forceinline__ unsigned med_pick_digit(const unsigned *hist, int64_t &kth, int lane) {
+    // lane l owns bins [8l, 8l+8); exclusive scan of the lane totals
+    unsigned c[8], tot = 0u;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { c[j] = hist[lane * 8 + j]; tot += c[j]; }
+    unsigned incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    unsigned excl = incl - tot;
+    int digit = -1;
+    unsigned below = 0u;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (digit < 0 && kth < (int64_t)(excl + c[j])) { digit = lane * 8 + j; below = excl; }
+        excl += c[j];
+    }
+    // cumulative counts are monotonic: the lowest lane that found a bin has the first bin crossing kth
+    const unsigned ballot = __ballot_sync(0xffffffffu, digit >= 0);
+    const int src = __ffs(ballot) - 1;
+    digit = __shfl_sync(0xffffffffu, digit, src);
+    below = __shfl_sync(0xffffffffu, below, src);
+    kth -= below;
+    return (unsigned)digit;
+}
+
+// histogram update for one candidate per lane, aggregated over the lanes that hit the same bin
+__device__ __forceinline__ void med_hist_add(unsigned *hist, bool act, unsigned digit, int lane) {
+    const unsigned amask = __ballot_sync(0xffffffffu, act);
+    if (act) {
+        const unsigned peers = __match_any_sync(amask, digit);
+        if (lane == __ffs(peers) - 1) atomicAdd(&hist[digit], (unsigned)__popc(peers));
+    }
+}
+
+// k-th smallest (0-based) of the n contiguous keys, solved by one warp; hist = 256 words of shared memory
+__device__ unsigned med_select_warp(const unsigned *keys, int64_t n, int64_t kth, unsigned *hist, int lane) {
+    unsigned prefix = 0u, mask = 0u;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int b = lane; b < 256; b += 32) hist[b] = 0u;
+        __syncwarp();
+        for (int64_t base = 0; base < n; base += 32) {
+            const int64_t i = base + lane;
+            const unsigned key = i < n ? keys[i] : 0u;
+            med_hist_add(hist, i < n && (key & mask) == prefix, (key >> shift) & 255u, lane);
+        }
+        __syncwarp();
+        const unsigned digit = med_pick_digit(hist, kth, lane);
+        prefix |= digit << shift;
+        mask |= 255u << shift;
+        __syncwarp();
+    }
+    return prefix;
+}
+
+__global__ void __launch_bounds__(256) median_kernel(const MedianK a) {
+    extern __shared__ __align__(16) unsigned s_keys[]; // [P][npad] staged keys, then 8 x 256 histogram words
+    const int P = a.P, npad = a.npad;
+    const int64_t px0 = (int64_t)blockIdx.x * P;
+    unsigned *hist = s_keys + (size_t)P * npad;
+    const int tid = threadIdx.x;
+    const int64_t total = a.n * P;
+    for (int64_t i = tid; i < total; i += 256) {
+        const int64_t k = i / P;
+        const int j = (int)(i - k * P);
+        if (px0 + j < a.n2) {
+            const float *src = a.cube + (a.start + k) * a.n2 + px0 + j;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(s_keys + (size_t)j * npad + k);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31;
+    unsigned nan = 0u;
+    for (int j = warp; j < P; j += 8) {
+        const int64_t px = px0 + j;
+        if (px >= a.n2) continue; // warp-uniform
+        unsigned *keys = s_keys + (size_t)j * npad;
+        for (int64_t i = lane; i < a.n; i += 32) {
+            const float f = __uint_as_float(keys[i]);
+            if (f != f) nan = 1u;
+            keys[i] = med_key(f);
+        }
+        __syncwarp();
+        float r;
+        if (a.n & 1) {
+            r = med_unkey(med_select_warp(keys, a.n, (a.n - 1) / 2, hist + warp * 256, lane));
+        } else {
+            const float hi = med_unkey(med_select_warp(keys, a.n, a.n / 2, hist + warp * 256, lane));
+            const float lo = med_unkey(med_select_warp(keys, a.n, a.n / 2 - 1, hist + warp * 256, lane));
+            r = __fdiv_rn(__fadd_rn(hi, lo), 2.0f);
+        }
+        if (lane == 0) a.out[px] = r;
+    }
+    if (nan && a.n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
+}
+
+// Long ranges that do not fit in shared memory even for one spaxel per CTA: the same radix select with the keys
+// re-read from global memory on every pass (L2 catches the re-reads of a single spaxel column).
+__global__ void __launch_bounds__(32) median_global_kernel(const MedianK a) {
+    __shared__ unsigned hist[256];
+    const int64_t px = blockIdx.x;
+    const int lane = threadIdx.x;
+    const float *col = a.cube + a.start * a.n2 + px;
+    unsigned nan = 0u;
+    auto select = [&](int64_t kth) -> unsigned {
+        unsigned prefix = 0u, mask = 0u;
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            for (int b = lane; b < 256; b += 32) hist[b] = 0u;
+            __syncwarp();
+            for (int64_t base = 0; base < a.n; base += 32) {
+                const int64_t i = base + lane;
+                const float f = i < a.n ? col[i * a.n2] : 0.0f;
+                if (f != f) nan = 1u;
+                const unsigned key = med_key(f);
+                med_hist_add(hist, i < a.n && (key & mask) == prefix, (key >> shift) & 255u, lane);
+            }
+            __syncwarp();
+            const unsigned digit = med_pick_digit(hist, kth, lane);
+            prefix |= digit << shift;
+            mask |= 255u << shift;
+            __syncwarp();
+        }
+        return prefix;
+    };
+    float r;
+    if (a.n & 1) r = med_unkey(select((a.n - 1) / 2));
+    else {
+        const float hi = med_unkey(select(a.n / 2)), lo = med_unkey(select(a.n / 2 - 1));
+        r = __fdiv_rn(__fadd_rn(hi, lo), 2.0f);
+    }
+    if (nan && a.n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
+    if (lane == 0) a.out[px] = r;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------
+static size_t a0_state_bytes(int op, int mode) {
+    switch (op) {
+    case A0_VARIANCE: case A0_STDDEV: return mode == SUM_SEQUENTIAL ? sizeof(VarSeq::State) : sizeof(VarComp::State);
+    case A0_ARGFOLD: return sizeof(ArgFold::State);
+    case A0_CENTROID: return mode == SUM_SEQUENTIAL ? sizeof(CentroidSeq::State) : sizeof(CentroidComp::State);
+    }
+    return 0;
+}
+
+Axis0Plan axis0_plan(const Axis0Args &a, int sm_count) {
+    Axis0Plan pl{};
+    const bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0);
+    pl.vec = aligned ? 4 : 1;
+    pl.ntiles = (a.n2 + 256 * pl.vec - 1) / (256 * pl.vec);
+    const int64_t n = a.end - a.start;
+    const bool mergeable = a.op == A0_ARGFOLD || a.mode != SUM_SEQUENTIAL;
+    pl.ksplit = 1;
+    const int64_t want = 2 * (int64_t)sm_count;
+    if (mergeable && pl.ntiles < want && n >= 32) {
+        int64_t ks = (want + pl.ntiles - 1) / pl.ntiles;
+        const int64_t max_ks = n / 16; // at least 16 frames per chunk
+        if (ks > max_ks) ks = max_ks;
+        if (ks > 1024) ks = 1024;
+        if (ks > 1) pl.ksplit = (int)ks;
+    }
+    pl.chunk = (n + pl.ksplit - 1) / pl.ksplit;
+    pl.ksplit = (int)((n + pl.chunk - 1) / pl.chunk);
+    pl.partial_bytes = pl.ksplit > 1 ? (size_t)pl.ksplit * (size_t)a.n2 * a0_state_bytes(a.op, a.mode) : 0;
+    return pl;
+}
+
+template <class F, bool WAVE> static void a0_go(const Axis0K &k, const Axis0Plan &pl, cudaStream_t s) {
+    const dim3 grid((unsigned)pl.ntiles, (unsigned)pl.ksplit);
+    if (pl.vec == 4) axis0_kernel<F, 4, 8, WAVE><<<grid, 256, 0, s>>>(k);
+    else axis0_kernel<F, 1, 16, WAVE><<<grid, 256, 0, s>>>(k);
+    count_launch();
+    if (pl.ksplit > 1) {
+        axis0_merge_kernel<F><<<(unsigned)((k.n2 + 255) / 256), 256, 0, s>>>(k);
+        count_launch();
+    }
+}
+
+cudaError_t axis0_launch(const Axis0Args &a, const Axis0Plan &pl, void *partials, unsigned *flag, cudaStream_t s) {
+    if (a.n2 <= 0) return cudaSuccess;
+    if (a.end <= a.start) return cudaErrorInvalidValue;
+    if (pl.ksplit > 1 && partials == nullptr) return cudaErrorInvalidValue;
+    Axis0K k{};
+    k.cube = a.cube; k.n2 = a.n2; k.nz = a.nz; k.start = a.start; k.end = a.end;
+    k.chunk = pl.chunk; k.ksplit = pl.ksplit;
+    k.is_min = a.is_min; k.r1 = a.r1; k.r2 = a.r2; k.out2_kind = a.out2_kind;
+    k.sqrt_out = a.op == A0_STDDEV;
+    k.use_wcs = a.use_wcs; k.crval = a.crval; k.crpix = a.crpix; k.cdelt = a.cdelt;
+    k.mask_lo = a.mask_lo; k.mask_hi = a.mask_hi;
+    k.out = a.out; k.out2 = a.out2; k.partials = partials; k.flag = flag;
+    const bool seq = a.mode == SUM_SEQUENTIAL;
+    switch (a.op) {
+    case A0_VARIANCE: case A0_STDDEV:
+        if (seq) a0_go<VarSeq, false>(k, pl, s); else a0_go<VarComp, false>(k, pl, s);
+        break;
+    case A0_ARGFOLD: a0_go<ArgFold, false>(k, pl, s); break;
+    case A0_CENTROID:
+        if (seq) a0_go<CentroidSeq, true>(k, pl, s); else a0_go<CentroidComp, true>(k, pl, s);
+        break;
+    case A0_CENTROID_MASK:
+        if (flag == nullptr || a.mask_lo == nullptr || a.mask_hi == nullptr) return cudaErrorInvalidValue;
+        if (seq) centroid_mask_kernel<false><<<(unsigned)((a.n2 + 255) / 256), 256, 0, s>>>(k);
+        else centroid_mask_kernel<true><<<(unsigned)((a.n2 + 255) / 256), 256, 0, s>>>(k);
+        count_launch();
+        break;
+    default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// shared memory for staged keys: 227 KB opt-in per CTA; prefer a tile that lets two CTAs share an SM, so one CTA's
+// staging overlaps the other's select
+static constexpr size_t kMedianSmemMax = 224 * 1024;
+static constexpr size_t kMedianHistBytes = 8 * 256 * sizeof(unsigned);
+
+static int median_npad(int64_t n, int P) {
+    const int want = 32 / P; // npad % 32 == 32/P: staging stores (P spaxels x 32/P frames per warp) hit 32 distinct banks
+    int64_t np = n;
+    while ((np % 32) != (want % 32)) ++np;
+    return (int)np;
+}
+
+int median_pixels_per_cta(int64_t n2, int64_t n) {
+    int fits_once = 0;
+    for (int P = 32; P >= 1; P >>= 1) {
+        const size_t bytes = (size_t)P * median_npad(n, P) * sizeof(unsigned) + kMedianHistBytes;
+        if (bytes <= kMedianSmemMax && fits_once == 0) fits_once = P;
+        if (bytes * 2 <= kMedianSmemMax + 3 * 1024) { // two resident CTAs
+            int best = P;
+            while (best > 4 && (n2 + best - 1) / best < 2 * 148) best >>= 1; // small images: more, narrower CTAs
+            return best;
+        }
+    }
+    return fits_once; // 0: not even one spaxel fits -> global variant
+}
+
+cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s) {
+    if (n2 <= 0) return cudaSuccess;
+    const int64_t n = end - start;
+    if (n < 1 || flag == nullptr) return cudaErrorInvalidValue;
+    MedianK k{cube, n2, start, n, 0, 0, out, flag};
+    const int P = n > (int64_t)(kMedianSmemMax / sizeof(unsigned)) ? 0 : median_pixels_per_cta(n2, n);
+    if (P == 0) {
+        median_global_kernel<<<(unsigned)n2, 32, 0, s>>>(k);
+        count_launch();
+        return cudaGetLastError();
+    }
+    k.P = P;
+    k.npad = median_npad(n, P);
+    const size_t smem = (size_t)P * k.npad * sizeof(unsigned) + kMedianHistBytes;
+    static bool attr_set[16] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 16 && !attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(median_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMedianSmemMax);
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+    }
+    median_kernel<<<(unsigned)((n2 + P - 1) / P), 256, smem, s>>>(k);
+    count_launch();
+    return cudaGetLastError();
+}
+
+} // namespace afk

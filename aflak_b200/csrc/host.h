@@ -145,6 +145,9 @@ Error op_min_max(const afk_image *img, float *mn, float *mx, bool *any);
 std::string unit_mul(bool has_a, const std::string &a, bool has_b, const std::string &b, bool *has_out);
 std::string unit_div(bool has_a, const std::string &a, bool has_b, const std::string &b, bool *has_out);
 
+// WcsArray::pix2world (unit.rs:335-342) on the linear per-axis WCS carried in the meta blob
+float image_pix2world(const afk_image *img, int axis, float pixel);
+
 void registry_init();
 
 } // namespace afk

@@ -18,6 +18,7 @@ namespace afk {
 static std::atomic<uint64_t> g_launches{0};
 uint64_t launch_count() { return g_launches.load(); }
 #define AFK_COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
+void count_launch() { AFK_COUNT_LAUNCH(); }
 
 // ----------------------------------------------------------------------------------------------------
 // load helpers: streaming 16-byte loads that do not allocate in L1 (every voxel is touched once)

@@ -74,6 +74,45 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &plan, const Red
 // stream-ordered wait until flags[i] >= epoch for i < n (n <= 32); *err gets 1+i of a flag that timed out
 cudaError_t gather_wait_launch(const unsigned *flags, int n, unsigned epoch, double timeout_s, unsigned *err, cudaStream_t s);
 
+// ---- other axis-0 reductions (axis0.cu) --------------------------------------------------------
+enum Axis0Op : int {
+    A0_VARIANCE = 0,      // var_axis(Axis(0), 1.0)                         lib.rs:1332-1334
+    A0_STDDEV = 1,        // std_axis(Axis(0), 1.0)                         lib.rs:1336-1338
+    A0_ARGFOLD = 2,       // run_create_argmap + run_minmax in one pass     lib.rs:1374-1464
+    A0_CENTROID = 3,      // run_centroid                                   lib.rs:1466-1527
+    A0_CENTROID_MASK = 4, // run_centroid_with_mask                         lib.rs:1529-1582
+    A0_MEDIAN_OP = 5,     // run_median (median_launch)                     lib.rs:1340-1372
+};
+
+struct Axis0Args {
+    int op;
+    int mode;          // SumMode: sequential = the reference's own f32 order (bit-exact), default = f64 accumulators
+    const float *cube; // [nz][n2]
+    int64_t n2, nz;
+    int64_t start, end;
+    int is_min;
+    int64_t r1, r2;    // A0_ARGFOLD: offsets added to the winning index for out / out2
+    int out2_kind;     // A0_ARGFOLD: 0 none, 1 max/min fold (run_minmax), 2 second arg map
+    int use_wcs;       // world(p) = (f32)(crval + cdelt * (p + 1 - crpix)) in f64; otherwise world(p) = p
+    double crval, crpix, cdelt;
+    const float *mask_lo, *mask_hi; // A0_CENTROID_MASK: per-pixel [start, end)
+    float *out, *out2;
+};
+
+struct Axis0Plan {
+    int vec;
+    int64_t ntiles;
+    int ksplit;
+    int64_t chunk;
+    size_t partial_bytes;
+};
+Axis0Plan axis0_plan(const Axis0Args &a, int sm_count);
+// partials: >= plan.partial_bytes of device scratch (may be nullptr when 0); flag: one zero-initialised word that is
+// set where the reference would panic (A0_CENTROID_MASK ranges outside the cube)
+cudaError_t axis0_launch(const Axis0Args &a, const Axis0Plan &plan, void *partials, unsigned *flag, cudaStream_t s);
+// run_median (lib.rs:1340-1372); *flag is set when a NaN is met (the reference panics)
+cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s);
+
 // ---- elementwise (K3) --------------------------------------------------------
 enum MapOp : int {
     MAP_LINCOMP = 0,    // out = fl(fl(u*a) + fl(v*b))                     lib.rs:1288-1297
@@ -142,5 +181,6 @@ cudaError_t gen_cube_launch(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, i
 
 // number of kernel launches issued by this library since load (bench.py's gpu_launches)
 uint64_t launch_count();
+void count_launch(); // for the other translation units
 
 } // namespace afk

@@ -216,8 +216,15 @@ static void meta_make_slice(const afk_image *src, afk_image *dst) {
     dst->meta.has_meta = src->meta.has_meta;
     if (src->meta.has_meta) {
         for (int i = 0; i < 4; ++i) dst->meta.axes[i] = (i < dst->ndim) ? src->meta.axes[i] : AxisMeta();
-        size_t per_axis = src->ndim > 0 ? src->meta.wcs.size() / (size_t)(src->ndim) : 0;
-        dst->meta.wcs.assign(src->meta.wcs.begin(), src->meta.wcs.begin() + std::min(src->meta.wcs.size(), per_axis * (size_t)dst->ndim));
+        // wcs.slice(&[0..ndim]) then transform(i, 0.0, 1.0): the kept FITS axes are unchanged, the dropped ones go
+        // back to the identity {CRVAL 0, CRPIX 1, CDELT 1}
+        dst->meta.wcs = src->meta.wcs;
+        if (dst->meta.wcs.size() == 12)
+            for (int i = dst->ndim; i < 4; ++i) {
+                dst->meta.wcs[3 * i + 0] = 0.0;
+                dst->meta.wcs[3 * i + 1] = 1.0;
+                dst->meta.wcs[3 * i + 2] = 1.0;
+            }
     }
 }
 
@@ -830,6 +837,310 @@ AFK_OP(op_down_sampling) {
 }
 
 // =============================================================================================================
+// Other axis-0 reductions: variance, stddev, median, arg maps, centrobaric wavelength
+// =============================================================================================================
+
+// linear WCS of one FITS axis: meta.wcs holds {CRVAL, CRPIX, CDELT} for each of the 4 axes (fitrs WCS restated as
+// the per-axis linear transform; parity unpinned); an image whose header carried no WCS keys has an empty
+// blob and maps a pixel to itself
+static bool wcs_axis(const afk_image *img, int axis, double *crval, double *crpix, double *cdelt) {
+    if (!img->meta.has_meta || img->meta.wcs.size() != 12 || axis < 0 || axis > 3) return false;
+    *crval = img->meta.wcs[3 * axis + 0];
+    *crpix = img->meta.wcs[3 * axis + 1];
+    *cdelt = img->meta.wcs[3 * axis + 2];
+    return true;
+}
+
+float image_pix2world(const afk_image *img, int axis, float pixel) { // unit.rs:335-342
+    double crval, crpix, cdelt;
+    if (!wcs_axis(img, axis, &crval, &crpix, &cdelt)) return pixel;
+    return (float)(crval + cdelt * ((double)pixel + (1.0 - crpix)));
+}
+
+// the axis run_create_argmap / run_centroid convert indices with (lib.rs:1413-1421): the last axis named "WAVE" whose
+// unit is Angstrom / Ang, else axis 0 (and then no unit on the result)
+static int wave_axis(const afk_image *img, bool *found) {
+    int trypix = 0;
+    *found = false;
+    for (int n = 0; n < 4; ++n) {
+        const AxisMeta &a = img->meta.axes[n];
+        if (a.name == "WAVE" && (a.unit == "Angstrom" || a.unit == "Ang")) {
+            trypix = n;
+            *found = true;
+        }
+    }
+    return trypix;
+}
+
+static Error op_axis0(const afk_image *cube, Axis0Args a, const afk_image *m_lo, const afk_image *m_hi, afk_image **out,
+                      afk_image **out2, const char *panic_message) {
+    cudaStream_t s;
+    int dev;
+    if (Error e = current_stream(&s, &dev)) return e;
+    if (Error e = same_device(cube, dev)) return e;
+    afk_image *o = nullptr, *o2 = nullptr;
+    if (Error e = image_new(cube->ndim - 1, cube->shape + 1, &o)) return e;
+    if (out2) {
+        if (Error e = image_new(cube->ndim - 1, cube->shape + 1, &o2)) {
+            afk_image_release(o);
+            return e;
+        }
+    }
+    a.mode = tls().sum_mode;
+    a.cube = cube->ptr;
+    a.n2 = cube->frame_len();
+    a.nz = cube->shape[0];
+    a.mask_lo = m_lo ? m_lo->ptr : nullptr;
+    a.mask_hi = m_hi ? m_hi->ptr : nullptr;
+    a.out = o->ptr;
+    a.out2 = o2 ? o2->ptr : nullptr;
+    Error err = ok();
+    void *partials = nullptr;
+    unsigned *flag = nullptr;
+    do {
+        if (a.n2 <= 0) break;
+        if ((err = image_wait(cube, s))) break;
+        if (m_lo && (err = image_wait(m_lo, s))) break;
+        if (m_hi && (err = image_wait(m_hi, s))) break;
+        cudaError_t ce = cudaSuccess;
+        if (a.op == A0_MEDIAN_OP) {
+            if ((err = scratch_u32(s, 1, &flag))) break;
+            ce = median_launch(a.cube, a.n2, a.start, a.end, a.out, flag, s);
+        } else {
+            Axis0Plan plan = a.op == A0_CENTROID_MASK ? Axis0Plan{1, 0, 1, 0, 0} : axis0_plan(a, sm_count(dev));
+            if (plan.partial_bytes) {
+                ce = cudaMallocAsync(&partials, plan.partial_bytes, s);
+                if (ce != cudaSuccess) {
+                    err = cuda_error(ce, "cudaMallocAsync(axis0 partials)");
+                    break;
+                }
+            }
+            if (a.op == A0_CENTROID_MASK && (err = scratch_u32(s, 1, &flag))) break;
+            ce = axis0_launch(a, plan, partials, flag, s);
+        }
+        if (ce != cudaSuccess) {
+            err = cuda_error(ce, "axis0 kernel launch");
+            break;
+        }
+        image_note_read(cube, s);
+        if (m_lo) image_note_read(m_lo, s);
+        if (m_hi) image_note_read(m_hi, s);
+        if (flag) { // the reference panics on these inputs: one 4-byte sync, like the tone-curve index check
+            unsigned h = 0;
+            ce = cudaMemcpyAsync(&h, flag, sizeof h, cudaMemcpyDeviceToHost, s);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+            if (ce != cudaSuccess) {
+                err = cuda_error(ce, "axis0 flag read-back");
+                break;
+            }
+            if (h) {
+                err = make_error(AFK_ERR_PANIC, panic_message);
+                break;
+            }
+        }
+    } while (0);
+    if (partials) cudaFreeAsync(partials, s);
+    if (flag) scratch_free(s, flag);
+    if (!err) err = image_mark_ready(o, s);
+    if (!err && o2) err = image_mark_ready(o2, s);
+    if (err) {
+        afk_image_release(o);
+        if (o2) afk_image_release(o2);
+        return err;
+    }
+    *out = o;
+    if (out2) *out2 = o2;
+    return ok();
+}
+
+static Error range_checks(const afk_image *img, int64_t start, int64_t end) {
+    Error e = try_into_unsigned("start", start);
+    if (!e) e = try_into_unsigned("end", end);
+    if (!e) e = is_sliceable_range("image", img, start, end);
+    return e;
+}
+
+// ---- variance / stddev (lib.rs:412-427, 1332-1338) ---------------------------------------------------------------
+static afk_status var_op(int op, const afk_value *const *in, size_t n_in, afk_result *out, size_t n_out) {
+    AFK_NEED_OUT(1)
+    if (!args_match(in, n_in, {AFK_T_IMAGE, AFK_T_INTEGER, AFK_T_INTEGER}, out, n_out)) return AFK_ERR_PANIC;
+    const afk_image *img = in[0]->img;
+    const int64_t start = in[1]->i, end = in[2]->i;
+    Error e = range_checks(img, start, end);
+    // ndarray 0.12.1 var_axis panics when ddof (1.0) >= the number of frames
+    if (!e && end - start < 2)
+        e = make_error(AFK_ERR_PANIC, "`ddof` needs to be strictly smaller than the length of the axis you are computing the variance/standard deviation for!");
+    afk_image *res = nullptr;
+    if (!e) {
+        Axis0Args a{};
+        a.op = op;
+        a.start = start;
+        a.end = end;
+        e = op_axis0(img, a, nullptr, nullptr, &res, nullptr, "");
+    }
+    if (e) {
+        set_err(&out[0], e);
+        return e.status;
+    }
+    meta_make_slice(img, res);
+    set_image(&out[0], res);
+    return AFK_OK;
+}
+AFK_OP(op_variance) { return var_op(A0_VARIANCE, in, n_in, out, n_out); }
+AFK_OP(op_stddev) { return var_op(A0_STDDEV, in, n_in, out, n_out); }
+
+// ---- median (lib.rs:428-435, 1340-1372) ------------------------------------------------------------------------------
+AFK_OP(op_median) {
+    AFK_NEED_OUT(1)
+    if (!args_match(in, n_in, {AFK_T_IMAGE, AFK_T_INTEGER, AFK_T_INTEGER}, out, n_out)) return AFK_ERR_PANIC;
+    const afk_image *img = in[0]->img;
+    const int64_t start = in[1]->i, end = in[2]->i;
+    Error e = range_checks(img, start, end);
+    afk_image *res = nullptr;
+    if (!e) {
+        Axis0Args a{};
+        a.op = A0_MEDIAN_OP;
+        a.start = start;
+        a.end = end;
+        // vals.sort_by(|a, b| a.partial_cmp(b).unwrap()) panics on the first NaN comparison
+        e = op_axis0(img, a, nullptr, nullptr, &res, nullptr, "called `Option::unwrap()` on a `None` value (NaN in median)");
+    }
+    if (e) {
+        set_err(&out[0], e);
+        return e.status;
+    }
+    // WcsArray::from_array(Dimensioned::new(result, Unit::None)): no meta, no unit, no tag
+    set_image(&out[0], res);
+    return AFK_OK;
+}
+
+// ---- arg maps (lib.rs:436-458, 1374-1464) -----------------------------------------------------------------------------
+// meta of the *cube* is attached unchanged to the 2-D result ("FIXME: Handle metadata" in the reference), tag kept
+static void argmap_meta(const afk_image *img, afk_image *res, bool wave_found) {
+    res->meta = img->meta;
+    res->meta.has_unit = wave_found;
+    res->meta.unit = wave_found ? "Ang" : "";
+    res->meta.homogeneous = true;
+}
+
+static afk_status argmap_op(const afk_image *img, int64_t start, int64_t end, bool is_min, bool actual, int64_t r1, int64_t r2,
+                            int out2_kind, afk_result *out) {
+    Error e = range_checks(img, start, end);
+    // image.meta().clone().unwrap() (lib.rs:1413)
+    if (!e && !img->meta.has_meta) e = make_error(AFK_ERR_PANIC, "called `Option::unwrap()` on a `None` value");
+    afk_image *res = nullptr, *res2 = nullptr;
+    bool found = false;
+    if (!e) {
+        const int trypix = wave_axis(img, &found);
+        Axis0Args a{};
+        a.op = A0_ARGFOLD;
+        a.start = start;
+        a.end = end;
+        a.is_min = is_min;
+        a.r1 = r1;
+        a.r2 = r2;
+        a.out2_kind = out2_kind;
+        a.use_wcs = actual && wcs_axis(img, trypix, &a.crval, &a.crpix, &a.cdelt);
+        e = op_axis0(img, a, nullptr, nullptr, &res, &res2, "");
+    }
+    if (e) {
+        set_err(&out[0], e);
+        set_err(&out[1], e);
+        return e.status;
+    }
+    argmap_meta(img, res, found);
+    if (out2_kind == 2) argmap_meta(img, res2, found);
+    else meta_make_slice(img, res2); // run_minmax goes through reduce_array_slice
+    set_image(&out[0], res);
+    set_image(&out[1], res2);
+    return AFK_OK;
+}
+
+AFK_OP(op_extract_argmin_max_wavelength) {
+    AFK_NEED_OUT(2)
+    if (!args_match(in, n_in, {AFK_T_IMAGE, AFK_T_INTEGER, AFK_T_INTEGER, AFK_T_BOOL}, out, n_out)) return AFK_ERR_PANIC;
+    return argmap_op(in[0]->img, in[1]->i, in[2]->i, in[3]->b, true, 0, 0, 1, out);
+}
+AFK_OP(op_peak_based_wavelength_range) {
+    AFK_NEED_OUT(2)
+    if (!args_match(in, n_in, {AFK_T_IMAGE, AFK_T_INTEGER, AFK_T_INTEGER, AFK_T_INTEGER, AFK_T_BOOL}, out, n_out)) return AFK_ERR_PANIC;
+    const int64_t range = in[3]->i;
+    return argmap_op(in[0]->img, in[1]->i, in[2]->i, in[4]->b, false, -range, range, 2, out);
+}
+
+// ---- centrobaric wavelength (lib.rs:459-479, 1466-1582) ----------------------------------------------------------------------
+AFK_OP(op_extract_centrobaric_wavelength) {
+    AFK_NEED_OUT(1)
+    if (!args_match(in, n_in, {AFK_T_IMAGE, AFK_T_INTEGER, AFK_T_INTEGER}, out, n_out)) return AFK_ERR_PANIC;
+    const afk_image *img = in[0]->img;
+    const int64_t start = in[1]->i, end = in[2]->i;
+    Error e = range_checks(img, start, end);
+    if (!e && !img->meta.has_meta) e = make_error(AFK_ERR_PANIC, "called `Option::unwrap()` on a `None` value");
+    afk_image *res = nullptr;
+    bool found = false;
+    if (!e) {
+        const int trypix = wave_axis(img, &found);
+        Axis0Args a{};
+        a.op = A0_CENTROID;
+        a.start = start;
+        a.end = end;
+        a.use_wcs = wcs_axis(img, trypix, &a.crval, &a.crpix, &a.cdelt);
+        e = op_axis0(img, a, nullptr, nullptr, &res, nullptr, "");
+    }
+    if (e) {
+        set_err(&out[0], e);
+        return e.status;
+    }
+    // &waveimg / &flux_sum (unit.rs:863-880): meta of waveimg (= the cube's), unit (u * waveunit) / u, tag dropped
+    res->meta = img->meta;
+    res->meta.has_tag = false;
+    res->meta.tag.clear();
+    bool h1;
+    const std::string u1 = unit_mul(img->meta.has_unit, img->meta.unit, found, found ? "Ang" : "", &h1);
+    res->meta.unit = unit_div(h1, u1, img->meta.has_unit, img->meta.unit, &res->meta.has_unit);
+    res->meta.homogeneous = true;
+    set_image(&out[0], res);
+    return AFK_OK;
+}
+
+AFK_OP(op_extract_centrobaric_wavelength_with_mask) {
+    AFK_NEED_OUT(1)
+    if (!args_match(in, n_in, {AFK_T_IMAGE, AFK_T_IMAGE, AFK_T_IMAGE}, out, n_out)) return AFK_ERR_PANIC;
+    const afk_image *img = in[0]->img, *lo = in[1]->img, *hi = in[2]->img;
+    Error e = ok();
+    // the reference indexes both masks with the cube's spatial index and panics on a mismatch
+    auto mask_ok = [&](const afk_image *m) {
+        if (img->ndim < 1 || m->ndim != img->ndim - 1) return false;
+        for (int i = 0; i < m->ndim; ++i)
+            if (m->shape[i] != img->shape[i + 1]) return false;
+        return true;
+    };
+    if (!mask_ok(lo) || !mask_ok(hi)) e = make_error(AFK_ERR_PANIC, "ndarray: index out of bounds (mask shape differs from the image's spatial shape)");
+    afk_image *res = nullptr;
+    if (!e) {
+        int dev = 0;
+        cudaStream_t s;
+        e = current_stream(&s, &dev);
+        if (!e) e = same_device(lo, dev);
+        if (!e) e = same_device(hi, dev);
+    }
+    if (!e) {
+        Axis0Args a{};
+        a.op = A0_CENTROID_MASK;
+        a.start = 0;
+        a.end = img->shape[0];
+        a.use_wcs = wcs_axis(img, 2, &a.crval, &a.crpix, &a.cdelt); // pix2world(2, ..) (lib.rs:1562)
+        e = op_axis0(img, a, lo, hi, &res, nullptr, "slice index out of range (start_mask > end_mask or end_mask > frame count)");
+    }
+    if (e) {
+        set_err(&out[0], e);
+        return e.status;
+    }
+    set_image(&out[0], res); // from_array(.., Unit::None)
+    return AFK_OK;
+}
+
+// =============================================================================================================
 // Registry
 // =============================================================================================================
 struct Entry {
@@ -920,6 +1231,27 @@ static void build_registry() {
         {IMG}, op_create_emission_line_map);
     add("down_sampling", "02. Make new data", "Keep every n-th pixel in x and y (decimation).", 1, 0, 0,
         {{"image", IMG, nullptr}, {"n", INT, I(1)}}, {IMG}, op_down_sampling);
+    add("variance", "07. Reduce dimension", "Sample variance (ddof = 1) of frames start..end (end exclusive).", 1, 0, 0,
+        {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}}, {IMG}, op_variance);
+    add("stddev", "07. Reduce dimension", "Sample standard deviation (ddof = 1) of frames start..end (end exclusive).", 1, 0, 0,
+        {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}}, {IMG}, op_stddev);
+    add("median", "07. Reduce dimension", "Per-pixel median of frames start..end (end exclusive).", 1, 0, 0,
+        {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}}, {IMG}, op_median);
+    add("extract_argmin_max_wavelength", "08. Reduce dimension (index)",
+        "Wavelength of the maximum (or minimum) flux of each pixel over frames start..end; second output is that flux.", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}, {"is_min", BOOL, B(false)}}, {IMG, IMG},
+        op_extract_argmin_max_wavelength);
+    add("peak_based_wavelength_range", "08. Reduce dimension (index)",
+        "Frame index of the flux peak of each pixel minus (first output) and plus (second output) range.", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}, {"range", INT, I(1)}, {"is_min", BOOL, B(false)}}, {IMG, IMG},
+        op_peak_based_wavelength_range);
+    add("extract_centrobaric_wavelength", "08. Reduce dimension (index)",
+        "Flux-weighted mean wavelength of each pixel over frames start..end: sum(f*w) / sum(f).", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}}, {IMG}, op_extract_centrobaric_wavelength);
+    add("extract_centrobaric_wavelength_with_mask", "08. Reduce dimension (index)",
+        "Flux-weighted mean wavelength of each pixel over its own frame range [start_mask, end_mask).", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"start_mask", IMG, nullptr}, {"end_mask", IMG, nullptr}}, {IMG},
+        op_extract_centrobaric_wavelength_with_mask);
     // additive entry (not in the reference registry): the `&WcsArray / &WcsArray` operator of unit.rs:863-880
     add("ratio", "06. Calculate", "Ratio of two images: u / v.", 1, 0, 0, {{"u", IMG, nullptr}, {"v", IMG, nullptr}}, {IMG}, op_ratio);
 }

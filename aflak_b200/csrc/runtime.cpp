@@ -518,6 +518,26 @@ int afk_image_set_axis(afk_image *img, int axis, const char *name, const char *u
     return AFK_OK;
 }
 
+int afk_image_set_wcs_axis(afk_image *img, int axis, double crval, double crpix, double cdelt) {
+    if (!img || axis < 0 || axis >= 4) return AFK_ERR_UNEXPECTED_INPUT;
+    img->meta.has_meta = true;
+    if (img->meta.wcs.size() != 12) {
+        img->meta.wcs.assign(12, 0.0);
+        for (int i = 0; i < 4; ++i) img->meta.wcs[3 * i + 1] = img->meta.wcs[3 * i + 2] = 1.0; // identity
+    }
+    img->meta.wcs[3 * axis + 0] = crval;
+    img->meta.wcs[3 * axis + 1] = crpix;
+    img->meta.wcs[3 * axis + 2] = cdelt;
+    return AFK_OK;
+}
+
+int afk_image_pix2world(const afk_image *img, int axis, float pixel, float *world) {
+    if (!img || !world || axis < 0 || axis >= 4) return 0;
+    if (!img->meta.has_meta) return 0; // Option::None (unit.rs:336)
+    *world = afk::image_pix2world(img, axis, pixel);
+    return 1;
+}
+
 const char *afk_image_axis_name(const afk_image *img, int axis) {
     return (img && img->meta.has_meta && axis >= 0 && axis < 4) ? img->meta.axes[axis].name.c_str() : "";
 }

@@ -112,6 +112,11 @@ int afk_image_set_tag(afk_image *img, const char *tag);
 int afk_image_has_meta(const afk_image *img);
 /* axis i of MetaWcsArray.axes (FITS order: axis 0 = NAXIS1): name/unit, "" when absent */
 int afk_image_set_axis(afk_image *img, int axis, const char *name, const char *unit);
+/* linear world coordinates of FITS axis i (MetaWcsArray.wcs, unit.rs:210-214): world = CRVAL + CDELT * (pixel + 1 - CRPIX),
+ * evaluated in f64 and returned as f32; pixel is 0-based.  Restates fitrs 0.5.0 `WCS` for axis-aligned headers. */
+int afk_image_set_wcs_axis(afk_image *img, int axis, double crval, double crpix, double cdelt);
+/* WcsArray::pix2world (unit.rs:335-342): returns 1 and writes *world, or 0 when the image carries no metadata (None) */
+int afk_image_pix2world(const afk_image *img, int axis, float pixel, float *world);
 const char *afk_image_axis_name(const afk_image *img, int axis);
 const char *afk_image_axis_unit(const afk_image *img, int axis);
 

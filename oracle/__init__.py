@@ -136,6 +136,88 @@ def middle_width(start, end):
     return m.value, w.value
 
 
+# ---- other axis-0 reductions (lib.rs:1332-1582) ----------------------------------
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _wcs(wcs):
+    """wcs = (crval, crpix, cdelt) or None -> (keep-alive array, pointer)"""
+    if wcs is None:
+        return None, None
+    w = np.asarray(wcs, dtype=np.float64)
+    return w, _dp(w)
+
+
+def _reduce_call(fn, cube, start, end, *extra):
+    cube = _f32(cube)
+    nz, n2 = _cube_dims(cube)
+    out = np.empty(cube.shape[1:], dtype=np.float32)
+    _check(fn(_fp(cube), C.c_int64(nz), C.c_int64(n2), C.c_int64(start), C.c_int64(end), *extra, _fp(out)))
+    return out
+
+
+def variance(cube, start, end):
+    return _reduce_call(lib().orc_variance, cube, start, end, C.c_int(0))
+
+
+def stddev(cube, start, end):
+    return _reduce_call(lib().orc_variance, cube, start, end, C.c_int(1))
+
+
+def variance_f64(cube, start, end):
+    cube = _f32(cube)
+    nz, n2 = _cube_dims(cube)
+    out = np.empty(cube.shape[1:], dtype=np.float64)
+    lib().orc_variance_f64(_fp(cube), C.c_int64(n2), C.c_int64(start), C.c_int64(end), _dp(out))
+    return out
+
+
+def median(cube, start, end):
+    return _reduce_call(lib().orc_median, cube, start, end)
+
+
+def minmax_fold(cube, start, end, is_min):
+    return _reduce_call(lib().orc_minmax_fold, cube, start, end, C.c_int(int(is_min)))
+
+
+def pix2world(wcs, pixel):
+    keep, p = _wcs(wcs)
+    f = lib().orc_pix2world
+    f.restype = C.c_float
+    return float(f(p, C.c_float(pixel)))
+
+
+def argmap(cube, start, end, rng, is_min, wcs=None):
+    keep, p = _wcs(wcs)
+    return _reduce_call(lib().orc_argmap, cube, start, end, C.c_int64(rng), C.c_int(int(is_min)), p)
+
+
+def centroid(cube, start, end, wcs=None):
+    keep, p = _wcs(wcs)
+    return _reduce_call(lib().orc_centroid, cube, start, end, p)
+
+
+def centroid_f64(cube, start, end, wcs=None):
+    cube = _f32(cube)
+    nz, n2 = _cube_dims(cube)
+    keep, p = _wcs(wcs)
+    out = np.empty(cube.shape[1:], dtype=np.float64)
+    lib().orc_centroid_f64(_fp(cube), C.c_int64(n2), C.c_int64(start), C.c_int64(end), p, _dp(out))
+    return out
+
+
+def centroid_mask(cube, start_mask, end_mask, wcs=None):
+    cube = _f32(cube)
+    nz, n2 = _cube_dims(cube)
+    lo, hi = _f32(start_mask), _f32(end_mask)
+    keep, p = _wcs(wcs)
+    out = np.empty(cube.shape[1:], dtype=np.float32)
+    _check(lib().orc_centroid_mask(_fp(cube), C.c_int64(nz), C.c_int64(n2), _fp(lo), _fp(hi), p, _fp(out)))
+    return out
+
+
 # ---- slicing / gather ----------------------------------------------------------
 
 def slice_one_frame(cube, frame):

@@ -162,6 +162,189 @@ void orc_sum_f64(const float *cube, int64_t n2, int64_t start, int64_t end, doub
     }
 }
 
+/* ------------------------------------------------------------------------- */
+/* Other axis-0 reductions: lib.rs:1332-1582                                   */
+/* ------------------------------------------------------------------------- */
+
+/*
+ * ndarray 0.12.1 `var_axis(Axis(0), ddof)` (called with ddof = 1.0, lib.rs:1333):
+ *   count = 0; mean = zeros; sum_sq = zeros;
+ *   for frame in axis_iter { count += 1; for each pixel { delta = x - mean; mean = mean + delta / count;
+ *                                                         sum_sq = (x - mean).mul_add(delta, sum_sq) } }
+ *   panic if ddof >= count; else sum_sq / (count - ddof)
+ * `std_axis` = var_axis(..).mapv(sqrt) (lib.rs:1337).  mul_add is a fused multiply-add.
+ */
+int orc_variance(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int take_sqrt, float *out) {
+    int rc = check_reduce_args(nz, start, end);
+    if (rc) return rc;
+    if (end - start < 2) {
+        snprintf(g_err, sizeof g_err, "`ddof` needs to be strictly smaller than the length of the axis you are computing the variance/standard deviation for!");
+        return ORC_ERR_PANIC;
+    }
+    float *mean = (float *)calloc((size_t)(n2 > 0 ? n2 : 1), sizeof(float));
+    for (int64_t i = 0; i < n2; ++i) out[i] = 0.0f; /* sum_sq */
+    float count = 0.0f;
+    for (int64_t k = start; k < end; ++k) {
+        const float *f = cube + k * n2;
+        count = count + 1.0f;
+        for (int64_t i = 0; i < n2; ++i) {
+            float delta = f[i] - mean[i];
+            mean[i] = mean[i] + delta / count;
+            out[i] = fmaf(f[i] - mean[i], delta, out[i]);
+        }
+    }
+    float dof = count - 1.0f;
+    for (int64_t i = 0; i < n2; ++i) {
+        out[i] = out[i] / dof;
+        if (take_sqrt) out[i] = sqrtf(out[i]);
+    }
+    free(mean);
+    return ORC_OK;
+}
+
+/* two-pass f64 variance (ddof = 1) of the f32 inputs: the tolerance oracle */
+void orc_variance_f64(const float *cube, int64_t n2, int64_t start, int64_t end, double *out) {
+    const double n = (double)(end - start);
+    for (int64_t i = 0; i < n2; ++i) {
+        double m = 0.0, v = 0.0;
+        for (int64_t k = start; k < end; ++k) m += (double)cube[k * n2 + i];
+        m /= n;
+        for (int64_t k = start; k < end; ++k) {
+            double d = (double)cube[k * n2 + i] - m;
+            v += d * d;
+        }
+        out[i] = v / (n - 1.0);
+    }
+}
+
+static int cmp_f32(const void *a, const void *b) {
+    float x = *(const float *)a, y = *(const float *)b;
+    return (x > y) - (x < y);
+}
+
+/* run_median, lib.rs:1340-1372: per pixel sort (partial_cmp().unwrap() panics on NaN), middle or mean of the two middles */
+int orc_median(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out) {
+    int rc = check_reduce_args(nz, start, end);
+    if (rc) return rc;
+    int64_t n = end - start;
+    float *vals = (float *)malloc((size_t)n * sizeof(float));
+    for (int64_t i = 0; i < n2; ++i) {
+        for (int64_t k = 0; k < n; ++k) {
+            vals[k] = cube[(start + k) * n2 + i];
+            if (vals[k] != vals[k] && n > 1) {
+                free(vals);
+                snprintf(g_err, sizeof g_err, "called `Option::unwrap()` on a `None` value");
+                return ORC_ERR_PANIC;
+            }
+        }
+        qsort(vals, (size_t)n, sizeof(float), cmp_f32);
+        out[i] = (n % 2 == 1) ? vals[(n - 1) / 2] : (vals[n / 2] + vals[n / 2 - 1]) / 2.0f;
+    }
+    free(vals);
+    return ORC_OK;
+}
+
+/* run_minmax, lib.rs:1374-1398: fold_axis(Axis(0), -inf, |x, y| if x > y {x} else {y}) (max) / (+inf, x < y) (min) */
+int orc_minmax_fold(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int is_min, float *out) {
+    int rc = check_reduce_args(nz, start, end);
+    if (rc) return rc;
+    for (int64_t i = 0; i < n2; ++i) {
+        float acc = is_min ? INFINITY : -INFINITY;
+        for (int64_t k = start; k < end; ++k) {
+            float y = cube[k * n2 + i];
+            if (is_min) acc = (acc < y) ? acc : y;
+            else acc = (acc > y) ? acc : y;
+        }
+        out[i] = acc;
+    }
+    return ORC_OK;
+}
+
+/*
+ * WcsArray::pix2world (unit.rs:335-342) over fitrs 0.5.0 `WCS` (external, not on disk): restated as the
+ * axis-aligned linear transform world = CRVAL + CDELT * (pixel + 1 - CRPIX) in f64, cast to f32.  wcs = {crval,
+ * crpix, cdelt} or NULL (no WCS keys: the pixel maps to itself).  Parity unpinned.
+ */
+float orc_pix2world(const double *wcs, float pixel) {
+    if (!wcs) return pixel;
+    return (float)(wcs[0] + wcs[2] * ((double)pixel + (1.0 - wcs[1])));
+}
+
+/*
+ * run_create_argmap, lib.rs:1400-1460: strict comparison from -inf (max) / +inf (min), `out` updated whenever a
+ * frame wins: out = pix2world(trypix, ((k + start) as i64 + range) as f32) when is_actual_value (wcs != NULL or
+ * identity), else the index itself.  Nothing won (all NaN) -> 0.0.
+ */
+int orc_argmap(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int64_t range, int is_min,
+               const double *wcs, float *out) {
+    int rc = check_reduce_args(nz, start, end);
+    if (rc) return rc;
+    for (int64_t i = 0; i < n2; ++i) {
+        float value = is_min ? INFINITY : -INFINITY;
+        float o = 0.0f;
+        for (int64_t k = 0; k < end - start; ++k) {
+            float x = cube[(start + k) * n2 + i];
+            if ((!is_min && x > value) || (is_min && x < value)) {
+                value = x;
+                o = orc_pix2world(wcs, (float)((k + start) + range));
+            }
+        }
+        out[i] = o;
+    }
+    return ORC_OK;
+}
+
+/* run_centroid, lib.rs:1466-1527: flux_sum and sum(flux * wavelength) as sequential f32 sums from 0.0, then waveimg / flux_sum */
+int orc_centroid(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, const double *wcs, float *out) {
+    int rc = check_reduce_args(nz, start, end);
+    if (rc) return rc;
+    for (int64_t i = 0; i < n2; ++i) {
+        float fs = 0.0f, ws = 0.0f;
+        for (int64_t k = 0; k < end - start; ++k) {
+            float flux = cube[(start + k) * n2 + i];
+            float wavelength = orc_pix2world(wcs, (float)(k + start));
+            fs += flux;
+            ws += flux * wavelength;
+        }
+        out[i] = ws / fs;
+    }
+    return ORC_OK;
+}
+
+/* f64 version of the same quotient (products of the f32 inputs and f32 wavelengths): the tolerance oracle */
+void orc_centroid_f64(const float *cube, int64_t n2, int64_t start, int64_t end, const double *wcs, double *out) {
+    for (int64_t i = 0; i < n2; ++i) {
+        double fs = 0.0, ws = 0.0;
+        for (int64_t k = start; k < end; ++k) {
+            double flux = (double)cube[k * n2 + i];
+            fs += flux;
+            ws += flux * (double)orc_pix2world(wcs, (float)k);
+        }
+        out[i] = ws / fs;
+    }
+}
+
+/* run_centroid_with_mask, lib.rs:1529-1582: per-pixel [start_mask as usize, end_mask as usize); slice_axis panics when
+ * start > end or end > nz; wavelength from pix2world(2, k) */
+int orc_centroid_mask(const float *cube, int64_t nz, int64_t n2, const float *start_mask, const float *end_mask,
+                      const double *wcs, float *out) {
+    for (int64_t i = 0; i < n2; ++i) {
+        uint64_t lo = rust_f32_as_usize(start_mask[i]), hi = rust_f32_as_usize(end_mask[i]);
+        if (lo > hi || hi > (uint64_t)nz) {
+            snprintf(g_err, sizeof g_err, "slice index out of range");
+            return ORC_ERR_PANIC;
+        }
+        float fs = 0.0f, ws = 0.0f;
+        for (uint64_t k = lo; k < hi; ++k) {
+            float flux = cube[(int64_t)k * n2 + i];
+            fs += flux;
+            ws += flux * orc_pix2world(wcs, (float)k);
+        }
+        out[i] = ws / fs;
+    }
+    return ORC_OK;
+}
+
 /* lib.rs:393-395: middle = (start as f32 + end as f32) / 2.0; width = end as f32 - start as f32 */
 void orc_middle_width(int64_t start, int64_t end, float *middle, float *width) {
     *middle = ((float)start + (float)end) / 2.0f;

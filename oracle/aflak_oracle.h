@@ -47,6 +47,20 @@ void orc_middle_width(int64_t start, int64_t end, float *middle, float *width);
 int orc_integral_mt(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out, int threads);
 int orc_average_mt(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out, int threads);
 
+/* ---- other axis-0 reductions (lib.rs:1332-1582) ---- */
+int orc_variance(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int take_sqrt, float *out);
+void orc_variance_f64(const float *cube, int64_t n2, int64_t start, int64_t end, double *out);
+int orc_median(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out);
+int orc_minmax_fold(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int is_min, float *out);
+/* wcs = {CRVAL, CRPIX, CDELT} of the axis, or NULL for "pixel maps to itself" */
+float orc_pix2world(const double *wcs, float pixel);
+int orc_argmap(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int64_t range, int is_min,
+               const double *wcs, float *out);
+int orc_centroid(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, const double *wcs, float *out);
+void orc_centroid_f64(const float *cube, int64_t n2, int64_t start, int64_t end, const double *wcs, double *out);
+int orc_centroid_mask(const float *cube, int64_t nz, int64_t n2, const float *start_mask, const float *end_mask,
+                      const double *wcs, float *out);
+
 /* ---- slicing / gather (lib.rs:912-925, 1894-1962) ---- */
 int orc_slice_one_frame(const float *cube, int64_t nz, int64_t n2, int64_t frame, float *out);
 int orc_down_sampling(const float *img, int ndim, const int64_t *shape, int64_t n, float *out, int64_t *out_shape);

@@ -52,6 +52,16 @@ REGISTRY = {
     "log10": ((1, 0, 0), [("image", "Image", None)], ["Image"]),
     "apply_tone_curve": ((1, 0, 0), [("image", "Image", None), ("tone_curve", "ToneCurve", None)], ["Image"]),
     "image_min_max": ((1, 0, 0), [("image", "Image", None)], ["Float", "Float"]),
+    "variance": ((1, 0, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
+    "stddev": ((1, 0, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
+    "median": ((1, 0, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
+    "extract_argmin_max_wavelength": ((0, 1, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1),
+                                                  ("is_min", "Bool", False)], ["Image", "Image"]),
+    "peak_based_wavelength_range": ((0, 1, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1),
+                                                ("range", "Integer", 1), ("is_min", "Bool", False)], ["Image", "Image"]),
+    "extract_centrobaric_wavelength": ((0, 1, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
+    "extract_centrobaric_wavelength_with_mask": ((0, 1, 0), [("image", "Image", None), ("start_mask", "Image", None),
+                                                             ("end_mask", "Image", None)], ["Image"]),
     "ratio_from_bands": ((1, 0, 0), [("z", "Float", None), ("z1", "Float", None), ("z2", "Float", None)], ["Float", "Float"]),
     "range_specification": ((0, 1, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
 }

@@ -162,3 +162,74 @@ def test_make_raw_image_flip_and_nan(orc):
     assert out[1, 0].tolist() == [0, 0, 0] and out[1, 1].tolist() == [255, 255, 255]
     rgba = orc.make_raw_image(img, 0.0, 1.0, table, channels=4)
     assert np.all(rgba[..., 3] == 255) and np.array_equal(rgba[..., :3], out)
+
+
+# ---- other axis-0 reductions (lib.rs:1332-1582): hand-derivable known answers ------------------------------------
+
+def test_variance_stddev_kat(orc):
+    # spectrum 1,2,3,4 per pixel: mean 2.5, sum of squares 5, ddof=1 -> 5/3; every Welford step is exact in f32 but the last division
+    cube = np.arange(1, 5, dtype=np.float32).reshape(4, 1, 1) * np.ones((1, 2, 3), np.float32)
+    v = orc.variance(cube, 0, 4)
+    assert v.shape == (2, 3) and np.all(v == np.float32(5.0) / np.float32(3.0))
+    assert np.all(orc.stddev(cube, 0, 4) == np.sqrt(np.float32(5.0) / np.float32(3.0), dtype=np.float32))
+    # constant spectrum -> exactly 0; two frames a,b -> (a-b)^2/2
+    assert np.all(orc.variance(np.full((9, 2, 2), 3.25, np.float32), 0, 9) == 0.0)
+    two = np.array([1.0, 4.0], np.float32).reshape(2, 1, 1)
+    assert orc.variance(two, 0, 2)[0, 0] == 4.5
+    # ndarray panics when ddof >= number of frames
+    with pytest.raises(orc.OracleError) as e:
+        orc.variance(cube, 1, 2)
+    assert e.value.code == orc.ERR_PANIC
+    # agrees with numpy's two-pass f64 variance on real data
+    crop = np.load(os.path.join(GOLD, "test_fits_crop.npy"))
+    v64 = crop[40:160].astype(np.float64).var(axis=0, ddof=1)
+    assert np.allclose(orc.variance_f64(crop, 40, 160), v64, rtol=1e-12)
+    assert np.allclose(orc.variance(crop, 40, 160), v64, rtol=2e-4)
+
+
+def test_median_kat(orc):
+    cube = np.array([5, 1, 4, 2, 3], np.float32).reshape(5, 1, 1)
+    assert orc.median(cube, 0, 5)[0, 0] == 3.0      # odd: the middle element
+    assert orc.median(cube, 0, 4)[0, 0] == 3.0      # even: (2 + 4) / 2
+    assert orc.median(cube, 1, 3)[0, 0] == 2.5
+    assert orc.median(cube, 2, 3)[0, 0] == 4.0
+    bad = cube.copy()
+    bad[1] = np.nan
+    with pytest.raises(orc.OracleError) as e:       # partial_cmp().unwrap() on NaN
+        orc.median(bad, 0, 5)
+    assert e.value.code == orc.ERR_PANIC
+    assert np.isnan(orc.median(bad, 1, 2)[0, 0])    # a single frame is never compared
+
+
+def test_argmap_and_fold_kat(orc):
+    spec = np.array([1, 7, 3, 7, np.nan, 2], np.float32).reshape(6, 1, 1)
+    # first maximum wins (strict >), NaN never wins
+    assert orc.argmap(spec, 0, 6, 0, False)[0, 0] == 1.0
+    assert orc.argmap(spec, 2, 6, 0, False)[0, 0] == 3.0
+    assert orc.argmap(spec, 0, 6, 0, True)[0, 0] == 0.0
+    assert orc.argmap(spec, 0, 6, -2, False)[0, 0] == -1.0   # peak_based_wavelength_range: index - range
+    assert orc.argmap(spec, 4, 5, 0, False)[0, 0] == 0.0     # nothing wins -> 0.0
+    # linear WCS: CRVAL 4000 at CRPIX 1, CDELT 0.5 -> pixel 1 -> 4000.5
+    assert orc.argmap(spec, 0, 6, 0, False, wcs=(4000.0, 1.0, 0.5))[0, 0] == 4000.5
+    # the fold restarts after a NaN: max over frames after the last NaN
+    assert orc.minmax_fold(spec, 0, 6, False)[0, 0] == 2.0
+    assert orc.minmax_fold(spec, 0, 4, False)[0, 0] == 7.0
+    assert np.isnan(orc.minmax_fold(spec, 0, 5, False)[0, 0])
+    assert orc.minmax_fold(spec, 0, 4, True)[0, 0] == 1.0
+
+
+def test_centroid_kat(orc):
+    # flux 1,2,1 at pixels 10,11,12 -> centroid 11 exactly
+    cube = np.zeros((20, 1, 2), np.float32)
+    cube[10:13, 0, 0] = [1, 2, 1]
+    cube[10:13, 0, 1] = [1, 0, 1]
+    c = orc.centroid(cube, 8, 15)
+    assert c[0, 0] == 11.0 and c[0, 1] == 11.0
+    assert orc.centroid(cube, 8, 15, wcs=(100.0, 1.0, 2.0))[0, 0] == 122.0
+    assert np.isnan(orc.centroid(cube, 0, 5)[0, 0])          # 0 / 0
+    lo = np.array([[10.9, 0.0]], np.float32)                  # `as usize` truncates
+    hi = np.array([[13.0, 20.0]], np.float32)
+    m = orc.centroid_mask(cube, lo, hi)
+    assert m[0, 0] == 11.0 and m[0, 1] == 11.0
+    with pytest.raises(orc.OracleError):
+        orc.centroid_mask(cube, lo, np.array([[21.0, 20.0]], np.float32))
