@@ -272,21 +272,26 @@ template <bool COMP> __global__ void __launch_bounds__(256) centroid_mask_kernel
 
 // ---------------------------------------------------------------------------------------------------------------
 // run_median (lib.rs:1340-1372): per-pixel median of n = end - start frames; n odd -> middle element, n even ->
-// fl((v[n/2] + v[n/2-1]) / 2).  The reference sorts with partial_cmp().unwrap(): it panics if any value is NaN.
+// fl((v[n/2] + v[n/2-1]) / 2).  The reference sorts with partial_cmp().unwrap(): it panics if any value is NaN
+// (and n > 1).  Values are compared as order-preserving integer keys, so the result is the reference's bit for bit
+// (among equal values -0.0 sorts before +0.0, which the sum of the two middles cannot tell apart).
 //
-// One CTA owns P consecutive spaxels.  Their n x P values are staged once into shared memory with cp.async
-// (thousands of 4-byte copies in flight per CTA, no registers held), transposed on the way in to [P][npad] so that a
-// spaxel's spectrum is contiguous (npad = n rounded up to 32/P mod 32 words: the staging stores and the select loads are
-// both bank-conflict free).  Each spaxel is then solved by one warp with a 4-pass radix select (8-bit digits,
-// warp-aggregated shared-memory histogram) over order-preserving integer keys.  HBM traffic is exactly one read of
-// the sub-cube.
+// All variants read the sub-cube from HBM exactly once, staged into shared memory with cp.async (thousands of copies in
+// flight per CTA, no registers held):
+//   n <= 64  median_rank_kernel: a CTA stages [n][128 spaxels] (frame-major, 16-byte copies), then every thread ranks its
+//            own spaxel's column by counting (n^2 shared loads, conflict-free).
+//   larger   median_select_kernel: a CTA stages P spaxels transposed to [P][npad] (npad = n padded so that both the
+//            staging stores and the per-spectrum loads are bank-conflict free); one warp per spaxel runs a radix select
+//            over key - min(key): the digits cover only the range the spectrum really spans (typically 3 passes of 8
+//            bits, well spread histogram bins).
+//   n beyond shared memory: median_global_kernel re-reads the column from L2 on every pass.
 // ---------------------------------------------------------------------------------------------------------------
 struct MedianK {
     const float *cube;
     int64_t n2;
     int64_t start, n;
-    int P;          // spaxels per CTA: power of two <= 32
-    int npad;       // words per staged spectrum
+    int P;          // spaxels per CTA
+    int npad;       // words per staged spectrum (select kernel)
     float *out;
     unsigned *flag; // 1: NaN present (reference panics)
 };
@@ -299,10 +304,71 @@ __device__ __forceinline__ float med_unkey(unsigned k) {
     const unsigned b = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
     return __uint_as_float(b);
 }
+__device__ __forceinline__ float med_finish(unsigned klo, unsigned khi, bool even) {
+    return even ? __fdiv_rn(__fadd_rn(med_unkey(khi), med_unkey(klo)), 2.0f) : med_unkey(klo);
+}
 
-// One radix-select digit step shared by both median kernels: given the 256-bin histogram of the candidates' current
-// digit, find the bin holding rank kth (0-based among the candidates), return it and make kth relative to that bin.
-__device__ __forceinline__ unsigned med_pick_digit(const unsigned *hist, int64_t &kth, int lane) {
+constexpr int kMedRankPixels = 128; // spaxels (= threads) per CTA of the rank kernel
+constexpr int kMedRankMaxN = 64;
+
+__global__ void __launch_bounds__(kMedRankPixels) median_rank_kernel(const MedianK a) {
+    extern __shared__ __align__(16) unsigned s_keys[]; // [n][128]
+    const int tid = threadIdx.x;
+    const int64_t px0 = (int64_t)blockIdx.x * kMedRankPixels;
+    const int n = (int)a.n;
+    const bool vec = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0);
+    if (vec) {
+        for (int i = tid; i < n * (kMedRankPixels / 4); i += kMedRankPixels) {
+            const int k = i / (kMedRankPixels / 4), j = i % (kMedRankPixels / 4);
+            const int64_t px = px0 + 4 * j;
+            if (px < a.n2) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(s_keys + k * kMedRankPixels + 4 * j);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(a.cube + (a.start + k) * a.n2 + px) : "memory");
+            }
+        }
+    } else {
+        for (int i = tid; i < n * kMedRankPixels; i += kMedRankPixels) {
+            const int k = i / kMedRankPixels, j = i % kMedRankPixels;
+            if (px0 + j < a.n2) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(s_keys + i);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(a.cube + (a.start + k) * a.n2 + px0 + j) : "memory");
+            }
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    const int64_t px = px0 + tid;
+    if (px >= a.n2) return;
+    unsigned *col = s_keys + tid;
+    bool nan = false;
+    for (int k = 0; k < n; ++k) {
+        const float f = __uint_as_float(col[k * kMedRankPixels]);
+        nan |= (f != f);
+        col[k * kMedRankPixels] = med_key(f);
+    }
+    if (nan && n > 1) atomicMax(a.flag, 1u);
+    // the element of rank r is the key with  #(keys < it) <= r < #(keys <= it)
+    const int r_lo = (n - 1) / 2, r_hi = n / 2; // equal when n is odd
+    unsigned klo = 0u, khi = 0u;
+    for (int i = 0; i < n; ++i) {
+        const unsigned ki = col[i * kMedRankPixels];
+        int lt = 0, le = 0;
+#pragma unroll 8
+        for (int j = 0; j < n; ++j) {
+            const unsigned kj = col[j * kMedRankPixels];
+            lt += kj < ki;
+            le += kj <= ki;
+        }
+        if (lt <= r_lo && r_lo < le) klo = ki;
+        if (lt <= r_hi && r_hi < le) khi = ki;
+    }
+    a.out[px] = med_finish(klo, khi, (n & 1) == 0);
+}
+
+// One radix-select digit step: given the histogram of the candidates' current digit (256 bins), find the bin holding
+// rank kth (0-based among the candidates), make kth relative to that bin, return the bin and its population.
+__device__ __forceinline__ unsigned med_pick_digit(const unsigned *hist, unsigned &kth, unsigned &bin_count, int lane) {
     // lane l owns bins [8l, 8l+8); exclusive scan of the lane totals
     unsigned c[8], tot = 0u;
 #pragma unroll
@@ -315,10 +381,10 @@ __device__ __forceinline__ unsigned med_pick_digit(const unsigned *hist, int64_t
     }
     unsigned excl = incl - tot;
     int digit = -1;
-    unsigned below = 0u;
+    unsigned below = 0u, cnt = 0u;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        if (digit < 0 && kth < (int64_t)(excl + c[j])) { digit = lane * 8 + j; below = excl; }
+        if (digit < 0 && kth < excl + c[j]) { digit = lane * 8 + j; below = excl; cnt = c[j]; }
         excl += c[j];
     }
     // cumulative counts are monotonic: the lowest lane that found a bin has the first bin crossing kth
@@ -326,47 +392,65 @@ __device__ __forceinline__ unsigned med_pick_digit(const unsigned *hist, int64_t
     const int src = __ffs(ballot) - 1;
     digit = __shfl_sync(0xffffffffu, digit, src);
     below = __shfl_sync(0xffffffffu, below, src);
+    bin_count = __shfl_sync(0xffffffffu, cnt, src);
     kth -= below;
     return (unsigned)digit;
 }
 
-// histogram update for one candidate per lane, aggregated over the lanes that hit the same bin
-__device__ __forceinline__ void med_hist_add(unsigned *hist, bool act, unsigned digit, int lane) {
-    const unsigned amask = __ballot_sync(0xffffffffu, act);
-    if (act) {
-        const unsigned peers = __match_any_sync(amask, digit);
-        if (lane == __ffs(peers) - 1) atomicAdd(&hist[digit], (unsigned)__popc(peers));
-    }
-}
-
-// k-th smallest (0-based) of the n contiguous keys, solved by one warp; hist = 256 words of shared memory
-__device__ unsigned med_select_warp(const unsigned *keys, int64_t n, int64_t kth, unsigned *hist, int lane) {
-    unsigned prefix = 0u, mask = 0u;
-    for (int shift = 24; shift >= 0; shift -= 8) {
+// keys: n offset keys (key - kmin) of one spectrum, contiguous; span = max offset key.  Finds the offset keys of ranks
+// r and (when want_next) r + 1.  One warp; hist = 256 words of shared memory.
+__device__ void med_select_warp(const unsigned *keys, int n, unsigned span, unsigned r, bool want_next, unsigned *hist, int lane,
+                                unsigned &k_r, unsigned &k_next) {
+    int bits_left = 32 - __clz(span); // 0 when every key is equal
+    unsigned prefix = 0u, kth = r, eq_count = (unsigned)n;
+    while (bits_left > 0) {
+        const int w = bits_left < 8 ? bits_left : 8;
+        const int shift = bits_left - w;
+        const unsigned dmask = (1u << w) - 1u;
+        const unsigned cmask = bits_left >= 32 ? 0u : ~((1u << bits_left) - 1u);
         for (int b = lane; b < 256; b += 32) hist[b] = 0u;
         __syncwarp();
-        for (int64_t base = 0; base < n; base += 32) {
-            const int64_t i = base + lane;
-            const unsigned key = i < n ? keys[i] : 0u;
-            med_hist_add(hist, i < n && (key & mask) == prefix, (key >> shift) & 255u, lane);
+        for (int base = 0; base < n; base += 128) {
+            unsigned key[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = base + 32 * u + lane;
+                key[u] = i < n ? keys[i] : 0xFFFFFFFFu; // padding can never match: prefix has zeros above span's top bit
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = base + 32 * u + lane;
+                if (i < n && (key[u] & cmask) == prefix) atomicAdd(&hist[(key[u] >> shift) & dmask], 1u);
+            }
         }
         __syncwarp();
-        const unsigned digit = med_pick_digit(hist, kth, lane);
+        const unsigned digit = med_pick_digit(hist, kth, eq_count, lane);
         prefix |= digit << shift;
-        mask |= 255u << shift;
+        bits_left = shift;
         __syncwarp();
     }
-    return prefix;
+    k_r = prefix;
+    // eq_count keys equal k_r and kth is r's position among them
+    if (!want_next || kth + 1 < eq_count) { k_next = prefix; return; }
+    unsigned m = 0xFFFFFFFFu; // smallest key above k_r
+    for (int i = lane; i < n; i += 32) {
+        const unsigned key = keys[i];
+        if (key > prefix && key < m) m = key;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+    k_next = m;
 }
 
-__global__ void __launch_bounds__(256) median_kernel(const MedianK a) {
-    extern __shared__ __align__(16) unsigned s_keys[]; // [P][npad] staged keys, then 8 x 256 histogram words
-    const int P = a.P, npad = a.npad;
+__global__ void __launch_bounds__(256) median_select_kernel(const MedianK a) {
+    extern __shared__ __align__(16) unsigned s_keys[]; // [P][npad] staged keys, then one 256-word histogram per warp
+    const int P = a.P, npad = a.npad, n = (int)a.n;
+    const int nthreads = blockDim.x;
     const int64_t px0 = (int64_t)blockIdx.x * P;
     unsigned *hist = s_keys + (size_t)P * npad;
     const int tid = threadIdx.x;
     const int64_t total = a.n * P;
-    for (int64_t i = tid; i < total; i += 256) {
+    for (int64_t i = tid; i < total; i += nthreads) {
         const int64_t k = i / P;
         const int j = (int)(i - k * P);
         if (px0 + j < a.n2) {
@@ -378,67 +462,66 @@ __global__ void __launch_bounds__(256) median_kernel(const MedianK a) {
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31;
-    unsigned nan = 0u;
-    for (int j = warp; j < P; j += 8) {
+    const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    bool nan = false;
+    for (int j = warp; j < P; j += nwarps) {
         const int64_t px = px0 + j;
         if (px >= a.n2) continue; // warp-uniform
         unsigned *keys = s_keys + (size_t)j * npad;
-        for (int64_t i = lane; i < a.n; i += 32) {
+        unsigned kmin = 0xFFFFFFFFu, kmax = 0u;
+        for (int i = lane; i < n; i += 32) {
             const float f = __uint_as_float(keys[i]);
-            if (f != f) nan = 1u;
-            keys[i] = med_key(f);
+            nan |= (f != f);
+            const unsigned key = med_key(f);
+            keys[i] = key;
+            kmin = min(kmin, key);
+            kmax = max(kmax, key);
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+            kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+        }
+        for (int i = lane; i < n; i += 32) keys[i] -= kmin; // each lane rewrites the words it wrote
         __syncwarp();
-        float r;
-        if (a.n & 1) {
-            r = med_unkey(med_select_warp(keys, a.n, (a.n - 1) / 2, hist + warp * 256, lane));
-        } else {
-            const float hi = med_unkey(med_select_warp(keys, a.n, a.n / 2, hist + warp * 256, lane));
-            const float lo = med_unkey(med_select_warp(keys, a.n, a.n / 2 - 1, hist + warp * 256, lane));
-            r = __fdiv_rn(__fadd_rn(hi, lo), 2.0f);
-        }
-        if (lane == 0) a.out[px] = r;
+        unsigned klo, khi;
+        med_select_warp(keys, n, kmax - kmin, (unsigned)((n - 1) / 2), (n & 1) == 0, hist + warp * 256, lane, klo, khi);
+        if (lane == 0) a.out[px] = med_finish(klo + kmin, khi + kmin, (n & 1) == 0);
     }
-    if (nan && a.n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
+    if (nan && n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
 }
 
-// Long ranges that do not fit in shared memory even for one spaxel per CTA: the same radix select with the keys
-// re-read from global memory on every pass (L2 catches the re-reads of a single spaxel column).
+// Ranges that do not fit in shared memory even for one spaxel per CTA: plain 4 x 8-bit radix select with the column
+// re-read on every pass (L2 catches the re-reads of a single spaxel column).
 __global__ void __launch_bounds__(32) median_global_kernel(const MedianK a) {
     __shared__ unsigned hist[256];
     const int64_t px = blockIdx.x;
     const int lane = threadIdx.x;
     const float *col = a.cube + a.start * a.n2 + px;
-    unsigned nan = 0u;
-    auto select = [&](int64_t kth) -> unsigned {
-        unsigned prefix = 0u, mask = 0u;
+    bool nan = false;
+    auto select = [&](unsigned kth) -> unsigned {
+        unsigned prefix = 0u, mask = 0u, cnt;
         for (int shift = 24; shift >= 0; shift -= 8) {
             for (int b = lane; b < 256; b += 32) hist[b] = 0u;
             __syncwarp();
-            for (int64_t base = 0; base < a.n; base += 32) {
-                const int64_t i = base + lane;
-                const float f = i < a.n ? col[i * a.n2] : 0.0f;
-                if (f != f) nan = 1u;
+            for (int64_t i = lane; i < a.n; i += 32) {
+                const float f = col[i * a.n2];
+                nan |= (f != f);
                 const unsigned key = med_key(f);
-                med_hist_add(hist, i < a.n && (key & mask) == prefix, (key >> shift) & 255u, lane);
+                if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
             }
             __syncwarp();
-            const unsigned digit = med_pick_digit(hist, kth, lane);
+            const unsigned digit = med_pick_digit(hist, kth, cnt, lane);
             prefix |= digit << shift;
             mask |= 255u << shift;
             __syncwarp();
         }
         return prefix;
     };
-    float r;
-    if (a.n & 1) r = med_unkey(select((a.n - 1) / 2));
-    else {
-        const float hi = med_unkey(select(a.n / 2)), lo = med_unkey(select(a.n / 2 - 1));
-        r = __fdiv_rn(__fadd_rn(hi, lo), 2.0f);
-    }
-    if (nan && a.n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
-    if (lane == 0) a.out[px] = r;
+    const unsigned klo = select((unsigned)((a.n - 1) / 2));
+    const unsigned khi = (a.n & 1) ? klo : select((unsigned)(a.n / 2));
+    if (nan && a.n > 1) atomicMax(a.flag, 1u);
+    if (lane == 0) a.out[px] = med_finish(klo, khi, (a.n & 1) == 0);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -521,19 +604,22 @@ cudaError_t axis0_launch(const Axis0Args &a, const Axis0Plan &pl, void *partials
 // shared memory for staged keys: 227 KB opt-in per CTA; prefer a tile that lets two CTAs share an SM, so one CTA's
 // staging overlaps the other's select
 static constexpr size_t kMedianSmemMax = 224 * 1024;
-static constexpr size_t kMedianHistBytes = 8 * 256 * sizeof(unsigned);
 
 static int median_npad(int64_t n, int P) {
-    const int want = 32 / P; // npad % 32 == 32/P: staging stores (P spaxels x 32/P frames per warp) hit 32 distinct banks
+    const int want = P >= 32 ? 1 : 32 / P; // npad % 32 == 32/P: a warp's staging stores (P spaxels x 32/P frames) hit 32 banks
     int64_t np = n;
     while ((np % 32) != (want % 32)) ++np;
     return (int)np;
+}
+static size_t median_select_smem(int64_t n, int P) {
+    const int warps = P < 8 ? P : 8;
+    return (size_t)P * median_npad(n, P) * sizeof(unsigned) + (size_t)warps * 256 * sizeof(unsigned);
 }
 
 int median_pixels_per_cta(int64_t n2, int64_t n) {
     int fits_once = 0;
     for (int P = 32; P >= 1; P >>= 1) {
-        const size_t bytes = (size_t)P * median_npad(n, P) * sizeof(unsigned) + kMedianHistBytes;
+        const size_t bytes = median_select_smem(n, P);
         if (bytes <= kMedianSmemMax && fits_once == 0) fits_once = P;
         if (bytes * 2 <= kMedianSmemMax + 3 * 1024) { // two resident CTAs
             int best = P;
@@ -547,8 +633,15 @@ int median_pixels_per_cta(int64_t n2, int64_t n) {
 cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s) {
     if (n2 <= 0) return cudaSuccess;
     const int64_t n = end - start;
-    if (n < 1 || flag == nullptr) return cudaErrorInvalidValue;
+    if (n < 1 || n > 0x7FFFFFFF || flag == nullptr) return cudaErrorInvalidValue;
     MedianK k{cube, n2, start, n, 0, 0, out, flag};
+    if (n <= kMedRankMaxN) {
+        k.P = kMedRankPixels;
+        const size_t smem = (size_t)n * kMedRankPixels * sizeof(unsigned);
+        median_rank_kernel<<<(unsigned)((n2 + kMedRankPixels - 1) / kMedRankPixels), kMedRankPixels, smem, s>>>(k);
+        count_launch();
+        return cudaGetLastError();
+    }
     const int P = n > (int64_t)(kMedianSmemMax / sizeof(unsigned)) ? 0 : median_pixels_per_cta(n2, n);
     if (P == 0) {
         median_global_kernel<<<(unsigned)n2, 32, 0, s>>>(k);
@@ -557,16 +650,16 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
     }
     k.P = P;
     k.npad = median_npad(n, P);
-    const size_t smem = (size_t)P * k.npad * sizeof(unsigned) + kMedianHistBytes;
+    const size_t smem = median_select_smem(n, P);
     static bool attr_set[16] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 16 && !attr_set[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(median_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMedianSmemMax);
+        cudaError_t e = cudaFuncSetAttribute(median_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMedianSmemMax);
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }
-    median_kernel<<<(unsigned)((n2 + P - 1) / P), 256, smem, s>>>(k);
+    median_select_kernel<<<(unsigned)((n2 + P - 1) / P), 32 * (P < 8 ? P : 8), smem, s>>>(k);
     count_launch();
     return cudaGetLastError();
 }
