@@ -120,6 +120,22 @@ _sig("afk_value_str", _P, C.c_char_p)
 _sig("afk_value_bool", _P, C.c_int)
 _sig("afk_value_image", _P, _P)
 _sig("afk_value_tone_curve", _P, _fp, C.c_size_t, _fp, C.c_size_t)
+_sig("afk_value_fits", _P, _P)
+_sig("afk_value_get_fits", _P, _P)
+_sig("afk_value_paths", _P, C.POINTER(C.c_char_p), C.c_size_t)
+_sig("afk_value_paths_count", C.c_size_t, _P)
+_sig("afk_value_paths_at", C.c_char_p, _P, C.c_size_t)
+_sig("afk_image_ingest", _P, _P, C.c_int, C.c_int, _i64p, C.c_int, C.c_int64, C.c_float, C.c_float)
+_sig("afk_image_ingest_band", _P, _P, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_float, C.c_float)
+_sig("afk_fits_open", _P, C.c_char_p)
+_sig("afk_fits_retain", None, _P)
+_sig("afk_fits_release", None, _P)
+_sig("afk_fits_hdu_count", C.c_size_t, _P)
+_sig("afk_fits_header", C.c_char_p, _P, C.c_size_t, C.c_char_p)
+_sig("afk_fits_to_image", C.c_int, _P, C.c_int64, C.c_char_p, C.POINTER(C.c_void_p))
+_sig("afk_fits_to_image_band", C.c_int, _P, C.c_int64, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p))
+_sig("afk_k_ingest", C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.c_int64, C.c_float, C.c_float, _P)
+_sig("afk_ingest_last_stats", C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64))
 _sig("afk_value_default_for", _P, C.c_int)
 _sig("afk_value_retain", None, _P)
 _sig("afk_value_release", None, _P)
@@ -332,6 +348,80 @@ class Image:
             self._h = None
 
 
+FITS_F32, FITS_F64, FITS_I16, FITS_I32, FITS_U32 = range(5)
+_FITS_DTYPES = {FITS_F32: ">f4", FITS_F64: ">f8", FITS_I16: ">i2", FITS_I32: ">i4", FITS_U32: ">u4"}
+
+
+def ingest(raw, fmt, shape, blank=None, bscale=1.0, bzero=0.0, band=None, sync=True):
+    """Decode a big-endian FITS data unit held in host memory (afk_image_ingest / afk_image_ingest_band).
+
+    raw: bytes-like or numpy array holding the data unit as it sits in the file; band = (y0, rows) of a 3-D cube."""
+    buf = np.frombuffer(raw, dtype=np.uint8) if not isinstance(raw, np.ndarray) else raw.view(np.uint8).reshape(-1)
+    has_blank, bl = (0, 0) if blank is None else (1, int(blank))
+    if band is None:
+        sh = (C.c_int64 * max(len(shape), 1))(*shape)
+        h = lib.afk_image_ingest(buf.ctypes.data_as(_P), fmt, len(shape), sh, has_blank, bl, bscale, bzero)
+    else:
+        nz, ny, nx = shape
+        h = lib.afk_image_ingest_band(buf.ctypes.data_as(_P), fmt, nz, ny, nx, band[0], band[1], has_blank, bl, bscale, bzero)
+    img = Image(h)
+    if sync:
+        synchronize()  # `raw` may be a temporary
+    return img
+
+
+def k_ingest(dev_raw, fmt, n, dev_out, blank=None, bscale=1.0, bzero=0.0):
+    _check(lib.afk_k_ingest(C.c_void_p(dev_raw), fmt, n, 0 if blank is None else 1, 0 if blank is None else int(blank), bscale, bzero,
+                            C.c_void_p(dev_out)))
+
+
+def ingest_stats():
+    ms = (C.c_double * 3)()
+    b = C.c_uint64()
+    lib.afk_ingest_last_stats(ms, C.byref(b))
+    return {"read_ms": ms[0], "wall_ms": ms[1], "device_ms": ms[2], "bytes": int(b.value)}
+
+
+class Fits:
+    """fitrs::Fits: parsed headers of every HDU; data units stay on disk until fits_to_image."""
+
+    def __init__(self, handle, retain=False):
+        if not handle:
+            raise AflakError(ERR_IO, lib.afk_last_error().decode())
+        self._h = C.c_void_p(handle)
+        if retain:
+            lib.afk_fits_retain(self._h)
+
+    @classmethod
+    def open(cls, path):
+        return cls(lib.afk_fits_open(str(path).encode()))
+
+    @property
+    def handle(self):
+        return self._h
+
+    def __len__(self):
+        return int(lib.afk_fits_hdu_count(self._h))
+
+    def header(self, key, hdu=0):
+        v = lib.afk_fits_header(self._h, hdu, key.encode())
+        return None if v is None else v.decode()
+
+    def to_image(self, hdu_idx=0, extension="", world=1, rank=0):
+        out = C.c_void_p()
+        _check(lib.afk_fits_to_image_band(self._h, hdu_idx, extension.encode(), world, rank, C.byref(out)))
+        return Image(out.value)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.afk_fits_release(self._h)
+            self._h = None
+
+
+class Paths(list):
+    """PATHS::FileList"""
+
+
 class ToneCurve:
     """ToneCurveState: `arr` table + control points (imgui_tone_curve/src/lib.rs:10-48)."""
 
@@ -352,6 +442,11 @@ def _to_value(x):
         return lib.afk_value_float(float(x))
     if isinstance(x, str):
         return lib.afk_value_str(x.encode())
+    if isinstance(x, Fits):
+        return lib.afk_value_fits(x.handle)
+    if isinstance(x, Paths):
+        arr = (C.c_char_p * max(len(x), 1))(*[str(p).encode() for p in x])
+        return lib.afk_value_paths(arr, len(x))
     if isinstance(x, ToneCurve):
         return lib.afk_value_tone_curve(x.arr.ctypes.data_as(_fp), x.arr.size, x.cp.ctypes.data_as(_fp), x.cp.shape[0])
     if isinstance(x, (tuple, list, np.ndarray)):
@@ -392,6 +487,10 @@ def _from_value(v):
         buf = (C.c_float * 4096)()
         n = lib.afk_value_get_floats(v, buf, 4096)
         return ToneCurve(np.array(buf[:n], dtype=np.float32))
+    if t == T_FITS:
+        return Fits(lib.afk_value_get_fits(v), retain=True)
+    if t == T_PATHS:
+        return Paths(lib.afk_value_paths_at(v, i).decode() for i in range(lib.afk_value_paths_count(v)))
     return None
 
 

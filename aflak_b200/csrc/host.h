@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <initializer_list>
 #include <map>
 #include <mutex>
 #include <string>
@@ -115,6 +116,8 @@ struct afk_value {
     afk_image *img = nullptr;
     std::vector<float> arr; // ToneCurve arr
     std::vector<float> cp;  // ToneCurve control points (x,y pairs)
+    std::vector<std::string> paths; // PATHS::FileList
+    afk_fits *fits = nullptr;       // Arc<fitrs::Fits>
 };
 
 namespace afk {
@@ -147,6 +150,18 @@ std::string unit_div(bool has_a, const std::string &a, bool has_b, const std::st
 
 // WcsArray::pix2world (unit.rs:335-342) on the linear per-axis WCS carried in the meta blob
 float image_pix2world(const afk_image *img, int axis, float pixel);
+
+// result helpers shared by the operator translation units (ops.cpp, fits.cpp)
+void set_ok(afk_result *r, afk_value *v);
+void set_err(afk_result *r, const Error &e);
+void set_image(afk_result *r, afk_image *img); // takes over the caller's reference
+bool args_match(const afk_value *const *in, size_t n_in, std::initializer_list<afk_type> types, afk_result *out, size_t n_out);
+Error unexpected(const std::string &m);
+Error try_into_unsigned(const char *name, int64_t v);
+
+// FITS operators (fits.cpp)
+afk_status op_open_fits(const afk_value *const *in, size_t n_in, afk_result *out, size_t n_out);
+afk_status op_fits_to_image(const afk_value *const *in, size_t n_in, afk_result *out, size_t n_out);
 
 void registry_init();
 

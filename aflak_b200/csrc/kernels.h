@@ -113,6 +113,26 @@ cudaError_t axis0_launch(const Axis0Args &a, const Axis0Plan &plan, void *partia
 // run_median (lib.rs:1340-1372); *flag is set when a NaN is met (the reference panics)
 cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s);
 
+// ---- FITS data unit -> f32 (ingest.cu) ----------------------------------------------------------
+enum IngestFormat : int { // values match afk_fits_format (include/aflak_b200.h)
+    ING_F32 = 0, // BITPIX -32
+    ING_F64 = 1, // BITPIX -64
+    ING_I16 = 2, // BITPIX 16
+    ING_I32 = 3, // BITPIX 32
+    ING_U32 = 4, // BITPIX 32 read as unsigned (fitrs FitsData::IntegersU32)
+};
+struct IngestArgs {
+    const void *raw; // big-endian elements as they sit in the file; may alias out for 4-byte formats
+    int fmt;
+    int64_t n;       // elements
+    int has_blank;
+    int64_t blank;   // BLANK: integer formats only
+    float bscale, bzero;
+    float *out;
+};
+int ingest_element_bytes(int fmt); // 0 for an unknown format
+cudaError_t ingest_launch(const IngestArgs &a, int sm_count, cudaStream_t s);
+
 // ---- elementwise (K3) --------------------------------------------------------
 enum MapOp : int {
     MAP_LINCOMP = 0,    // out = fl(fl(u*a) + fl(v*b))                     lib.rs:1288-1297

@@ -156,9 +156,9 @@ std::string unit_div(bool has_a, const std::string &a, bool has_b, const std::st
 // =============================================================================================================
 // Precondition checks with the reference's wording (precond.rs)
 // =============================================================================================================
-static Error unexpected(const std::string &m) { return make_error(AFK_ERR_UNEXPECTED_INPUT, m); }
+Error unexpected(const std::string &m) { return make_error(AFK_ERR_UNEXPECTED_INPUT, m); }
 
-static Error try_into_unsigned(const char *name, int64_t v) { // precond.rs:3-15
+Error try_into_unsigned(const char *name, int64_t v) { // precond.rs:3-15
     if (v >= 0) return ok();
     return unexpected(fmt("'%s' must be positive, but got %lld", name, (long long)v));
 }
@@ -367,25 +367,25 @@ Error op_min_max(const afk_image *img, float *mn, float *mx, bool *any) {
 static void meta_clone(const afk_image *src, afk_image *dst) { dst->meta = src->meta; }
 
 // ---- result helpers ---------------------------------------------------------------------------------------------
-static void set_ok(afk_result *r, afk_value *v) {
+void set_ok(afk_result *r, afk_value *v) {
     r->status = AFK_OK;
     r->value = v;
     r->message = nullptr;
 }
-static void set_err(afk_result *r, const Error &e) {
+void set_err(afk_result *r, const Error &e) {
     r->status = e.status;
     r->value = nullptr;
     r->message = strdup(e.message.c_str());
     set_last_error(e.message);
 }
-static void set_image(afk_result *r, afk_image *img) {
+void set_image(afk_result *r, afk_image *img) {
     afk_value *v = afk_value_image(img);
     afk_image_release(img); // the value holds the only reference
     set_ok(r, v);
 }
 
 // cake_fn! wrapper (aflak_cake/src/lib.rs:129-141): mismatching variants are a panic in the reference
-static bool args_match(const afk_value *const *in, size_t n_in, std::initializer_list<afk_type> types, afk_result *out, size_t n_out) {
+bool args_match(const afk_value *const *in, size_t n_in, std::initializer_list<afk_type> types, afk_result *out, size_t n_out) {
     bool good = n_in == types.size();
     size_t i = 0;
     for (afk_type t : types) {
@@ -1183,8 +1183,14 @@ static afk_value *S(const char *v) { return afk_value_str(v); }
 
 static void build_registry() {
     const afk_type IMG = AFK_T_IMAGE, INT = AFK_T_INTEGER, FLT = AFK_T_FLOAT, BOOL = AFK_T_BOOL, STR = AFK_T_STR, TC = AFK_T_TONECURVE;
+    const afk_type PATHS = AFK_T_PATHS, FITS = AFK_T_FITS;
     // Names, kinds, versions, slot names, types and defaults follow lib.rs:141-747 (they are the RON on-disk contract,
     // aflak_cake/src/export.rs:80-85).  Descriptions are UI help text, reworded.
+    add("open_fits", "01. Open File", "Open the n-th FITS file of a path list (headers are parsed, data stays on disk).", 1, 0, 0,
+        {{"path", PATHS, nullptr}, {"n", INT, I(0)}}, {FITS}, op_open_fits);
+    add("fits_to_image", "04. Extract part of data",
+        "Decode the data unit of an HDU (by extension name, else by index) into a device-resident image.", 1, 0, 0,
+        {{"fits", FITS, nullptr}, {"hdu_idx", INT, I(0)}, {"extension", STR, S("")}}, {IMG}, op_fits_to_image);
     add("range_specification", "04. Extract part of data", "Keep frames start..end (end exclusive) of the 0th axis.", 0, 1, 0,
         {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}}, {IMG}, op_range_specification);
     add("image_min_max", "04. Extract part of data", "Minimum (first output) and maximum (second output) of an image.", 1, 0, 0,

@@ -633,6 +633,7 @@ void afk_value_retain(afk_value *v) {
 void afk_value_release(afk_value *v) {
     if (v && v->rc.fetch_sub(1, std::memory_order_acq_rel) == 1) {
         if (v->img) afk_image_release(v->img);
+        if (v->fits) afk_fits_release(v->fits);
         delete v;
     }
 }
@@ -727,7 +728,8 @@ int afk_value_eq(const afk_value *a, const afk_value *b) {
     case AFK_T_BOOL: return a->b == b->b;
     case AFK_T_IMAGE: return image_eq(a->img, b->img);
     case AFK_T_TONECURVE: return a->cp == b->cp; // control points only (imgui_tone_curve/src/lib.rs:50-56)
-    case AFK_T_ROI: case AFK_T_PATHS: return 1;  // only the defaults (ROI::All, empty list) are representable
+    case AFK_T_PATHS: return a->paths == b->paths;
+    case AFK_T_ROI: return 1;  // only the default (ROI::All) is representable
     default: return 0;
     }
 }

@@ -83,6 +83,7 @@ int afk_type_editable(afk_type t);
 
 /* ---- images: device-resident WcsArray (unit.rs:203-208) ---- */
 typedef struct afk_image afk_image;
+typedef struct afk_fits afk_fits;
 #define AFK_MAX_NDIM 4
 
 /* Upload a host array (C order, shape[0] slowest: [NAXISn..NAXIS1], fits.rs:42-49) to the current device.
@@ -120,6 +121,42 @@ int afk_image_pix2world(const afk_image *img, int axis, float pixel, float *worl
 const char *afk_image_axis_name(const afk_image *img, int axis);
 const char *afk_image_axis_unit(const afk_image *img, int axis);
 
+/* ---- FITS ingest: WcsArray::from_hdu (unit.rs:283-331) + FitsDataToArray (fits.rs:42-103) over fitrs 0.5.0.
+ *      The header is parsed on the host; the data unit crosses PCIe as the raw big-endian bytes of the file and is
+ *      decoded on the device (byte swap, i16/i32/u32/f64 -> f32, BLANK -> NaN, then value * BSCALE + BZERO in two
+ *      rounded f32 steps), chunk by chunk, each decode overlapping the next chunk's copy. ---- */
+typedef enum afk_fits_format {
+    AFK_FITS_F32 = 0, /* BITPIX -32  FitsData::FloatingPoint32 */
+    AFK_FITS_F64 = 1, /* BITPIX -64  FitsData::FloatingPoint64, `f as f32` */
+    AFK_FITS_I16 = 2, /* BITPIX  16  FitsData::IntegersI32 */
+    AFK_FITS_I32 = 3, /* BITPIX  32  FitsData::IntegersI32 */
+    AFK_FITS_U32 = 4  /* BITPIX  32 read as unsigned: FitsData::IntegersU32 */
+} afk_fits_format;
+/* Decode a data unit that is already in host memory (pinned memory makes the copies asynchronous).  shape as
+ * afk_image_upload: [NAXISn..NAXIS1].  blank is only read when has_blank (integer formats). */
+afk_image *afk_image_ingest(const void *raw_be, afk_fits_format fmt, int ndim, const int64_t *shape, int has_blank,
+                            int64_t blank, float bscale, float bzero);
+/* Same for one spatial band of a [nz, ny, nx] cube (rows [y0, y0+rows) of every frame): the per-GPU upload of a
+ * sharded cube (afk_shard_band).  The result has shape [nz, rows, nx]. */
+afk_image *afk_image_ingest_band(const void *raw_be, afk_fits_format fmt, int64_t nz, int64_t ny, int64_t nx, int64_t y0,
+                                 int64_t rows, int has_blank, int64_t blank, float bscale, float bzero);
+/* fitrs::Fits::open (lib.rs:826-835): parse every HDU header; the data units stay on disk.  NULL on failure
+ * (afk_last_error() has the reference's "Could not open file ..." wording). */
+afk_fits *afk_fits_open(const char *path);
+void afk_fits_retain(afk_fits *f);
+void afk_fits_release(afk_fits *f);
+size_t afk_fits_hdu_count(const afk_fits *f);
+/* value of a header card as text (strings unquoted and right-trimmed), NULL when the key is absent */
+const char *afk_fits_header(const afk_fits *f, size_t hdu, const char *key);
+/* run_fits_to_image (lib.rs:883-910): HDU by EXTNAME, else by index; reads the data unit through a pinned double
+ * buffer and decodes it on the device; attaches BUNIT, CTYPEn/CUNITn and the linear WCS (CRVALn/CRPIXn/CDELTn). */
+afk_status afk_fits_to_image(const afk_fits *f, int64_t hdu_idx, const char *extension, afk_image **out);
+/* same for this rank's band of a 3-D HDU (rows split with afk_shard_band): each GPU reads only its own rows */
+afk_status afk_fits_to_image_band(const afk_fits *f, int64_t hdu_idx, const char *extension, int world, int rank, afk_image **out);
+/* timings of the last ingest on this thread, in ms: [0] file/host read into pinned memory, [1] whole call (wall),
+ * [2] device span from the first copy to the last decode (CUDA events); bytes = raw bytes moved over PCIe */
+int afk_ingest_last_stats(double ms[3], uint64_t *bytes);
+
 /* ---- values: IOValue (lib.rs:66-83), refcounted like the Arc<T> the cake cache stores ---- */
 typedef struct afk_value afk_value;
 afk_value *afk_value_integer(int64_t v);
@@ -130,6 +167,11 @@ afk_value *afk_value_float3x3(const float v[9]);
 afk_value *afk_value_str(const char *s);
 afk_value *afk_value_bool(int b);
 afk_value *afk_value_image(afk_image *img); /* retains img */
+afk_value *afk_value_fits(afk_fits *f);     /* retains f: IOValue::Fits(Arc<fitrs::Fits>) */
+afk_fits *afk_value_get_fits(const afk_value *v); /* borrowed */
+afk_value *afk_value_paths(const char *const *paths, size_t n); /* IOValue::Paths(PATHS::FileList) */
+size_t afk_value_paths_count(const afk_value *v);
+const char *afk_value_paths_at(const afk_value *v, size_t i);
 /* ToneCurveState: only `arr` is read by operators (imgui_tone_curve/src/lib.rs:10-48); cp = n_cp (x,y) pairs */
 afk_value *afk_value_tone_curve(const float *arr, size_t n, const float *cp_xy, size_t n_cp);
 /* DefaultFor::default_for (lib.rs:760-776); NULL for types without a default (Image, Fits, Map2dTo3dCoords) */
@@ -247,6 +289,9 @@ afk_status afk_colormap_rgb_host(const afk_image *img, const afk_lut *const lut[
 /* epilogue: 0 sum, 1 mean, 2 mean0/mean1, 3 EW(params = a,b,fl,max,sign). `out` may be a peer-mapped pointer. */
 afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends,
                         int epilogue, const float *params, int sum_mode, float *out);
+/* the ingest decode kernel alone: device raw bytes -> device f32 (out may alias raw for 4-byte formats) */
+afk_status afk_k_ingest(const void *device_raw_be, afk_fits_format fmt, int64_t n, int has_blank, int64_t blank, float bscale,
+                        float bzero, float *device_out);
 /* CUDA-event timing of reduce-kernel launches on this thread: enable, run, then read (sum of ms, launches). */
 int afk_profile_reduce(int enable);
 int afk_profile_reduce_read(double *total_ms, uint64_t *launches);

@@ -136,6 +136,17 @@ def middle_width(start, end):
     return m.value, w.value
 
 
+# ---- FITS data unit -> f32 (unit.rs:283-331, fits.rs:42-103) ----------------------
+
+def fits_decode(raw, fmt, n, blank=None, bscale=1.0, bzero=0.0):
+    """raw: bytes of the big-endian data unit; fmt: 0 f32, 1 f64, 2 i16, 3 i32, 4 u32."""
+    buf = np.frombuffer(raw, dtype=np.uint8) if not isinstance(raw, np.ndarray) else raw.view(np.uint8).reshape(-1)
+    out = np.empty(n, dtype=np.float32)
+    _check(lib().orc_fits_decode(_u8p(buf), C.c_int(fmt), C.c_int64(n), C.c_int(0 if blank is None else 1),
+                                 C.c_int64(0 if blank is None else int(blank)), C.c_float(bscale), C.c_float(bzero), _fp(out)))
+    return out
+
+
 # ---- other axis-0 reductions (lib.rs:1332-1582) ----------------------------------
 
 def _dp(a):

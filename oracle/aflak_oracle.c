@@ -163,6 +163,62 @@ void orc_sum_f64(const float *cube, int64_t n2, int64_t start, int64_t end, doub
 }
 
 /* ------------------------------------------------------------------------- */
+/* FITS data unit -> f32: unit.rs:283-331, fits.rs:42-103 over fitrs 0.5.0     */
+/* ------------------------------------------------------------------------- */
+
+/*
+ * fitrs 0.5.0 `Hdu::read_data` (external, not on disk; restated from the FITS standard): the data unit is big-endian;
+ * BITPIX -32 -> FloatingPoint32, -64 -> FloatingPoint64, 16 and 32 -> IntegersI32(Option<i32>) with BLANK -> None,
+ * unsigned 32 -> IntegersU32.  aflak then maps to f32 (fits.rs:42-103: `f as f32`, `int as f32`, None -> NaN) and
+ * applies `image * bscale + bzero` (unit.rs:328): two separately rounded f32 steps, always executed.
+ * fmt: 0 f32, 1 f64, 2 i16, 3 i32, 4 u32.
+ */
+int orc_fits_decode(const uint8_t *raw, int fmt, int64_t n, int has_blank, int64_t blank, float bscale, float bzero, float *out) {
+    for (int64_t i = 0; i < n; ++i) {
+        float v;
+        switch (fmt) {
+        case 0: {
+            const uint8_t *p = raw + 4 * i;
+            uint32_t b = ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
+            memcpy(&v, &b, 4);
+            break;
+        }
+        case 1: {
+            const uint8_t *p = raw + 8 * i;
+            uint64_t b = 0;
+            for (int j = 0; j < 8; ++j) b = (b << 8) | p[j];
+            double d;
+            memcpy(&d, &b, 8);
+            v = (float)d;
+            break;
+        }
+        case 2: {
+            const uint8_t *p = raw + 2 * i;
+            int32_t x = (int16_t)(uint16_t)(((uint16_t)p[0] << 8) | p[1]);
+            v = (has_blank && (int64_t)x == blank) ? NAN : (float)x;
+            break;
+        }
+        case 3: case 4: {
+            const uint8_t *p = raw + 4 * i;
+            uint32_t b = ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
+            if (fmt == 3) {
+                int32_t x = (int32_t)b;
+                v = (has_blank && (int64_t)x == blank) ? NAN : (float)x;
+            } else {
+                v = (has_blank && (int64_t)b == blank) ? NAN : (float)b;
+            }
+            break;
+        }
+        default:
+            snprintf(g_err, sizeof g_err, "Unsupported data array format");
+            return ORC_ERR_UNEXPECTED_INPUT;
+        }
+        out[i] = v * bscale + bzero;
+    }
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------- */
 /* Other axis-0 reductions: lib.rs:1332-1582                                   */
 /* ------------------------------------------------------------------------- */
 

@@ -47,6 +47,9 @@ void orc_middle_width(int64_t start, int64_t end, float *middle, float *width);
 int orc_integral_mt(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out, int threads);
 int orc_average_mt(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out, int threads);
 
+/* ---- FITS data unit -> f32 (unit.rs:283-331, fits.rs:42-103); fmt: 0 f32, 1 f64, 2 i16, 3 i32, 4 u32 ---- */
+int orc_fits_decode(const uint8_t *raw, int fmt, int64_t n, int has_blank, int64_t blank, float bscale, float bzero, float *out);
+
 /* ---- other axis-0 reductions (lib.rs:1332-1582) ---- */
 int orc_variance(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, int take_sqrt, float *out);
 void orc_variance_f64(const float *cube, int64_t n2, int64_t start, int64_t end, double *out);

@@ -10,6 +10,8 @@ Three kinds of fixture, none of which is produced by code of this repository:
   test_fits_facts.json   aflak_primitives/test/test.fits (49x49x200, BITPIX -32, BUNIT K), decoded here by a
                          20-line FITS reader (big-endian f32, BSCALE 1 / BZERO 0), plus the header facts and
                          f64 column sums of the crop computed with numpy -- a real-data input for the parity tests.
+  test_fits_crop.fits    the same crop written back as a FITS file under the reference file's own header cards
+                         (NAXIS1/2 and CRPIX1/2 adjusted to the crop): input of the header-parser / ingest tests.
   kat.json               hand-derivable known answers for the operators that have no value-asserting reference test
                          (SURVEY.md 8c): closed forms worked out from the reference's formulas, and the error
                          strings of aflak_primitives/src/precond.rs.
@@ -78,6 +80,36 @@ def fits_crop():
     return facts
 
 
+def fits_crop_file():
+    """test_fits_crop.fits: the same crop as a FITS file -- the reference file's own header cards (free-format values and
+    all), with NAXIS1/NAXIS2 set to the crop size and CRPIX1/CRPIX2 moved by the crop origin, followed by the crop as
+    big-endian f32.  Input of the header-parser / ingest tests (the full 1.9 MB file stays in /root/reference)."""
+    b = open(os.path.join(REF, "aflak_primitives/test/test.fits"), "rb").read()
+    cards, i = [], 0
+    while True:
+        card = b[i:i + 80].decode("ascii")
+        i += 80
+        cards.append(card)
+        if card.startswith("END"):
+            break
+    out = []
+    for c in cards:
+        k = c[:8].strip()
+        if k in ("NAXIS1", "NAXIS2"):
+            c = f"{k:<8}=      12 /".ljust(80)
+        elif k in ("CRPIX1", "CRPIX2"):
+            v = float(c.split("=", 1)[1].split("/")[0])
+            c = f"{k:<8}=      {v - 18.0:.6E} /".ljust(80)
+        out.append(c)
+    hdr = "".join(out).encode("ascii")
+    hdr += b" " * (-len(hdr) % 2880)
+    crop = np.load(os.path.join(HERE, "test_fits_crop.npy"))
+    data = crop.astype(">f4").tobytes()
+    data += b"\0" * (-len(data) % 2880)
+    with open(os.path.join(HERE, "test_fits_crop.fits"), "wb") as f:
+        f.write(hdr + data)
+
+
 def kat():
     f32 = np.float32
     return {
@@ -121,4 +153,5 @@ if __name__ == "__main__":
     json.dump(kat(), open(os.path.join(HERE, "kat.json"), "w"), indent=1)
     if os.path.exists(REF):
         json.dump(fits_crop(), open(os.path.join(HERE, "test_fits_facts.json"), "w"), indent=1)
+        fits_crop_file()
     print(sorted(os.listdir(HERE)))

@@ -55,3 +55,44 @@ def assert_reduction(got, sum64, abs64, what="", divisor=1.0):
     err = np.abs(got[fin] - o[fin])
     ok = (err <= 1e-5 * np.abs(o[fin])) | (err <= 4 * 2.0 ** -24 * a[fin])
     assert ok.all(), f"{what}: {(~ok).sum()} pixels outside tolerance, worst rel err {np.max(err / np.maximum(np.abs(o[fin]), 1e-300))}"
+
+
+# ---- a minimal FITS writer for the ingest tests (FITS standard 4.0: 80-char cards, 2880-byte blocks, big-endian data) ----
+def fits_card(key, value=None, comment=""):
+    if value is None:
+        return f"{key:<8}".ljust(80)
+    if isinstance(value, bool):
+        v = f"{'T' if value else 'F':>20}"
+    elif isinstance(value, (int, np.integer)):
+        v = f"{int(value):>20}"
+    elif isinstance(value, (float, np.floating)):
+        v = f"{float(value):>20.12E}"
+    else:
+        v = "'" + str(value).replace("'", "''").ljust(8) + "'"
+    c = f"{key:<8}= {v}"
+    if comment:
+        c += f" / {comment}"
+    assert len(c) <= 80, c
+    return c.ljust(80)
+
+
+def fits_hdu_bytes(data_be, cards, primary=True, extname=None):
+    """data_be: numpy array in its on-disk big-endian dtype (or None); cards: list of (key, value) after NAXISn."""
+    bitpix = {">f4": -32, ">f8": -64, ">i2": 16, ">i4": 32, ">u4": 32, "|u1": 8, ">u1": 8}
+    out = [fits_card("SIMPLE", True) if primary else fits_card("XTENSION", "IMAGE")]
+    if data_be is None:
+        out += [fits_card("BITPIX", 8), fits_card("NAXIS", 0)]
+    else:
+        out += [fits_card("BITPIX", bitpix[data_be.dtype.str]), fits_card("NAXIS", data_be.ndim)]
+        out += [fits_card(f"NAXIS{i + 1}", n) for i, n in enumerate(reversed(data_be.shape))]
+    if not primary:
+        out += [fits_card("PCOUNT", 0), fits_card("GCOUNT", 1)]
+    if extname is not None:
+        out.append(fits_card("EXTNAME", extname))
+    out += [fits_card(k, v) for k, v in cards]
+    out.append("END".ljust(80))
+    hdr = "".join(out).encode("ascii")
+    hdr += b" " * (-len(hdr) % 2880)
+    data = b"" if data_be is None else data_be.tobytes()
+    data += b"\0" * (-len(data) % 2880)
+    return hdr + data
