@@ -134,6 +134,11 @@ _sig("afk_fits_hdu_count", C.c_size_t, _P)
 _sig("afk_fits_header", C.c_char_p, _P, C.c_size_t, C.c_char_p)
 _sig("afk_fits_to_image", C.c_int, _P, C.c_int64, C.c_char_p, C.POINTER(C.c_void_p))
 _sig("afk_fits_to_image_band", C.c_int, _P, C.c_int64, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p))
+_u64p = C.POINTER(C.c_uint64)
+_sig("afk_image_histogram", C.c_int, _P, C.c_float, C.c_float, _u64p, _fp, _fp)
+_sig("afk_image_histogram_color", C.c_int, _P, C.c_float, C.c_float, _u64p, _fp, _fp)
+_sig("afk_image_vmed_vmad", C.c_int, _P, C.POINTER(C.c_float), C.POINTER(C.c_float))
+_sig("afk_image_zscale", C.c_int, _P, C.c_int, C.c_float, C.POINTER(C.c_int), C.POINTER(C.c_float), C.POINTER(C.c_float))
 _sig("afk_k_ingest", C.c_int, _P, C.c_int, C.c_int64, C.c_int, C.c_int64, C.c_float, C.c_float, _P)
 _sig("afk_ingest_last_stats", C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64))
 _sig("afk_value_default_for", _P, C.c_int)
@@ -336,6 +341,25 @@ class Image:
         assert out.dtype == np.float32 and out.flags.c_contiguous and out.size == int(np.prod(self.shape, dtype=np.int64))
         _check(lib.afk_image_download(self._h, out.ctypes.data_as(_P)))
         return out
+
+    def histogram(self, vmin, vmax, color=False):
+        """hist::histogram / histogram_color: (counts, starts, ends); counts is [100] or [256, 3]."""
+        nb = 256 if color else 100
+        counts = np.zeros(nb * (3 if color else 1), dtype=np.uint64)
+        starts, ends = np.empty(nb, dtype=np.float32), np.empty(nb, dtype=np.float32)
+        fn = lib.afk_image_histogram_color if color else lib.afk_image_histogram
+        _check(fn(self._h, vmin, vmax, counts.ctypes.data_as(_u64p), starts.ctypes.data_as(_fp), ends.ctypes.data_as(_fp)))
+        return (counts.reshape(nb, 3) if color else counts), starts, ends
+
+    def vmed_vmad(self):
+        a, b = C.c_float(), C.c_float()
+        _check(lib.afk_image_vmed_vmad(self._h, C.byref(a), C.byref(b)))
+        return np.float32(a.value), np.float32(b.value)
+
+    def zscale(self, nsamples=1000, contrast=0.25):
+        has, z1, z2 = C.c_int(), C.c_float(), C.c_float()
+        _check(lib.afk_image_zscale(self._h, nsamples, contrast, C.byref(has), C.byref(z1), C.byref(z2)))
+        return (np.float32(z1.value), np.float32(z2.value)) if has.value else (None, None)
 
     def vmin_vmax(self):
         a, b = C.c_float(), C.c_float()

@@ -171,6 +171,26 @@ cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_
 float minmax_decode_min(unsigned inv_key);
 float minmax_decode_max(unsigned key);
 
+// ---- display statistics (stats.cu) ----------------------------------------------------------------
+// hist::histogram / histogram_color (aflak_plot/src/imshow/hist.rs:10-66): counts_dev is [nbins][channels] u64, zeroed
+cudaError_t histogram_launch(const float *img, int64_t n_per_channel, int channels, float mn, float mx, int nbins,
+                             unsigned long long *counts_dev, int sm_count, cudaStream_t s);
+struct StatParams {
+    float vmin, vmax; // d = (v - vmin) / (vmax - vmin)
+    int use_vmed;     // select over |d - vmed| with vmed read from the previous statistic's state (lims.rs:87)
+};
+struct StatState {    // device-resident state of one radix select; zero-initialised
+    unsigned prefix, mask;
+    unsigned long long kth, n, eq_count;
+    unsigned next_key;
+    int even, error;
+    float result;
+};
+cudaError_t stat_select_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, unsigned *hist,
+                               int sm_count, cudaStream_t s);
+cudaError_t zsample_launch(const float *img, int64_t ny, int64_t nx, int64_t stride, int64_t rows_s, int64_t cols_s, float *out,
+                           cudaStream_t s);
+
 // ---- gather (K6) ----------------------------------------------------------------
 cudaError_t downsample_launch(const float *img, int64_t c, int64_t ny, int64_t nx, int64_t n, float *out, int64_t oy,
                               int64_t ox, cudaStream_t s);

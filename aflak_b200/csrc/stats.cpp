@@ -1,0 +1,251 @@
+// stats.cpp -- host side of the display statistics: histogram, normalised median / MAD, zscale.
+//
+// Replaces aflak_plot/src/imshow/hist.rs:10-66, lims.rs:37-106 and zscale.rs:45-242 (`Image::new` runs the first two on
+// every new image, `zscale` on demand; all on the UI thread).  The image passes run on the device (stats.cu); zscale's
+// line fit works on <= ~1000 samples and stays on the host, restated step by step in f32.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+#include "host.h"
+
+namespace afk {
+
+static Error stats_ctx(const afk_image *img, cudaStream_t *s, int *dev) {
+    if (Error e = current_stream(s, dev)) return e;
+    if (img->device != *dev)
+        return make_error(AFK_ERR_CUDA, fmt("CUDA: image lives on device %d but the calling thread uses device %d", img->device, *dev));
+    return image_wait(img, *s);
+}
+
+static Error histogram_run(const afk_image *img, int channels, int nbins, float vmin, float vmax, uint64_t *counts, float *starts, float *ends) {
+    cudaStream_t s;
+    int dev;
+    if (Error e = stats_ctx(img, &s, &dev)) return e;
+    const int64_t n_per = img->len() / channels;
+    const size_t bytes = (size_t)nbins * channels * sizeof(unsigned long long);
+    unsigned long long *d = nullptr;
+    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), bytes, s));
+    cudaError_t ce = cudaMemsetAsync(d, 0, bytes, s);
+    if (ce == cudaSuccess) ce = histogram_launch(img->ptr, n_per, channels, vmin, vmax, nbins, d, sm_count(dev), s);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(counts, d, bytes, cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    cudaFreeAsync(d, s);
+    if (ce != cudaSuccess) return cuda_error(ce, "histogram_kernel");
+    image_note_read(img, s);
+    // Bin { start: min + i as f32 * size, end: min + (i + 1) as f32 * size } with size = (max - min) / NB (hist.rs:16-23)
+    const float size = (vmax - vmin) / (float)nbins;
+    for (int i = 0; i < nbins; ++i) {
+        if (starts) starts[i] = vmin + (float)i * size;
+        if (ends) ends[i] = vmin + (float)(i + 1) * size;
+    }
+    return ok();
+}
+
+static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
+    if (img->len() == 0) return make_error(AFK_ERR_UNEXPECTED_INPUT, "Could not get vmed from normalized image"); // get_vmax/get_vmin fail
+    float vmin, vmax;
+    bool any;
+    if (Error e = op_min_max(img, &vmin, &vmax, &any)) return e;
+    cudaStream_t s;
+    int dev;
+    if (Error e = stats_ctx(img, &s, &dev)) return e;
+    // two select states + one histogram, zeroed
+    const size_t bytes = 2 * sizeof(StatState) + 256 * sizeof(unsigned);
+    char *d = nullptr;
+    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), bytes, s));
+    StatState *st = reinterpret_cast<StatState *>(d);
+    unsigned *hist = reinterpret_cast<unsigned *>(d + 2 * sizeof(StatState));
+    cudaError_t ce = cudaMemsetAsync(d, 0, bytes, s);
+    StatParams p{vmin, vmax, 0};
+    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, img->len(), p, nullptr, &st[0], hist, sm_count(dev), s);
+    p.use_vmed = 1;
+    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, img->len(), p, &st[0], &st[1], hist, sm_count(dev), s);
+    StatState h[2];
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, st, sizeof h, cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    cudaFreeAsync(d, s);
+    if (ce != cudaSuccess) return cuda_error(ce, "stat_select");
+    image_note_read(img, s);
+    if (h[0].error) return make_error(AFK_ERR_UNEXPECTED_INPUT, "Empty data!, med"); // lims.rs:53
+    if (h[1].error) return make_error(AFK_ERR_UNEXPECTED_INPUT, "Empty data!, mad"); // lims.rs:92
+    *vmed = h[0].result;
+    *vmad = h[1].result;
+    return ok();
+}
+
+// ---- zscale (zscale.rs:45-242), f32 throughout, sums left to right like Iterator::sum ---------------------------------------
+static int rust_f32_as_i32(float f) {
+    if (f != f) return 0;
+    if (f >= 2147483648.0f) return std::numeric_limits<int>::max();
+    if (f <= -2147483648.0f) return std::numeric_limits<int>::min();
+    return (int)f;
+}
+static uint64_t rust_f32_as_usize(float f) {
+    if (!(f > 0.0f)) return 0;
+    if (f >= 18446744073709551616.0f) return std::numeric_limits<uint64_t>::max();
+    return (uint64_t)f;
+}
+
+// zsc_compute_sigma (zscale.rs:205-241)
+static void zsc_compute_sigma(const std::vector<float> &flat, const std::vector<int> &badpix, int *ngoodpix, bool *has_sigma, float *sigma) {
+    float sumz = 0.0f, sumsq = 0.0f;
+    int ng = 0;
+    for (size_t i = 0; i < flat.size(); ++i)
+        if (badpix[i] == 0) {
+            sumz = sumz + flat[i];
+            ++ng;
+        }
+    for (size_t i = 0; i < flat.size(); ++i)
+        if (badpix[i] == 0) sumsq = sumsq + flat[i] * flat[i];
+    *ngoodpix = ng;
+    *has_sigma = false;
+    if (ng >= 2) {
+        // i32 product like the reference: ngoodpix * (ngoodpix - 1)
+        const float temp = sumsq / (float)(ng - 1) - sumz * sumz / (float)(ng * (ng - 1));
+        *has_sigma = true;
+        *sigma = temp < 0.0f ? 0.0f : sqrtf(temp);
+    }
+}
+
+// zsc_fit_line (zscale.rs:127-203)
+static void zsc_fit_line(const std::vector<float> &samples, int npix, float krej, int ngrow, int maxiter, int min_npixels, float max_reject,
+                         int *ngoodpix_out, float *zslope_out) {
+    const float xscale = 2.0f / (float)(npix - 1);
+    std::vector<float> xnorm((size_t)npix);
+    for (int v = 0; v < npix; ++v) xnorm[(size_t)v] = (float)v * xscale - 1.0f;
+    int ngoodpix = npix;
+    const int minpix = std::max(min_npixels, rust_f32_as_i32((float)npix * max_reject));
+    const int last_ngoodpix = npix + 1;
+    std::vector<int> badpix((size_t)npix, 0);
+    float slope = 0.0f;
+    std::vector<float> flat((size_t)npix);
+    for (int it = 0; it < maxiter; ++it) {
+        if (ngoodpix >= last_ngoodpix || ngoodpix < minpix) break;
+        int sum = 0;
+        float sumx = 0.0f, sumxx = 0.0f, sumxy = 0.0f, sumy = 0.0f;
+        for (int i = 0; i < npix; ++i)
+            if (badpix[(size_t)i] == 0) {
+                ++sum;
+                sumx = sumx + xnorm[(size_t)i];
+            }
+        for (int i = 0; i < npix; ++i)
+            if (badpix[(size_t)i] == 0) sumxx = sumxx + xnorm[(size_t)i] * xnorm[(size_t)i];
+        for (int i = 0; i < npix; ++i)
+            if (badpix[(size_t)i] == 0) sumxy = sumxy + xnorm[(size_t)i] * samples[(size_t)i];
+        for (int i = 0; i < npix; ++i)
+            if (badpix[(size_t)i] == 0) sumy = sumy + samples[(size_t)i];
+        const float delta = (float)sum * sumxx - sumx * sumx;
+        const float intercept = (sumxx * sumy - sumx * sumxy) / delta;
+        slope = ((float)sum * sumxy - sumx * sumy) / delta;
+        for (int i = 0; i < npix; ++i) flat[(size_t)i] = samples[(size_t)i] - (xnorm[(size_t)i] * slope + intercept);
+        int ng;
+        bool has_sigma;
+        float sigma = 0.0f;
+        zsc_compute_sigma(flat, badpix, &ng, &has_sigma, &sigma);
+        ngoodpix = ng;
+        if (has_sigma) { // (Some(mean), Some(sigma))
+            const float threshold = sigma * krej, lcut = -threshold, hcut = threshold;
+            std::vector<int> next((size_t)npix);
+            for (int i = 0; i < npix; ++i) next[(size_t)i] = (flat[(size_t)i] < lcut || flat[(size_t)i] > hcut) ? 1 : 0;
+            // convolve(next_badpix, [1, ngrow]): ret[head] = target[head] + target[head-1] * ngrow
+            for (int head = 0; head < npix; ++head) {
+                int data = next[(size_t)head];
+                if (head >= 1) data += next[(size_t)head - 1] * ngrow;
+                badpix[(size_t)head] = data;
+            }
+            ngoodpix = 0;
+            for (int i = 0; i < npix; ++i) ngoodpix += badpix[(size_t)i] == 0;
+        }
+    }
+    *ngoodpix_out = ngoodpix;
+    *zslope_out = slope * xscale;
+}
+
+static Error zscale_run(const afk_image *img, int nsamples, float contrast, int *has, float *z1, float *z2) {
+    *has = 0;
+    if (img->ndim != 2) return make_error(AFK_ERR_PANIC, "called `Result::unwrap()` on an `Err` value: Msg(\"zsc sample failed.\")");
+    const int64_t nc = img->shape[0], nl = img->shape[1];
+    // stride = 1.max((((nc - 1) * (nl - 1)) as f32 / maxpix as f32).sqrt() as usize)   (usize arithmetic wraps for empty axes:
+    // an empty image has no samples either way)
+    std::vector<float> sample;
+    if (nc > 0 && nl > 0) {
+        const uint64_t raw = rust_f32_as_usize(sqrtf((float)((uint64_t)(nc - 1) * (uint64_t)(nl - 1)) / (float)nsamples));
+        const int64_t stride = (int64_t)std::min<uint64_t>(std::max<uint64_t>(1, raw), (uint64_t)std::numeric_limits<int64_t>::max());
+        const int64_t rows_s = (nc - 1) / stride + 1, cols_s = (nl - 1) / stride + 1;
+        std::vector<float> grid((size_t)(rows_s * cols_s));
+        cudaStream_t s;
+        int dev;
+        if (Error e = stats_ctx(img, &s, &dev)) return e;
+        float *d = nullptr;
+        AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), grid.size() * sizeof(float), s));
+        cudaError_t ce = zsample_launch(img->ptr, nc, nl, stride, rows_s, cols_s, d, s);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(grid.data(), d, grid.size() * sizeof(float), cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        cudaFreeAsync(d, s);
+        if (ce != cudaSuccess) return cuda_error(ce, "zsample_kernel");
+        image_note_read(img, s);
+        for (float v : grid)
+            if (v == v) sample.push_back(v);
+    }
+    // v.truncate(maxpix as usize): a negative i32 becomes a huge usize and keeps everything
+    if (nsamples >= 0 && sample.size() > (size_t)nsamples) sample.resize((size_t)nsamples);
+    std::sort(sample.begin(), sample.end()); // no NaN left: partial_cmp never fails
+    const size_t npix = sample.size();
+    if (npix == 0) return ok(); // (None, None)
+    const float zmin = sample.front(), zmax = sample.back();
+    const size_t center_pixel = (npix - 1) / 2;
+    float median;
+    if (npix % 2 == 1) median = sample[center_pixel];
+    else median = 0.5f * (sample[center_pixel] + sample[center_pixel + 1]);
+    const int MIN_NPIXELS = 5, MAX_ITERATIONS = 5;
+    const float MAX_REJECT = 0.5f, KREJ = 2.5f;
+    const int minpix = std::max(MIN_NPIXELS, rust_f32_as_i32((float)npix * MAX_REJECT));
+    const int ngrow = std::max(1, rust_f32_as_i32((float)npix * 0.01f));
+    int ngoodpix;
+    float zslope;
+    zsc_fit_line(sample, (int)npix, KREJ, ngrow, MAX_ITERATIONS, MIN_NPIXELS, MAX_REJECT, &ngoodpix, &zslope);
+    if (ngoodpix < minpix) {
+        *z1 = zmin;
+        *z2 = zmax;
+    } else {
+        if (contrast > 0.0f) zslope = zslope / contrast;
+        // (center_pixel - 1) is usize arithmetic: it would overflow (panic in debug) for npix <= 2, which cannot pass ngoodpix >= 5
+        *z1 = fmaxf(zmin, median - (float)(center_pixel - 1) * zslope);
+        *z2 = fminf(zmax, median + (float)(npix - center_pixel) * zslope);
+    }
+    *has = 1;
+    return ok();
+}
+
+} // namespace afk
+
+using namespace afk;
+
+extern "C" {
+
+afk_status afk_image_histogram(const afk_image *img, float vmin, float vmax, uint64_t counts[100], float starts[100], float ends[100]) {
+    if (!img || !counts) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument"));
+    memset(counts, 0, 100 * sizeof(uint64_t));
+    return fail(histogram_run(img, 1, 100, vmin, vmax, counts, starts, ends));
+}
+
+afk_status afk_image_histogram_color(const afk_image *img, float vmin, float vmax, uint64_t counts[768], float starts[256], float ends[256]) {
+    if (!img || !counts) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument"));
+    if (img->ndim != 3 || img->shape[0] != 3) return fail(make_error(AFK_ERR_SHAPE, "histogram_color needs a [3, ny, nx] image"));
+    memset(counts, 0, 768 * sizeof(uint64_t));
+    return fail(histogram_run(img, 3, 256, vmin, vmax, counts, starts, ends));
+}
+
+afk_status afk_image_vmed_vmad(const afk_image *img, float *vmed, float *vmad) {
+    if (!img || !vmed || !vmad) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument"));
+    return fail(vmed_vmad_run(img, vmed, vmad));
+}
+
+afk_status afk_image_zscale(const afk_image *img, int nsamples, float contrast, int *has_limits, float *z1, float *z2) {
+    if (!img || !has_limits || !z1 || !z2) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument"));
+    return fail(zscale_run(img, nsamples, contrast, has_limits, z1, z2));
+}
+
+} // extern "C"

@@ -266,6 +266,20 @@ size_t afk_lut_bounds(const afk_lut *lut, float *v1, uint8_t *c1, float *v2, uin
 /* lims::get_vmin / get_vmax (aflak_plot/src/lims.rs:7-35): NaN-skipping, NaN when every pixel is NaN */
 afk_status afk_image_vmin_vmax(const afk_image *img, float *vmin, float *vmax);
 
+/* ---- display statistics `Image::new` computes beside the colour mapping (aflak_plot/src/imshow/image.rs:155-176) ---- */
+/* hist::histogram (hist.rs:10-36): 100 bins over [vmin, vmax]; every pixel is counted (NaN and values below vmin in
+ * bin 0, values at or above vmax in bin 99).  starts / ends (may be NULL) receive Bin.start / Bin.end. */
+afk_status afk_image_histogram(const afk_image *img, float vmin, float vmax, uint64_t counts[100], float starts[100], float ends[100]);
+/* hist::histogram_color (hist.rs:38-66): img is [3, ny, nx]; 256 bins; counts[bin * 3 + channel] */
+afk_status afk_image_histogram_color(const afk_image *img, float vmin, float vmax, uint64_t counts[768], float starts[256], float ends[256]);
+/* lims::get_vmed_normalized and get_vmad_normalized(image, vmed) (lims.rs:37-106): median of (v - vmin) / (vmax - vmin)
+ * over the pixels where that is finite, and the median absolute deviation from it.  Exact order statistics.
+ * Errors (AFK_ERR_UNEXPECTED_INPUT): "Empty data!, med", "Empty data!, mad". */
+afk_status afk_image_vmed_vmad(const afk_image *img, float *vmed, float *vmad);
+/* Image::zscale(nsamples, contrast) (zscale.rs:45-100; the UI calls it with (1000, 0.25)): *has_limits = 0 is the
+ * reference's (None, None) */
+afk_status afk_image_zscale(const afk_image *img, int nsamples, float contrast, int *has_limits, float *z1, float *z2);
+
 typedef struct afk_colormap_chain { /* optional fused upstream chain (BASELINE config 4) */
     float logscale_a, logscale_vmin, logscale_vmax; /* convert_to_logscale */
     float normalize_min, normalize_max;             /* normalize_image */

@@ -447,3 +447,38 @@ def gen_cube(seed, nz, ny, nx, y0=0, rows=None, pathology=False, threads=0):
     lib().orc_gen_cube(C.c_uint64(seed), C.c_int64(nz), C.c_int64(ny), C.c_int64(nx), C.c_int64(y0), C.c_int64(rows),
                        C.c_int(int(pathology)), _fp(out), C.c_int(threads or max_threads()))
     return out
+
+
+# ---- display statistics (aflak_plot/src/imshow/hist.rs, lims.rs:37-106, zscale.rs) ---------------------------
+
+def histogram(img, vmin, vmax, color=False):
+    """hist::histogram (100 bins) / histogram_color ([3,ny,nx], 256 bins): (counts, starts, ends)."""
+    img = _f32(img)
+    nb, ch = (256, 3) if color else (100, 1)
+    counts = np.zeros(nb * ch, dtype=np.uint64)
+    lib().orc_histogram(_fp(img), C.c_int64(img.size // ch), C.c_int(ch), C.c_float(vmin), C.c_float(vmax), C.c_int(nb),
+                        counts.ctypes.data_as(C.POINTER(C.c_uint64)))
+    starts, ends = np.empty(nb, dtype=np.float32), np.empty(nb, dtype=np.float32)
+    lib().orc_histogram_bins(C.c_float(vmin), C.c_float(vmax), C.c_int(nb), _fp(starts), _fp(ends))
+    return (counts.reshape(nb, 3) if color else counts), starts, ends
+
+
+def vmed_vmad(img):
+    """(vmed, vmad) of lims::get_vmed_normalized / get_vmad_normalized; raises OracleError for the "Empty data!" cases."""
+    img = _f32(img)
+    vmin, vmax = get_vmin(img), get_vmax(img)
+    med, mad = C.c_float(), C.c_float()
+    if lib().orc_vmed_normalized(_fp(img), C.c_int64(img.size), C.c_float(vmin), C.c_float(vmax), C.byref(med)):
+        raise OracleError(ERR_UNEXPECTED_INPUT, "Empty data!, med")
+    if lib().orc_vmad_normalized(_fp(img), C.c_int64(img.size), C.c_float(vmin), C.c_float(vmax), med, C.byref(mad)):
+        raise OracleError(ERR_UNEXPECTED_INPUT, "Empty data!, mad")
+    return np.float32(med.value), np.float32(mad.value)
+
+
+def zscale(img, nsamples=1000, contrast=0.25):
+    img = _f32(img)
+    assert img.ndim == 2
+    has, z1, z2 = C.c_int(), C.c_float(), C.c_float()
+    _check(lib().orc_zscale(_fp(img), C.c_int64(img.shape[0]), C.c_int64(img.shape[1]), C.c_int(nsamples), C.c_float(contrast),
+                            C.byref(has), C.byref(z1), C.byref(z2)))
+    return (np.float32(z1.value), np.float32(z2.value)) if has.value else (None, None)

@@ -965,6 +965,190 @@ int orc_make_raw_image_rgb(const float *img, int64_t ny, int64_t nx, const float
 }
 
 /* ------------------------------------------------------------------------- */
+/* Display statistics: aflak_plot/src/imshow/hist.rs, lims.rs:37-106, zscale.rs */
+/* ------------------------------------------------------------------------- */
+
+/* hist::histogram (hist.rs:10-36) and histogram_color (hist.rs:38-66): counts is [nb][channels] */
+void orc_histogram(const float *img, int64_t n_per_channel, int channels, float min, float max, int nb, uint64_t *counts) {
+    for (int64_t i = 0; i < (int64_t)nb * channels; ++i) counts[i] = 0;
+    for (int c = 0; c < channels; ++c)
+        for (int64_t k = 0; k < n_per_channel; ++k) {
+            float val = img[(int64_t)c * n_per_channel + k];
+            float fi = (val - min) / (max - min) * (float)nb;
+            uint64_t i = rust_f32_as_usize(fi);
+            if (i >= (uint64_t)nb) i = (uint64_t)nb - 1;
+            counts[i * channels + c] += 1;
+        }
+}
+
+/* Bin.start / Bin.end (hist.rs:16-23) */
+void orc_histogram_bins(float min, float max, int nb, float *starts, float *ends) {
+    float size = (max - min) / (float)nb;
+    for (int i = 0; i < nb; ++i) {
+        starts[i] = min + (float)i * size;
+        ends[i] = min + (float)(i + 1) * size;
+    }
+}
+
+static int median_of_sorted(float *data, int64_t len, float *out) {
+    if (len == 0) return 1;
+    qsort(data, (size_t)len, sizeof(float), cmp_f32);
+    int64_t mid = len / 2;
+    *out = (len % 2 == 0) ? (data[mid] + data[mid - 1]) / 2.0f : data[mid];
+    return 0;
+}
+
+/* lims::get_vmed_normalized (lims.rs:37-67); vmin/vmax from orc_get_vmin/orc_get_vmax. Returns 1 for "Empty data!, med" */
+int orc_vmed_normalized(const float *img, int64_t n, float vmin, float vmax, float *out) {
+    float *data = (float *)malloc((size_t)(n > 0 ? n : 1) * sizeof(float));
+    int64_t len = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        float d = (img[i] - vmin) / (vmax - vmin);
+        if (!isnan(d) && !isinf(d)) data[len++] = d;
+    }
+    int rc = median_of_sorted(data, len, out);
+    free(data);
+    return rc;
+}
+
+/* lims::get_vmad_normalized (lims.rs:69-106) with the median already known. Returns 1 for "Empty data!, mad" */
+int orc_vmad_normalized(const float *img, int64_t n, float vmin, float vmax, float vmed, float *out) {
+    float *data = (float *)malloc((size_t)(n > 0 ? n : 1) * sizeof(float));
+    int64_t len = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        float d = fabsf((img[i] - vmin) / (vmax - vmin) - vmed);
+        if (!isnan(d) && !isinf(d)) data[len++] = d;
+    }
+    int rc = median_of_sorted(data, len, out);
+    free(data);
+    return rc;
+}
+
+static int32_t rust_f32_as_i32(float f) {
+    if (f != f) return 0;
+    if (f >= 2147483648.0f) return INT32_MAX;
+    if (f <= -2147483648.0f) return INT32_MIN;
+    return (int32_t)f;
+}
+
+/* zsc_compute_sigma, zscale.rs:205-241 */
+static void zsc_sigma(const float *flat, const int *badpix, int npix, int *ngoodpix, int *has_mean, int *has_sigma, float *sigma) {
+    float sumz = 0.0f, sumsq = 0.0f;
+    int ng = 0;
+    for (int i = 0; i < npix; ++i)
+        if (badpix[i] == 0) sumz = sumz + flat[i];
+    for (int i = 0; i < npix; ++i)
+        if (badpix[i] == 0) sumsq = sumsq + flat[i] * flat[i];
+    for (int i = 0; i < npix; ++i) ng += badpix[i] == 0;
+    *ngoodpix = ng;
+    *has_mean = ng >= 1;
+    *has_sigma = 0;
+    if (ng >= 2) {
+        float temp = sumsq / (float)(ng - 1) - sumz * sumz / (float)(ng * (ng - 1));
+        *has_sigma = 1;
+        *sigma = temp < 0.0f ? 0.0f : sqrtf(temp);
+    }
+}
+
+/*
+ * Image::zscale(nsamples, contrast), zscale.rs:45-100, with zsc_sample (:101-126: every stride-th pixel of every
+ * stride-th row of the vertically flipped image, NaN dropped, truncated to nsamples) and zsc_fit_line (:127-203).
+ * img is [nc][nl] (dim.0, dim.1).  *has = 0 is (None, None).
+ */
+int orc_zscale(const float *img, int64_t nc, int64_t nl, int nsamples, float contrast, int *has, float *z1, float *z2) {
+    *has = 0;
+    if (nc <= 0 || nl <= 0) return ORC_OK;
+    uint64_t st = rust_f32_as_usize(sqrtf((float)((uint64_t)(nc - 1) * (uint64_t)(nl - 1)) / (float)nsamples));
+    if (st < 1) st = 1;
+    if (st > (uint64_t)INT64_MAX) st = (uint64_t)INT64_MAX;
+    int64_t stride = (int64_t)st;
+    int64_t cap = ((nc - 1) / stride + 1) * ((nl - 1) / stride + 1);
+    float *sample = (float *)malloc((size_t)cap * sizeof(float));
+    int64_t np_ = 0;
+    for (int64_t r = 0; r < nc; r += stride) {
+        const float *line = img + (nc - 1 - r) * nl; /* flipped rows, image.rs:123-129 */
+        for (int64_t c = 0; c < nl; c += stride)
+            if (!isnan(line[c])) sample[np_++] = line[c];
+        if (stride > nc) break;
+    }
+    if (nsamples >= 0 && np_ > (int64_t)nsamples) np_ = nsamples; /* truncate(maxpix as usize) */
+    if (np_ == 0) {
+        free(sample);
+        return ORC_OK;
+    }
+    qsort(sample, (size_t)np_, sizeof(float), cmp_f32);
+    int npix = (int)np_;
+    float zmin = sample[0], zmax = sample[npix - 1];
+    int center_pixel = (npix - 1) / 2;
+    float median = (npix % 2 == 1) ? sample[center_pixel] : 0.5f * (sample[center_pixel] + sample[center_pixel + 1]);
+    const int MIN_NPIXELS = 5, MAX_ITERATIONS = 5;
+    const float MAX_REJECT = 0.5f, KREJ = 2.5f;
+    int minpix = rust_f32_as_i32((float)npix * MAX_REJECT);
+    if (minpix < MIN_NPIXELS) minpix = MIN_NPIXELS;
+    int ngrow = rust_f32_as_i32((float)npix * 0.01f);
+    if (ngrow < 1) ngrow = 1;
+    /* zsc_fit_line */
+    float xscale = 2.0f / (float)(npix - 1);
+    float *xnorm = (float *)malloc((size_t)npix * sizeof(float));
+    float *flat = (float *)malloc((size_t)npix * sizeof(float));
+    int *badpix = (int *)calloc((size_t)npix, sizeof(int));
+    int *nextbad = (int *)malloc((size_t)npix * sizeof(int));
+    for (int v = 0; v < npix; ++v) xnorm[v] = (float)v * xscale - 1.0f;
+    int ngoodpix = npix, last_ngoodpix = npix + 1;
+    float slope = 0.0f, intercept = 0.0f;
+    for (int it = 0; it < MAX_ITERATIONS; ++it) {
+        if (ngoodpix >= last_ngoodpix || ngoodpix < minpix) break;
+        int sum = 0;
+        float sumx = 0.0f, sumxx = 0.0f, sumxy = 0.0f, sumy = 0.0f;
+        for (int i = 0; i < npix; ++i) if (badpix[i] == 0) { sum += 1; sumx = sumx + xnorm[i]; }
+        for (int i = 0; i < npix; ++i) if (badpix[i] == 0) sumxx = sumxx + xnorm[i] * xnorm[i];
+        for (int i = 0; i < npix; ++i) if (badpix[i] == 0) sumxy = sumxy + xnorm[i] * sample[i];
+        for (int i = 0; i < npix; ++i) if (badpix[i] == 0) sumy = sumy + sample[i];
+        float delta = (float)sum * sumxx - sumx * sumx;
+        intercept = (sumxx * sumy - sumx * sumxy) / delta;
+        slope = ((float)sum * sumxy - sumx * sumy) / delta;
+        for (int i = 0; i < npix; ++i) {
+            float fitted = xnorm[i] * slope + intercept;
+            flat[i] = sample[i] - fitted;
+        }
+        int ng, has_mean, has_sigma;
+        float sigma = 0.0f;
+        zsc_sigma(flat, badpix, npix, &ng, &has_mean, &has_sigma, &sigma);
+        ngoodpix = ng;
+        if (has_mean && has_sigma) {
+            float threshold = sigma * KREJ, lcut = -threshold, hcut = threshold;
+            for (int i = 0; i < npix; ++i) nextbad[i] = (flat[i] < lcut || flat[i] > hcut) ? 1 : 0;
+            /* convolve(next_badpix, vec![1, ngrow]) */
+            for (int head = 0; head < npix; ++head) {
+                int data = 0;
+                const int filter[2] = {1, ngrow};
+                for (int m = 0; m < 2; ++m) {
+                    if (head < m) break;
+                    data += nextbad[head - m] * filter[m];
+                }
+                badpix[head] = data;
+            }
+            ngoodpix = 0;
+            for (int i = 0; i < npix; ++i) ngoodpix += badpix[i] == 0;
+        }
+    }
+    float zslope = slope * xscale;
+    (void)intercept;
+    if (ngoodpix < minpix) {
+        *z1 = zmin;
+        *z2 = zmax;
+    } else {
+        if (contrast > 0.0f) zslope = zslope / contrast;
+        float a = median - (float)(center_pixel - 1) * zslope, b = median + (float)(npix - center_pixel) * zslope;
+        *z1 = fmaxf(zmin, a);
+        *z2 = fminf(zmax, b);
+    }
+    *has = 1;
+    free(sample); free(xnorm); free(flat); free(badpix); free(nextbad);
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------------------- */
 /* Synthetic generator (not from the reference; shared bit-for-bit with the    */
 /* device generator in aflak_b200/csrc/gen.cuh -- only +,-,*,/ in f32)         */
 /* ------------------------------------------------------------------------- */

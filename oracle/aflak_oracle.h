@@ -109,6 +109,13 @@ int orc_make_raw_image_rgb(const float *img, int64_t ny, int64_t nx, const float
 int orc_make_raw_image_mt(const float *img, int64_t ny, int64_t nx, float vmin, float vmax, const uint8_t *lut,
                           const float lims[3], int channels, uint8_t *out, int threads);
 
+/* ---- display statistics (aflak_plot/src/imshow/hist.rs, lims.rs:37-106, zscale.rs) ---- */
+void orc_histogram(const float *img, int64_t n_per_channel, int channels, float min, float max, int nb, uint64_t *counts);
+void orc_histogram_bins(float min, float max, int nb, float *starts, float *ends);
+int orc_vmed_normalized(const float *img, int64_t n, float vmin, float vmax, float *out);
+int orc_vmad_normalized(const float *img, int64_t n, float vmin, float vmax, float vmed, float *out);
+int orc_zscale(const float *img, int64_t nc, int64_t nl, int nsamples, float contrast, int *has, float *z1, float *z2);
+
 /* ---- synthetic cube generator shared with the device (DESIGN.md "Synthetic inputs") ---- */
 /* fills out[nz, rows, nx] for rows [y0, y0+rows) of a cube whose full size is [nz, ny, nx] */
 void orc_gen_cube(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t y0, int64_t rows, int pathology,

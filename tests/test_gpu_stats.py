@@ -1,0 +1,116 @@
+"""GPU parity: display statistics -- histogram, normalised median / MAD, zscale.
+
+Reference: aflak_plot/src/imshow/hist.rs:10-66, lims.rs:37-106, zscale.rs:45-242, image.rs:155-176.
+Tier A: counts, order statistics and zscale limits are bit-identical to the oracle's restatement.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def images(orc):
+    rng = np.random.default_rng(21)
+    yield "lognormal 257x300", rng.lognormal(0.0, 1.0, (257, 300)).astype(np.float32)
+    a = rng.normal(100.0, 15.0, (512, 512)).astype(np.float32)
+    a[::37, ::11] = np.nan
+    yield "normal 512x512 with NaN", a.copy()
+    a[5, 5] = np.inf
+    yield "normal 512x512 with NaN and +Inf", a.copy()
+    a[6, 6] = -np.inf
+    yield "normal 512x512 with NaN and +-Inf", a
+    yield "cube frame 74x74", orc.gen_cube(0xAF1A0021, 8, 74, 74)[3]
+    b = np.round(rng.normal(0, 3, (129, 67))).astype(np.float32)  # heavy ties
+    yield "quantised 129x67", b
+    yield "single row 1x1000", rng.uniform(-1, 1, (1, 1000)).astype(np.float32)
+    yield "tiny 2x2", np.array([[1.0, 2.0], [4.0, 8.0]], np.float32)
+    yield "even count 4x5", rng.uniform(0, 1, (4, 5)).astype(np.float32)
+
+
+def test_histogram_counts_exact(gpu, orc):
+    for name, a in images(orc):
+        img = gpu.Image.upload(a)
+        fin = a[np.isfinite(a)]
+        for vmin, vmax in [(float(fin.min()), float(fin.max())), (float(np.median(fin)), float(fin.max())), (0.0, 1.0)]:
+            got, s0, e0 = img.histogram(vmin, vmax)
+            want, s1, e1 = orc.histogram(a, vmin, vmax)
+            assert np.array_equal(got, want), f"{name} [{vmin},{vmax}]"
+            assert got.sum() == a.size
+            assert np.array_equal(s0, s1) and np.array_equal(e0, e1)
+
+
+def test_histogram_color(gpu, orc):
+    rng = np.random.default_rng(22)
+    rgb = rng.uniform(-100, 70000, (3, 211, 130)).astype(np.float32)
+    rgb[1, ::7] = np.nan
+    got, s0, e0 = gpu.Image.upload(rgb).histogram(0.0, 65535.0, color=True)
+    want, s1, e1 = orc.histogram(rgb, 0.0, 65535.0, color=True)
+    assert got.shape == (256, 3) and np.array_equal(got, want) and np.array_equal(s0, s1) and np.array_equal(e0, e1)
+    e = None
+    try:
+        gpu.Image.upload(rgb[:2]).histogram(0.0, 1.0, color=True)
+    except gpu.AflakError as err:
+        e = err
+    assert e is not None and e.status == gpu.ERR_SHAPE
+
+
+def test_vmed_vmad_bit_exact(gpu, orc):
+    for name, a in images(orc):
+        try:
+            want = orc.vmed_vmad(a)
+        except orc.OracleError as err:  # vmin = -inf / vmax = +inf: every normalised value is NaN -> "Empty data!, med"
+            with pytest.raises(gpu.AflakError) as e:
+                gpu.Image.upload(a).vmed_vmad()
+            assert err.msg in str(e.value), name
+            continue
+        got = gpu.Image.upload(a).vmed_vmad()
+        assert got[0].tobytes() == want[0].tobytes() and got[1].tobytes() == want[1].tobytes(), f"{name}: {got} != {want}"
+
+
+def test_vmed_vmad_full_size_c4(gpu, orc):
+    """4096 x 4096 (BASELINE config 4 size): the select runs over 16.7 M pixels; checked against numpy's partition."""
+    rng = np.random.default_rng(23)
+    a = rng.lognormal(0.0, 1.0, (4096, 4096)).astype(np.float32)
+    a[::1000, ::3] = np.nan
+    got = gpu.Image.upload(a).vmed_vmad()
+    vmin, vmax = np.nanmin(a), np.nanmax(a)
+    d = ((a - vmin) / (vmax - vmin)).reshape(-1)
+    d = d[np.isfinite(d)]
+    mid = d.size // 2
+    part = np.partition(d, [mid - 1, mid])
+    vmed = (part[mid] + part[mid - 1]) / np.float32(2.0) if d.size % 2 == 0 else part[mid]
+    e = np.abs(d - vmed)
+    part = np.partition(e, [mid - 1, mid])
+    vmad = (part[mid] + part[mid - 1]) / np.float32(2.0) if d.size % 2 == 0 else part[mid]
+    assert got[0] == np.float32(vmed) and got[1] == np.float32(vmad)
+
+
+def test_vmed_vmad_errors(gpu, orc):
+    for a in [np.full((5, 5), 2.0, np.float32), np.full((3, 3), np.nan, np.float32)]:
+        with pytest.raises(gpu.AflakError) as e:
+            gpu.Image.upload(a).vmed_vmad()
+        assert e.value.status == gpu.ERR_UNEXPECTED_INPUT and "Empty data!, med" in str(e.value)
+
+
+def test_zscale_bit_exact(gpu, orc):
+    rng = np.random.default_rng(24)
+    cases = list(images(orc))
+    big = rng.lognormal(0.0, 1.0, (1500, 2100)).astype(np.float32)
+    big[::50] = np.nan
+    cases.append(("lognormal 1500x2100, NaN rows", big))
+    star = rng.normal(10.0, 1.0, (600, 600)).astype(np.float32)
+    star[280:320, 280:320] += 500.0  # a bright source: the iterative rejection kicks in
+    cases.append(("gaussian + source", star))
+    for name, a in cases:
+        img = gpu.Image.upload(a)
+        for nsamples, contrast in [(1000, 0.25), (1000, 1.0), (100, 0.25), (37, -1.0), (5, 0.25)]:
+            got = img.zscale(nsamples, contrast)
+            want = orc.zscale(a, nsamples, contrast)
+            if want[0] is None:
+                assert got == (None, None), name
+            else:
+                assert got[0].tobytes() == want[0].tobytes() and got[1].tobytes() == want[1].tobytes(), f"{name} ({nsamples},{contrast}): {got} != {want}"
+    assert gpu.Image.upload(np.full((6, 6), np.nan, np.float32)).zscale() == (None, None)
+    assert gpu.Image.upload(cases[0][1]).zscale(0, 0.25) == (None, None)
+    with pytest.raises(gpu.AflakError):  # zsc_sample fails on anything but 2-D and the reference unwraps it
+        gpu.Image.upload(np.zeros((2, 3, 4), np.float32)).zscale()

@@ -233,3 +233,50 @@ def test_centroid_kat(orc):
     assert m[0, 0] == 11.0 and m[0, 1] == 11.0
     with pytest.raises(orc.OracleError):
         orc.centroid_mask(cube, lo, np.array([[21.0, 20.0]], np.float32))
+
+
+# ---- display statistics (aflak_plot hist.rs, lims.rs:37-106, zscale.rs): known answers ---------------------------------
+
+def test_histogram_kat(orc):
+    img = np.array([[0.0, 0.5, 9.99, 10.0], [np.nan, -3.0, 25.0, 5.0]], np.float32)
+    counts, starts, ends = orc.histogram(img, 0.0, 10.0)
+    assert counts.sum() == 8                      # every pixel is counted
+    assert counts[0] == 3                         # 0.0, NaN (as usize -> 0) and -3.0 (saturates to 0)
+    assert counts[5] == 1 and counts[50] == 1     # 0.5 -> 5, 5.0 -> 50
+    assert counts[99] == 3                        # 9.99 -> 99, 10.0 -> 100 -> clamped, 25.0 clamped
+    assert starts[0] == 0.0 and ends[99] == np.float32(0.0) + np.float32(100.0) * (np.float32(10.0) / np.float32(100.0))
+    rgb = np.stack([np.full((2, 2), 0.0), np.full((2, 2), 65535.0), np.full((2, 2), 32768.0)]).astype(np.float32)
+    c3, _, _ = orc.histogram(rgb, 0.0, 65535.0, color=True)
+    assert c3.shape == (256, 3) and c3[0, 0] == 4 and c3[255, 1] == 4 and c3[128, 2] == 4 and c3.sum() == 12
+
+
+def test_vmed_vmad_kat(orc):
+    # values 0..4 -> normalised 0, .25, .5, .75, 1 -> median .5, deviations .5 .25 0 .25 .5 -> MAD .25
+    img = np.array([[3, 0, 4], [1, 2, np.nan]], np.float32)
+    vmed, vmad = orc.vmed_vmad(img)
+    assert vmed == 0.5 and vmad == 0.25
+    # even count: mean of the two middle values
+    img = np.array([0, 1, 2, 4], np.float32)
+    vmed, vmad = orc.vmed_vmad(img)
+    assert vmed == np.float32(0.375) and vmad == np.float32((np.float32(0.125) + np.float32(0.375)) / 2)
+    with pytest.raises(orc.OracleError):          # constant image: (v - vmin) / 0 is NaN everywhere
+        orc.vmed_vmad(np.full((3, 3), 2.0, np.float32))
+
+
+def test_zscale_kat(orc):
+    # a linear ramp is its own fit: nothing is rejected.  30x30 -> stride 1, all 900 samples, slope 1 per sample:
+    # z1 = max(zmin, median - (center_pixel - 1) * slope / contrast), z2 = min(zmax, median + (npix - center_pixel) * slope / contrast)
+    img = np.arange(30 * 30, dtype=np.float32).reshape(30, 30)
+    assert orc.zscale(img, 1000, 0.25) == (0.0, 899.0)            # slope x4: both limits clamp to the sample range
+    z1, z2 = orc.zscale(img, 1000, 1.0)
+    assert abs(float(z1) - (449.5 - 448.0)) < 1e-2 and z2 == 899.0
+    # 32x32 with nsamples 1000: the sample is the first 1000 pixels of the *flipped* image (rows 31..1 and 8 pixels of row 0)
+    img = np.arange(32 * 32, dtype=np.float32).reshape(32, 32)
+    assert orc.zscale(img, 1000, 0.25) == (0.0, 1023.0)
+    img[0, :8] = -50.0   # inside the sample
+    img[0, 8:] = -99.0   # beyond the truncation
+    assert orc.zscale(img, 1000, 0.25)[0] == -50.0
+    assert orc.zscale(np.full((4, 4), np.nan, np.float32)) == (None, None)
+    assert orc.zscale(img, 0, 0.25) == (None, None)
+    z1, z2 = orc.zscale(np.full((40, 40), 3.0, np.float32))   # constant image: slope 0 -> both limits are the value
+    assert z1 == 3.0 and z2 == 3.0
