@@ -120,6 +120,13 @@ _sig("afk_value_str", _P, C.c_char_p)
 _sig("afk_value_bool", _P, C.c_int)
 _sig("afk_value_image", _P, _P)
 _sig("afk_value_tone_curve", _P, _fp, C.c_size_t, _fp, C.c_size_t)
+_sig("afk_value_roi_all", _P)
+_sig("afk_value_roi_pixels", _P, C.POINTER(C.c_uint64), C.c_size_t)
+_sig("afk_value_roi_is_all", C.c_int, _P)
+_sig("afk_value_roi_count", C.c_size_t, _P)
+_sig("afk_value_roi_data", C.POINTER(C.c_uint64), _P)
+_sig("afk_value_map2dto3d", _P, _fp, C.c_int64, C.c_int64)
+_sig("afk_value_get_map", _fp, _P, _i64p, _i64p)
 _sig("afk_value_fits", _P, _P)
 _sig("afk_value_get_fits", _P, _P)
 _sig("afk_value_paths", _P, C.POINTER(C.c_char_p), C.c_size_t)
@@ -446,6 +453,27 @@ class Paths(list):
     """PATHS::FileList"""
 
 
+class Roi:
+    """roi::ROI: Roi() is ROI::All, Roi([(x, y), ...]) is ROI::PixelList (pairs are (i, j) = (column, row))."""
+
+    def __init__(self, pixels=None):
+        self.pixels = None if pixels is None else [(int(x), int(y)) for x, y in pixels]
+
+    def __eq__(self, other):
+        return isinstance(other, Roi) and self.pixels == other.pixels
+
+    def __repr__(self):
+        return "Roi(All)" if self.pixels is None else f"Roi({len(self.pixels)} pixels)"
+
+
+class Map3d:
+    """Map2dTo3dCoords: Array2<[f32; 3]> as a [rows, cols, 3] float32 array."""
+
+    def __init__(self, xyz):
+        self.xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+        assert self.xyz.ndim == 3 and self.xyz.shape[2] == 3
+
+
 class ToneCurve:
     """ToneCurveState: `arr` table + control points (imgui_tone_curve/src/lib.rs:10-48)."""
 
@@ -454,8 +482,24 @@ class ToneCurve:
         self.cp = np.ascontiguousarray(cp, dtype=np.float32).reshape(-1, 2)
 
 
+class Value:
+    """An IOValue converted once and kept (like a constant node or a cached output of the cake graph): passing it to
+    several calls reuses the same afk_value, including whatever the library has attached to it (the device copy of a mesh)."""
+
+    def __init__(self, x):
+        self._v = C.c_void_p(_to_value(x))
+
+    def __del__(self):
+        if getattr(self, "_v", None) and lib is not None:
+            lib.afk_value_release(self._v)
+            self._v = None
+
+
 def _to_value(x):
     """Python object -> new afk_value* (caller releases)."""
+    if isinstance(x, Value):
+        lib.afk_value_retain(x._v)
+        return x._v.value
     if isinstance(x, Image):
         return lib.afk_value_image(x.handle)
     if isinstance(x, bool):
@@ -466,6 +510,13 @@ def _to_value(x):
         return lib.afk_value_float(float(x))
     if isinstance(x, str):
         return lib.afk_value_str(x.encode())
+    if isinstance(x, Roi):
+        if x.pixels is None:
+            return lib.afk_value_roi_all()
+        a = np.ascontiguousarray(x.pixels, dtype=np.uint64).reshape(-1)
+        return lib.afk_value_roi_pixels(a.ctypes.data_as(C.POINTER(C.c_uint64)), a.size // 2)
+    if isinstance(x, Map3d):
+        return lib.afk_value_map2dto3d(x.xyz.ctypes.data_as(_fp), x.xyz.shape[0], x.xyz.shape[1])
     if isinstance(x, Fits):
         return lib.afk_value_fits(x.handle)
     if isinstance(x, Paths):
@@ -511,6 +562,17 @@ def _from_value(v):
         buf = (C.c_float * 4096)()
         n = lib.afk_value_get_floats(v, buf, 4096)
         return ToneCurve(np.array(buf[:n], dtype=np.float32))
+    if t == T_ROI:
+        if lib.afk_value_roi_is_all(v):
+            return Roi()
+        n = lib.afk_value_roi_count(v)
+        d = lib.afk_value_roi_data(v)
+        return Roi([(d[2 * i], d[2 * i + 1]) for i in range(n)])
+    if t == T_MAP2DTO3DCOORDS:
+        r, c = C.c_int64(), C.c_int64()
+        p = lib.afk_value_get_map(v, C.byref(r), C.byref(c))
+        n = r.value * c.value * 3
+        return Map3d(np.ctypeslib.as_array(p, shape=(n,)).copy().reshape(r.value, c.value, 3) if n else np.zeros((r.value, c.value, 3), np.float32))
     if t == T_FITS:
         return Fits(lib.afk_value_get_fits(v), retain=True)
     if t == T_PATHS:

@@ -118,6 +118,17 @@ struct afk_value {
     std::vector<float> cp;  // ToneCurve control points (x,y pairs)
     std::vector<std::string> paths; // PATHS::FileList
     afk_fits *fits = nullptr;       // Arc<fitrs::Fits>
+    bool roi_all = true;            // ROI::All, else ROI::PixelList(roi_xy)
+    std::vector<uint64_t> roi_xy;   // (i, j) = (x, y) pairs (roi.rs:5-10)
+    std::vector<float> map;         // Map2dTo3dCoords: Array2<[f32; 3]>, [map_rows][map_cols][3]
+    int64_t map_rows = 0, map_cols = 0;
+    // lazily built by slice_3d_to_2d and kept with the (immutable) value: device copy of the mesh and its axis analysis
+    std::mutex map_mu;
+    float *map_dev = nullptr;
+    int map_dev_device = -1;
+    int map_sliced = -1; // -1 not analysed, 0 None, 1 Some(map_axis, map_start, map_step)
+    int map_axis[2] = {0, 0};
+    float map_start[2] = {0, 0}, map_step[2] = {0, 0};
 };
 
 namespace afk {
@@ -158,6 +169,23 @@ void set_image(afk_result *r, afk_image *img); // takes over the caller's refere
 bool args_match(const afk_value *const *in, size_t n_in, std::initializer_list<afk_type> types, afk_result *out, size_t n_out);
 Error unexpected(const std::string &m);
 Error try_into_unsigned(const char *name, int64_t v);
+
+// operators of ops_spatial.cpp
+#define AFK_DECL_OP(name) afk_status name(const afk_value *const *in, size_t n_in, afk_result *out, size_t n_out)
+AFK_DECL_OP(op_make_float3);
+AFK_DECL_OP(op_make_plane3d);
+AFK_DECL_OP(op_slice_3d_to_2d);
+AFK_DECL_OP(op_extrude);
+AFK_DECL_OP(op_extract_wave);
+AFK_DECL_OP(op_create_velocity_field_map);
+AFK_DECL_OP(op_histogram_transformation);
+AFK_DECL_OP(op_histogram_transformation_rgb);
+AFK_DECL_OP(op_apply_arcsinh_stretch);
+AFK_DECL_OP(op_color_image_to_hsv);
+AFK_DECL_OP(op_color_image_from_rgb);
+Error are_same_dim(const char *n1, const afk_image *a, const char *n2, const afk_image *b);
+Error same_device(const afk_image *a, int device);
+std::string rust_f32_display(float f);
 
 // FITS operators (fits.cpp)
 afk_status op_open_fits(const afk_value *const *in, size_t n_in, afk_result *out, size_t n_out);

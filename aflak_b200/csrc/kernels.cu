@@ -575,6 +575,7 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
 struct MapK {
     float a, b, c, ln_a;
     int flag0, flag1;
+    float d, e;
 };
 
 template <int OP> __device__ __forceinline__ float map_one(float u, float v, const MapK &k) {
@@ -592,6 +593,18 @@ template <int OP> __device__ __forceinline__ float map_one(float u, float v, con
         float d = __fdiv_rn(__fsub_rn(u, k.b), __fsub_rn(k.c, k.b));
         float t = __fadd_rn(__fmul_rn(k.a, d), 1.0f);
         return __fdiv_rn(logf(t), k.ln_a);
+    }
+    if (OP == MAP_VELOCITY) return __fdiv_rn(__fmul_rn(__fsub_rn(u, k.a), 3e5f), k.a); // (image - w_0) * c / w_0
+    if (OP == MAP_HISTTRANS) {
+        // min = a, max = b, parameters = (c, d, e): every step rounded like the closure at lib.rs:574-586
+        const float range = __fsub_rn(k.b, k.a);
+        const float point = __fdiv_rn(__fsub_rn(u, k.a), range);
+        const float x = __fdiv_rn(__fsub_rn(point, k.c), __fsub_rn(k.e, k.c));
+        float c;
+        if (x > 1.0f) c = 1.0f;
+        else if (x < 0.0f) c = 0.0f;
+        else c = __fdiv_rn(__fmul_rn(__fsub_rn(k.d, 1.0f), x), __fsub_rn(__fmul_rn(__fsub_rn(__fmul_rn(2.0f, k.d), 1.0f), x), k.d));
+        return __fadd_rn(__fmul_rn(c, range), k.a);
     }
     if (OP == MAP_LOG10) return log10f(u);
     if (OP == MAP_NEGATION) return -u;
@@ -640,7 +653,7 @@ template <int OP, bool BINARY> static void map_go(const MapArgs &a, const MapK &
 
 cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
-    MapK k{a.a, a.b, a.c, 0.0f, a.flag0, a.flag1};
+    MapK k{a.a, a.b, a.c, 0.0f, a.flag0, a.flag1, a.d, a.e};
     if (a.op == MAP_LOGSCALE) k.ln_a = logf(a.a); // a.ln(): host libm, same call the reference makes
     auto al = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
     const int vec_ok = al(a.u) && al(a.out) && (a.v == nullptr || al(a.v));
@@ -657,8 +670,74 @@ cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s) {
     case MAP_NORMALIZE: map_go<MAP_NORMALIZE, false>(a, k, vec_ok, grid, s); break;
     case MAP_CLIP: map_go<MAP_CLIP, false>(a, k, vec_ok, grid, s); break;
     case MAP_REPLACE_NAN: map_go<MAP_REPLACE_NAN, false>(a, k, vec_ok, grid, s); break;
+    case MAP_VELOCITY: map_go<MAP_VELOCITY, false>(a, k, vec_ok, grid, s); break;
+    case MAP_HISTTRANS: map_go<MAP_HISTTRANS, false>(a, k, vec_ok, grid, s); break;
     default: return cudaErrorInvalidValue;
     }
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
+}
+
+// per-pixel operators across the 3 channels of a [3][n] image: 12 bytes read + 12 written per pixel, one pass
+template <int OP> __device__ __forceinline__ void color3_one(float r, float g, float b, float beta, double asinh_beta, float (&o)[3]) {
+    if (OP == C3_ARCSINH) {
+        // l = (data[0] + data[1] + data[2]) / 3.0; s_fact = asinh((l * beta) as f64) / (l as f64 * asinh(beta as f64)) as f32
+        const float l = __fdiv_rn(__fadd_rn(__fadd_rn(r, g), b), 3.0f);
+        const float s = (float)(asinh((double)__fmul_rn(l, beta)) / ((double)l * asinh_beta));
+        o[0] = __fmul_rn(s, r); o[1] = __fmul_rn(s, g); o[2] = __fmul_rn(s, b);
+    } else {
+        // Rust f32::max / min return the other operand when one is NaN == fmaxf / fminf
+        const float mx = fmaxf(fmaxf(r, g), b), mn = fminf(fminf(r, g), b);
+        const float range = __fsub_rn(mx, mn);
+        float hue = 0.0f;
+        if (r >= g && r >= b) hue = __fmul_rn(60.0f, __fdiv_rn(__fsub_rn(g, b), range));
+        else if (g >= r && g >= b) hue = __fadd_rn(__fmul_rn(60.0f, __fdiv_rn(__fsub_rn(b, r), range)), 120.0f);
+        else if (b >= r && b >= g) hue = __fadd_rn(__fmul_rn(60.0f, __fdiv_rn(__fsub_rn(r, g), range)), 240.0f);
+        if (hue < 0.0f) hue = __fadd_rn(hue, 360.0f);
+        o[0] = __fmul_rn(__fdiv_rn(hue, 360.0f), 65535.0f);
+        o[1] = __fmul_rn(__fdiv_rn(range, mx), 65535.0f);
+        o[2] = mx;
+    }
+}
+
+template <int OP>
+__global__ void __launch_bounds__(256) color3_kernel(const float *__restrict__ img, int64_t n, float beta, double asinh_beta,
+                                                      float *__restrict__ out, int vec_ok) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t n4 = n >> 2;
+        for (int64_t i = tid; i < n4; i += nthreads) {
+            const float4 r = ld_stream(reinterpret_cast<const float4 *>(img) + i);
+            const float4 g = ld_stream(reinterpret_cast<const float4 *>(img + n) + i);
+            const float4 b = ld_stream(reinterpret_cast<const float4 *>(img + 2 * n) + i);
+            float o0[3], o1[3], o2[3], o3[3];
+            color3_one<OP>(r.x, g.x, b.x, beta, asinh_beta, o0);
+            color3_one<OP>(r.y, g.y, b.y, beta, asinh_beta, o1);
+            color3_one<OP>(r.z, g.z, b.z, beta, asinh_beta, o2);
+            color3_one<OP>(r.w, g.w, b.w, beta, asinh_beta, o3);
+            reinterpret_cast<float4 *>(out)[i] = make_float4(o0[0], o1[0], o2[0], o3[0]);
+            reinterpret_cast<float4 *>(out + n)[i] = make_float4(o0[1], o1[1], o2[1], o3[1]);
+            reinterpret_cast<float4 *>(out + 2 * n)[i] = make_float4(o0[2], o1[2], o2[2], o3[2]);
+        }
+        done = n4 << 2;
+    }
+    for (int64_t i = done + tid; i < n; i += nthreads) {
+        float o[3];
+        color3_one<OP>(img[i], img[n + i], img[2 * n + i], beta, asinh_beta, o);
+        out[i] = o[0]; out[n + i] = o[1]; out[2 * n + i] = o[2];
+    }
+}
+
+cudaError_t color3_launch(int op, const float *img, int64_t n, float beta, float *out, int sm_count, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    const int vec_ok = (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(img) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
+    const int grid = grid_for(vec_ok ? (n + 3) / 4 : n, 256, sm_count, 8);
+    const double asinh_beta = asinh((double)beta); // host libm: the same f64 value for every pixel, as in the reference
+    if (op == C3_ARCSINH) color3_kernel<C3_ARCSINH><<<grid, 256, 0, s>>>(img, n, beta, asinh_beta, out, vec_ok);
+    else if (op == C3_TO_HSV) color3_kernel<C3_TO_HSV><<<grid, 256, 0, s>>>(img, n, beta, asinh_beta, out, vec_ok);
+    else return cudaErrorInvalidValue;
     AFK_COUNT_LAUNCH();
     return cudaGetLastError();
 }

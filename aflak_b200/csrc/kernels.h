@@ -146,6 +146,8 @@ enum MapOp : int {
     MAP_CLIP = 8,       // NaN where (ceil && u >= a) || (floor && u <= b)  lib.rs:1258-1274
     MAP_REPLACE_NAN = 9,// u is NaN ? a : u                                 lib.rs:1276-1286
     MAP_EMISSION_LINE = 10, // like EW without the division                 lib.rs run_create_emission_line_map
+    MAP_VELOCITY = 11,  // out = ((u - a) * 3e5) / a                        lib.rs:509-526
+    MAP_HISTTRANS = 12, // midtone transfer between min=a, max=b with parameters (c, d, e)   lib.rs:562-591
 };
 
 struct MapArgs {
@@ -156,6 +158,7 @@ struct MapArgs {
     int flag0, flag1;
     int64_t n;
     float *out;
+    float d = 0.0f, e = 0.0f; // MAP_HISTTRANS only
 };
 cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s);
 
@@ -164,6 +167,24 @@ cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s);
 constexpr int kMaxToneTable = 4096;
 cudaError_t tone_curve_launch(const float *img, int64_t n, const float *table_dev, int table_len, float *out,
                               unsigned *oob_flag, int sm_count, cudaStream_t s);
+
+// per-pixel operators on 3-channel [3][n] images
+enum Color3Op : int {
+    C3_ARCSINH = 0, // apply_arcsinh_stretch (lib.rs:1873-1892): s = asinh(l*beta) / (l * asinh(beta)) in f64, l = (r+g+b)/3
+    C3_TO_HSV = 1,  // color_image_to_hsv   (lib.rs:1795-1826)
+};
+cudaError_t color3_launch(int op, const float *img, int64_t n_per_channel, float beta, float *out, int sm_count, cudaStream_t s);
+
+// ---- spatial reductions / gathers (spatial.cu) ---------------------------------------------------
+// extract_wave: out[k] = sum over the region (offsets_dev: linear pixel offsets in list order, or nullptr = whole frame)
+size_t wave_partial_bytes(int64_t nz, int64_t count, int *chunks_out, int64_t *chunk_out);
+cudaError_t wave_launch(const float *cube, int64_t nz, int64_t n2, const int64_t *offsets_dev, int64_t count, int mode, void *partials,
+                        float *out, cudaStream_t s);
+cudaError_t extrude_launch(const float *cube, int64_t nz, int64_t n2, const int64_t *offsets_dev, int64_t count, float *out, int sm_count,
+                           cudaStream_t s);
+// *first_bad (device, initialised to ~0ull) receives the smallest map index that falls outside the cube
+cudaError_t slice3d_launch(const float *cube, int64_t d0, int64_t d1, int64_t d2, const float *map_dev, int64_t n, float *out,
+                           unsigned long long *first_bad, int sm_count, cudaStream_t s);
 
 // ---- min/max (K4) -------------------------------------------------------------
 // result[0] = ~key(min), result[1] = key(max), result[2] = number-of-non-NaN > 0 ; all via atomicMax, zero-init.

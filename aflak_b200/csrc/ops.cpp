@@ -194,7 +194,7 @@ static std::string dim_debug(const afk_image *img) { // {:?} of IxDyn: "[4563, 7
     return s + "]";
 }
 
-static Error are_same_dim(const char *n1, const afk_image *a, const char *n2, const afk_image *b) { // precond.rs:101-114
+Error are_same_dim(const char *n1, const afk_image *a, const char *n2, const afk_image *b) { // precond.rs:101-114
     bool same = a->ndim == b->ndim;
     for (int i = 0; same && i < a->ndim; ++i) same = a->shape[i] == b->shape[i];
     if (same) return ok();
@@ -202,7 +202,7 @@ static Error are_same_dim(const char *n1, const afk_image *a, const char *n2, co
                           dim_debug(a).c_str(), n2, dim_debug(b).c_str()));
 }
 
-static Error same_device(const afk_image *a, int device) {
+Error same_device(const afk_image *a, int device) {
     if (a->device != device) return make_error(AFK_ERR_CUDA, fmt("CUDA: image lives on device %d but the calling thread uses device %d", a->device, device));
     return ok();
 }
@@ -519,7 +519,7 @@ AFK_OP(op_image_min_max) {
 }
 
 // ---- ratio_from_bands (lib.rs:226-246): host scalars ------------------------------------------------------------------
-static std::string rust_f32_display(float f) {
+std::string rust_f32_display(float f) {
     // Rust's `{}` for f32 prints the shortest string that round-trips, without exponent for these magnitudes
     if (f != f) return "NaN";
     if (std::isinf(f)) return f > 0 ? "inf" : "-inf";
@@ -1183,7 +1183,9 @@ static afk_value *S(const char *v) { return afk_value_str(v); }
 
 static void build_registry() {
     const afk_type IMG = AFK_T_IMAGE, INT = AFK_T_INTEGER, FLT = AFK_T_FLOAT, BOOL = AFK_T_BOOL, STR = AFK_T_STR, TC = AFK_T_TONECURVE;
-    const afk_type PATHS = AFK_T_PATHS, FITS = AFK_T_FITS;
+    const afk_type PATHS = AFK_T_PATHS, FITS = AFK_T_FITS, F2 = AFK_T_FLOAT2, F3 = AFK_T_FLOAT3, F33 = AFK_T_FLOAT3X3, ROI = AFK_T_ROI,
+                   MAP = AFK_T_MAP2DTO3DCOORDS;
+    auto V3 = [](float a, float b, float c) { const float v[3] = {a, b, c}; return afk_value_float3(v); };
     // Names, kinds, versions, slot names, types and defaults follow lib.rs:141-747 (they are the RON on-disk contract,
     // aflak_cake/src/export.rs:80-85).  Descriptions are UI help text, reworded.
     add("open_fits", "01. Open File", "Open the n-th FITS file of a path list (headers are parsed, data stays on disk).", 1, 0, 0,
@@ -1191,6 +1193,12 @@ static void build_registry() {
     add("fits_to_image", "04. Extract part of data",
         "Decode the data unit of an HDU (by extension name, else by index) into a device-resident image.", 1, 0, 0,
         {{"fits", FITS, nullptr}, {"hdu_idx", INT, I(0)}, {"extension", STR, S("")}}, {IMG}, op_fits_to_image);
+    add("make_float3", "02. Make new data", "Make a Float3 from 3 float values.", 1, 0, 0,
+        {{"f1", FLT, F(0.0f)}, {"f2", FLT, F(0.0f)}, {"f3", FLT, F(0.0f)}}, {F3}, op_make_float3);
+    add("make_plane3d", "02. Make new data",
+        "2-D mesh of points p0 + i*dir1 + j*dir2 (0 <= i < count1, 0 <= j < count2) on a plane of the 3-D index space.", 1, 0, 0,
+        {{"p0", F3, V3(0, 0, 0)}, {"dir1", F3, V3(0, 0, 1)}, {"dir2", F3, V3(0, 1, 0)}, {"count1", INT, I(1)}, {"count2", INT, I(1)}}, {MAP},
+        op_make_plane3d);
     add("range_specification", "04. Extract part of data", "Keep frames start..end (end exclusive) of the 0th axis.", 0, 1, 0,
         {{"image", IMG, nullptr}, {"start", INT, I(0)}, {"end", INT, I(1)}}, {IMG}, op_range_specification);
     add("image_min_max", "04. Extract part of data", "Minimum (first output) and maximum (second output) of an image.", 1, 0, 0,
@@ -1258,6 +1266,27 @@ static void build_registry() {
         "Flux-weighted mean wavelength of each pixel over its own frame range [start_mask, end_mask).", 0, 1, 0,
         {{"image", IMG, nullptr}, {"start_mask", IMG, nullptr}, {"end_mask", IMG, nullptr}}, {IMG},
         op_extract_centrobaric_wavelength_with_mask);
+    add("slice_3d_to_2d", "07. Reduce dimension", "Sample a 3-D dataset on the points of a 2-D mesh (nearest voxel).", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"map", MAP, nullptr}}, {IMG}, op_slice_3d_to_2d);
+    add("extrude", "07. Reduce dimension", "Spectra of the pixels of a region of interest, one column per pixel, frames in reverse order.", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"roi", ROI, afk_value_default_for(AFK_T_ROI)}}, {IMG}, op_extrude);
+    add("extract_wave", "07. Reduce dimension", "Sum of the region of interest in every frame: a 1-D spectrum.", 1, 0, 0,
+        {{"image", IMG, nullptr}, {"roi", ROI, afk_value_default_for(AFK_T_ROI)}}, {IMG}, op_extract_wave);
+    add("create_velocity_field_map", "10. Create astronomy-specific map", "Velocity v = c * (w - w_0) / w_0 with c = 3e5 km/s.", 1, 0, 0,
+        {{"image", IMG, nullptr}, {"w_0", FLT, F(0.0f)}}, {IMG}, op_create_velocity_field_map);
+    add("color_image_to_hsv", "09. Reduce dimension (color image)", "HSV channels of an RGB image.", 1, 0, 0, {{"image", IMG, nullptr}}, {IMG},
+        op_color_image_to_hsv);
+    add("color_image_from_rgb", "03. Make new data (color)", "Stack three 2-D images into one [3, ny, nx] colour image.", 1, 0, 0,
+        {{"image_r", IMG, nullptr}, {"image_g", IMG, nullptr}, {"image_b", IMG, nullptr}}, {IMG}, op_color_image_from_rgb);
+    add("histogram_transformation", "05. Convert data", "Midtone transfer function between the image minimum and maximum.", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"parameters", F3, V3(0.0f, 0.5f, 1.0f)}, {"_dynamic_range", F2, []() { const float v[2] = {0.0f, 1.0f}; return afk_value_float2(v); }()}},
+        {IMG}, op_histogram_transformation);
+    add("histogram_transformation_rgb", "05. Convert data", "Midtone transfer function per colour channel.", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"parameters", F33, []() { const float v[9] = {0.0f, 0.5f, 1.0f, 0.0f, 0.5f, 1.0f, 0.0f, 0.5f, 1.0f}; return afk_value_float3x3(v); }()},
+         {"_dynamic_range", F2, []() { const float v[2] = {0.0f, 1.0f}; return afk_value_float2(v); }()}},
+        {IMG}, op_histogram_transformation_rgb);
+    add("apply_arcsinh_stretch", "05. Convert data", "Arcsinh stretch of a colour image: every channel scaled by asinh(l*beta) / (l*asinh(beta)).", 0, 1, 0,
+        {{"image", IMG, nullptr}, {"beta", FLT, F(0.000000001f)}}, {IMG}, op_apply_arcsinh_stretch);
     // additive entry (not in the reference registry): the `&WcsArray / &WcsArray` operator of unit.rs:863-880
     add("ratio", "06. Calculate", "Ratio of two images: u / v.", 1, 0, 0, {{"u", IMG, nullptr}, {"v", IMG, nullptr}}, {IMG}, op_ratio);
 }

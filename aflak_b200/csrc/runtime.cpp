@@ -601,6 +601,31 @@ afk_value *afk_value_tone_curve(const float *arr, size_t n, const float *cp_xy, 
     return v;
 }
 
+afk_value *afk_value_roi_all(void) { return new_value(AFK_T_ROI); }
+afk_value *afk_value_roi_pixels(const uint64_t *xy, size_t n_pixels) {
+    afk_value *v = new_value(AFK_T_ROI);
+    v->roi_all = false;
+    if (xy) v->roi_xy.assign(xy, xy + 2 * n_pixels);
+    return v;
+}
+int afk_value_roi_is_all(const afk_value *v) { return v && v->type == AFK_T_ROI && v->roi_all; }
+size_t afk_value_roi_count(const afk_value *v) { return (v && v->type == AFK_T_ROI && !v->roi_all) ? v->roi_xy.size() / 2 : 0; }
+const uint64_t *afk_value_roi_data(const afk_value *v) { return (v && v->type == AFK_T_ROI && !v->roi_all) ? v->roi_xy.data() : nullptr; }
+afk_value *afk_value_map2dto3d(const float *xyz, int64_t rows, int64_t cols) {
+    if (rows < 0 || cols < 0 || (!xyz && rows * cols > 0)) return nullptr;
+    afk_value *v = new_value(AFK_T_MAP2DTO3DCOORDS);
+    v->map_rows = rows;
+    v->map_cols = cols;
+    if (xyz) v->map.assign(xyz, xyz + 3 * rows * cols);
+    return v;
+}
+const float *afk_value_get_map(const afk_value *v, int64_t *rows, int64_t *cols) {
+    if (!v || v->type != AFK_T_MAP2DTO3DCOORDS) return nullptr;
+    if (rows) *rows = v->map_rows;
+    if (cols) *cols = v->map_cols;
+    return v->map.data();
+}
+
 afk_value *afk_value_default_for(afk_type t) {
     // DefaultFor (lib.rs:760-776)
     switch (t) {
@@ -634,6 +659,7 @@ void afk_value_release(afk_value *v) {
     if (v && v->rc.fetch_sub(1, std::memory_order_acq_rel) == 1) {
         if (v->img) afk_image_release(v->img);
         if (v->fits) afk_fits_release(v->fits);
+        if (v->map_dev) cudaFree(v->map_dev);
         delete v;
     }
 }
@@ -729,7 +755,8 @@ int afk_value_eq(const afk_value *a, const afk_value *b) {
     case AFK_T_IMAGE: return image_eq(a->img, b->img);
     case AFK_T_TONECURVE: return a->cp == b->cp; // control points only (imgui_tone_curve/src/lib.rs:50-56)
     case AFK_T_PATHS: return a->paths == b->paths;
-    case AFK_T_ROI: return 1;  // only the default (ROI::All) is representable
+    case AFK_T_ROI: return a->roi_all == b->roi_all && (a->roi_all || a->roi_xy == b->roi_xy);
+    case AFK_T_MAP2DTO3DCOORDS: return a->map_rows == b->map_rows && a->map_cols == b->map_cols && a->map == b->map;
     default: return 0;
     }
 }

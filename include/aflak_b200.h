@@ -172,6 +172,15 @@ afk_fits *afk_value_get_fits(const afk_value *v); /* borrowed */
 afk_value *afk_value_paths(const char *const *paths, size_t n); /* IOValue::Paths(PATHS::FileList) */
 size_t afk_value_paths_count(const afk_value *v);
 const char *afk_value_paths_at(const afk_value *v, size_t i);
+/* roi::ROI (roi.rs:5-10): All, or PixelList of (i, j) = (x, y) pairs: xy holds 2 * n_pixels values */
+afk_value *afk_value_roi_all(void);
+afk_value *afk_value_roi_pixels(const uint64_t *xy, size_t n_pixels);
+int afk_value_roi_is_all(const afk_value *v);
+size_t afk_value_roi_count(const afk_value *v);
+const uint64_t *afk_value_roi_data(const afk_value *v);
+/* Map2dTo3dCoords: Array2<[f32; 3]> (lib.rs:79), [rows][cols][3] */
+afk_value *afk_value_map2dto3d(const float *xyz, int64_t rows, int64_t cols);
+const float *afk_value_get_map(const afk_value *v, int64_t *rows, int64_t *cols);
 /* ToneCurveState: only `arr` is read by operators (imgui_tone_curve/src/lib.rs:10-48); cp = n_cp (x,y) pairs */
 afk_value *afk_value_tone_curve(const float *arr, size_t n, const float *cp_xy, size_t n_cp);
 /* DefaultFor::default_for (lib.rs:760-776); NULL for types without a default (Image, Fits, Map2dTo3dCoords) */

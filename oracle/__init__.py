@@ -482,3 +482,82 @@ def zscale(img, nsamples=1000, contrast=0.25):
     _check(lib().orc_zscale(_fp(img), C.c_int64(img.shape[0]), C.c_int64(img.shape[1]), C.c_int(nsamples), C.c_float(contrast),
                             C.byref(has), C.byref(z1), C.byref(z2)))
     return (np.float32(z1.value), np.float32(z2.value)) if has.value else (None, None)
+
+
+# ---- spatial reductions / gathers and the remaining elementwise operators ----------------------------------------
+
+def _roi(pixels):
+    if pixels is None:
+        return 1, None, 0, None
+    a = np.ascontiguousarray(pixels, dtype=np.uint64).reshape(-1)
+    return 0, a.ctypes.data_as(C.POINTER(C.c_uint64)), a.size // 2, a
+
+
+def extract_wave(cube, pixels=None, f64=False):
+    """run_extract_wave with ROI::All (pixels=None) or ROI::PixelList([(x, y), ...])."""
+    cube = _f32(cube)
+    nz, ny, nx = cube.shape
+    roi_all, p, n, keep = _roi(pixels)
+    out = np.empty(nz, dtype=np.float32)
+    out64 = np.empty(nz, dtype=np.float64)
+    _check(lib().orc_extract_wave(_fp(cube), C.c_int64(nz), C.c_int64(ny), C.c_int64(nx), C.c_int(roi_all), p, C.c_int64(n), _fp(out), _dp(out64)))
+    return out64 if f64 else out
+
+
+def extrude(cube, pixels=None):
+    cube = _f32(cube)
+    nz, ny, nx = cube.shape
+    roi_all, p, n, keep = _roi(pixels)
+    out = np.empty((nz, n), dtype=np.float32)
+    _check(lib().orc_extrude(_fp(cube), C.c_int64(nz), C.c_int64(ny), C.c_int64(nx), C.c_int(roi_all), p, C.c_int64(n), _fp(out)))
+    return out
+
+
+def make_plane3d(p0, d1, d2, count1, count2):
+    a, b, c = (np.ascontiguousarray(v, dtype=np.float32) for v in (p0, d1, d2))
+    out = np.empty((count2, count1, 3), dtype=np.float32)
+    lib().orc_make_plane3d(_fp(a), _fp(b), _fp(c), C.c_int64(count1), C.c_int64(count2), _fp(out))
+    return out
+
+
+def slice_3d_to_2d(cube, xyz):
+    cube, xyz = _f32(cube), _f32(xyz)
+    out = np.empty(xyz.shape[:2], dtype=np.float32)
+    _check(lib().orc_slice_3d_to_2d(_fp(cube), C.c_int64(cube.shape[0]), C.c_int64(cube.shape[1]), C.c_int64(cube.shape[2]), _fp(xyz),
+                                    C.c_int64(out.size), _fp(out)))
+    return out
+
+
+def velocity_field(img, w0):
+    img = _f32(img)
+    out = np.empty_like(img)
+    lib().orc_velocity_field(_fp(img), C.c_int64(img.size), C.c_float(w0), _fp(out))
+    return out
+
+
+def histogram_transformation(img, parameters):
+    img = _f32(img)
+    p = np.ascontiguousarray(parameters, dtype=np.float32)
+    out = np.empty_like(img)
+    lib().orc_histogram_transformation(_fp(img), C.c_int64(img.size), _fp(p), _fp(out))
+    return out
+
+
+def histogram_transformation_rgb(img, parameters):
+    img = _f32(img)
+    p = np.ascontiguousarray(parameters, dtype=np.float32).reshape(-1, 3)
+    return np.stack([histogram_transformation(img[c], p[c]) for c in range(img.shape[0])]) if img.shape[0] else img.copy()
+
+
+def arcsinh_stretch(img, beta):
+    img = _f32(img)
+    out = img.copy()
+    lib().orc_arcsinh_stretch(_fp(img), C.c_int64(img.shape[1] * img.shape[2]), C.c_float(beta), _fp(out))
+    return out
+
+
+def color_image_to_hsv(img):
+    img = _f32(img)
+    out = img.copy()
+    lib().orc_color_image_to_hsv(_fp(img), C.c_int64(img.shape[1] * img.shape[2]), _fp(out))
+    return out

@@ -965,6 +965,173 @@ int orc_make_raw_image_rgb(const float *img, int64_t ny, int64_t nx, const float
 }
 
 /* ------------------------------------------------------------------------- */
+/* Spatial reductions / gathers and the remaining elementwise operators        */
+/* ------------------------------------------------------------------------- */
+
+/*
+ * ROI::filter (roi.rs:15-37) followed by the sum of run_extract_wave (lib.rs:1147-1169): res = 0.0; res += val.
+ * ROI::All iterates `for j in 0..size.1 { for i in 0..size.0 { data.get([j, i]).unwrap() } }` with size = (ny, nx):
+ * the bounds are swapped, so a non-square frame indexes out of range and the unwrap panics.
+ * PixelList: (i, j) -> data.get([j, i]), pixels outside the frame are skipped.  xy = npix pairs (i, j).
+ * out64 (optional) receives the f64 sums of the same values: the tolerance oracle.
+ */
+int orc_extract_wave(const float *cube, int64_t nz, int64_t ny, int64_t nx, int roi_all, const uint64_t *xy, int64_t npix,
+                     float *out, double *out64) {
+    if (roi_all && ny != nx) {
+        snprintf(g_err, sizeof g_err, "called `Option::unwrap()` on a `None` value");
+        return ORC_ERR_PANIC;
+    }
+    for (int64_t k = 0; k < nz; ++k) {
+        const float *data = cube + k * ny * nx;
+        float res = 0.0f;
+        double res64 = 0.0;
+        if (roi_all) {
+            for (int64_t j = 0; j < nx; ++j)
+                for (int64_t i = 0; i < ny; ++i) {
+                    res += data[j * nx + i];
+                    res64 += (double)data[j * nx + i];
+                }
+        } else {
+            for (int64_t p = 0; p < npix; ++p) {
+                uint64_t i = xy[2 * p], j = xy[2 * p + 1];
+                if (j < (uint64_t)ny && i < (uint64_t)nx) {
+                    res += data[j * nx + i];
+                    res64 += (double)data[j * nx + i];
+                }
+            }
+        }
+        out[k] = res;
+        if (out64) out64[k] = res64;
+    }
+    return ORC_OK;
+}
+
+/* run_extrude, lib.rs:1233-1256: frames in reverse order, region in list order; the shape (nz, roi.datalen()) must
+ * match the number of pushed values or from_shape_vec(..).unwrap() panics (ROI::All: datalen 0; skipped pixels) */
+int orc_extrude(const float *cube, int64_t nz, int64_t ny, int64_t nx, int roi_all, const uint64_t *xy, int64_t npix, float *out) {
+    int64_t pushed = 0;
+    if (roi_all) {
+        if (ny != nx) {
+            snprintf(g_err, sizeof g_err, "called `Option::unwrap()` on a `None` value");
+            return ORC_ERR_PANIC;
+        }
+        pushed = ny * nx;
+    } else {
+        for (int64_t p = 0; p < npix; ++p) pushed += (xy[2 * p + 1] < (uint64_t)ny && xy[2 * p] < (uint64_t)nx);
+    }
+    int64_t datalen = roi_all ? 0 : npix;
+    if (nz * pushed != nz * datalen) {
+        snprintf(g_err, sizeof g_err, "called `Result::unwrap()` on an `Err` value: ShapeError");
+        return ORC_ERR_PANIC;
+    }
+    int64_t o = 0;
+    for (int64_t k = nz - 1; k >= 0; --k)
+        for (int64_t p = 0; p < npix; ++p) out[o++] = cube[(k * ny + (int64_t)xy[2 * p + 1]) * nx + (int64_t)xy[2 * p]];
+    return ORC_OK;
+}
+
+/* run_make_plane3d, lib.rs:1130-1145: map[(j, i)] = p0 + i*dir1 + j*dir2, f32, evaluated left to right */
+void orc_make_plane3d(const float p0[3], const float d1[3], const float d2[3], int64_t count1, int64_t count2, float *map) {
+    for (int64_t j = 0; j < count2; ++j)
+        for (int64_t i = 0; i < count1; ++i)
+            for (int c = 0; c < 3; ++c) {
+                float fi = (float)i, fj = (float)j;
+                map[3 * (j * count1 + i) + c] = p0[c] + fi * d1[c] + fj * d2[c];
+            }
+}
+
+/* Rust `{}` of an f32 for the magnitudes that occur in index errors */
+static void rust_f32_display(float f, char *buf, size_t cap) {
+    if (f != f) { snprintf(buf, cap, "NaN"); return; }
+    if (isinf(f)) { snprintf(buf, cap, f > 0 ? "inf" : "-inf"); return; }
+    if (f == floorf(f) && fabsf(f) < 1e16f) { snprintf(buf, cap, "%.0f", (double)f); return; }
+    for (int prec = 1; prec < 12; ++prec) {
+        snprintf(buf, cap, "%.*g", prec, (double)f);
+        if (strtof(buf, NULL) == f && !strchr(buf, 'e')) return;
+    }
+    snprintf(buf, cap, "%.9g", (double)f);
+}
+
+/* run_slice_3d_to_2d, lib.rs:1096-1110: out = image[x as usize, y as usize, z as usize], nearest by truncation */
+int orc_slice_3d_to_2d(const float *cube, int64_t d0, int64_t d1, int64_t d2, const float *map, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) {
+        uint64_t a = rust_f32_as_usize(map[3 * i]), b = rust_f32_as_usize(map[3 * i + 1]), c = rust_f32_as_usize(map[3 * i + 2]);
+        if (a >= (uint64_t)d0 || b >= (uint64_t)d1 || c >= (uint64_t)d2) {
+            char x[64], y[64], z[64];
+            rust_f32_display(map[3 * i], x, sizeof x);
+            rust_f32_display(map[3 * i + 1], y, sizeof y);
+            rust_f32_display(map[3 * i + 2], z, sizeof z);
+            snprintf(g_err, sizeof g_err, "Input maps to out of bound pixel!: [%s, %s, %s]", x, y, z);
+            return ORC_ERR_UNEXPECTED_INPUT;
+        }
+        out[i] = cube[((int64_t)a * d1 + (int64_t)b) * d2 + (int64_t)c];
+    }
+    return ORC_OK;
+}
+
+/* create_velocity_field_map, lib.rs:509-526: (image - w_0) * c / w_0 with c = 3e5 as f32 */
+void orc_velocity_field(const float *img, int64_t n, float w0, float *out) {
+    const float c = 3e5f;
+    for (int64_t i = 0; i < n; ++i) out[i] = (img[i] - w0) * c / w0;
+}
+
+/* histogram_transformation, lib.rs:562-591 (one channel; _rgb, lib.rs:592-631, applies the same per channel) */
+void orc_histogram_transformation(const float *img, int64_t n, const float parameters[3], float *out) {
+    float min = FLT_MAX, max = -FLT_MAX;
+    for (int64_t i = 0; i < n; ++i) {
+        if (!(img[i] != img[i])) { /* f32::min / max ignore a NaN operand */
+            min = img[i] < min ? img[i] : min;
+            max = img[i] > max ? img[i] : max;
+        }
+    }
+    for (int64_t i = 0; i < n; ++i) {
+        float point = (img[i] - min) / (max - min);
+        float x = (point - parameters[0]) / (parameters[2] - parameters[0]);
+        float c;
+        if (x > 1.0f) c = 1.0f;
+        else if (x < 0.0f) c = 0.0f;
+        else {
+            float m = parameters[1];
+            c = (m - 1.0f) * x / ((2.0f * m - 1.0f) * x - m);
+        }
+        out[i] = c * (max - min) + min;
+    }
+}
+
+/* run_apply_arcsinh_stretch, lib.rs:1873-1892 ([3][n] image); asinh is libm::asinh (f64) in the reference, glibc's here */
+void orc_arcsinh_stretch(const float *img, int64_t n, float beta, float *out) {
+    for (int64_t i = 0; i < n; ++i) {
+        float d0 = img[i], d1 = img[n + i], d2 = img[2 * n + i];
+        float l = (d0 + d1 + d2) / 3.0f;
+        double s64 = asinh((double)(l * beta)) / ((double)l * asinh((double)beta));
+        float s = (float)s64;
+        out[i] = s * d0;
+        out[n + i] = s * d1;
+        out[2 * n + i] = s * d2;
+    }
+}
+
+static float rust_max(float a, float b) { return (a != a) ? b : (b != b) ? a : (a > b ? a : b); }
+static float rust_min(float a, float b) { return (a != a) ? b : (b != b) ? a : (a < b ? a : b); }
+
+/* run_color_image_to_hsv, lib.rs:1795-1826 ([3][n] image) */
+void orc_color_image_to_hsv(const float *img, int64_t n, float *out) {
+    for (int64_t i = 0; i < n; ++i) {
+        float d0 = img[i], d1 = img[n + i], d2 = img[2 * n + i];
+        float hue = 0.0f;
+        float max = rust_max(rust_max(d0, d1), d2), min = rust_min(rust_min(d0, d1), d2);
+        if (d0 >= d1 && d0 >= d2) hue = 60.0f * ((d1 - d2) / (max - min));
+        else if (d1 >= d0 && d1 >= d2) hue = 60.0f * ((d2 - d0) / (max - min)) + 120.0f;
+        else if (d2 >= d0 && d2 >= d1) hue = 60.0f * ((d0 - d1) / (max - min)) + 240.0f;
+        if (hue < 0.0f) hue += 360.0f;
+        hue = hue / 360.0f * 65535.0f;
+        out[i] = hue;
+        out[n + i] = (max - min) / max * 65535.0f;
+        out[2 * n + i] = max;
+    }
+}
+
+/* ------------------------------------------------------------------------- */
 /* Display statistics: aflak_plot/src/imshow/hist.rs, lims.rs:37-106, zscale.rs */
 /* ------------------------------------------------------------------------- */
 

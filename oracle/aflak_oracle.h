@@ -109,6 +109,17 @@ int orc_make_raw_image_rgb(const float *img, int64_t ny, int64_t nx, const float
 int orc_make_raw_image_mt(const float *img, int64_t ny, int64_t nx, float vmin, float vmax, const uint8_t *lut,
                           const float lims[3], int channels, uint8_t *out, int threads);
 
+/* ---- spatial reductions / gathers and remaining elementwise operators (lib.rs:509-631, 928-1169, 1233-1256, 1795-1892) ---- */
+int orc_extract_wave(const float *cube, int64_t nz, int64_t ny, int64_t nx, int roi_all, const uint64_t *xy, int64_t npix,
+                     float *out, double *out64);
+int orc_extrude(const float *cube, int64_t nz, int64_t ny, int64_t nx, int roi_all, const uint64_t *xy, int64_t npix, float *out);
+void orc_make_plane3d(const float p0[3], const float d1[3], const float d2[3], int64_t count1, int64_t count2, float *map);
+int orc_slice_3d_to_2d(const float *cube, int64_t d0, int64_t d1, int64_t d2, const float *map, int64_t n, float *out);
+void orc_velocity_field(const float *img, int64_t n, float w0, float *out);
+void orc_histogram_transformation(const float *img, int64_t n, const float parameters[3], float *out);
+void orc_arcsinh_stretch(const float *img, int64_t n, float beta, float *out);
+void orc_color_image_to_hsv(const float *img, int64_t n, float *out);
+
 /* ---- display statistics (aflak_plot/src/imshow/hist.rs, lims.rs:37-106, zscale.rs) ---- */
 void orc_histogram(const float *img, int64_t n_per_channel, int channels, float min, float max, int nb, uint64_t *counts);
 void orc_histogram_bins(float min, float max, int nb, float *starts, float *ends);

@@ -52,6 +52,20 @@ REGISTRY = {
     "log10": ((1, 0, 0), [("image", "Image", None)], ["Image"]),
     "apply_tone_curve": ((1, 0, 0), [("image", "Image", None), ("tone_curve", "ToneCurve", None)], ["Image"]),
     "image_min_max": ((1, 0, 0), [("image", "Image", None)], ["Float", "Float"]),
+    "open_fits": ((1, 0, 0), [("path", "Paths", None), ("n", "Integer", 0)], ["Fits"]),
+    "fits_to_image": ((1, 0, 0), [("fits", "Fits", None), ("hdu_idx", "Integer", 0), ("extension", "Str", "")], ["Image"]),
+    "make_float3": ((1, 0, 0), [("f1", "Float", 0.0), ("f2", "Float", 0.0), ("f3", "Float", 0.0)], ["Float3"]),
+    "make_plane3d": ((1, 0, 0), [("p0", "Float3", (0.0, 0.0, 0.0)), ("dir1", "Float3", (0.0, 0.0, 1.0)), ("dir2", "Float3", (0.0, 1.0, 0.0)), ("count1", "Integer", 1),
+                                 ("count2", "Integer", 1)], ["Map2dTo3dCoords"]),
+    "slice_3d_to_2d": ((0, 1, 0), [("image", "Image", None), ("map", "Map2dTo3dCoords", None)], ["Image"]),
+    "extrude": ((0, 1, 0), [("image", "Image", None), ("roi", "Roi", "All")], ["Image"]),
+    "extract_wave": ((1, 0, 0), [("image", "Image", None), ("roi", "Roi", "All")], ["Image"]),
+    "create_velocity_field_map": ((1, 0, 0), [("image", "Image", None), ("w_0", "Float", 0.0)], ["Image"]),
+    "color_image_to_hsv": ((1, 0, 0), [("image", "Image", None)], ["Image"]),
+    "color_image_from_rgb": ((1, 0, 0), [("image_r", "Image", None), ("image_g", "Image", None), ("image_b", "Image", None)], ["Image"]),
+    "histogram_transformation": ((0, 1, 0), [("image", "Image", None), ("parameters", "Float3", (0.0, 0.5, 1.0)), ("_dynamic_range", "Float2", (0.0, 1.0))], ["Image"]),
+    "histogram_transformation_rgb": ((0, 1, 0), [("image", "Image", None), ("parameters", "Float3x3", (0.0, 0.5, 1.0) * 3), ("_dynamic_range", "Float2", (0.0, 1.0))], ["Image"]),
+    "apply_arcsinh_stretch": ((0, 1, 0), [("image", "Image", None), ("beta", "Float", float(np.float32(0.000000001)))], ["Image"]),
     "variance": ((1, 0, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
     "stddev": ((1, 0, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
     "median": ((1, 0, 0), [("image", "Image", None), ("start", "Integer", 0), ("end", "Integer", 1)], ["Image"]),
@@ -79,6 +93,10 @@ def test_registry_matches_reference(afk):
         for got, want in zip(t.inputs, slots):
             if want[2] is None:
                 assert got[2] is None or want[1] == "ToneCurve", (name, got)
+            elif want[1] == "Roi":
+                assert got[2] == afk.Roi(), (name, got)  # roi::ROI::All
+            elif isinstance(want[2], tuple):
+                assert np.array_equal(got[2], np.array(want[2], dtype=np.float32)), (name, got, want)
             else:
                 assert got[2] == want[2], (name, got, want)
     assert afk.get_transform("no_such_transform") is None

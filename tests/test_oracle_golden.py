@@ -280,3 +280,61 @@ def test_zscale_kat(orc):
     assert orc.zscale(img, 0, 0.25) == (None, None)
     z1, z2 = orc.zscale(np.full((40, 40), 3.0, np.float32))   # constant image: slope 0 -> both limits are the value
     assert z1 == 3.0 and z2 == 3.0
+
+
+# ---- spatial reductions / gathers and remaining elementwise operators: known answers ------------------------------------
+
+def test_extract_wave_and_extrude_kat(orc):
+    cube = np.arange(3 * 4 * 4, dtype=np.float32).reshape(3, 4, 4)
+    # ROI::All on a square frame: plain sum of the frame
+    assert orc.extract_wave(cube).tolist() == [120.0, 376.0, 632.0]
+    # PixelList (i, j) = (column, row); pixels outside the frame are skipped
+    assert orc.extract_wave(cube, [(1, 0), (3, 2), (9, 9)]).tolist() == [1.0 + 11.0, 17.0 + 27.0, 33.0 + 43.0]
+    assert orc.extract_wave(cube, []).tolist() == [0.0, 0.0, 0.0]
+    with pytest.raises(orc.OracleError) as e:   # the swapped loop bounds of ROI::All index out of range on non-square frames
+        orc.extract_wave(np.zeros((2, 3, 4), np.float32))
+    assert e.value.code == orc.ERR_PANIC
+    # extrude: frames in reverse order, one column per pixel
+    ex = orc.extrude(cube, [(1, 0), (3, 2)])
+    assert ex.tolist() == [[33.0, 43.0], [17.0, 27.0], [1.0, 11.0]]
+    for bad in (None, [(1, 0), (9, 9)]):       # ROI::All has datalen 0; a skipped pixel leaves the vector short
+        with pytest.raises(orc.OracleError):
+            orc.extrude(cube, bad)
+
+
+def test_plane_and_slice_kat(orc):
+    cube = np.arange(5 * 6 * 7, dtype=np.float32).reshape(5, 6, 7)
+    # defaults of make_plane3d: dir1 = z, dir2 = y; p0 = (2, 0, 0) -> the frame cube[2]
+    xyz = orc.make_plane3d((2, 0, 0), (0, 0, 1), (0, 1, 0), 7, 6)
+    assert xyz.shape == (6, 7, 3) and xyz[3, 4].tolist() == [2.0, 3.0, 4.0]
+    assert np.array_equal(orc.slice_3d_to_2d(cube, xyz), cube[2])
+    # nearest voxel by truncation; negative and NaN coordinates become index 0
+    pts = np.array([[[1.9, 2.2, 3.99], [-0.5, np.nan, 0.0]]], np.float32)
+    assert orc.slice_3d_to_2d(cube, pts).tolist() == [[cube[1, 2, 3], cube[0, 0, 0]]]
+    with pytest.raises(orc.OracleError) as e:
+        orc.slice_3d_to_2d(cube, np.array([[[0, 0, 0], [5, 0.5, 2]]], np.float32))
+    assert e.value.msg == "Input maps to out of bound pixel!: [5, 0.5, 2]"
+
+
+def test_elementwise_next_kat(orc):
+    # velocity: (w - w0) * 3e5 / w0
+    assert orc.velocity_field(np.array([6562.8, 6569.3628], np.float32), 6562.8)[0] == 0.0
+    v = orc.velocity_field(np.array([2.0], np.float32), 1.0)
+    assert v[0] == 300000.0
+    # histogram transformation with the default parameters (0, 0.5, 1) is the identity up to rounding: c = x
+    img = np.array([0.0, 1.0, 2.0, 4.0], np.float32)
+    assert orc.histogram_transformation(img, (0.0, 0.5, 1.0)).tolist() == [0.0, 1.0, 2.0, 4.0]
+    # midtone 0.25 lifts the middle: x = .5 -> (m-1)x / ((2m-1)x - m) = -.375 / -.5 = .75
+    assert orc.histogram_transformation(img, (0.0, 0.25, 1.0))[2] == 3.0
+    # clipping: x > 1 -> max, x < 0 -> min
+    out = orc.histogram_transformation(img, (0.25, 0.5, 0.5))
+    assert out[0] == 0.0 and out[3] == 4.0 and out[2] == 4.0
+    # hsv of pure colours (scaled to 65535)
+    rgb = np.array([[[1.0, 0.0, 0.0, 0.5]], [[0.0, 1.0, 0.0, 0.5]], [[0.0, 0.0, 1.0, 0.5]]], np.float32)
+    hsv = orc.color_image_to_hsv(rgb)
+    assert hsv[0, 0, 0] == 0.0 and hsv[0, 0, 1] == np.float32(120.0) / np.float32(360.0) * np.float32(65535.0)
+    assert hsv[1, 0, 0] == 65535.0 and hsv[2, 0, 2] == 1.0
+    assert np.isnan(hsv[0, 0, 3]) and hsv[1, 0, 3] == 0.0   # grey: 0/0 hue, zero saturation
+    # arcsinh stretch with a tiny beta is the identity to first order: asinh(l*b) / (l * asinh(b)) -> 1
+    out = orc.arcsinh_stretch(np.full((3, 1, 2), 100.0, np.float32), 1e-9)
+    assert np.allclose(out, 100.0, rtol=1e-6)
