@@ -55,5 +55,46 @@ def main(rep, out):
     print(json.dumps(summ, indent=1))
 
 
+def main_grouped(rep, out):
+    """One summary entry per kernel name (reports that captured several different kernels)."""
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+
+    def val(r, name):
+        i = hdr.index(name)
+        try:
+            return float(r[i].replace(",", "")) * SCALE.get(units[i], 1.0)
+        except ValueError:
+            return float("nan")
+
+    groups = {}
+    for r in data:
+        groups.setdefault(r[hdr.index("Kernel Name")], []).append(r)
+    summ = {"report": rep, "note": "ncu --set full --clock-control none; per-launch averages per kernel; times are under the profiler (not bench values)", "kernels": []}
+    for name, rs in groups.items():
+        n = len(rs)
+        avg = lambda k: sum(val(r, k) for r in rs) / n
+        t_ns = avg("gpu__time_duration.sum") * (1e6 if units[hdr.index("gpu__time_duration.sum")] == "ms" else 1e3 if units[hdr.index("gpu__time_duration.sum")] == "us" else 1.0)
+        rd, wr = avg("dram__bytes_read.sum"), avg("dram__bytes_write.sum")
+        summ["kernels"].append({
+            "kernel": name, "launches_captured": n, "grid": rs[0][hdr.index("Grid Size")], "block": rs[0][hdr.index("Block Size")],
+            "gpu_time_ms": t_ns / 1e6, "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_GBps": (rd + wr) / t_ns if t_ns else None,
+            "dram_throughput_pct_of_peak": avg("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+            "sm_throughput_pct": avg("sm__throughput.avg.pct_of_peak_sustained_elapsed"),
+            "warps_active_pct": avg("sm__warps_active.avg.pct_of_peak_sustained_active"),
+            "registers_per_thread": val(rs[0], "launch__registers_per_thread"),
+            "l2_hit_rate_pct": avg("lts__t_sector_hit_rate.pct"),
+        })
+    with open(out + ".json", "w") as f:
+        json.dump(summ, f, indent=1)
+    for k in summ["kernels"]:
+        print(f"{k['kernel'][:70]:70s} x{k['launches_captured']} {k['gpu_time_ms']:9.3f} ms  rd {k['dram_bytes_read']/1e9:8.3f} GB wr {k['dram_bytes_write']/1e9:7.3f} GB "
+              f"dram {k['dram_throughput_pct_of_peak']:5.1f}% sm {k['sm_throughput_pct']:5.1f}% regs {k['registers_per_thread']:.0f}")
+
+
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2])
+    if len(sys.argv) > 3 and sys.argv[3] == "--grouped":
+        main_grouped(sys.argv[1], sys.argv[2])
+    else:
+        main(sys.argv[1], sys.argv[2])

@@ -45,5 +45,45 @@ elif args.workload == "lut":
     vmin, vmax = img.vmin_vmax()
     for _ in range(args.launches):
         afk.colormap_device(img, lut, float(vmin), float(vmax), outb.device_ptr, channels=4)
+elif args.workload == "variance":  # axis0_kernel<VarComp> and <VarSeq> on the ALMA-shape cube
+    nz, ny, nx = 3840, 1024, 1024
+    cube = afk.Image.synthetic(0xAF1A0003, nz, ny, nx)
+    for _ in range(args.launches):
+        afk.call("variance", cube, 0, nz)
+    afk.set_sum_mode(afk.SUM_SEQUENTIAL)
+    for _ in range(args.launches):
+        afk.call("variance", cube, 0, nz)
+    afk.set_sum_mode(afk.SUM_COMPENSATED)
+elif args.workload == "argmax":
+    nz, ny, nx = 3840, 1024, 1024
+    cube = afk.Image.synthetic(0xAF1A0003, nz, ny, nx)
+    cube.set_axis(2, "WAVE", "Angstrom")
+    for _ in range(args.launches):
+        afk.call("extract_argmin_max_wavelength", cube, 0, nz, False)
+elif args.workload == "median":
+    nz, ny, nx = 3840, 1024, 1024
+    cube = afk.Image.synthetic(0xAF1A0003, nz, ny, nx)
+    for _ in range(args.launches):
+        afk.call("median", cube, 0, nz)
+elif args.workload == "wave":
+    nz, ny, nx = 3840, 1024, 1024
+    cube = afk.Image.synthetic(0xAF1A0003, nz, ny, nx)
+    for _ in range(args.launches):
+        afk.call("extract_wave", cube, afk.Roi())
+elif args.workload == "ingest":  # decode kernel on device-resident raw bytes: BITPIX -32 then BITPIX 16
+    n = 1 << 31
+    dst = afk.Image.alloc((n,))
+    raw = afk.Image.synthetic(0xAF1A0006, 1, 1, n)  # any bytes will do
+    for _ in range(args.launches):
+        afk.k_ingest(raw.device_ptr, afk.FITS_F32, n, dst.device_ptr, bscale=0.5, bzero=1.0)
+    for _ in range(args.launches):
+        afk.k_ingest(raw.device_ptr, afk.FITS_I16, n, dst.device_ptr, bscale=0.5, bzero=1.0)
+elif args.workload == "stats":
+    rng = np.random.default_rng(4)
+    img = afk.Image.upload(np.exp(rng.standard_normal((4096, 4096))).astype(np.float32))
+    vmin, vmax = img.vmin_vmax()
+    for _ in range(args.launches):
+        img.histogram(float(vmin), float(vmax))
+        img.vmed_vmad()
 afk.synchronize()
 print("ncu target ok:", args.workload, afk.launch_count(), "launches")
