@@ -374,7 +374,7 @@ class Image:
         return np.float32(a.value), np.float32(b.value)
 
     def __del__(self):
-        if getattr(self, "_owned", False) and self._h:
+        if getattr(self, "_owned", False) and self._h and lib is not None:  # lib is None during interpreter shutdown
             lib.afk_image_release(self._h)
             self._h = None
 
@@ -444,7 +444,7 @@ class Fits:
         return Image(out.value)
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib.afk_fits_release(self._h)
             self._h = None
 
@@ -734,7 +734,7 @@ class Gather:
         return Image(lib.afk_gather_result_image(self._h))
 
     def close(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib.afk_gather_destroy(self._h)
             self._h = None
 
@@ -802,7 +802,7 @@ class Lut:
         return [((float(v1[i]), tuple(c1[3 * i:3 * i + 3])), (float(v2[i]), tuple(c2[3 * i:3 * i + 3]))) for i in range(n)]
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib.afk_lut_release(self._h)
             self._h = None
 
@@ -896,6 +896,6 @@ class Graph:
         lib.afk_graph_set_fusion(self._h, int(enable))
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib.afk_graph_free(self._h)
             self._h = None

@@ -397,10 +397,18 @@ __device__ __forceinline__ unsigned med_pick_digit(const unsigned *hist, unsigne
     return (unsigned)digit;
 }
 
-// keys: n offset keys (key - kmin) of one spectrum, contiguous; span = max offset key.  Finds the offset keys of ranks
-// r and (when want_next) r + 1.  One warp; hist = 256 words of shared memory.
-__device__ void med_select_warp(const unsigned *keys, int n, unsigned span, unsigned r, bool want_next, unsigned *hist, int lane,
-                                unsigned &k_r, unsigned &k_next) {
+// A spectrum is solved by a group of G warps (G = 8 / min(P, 8): with few spaxels per CTA all eight warps still work);
+// the group synchronises on its own named barrier, or with __syncwarp when it is a single warp.
+__device__ __forceinline__ void med_group_sync(int G, int grp) {
+    if (G == 1) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(G * 32) : "memory");
+}
+
+// keys: the n order-preserving keys of one spectrum, contiguous; digits are taken from key - kmin, span = kmax - kmin.
+// Finds the offset keys of ranks r and (when want_next) r + 1; every thread of the group returns the same values.
+// hist = 256 words, red = 8 words of shared memory owned by the group.
+__device__ void med_select_group(const unsigned *keys, int n, unsigned kmin, unsigned span, unsigned r, bool want_next, unsigned *hist,
+                                 unsigned *red, int gt, int gsize, int lane, int G, int grp, unsigned &k_r, unsigned &k_next) {
     int bits_left = 32 - __clz(span); // 0 when every key is equal
     unsigned prefix = 0u, kth = r, eq_count = (unsigned)n;
     while (bits_left > 0) {
@@ -408,49 +416,56 @@ __device__ void med_select_warp(const unsigned *keys, int n, unsigned span, unsi
         const int shift = bits_left - w;
         const unsigned dmask = (1u << w) - 1u;
         const unsigned cmask = bits_left >= 32 ? 0u : ~((1u << bits_left) - 1u);
-        for (int b = lane; b < 256; b += 32) hist[b] = 0u;
-        __syncwarp();
-        for (int base = 0; base < n; base += 128) {
+        for (int b = gt; b < 256; b += gsize) hist[b] = 0u;
+        med_group_sync(G, grp);
+        for (int base = 0; base < n; base += 4 * gsize) {
             unsigned key[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int i = base + 32 * u + lane;
-                key[u] = i < n ? keys[i] : 0xFFFFFFFFu; // padding can never match: prefix has zeros above span's top bit
+                const int i = base + u * gsize + gt;
+                key[u] = i < n ? keys[i] - kmin : 0u;
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int i = base + 32 * u + lane;
+                const int i = base + u * gsize + gt;
                 if (i < n && (key[u] & cmask) == prefix) atomicAdd(&hist[(key[u] >> shift) & dmask], 1u);
             }
         }
-        __syncwarp();
-        const unsigned digit = med_pick_digit(hist, kth, eq_count, lane);
+        med_group_sync(G, grp);
+        const unsigned digit = med_pick_digit(hist, kth, eq_count, lane); // every warp of the group reads the same histogram
         prefix |= digit << shift;
         bits_left = shift;
-        __syncwarp();
+        med_group_sync(G, grp); // nobody may still be reading when the histogram is cleared again
     }
     k_r = prefix;
     // eq_count keys equal k_r and kth is r's position among them
-    if (!want_next || kth + 1 < eq_count) { k_next = prefix; return; }
-    unsigned m = 0xFFFFFFFFu; // smallest key above k_r
-    for (int i = lane; i < n; i += 32) {
-        const unsigned key = keys[i];
+    if (!want_next || kth + 1 < eq_count) { k_next = prefix; return; } // group-uniform
+    unsigned m = 0xFFFFFFFFu; // smallest offset key above k_r
+    for (int i = gt; i < n; i += gsize) {
+        const unsigned key = keys[i] - kmin;
         if (key > prefix && key < m) m = key;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (G > 1) {
+        if (lane == 0) red[gt >> 5] = m;
+        med_group_sync(G, grp);
+        m = 0xFFFFFFFFu;
+        for (int w = 0; w < G; ++w) m = min(m, red[w]);
+        med_group_sync(G, grp);
+    }
     k_next = m;
 }
 
 __global__ void __launch_bounds__(256) median_select_kernel(const MedianK a) {
-    extern __shared__ __align__(16) unsigned s_keys[]; // [P][npad] staged keys, then one 256-word histogram per warp
+    extern __shared__ __align__(16) unsigned s_keys[]; // [P][npad] staged keys | 8 x 256 histogram words | 8 x 16 reduction words
     const int P = a.P, npad = a.npad, n = (int)a.n;
-    const int nthreads = blockDim.x;
     const int64_t px0 = (int64_t)blockIdx.x * P;
-    unsigned *hist = s_keys + (size_t)P * npad;
+    unsigned *s_hist = s_keys + (size_t)P * npad;
+    unsigned *s_red = s_hist + 8 * 256;
     const int tid = threadIdx.x;
     const int64_t total = a.n * P;
-    for (int64_t i = tid; i < total; i += nthreads) {
+    for (int64_t i = tid; i < total; i += 256) {
         const int64_t k = i / P;
         const int j = (int)(i - k * P);
         if (px0 + j < a.n2) {
@@ -462,14 +477,17 @@ __global__ void __launch_bounds__(256) median_select_kernel(const MedianK a) {
     asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int G = P >= 8 ? 1 : 8 / P, ngroups = 8 / G;
+    const int grp = warp / G, gt = (warp % G) * 32 + lane, gsize = G * 32;
+    unsigned *hist = s_hist + grp * 256, *red = s_red + grp * 16;
     bool nan = false;
-    for (int j = warp; j < P; j += nwarps) {
+    for (int j = grp; j < P; j += ngroups) {
         const int64_t px = px0 + j;
-        if (px >= a.n2) continue; // warp-uniform
+        if (px >= a.n2) continue; // group-uniform
         unsigned *keys = s_keys + (size_t)j * npad;
         unsigned kmin = 0xFFFFFFFFu, kmax = 0u;
-        for (int i = lane; i < n; i += 32) {
+        for (int i = gt; i < n; i += gsize) {
             const float f = __uint_as_float(keys[i]);
             nan |= (f != f);
             const unsigned key = med_key(f);
@@ -482,11 +500,15 @@ __global__ void __launch_bounds__(256) median_select_kernel(const MedianK a) {
             kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
             kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
         }
-        for (int i = lane; i < n; i += 32) keys[i] -= kmin; // each lane rewrites the words it wrote
-        __syncwarp();
+        if (G > 1) {
+            if (lane == 0) { red[2 * (gt >> 5)] = kmin; red[2 * (gt >> 5) + 1] = kmax; }
+            med_group_sync(G, grp);
+            for (int w = 0; w < G; ++w) { kmin = min(kmin, red[2 * w]); kmax = max(kmax, red[2 * w + 1]); }
+        }
+        med_group_sync(G, grp); // the converted keys are visible to the whole group; `red` may be reused
         unsigned klo, khi;
-        med_select_warp(keys, n, kmax - kmin, (unsigned)((n - 1) / 2), (n & 1) == 0, hist + warp * 256, lane, klo, khi);
-        if (lane == 0) a.out[px] = med_finish(klo + kmin, khi + kmin, (n & 1) == 0);
+        med_select_group(keys, n, kmin, kmax - kmin, (unsigned)((n - 1) / 2), (n & 1) == 0, hist, red, gt, gsize, lane, G, grp, klo, khi);
+        if (gt == 0) a.out[px] = med_finish(klo + kmin, khi + kmin, (n & 1) == 0);
     }
     if (nan && n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
 }
@@ -612,8 +634,7 @@ static int median_npad(int64_t n, int P) {
     return (int)np;
 }
 static size_t median_select_smem(int64_t n, int P) {
-    const int warps = P < 8 ? P : 8;
-    return (size_t)P * median_npad(n, P) * sizeof(unsigned) + (size_t)warps * 256 * sizeof(unsigned);
+    return (size_t)P * median_npad(n, P) * sizeof(unsigned) + (size_t)(8 * 256 + 8 * 16) * sizeof(unsigned);
 }
 
 int median_pixels_per_cta(int64_t n2, int64_t n) {
@@ -659,7 +680,7 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }
-    median_select_kernel<<<(unsigned)((n2 + P - 1) / P), 32 * (P < 8 ? P : 8), smem, s>>>(k);
+    median_select_kernel<<<(unsigned)((n2 + P - 1) / P), 256, smem, s>>>(k);
     count_launch();
     return cudaGetLastError();
 }

@@ -256,26 +256,36 @@ static Error ingest_streams(int dev, cudaStream_t out[2]) {
     return ok();
 }
 
-// read `bytes` at `off` with several threads (page cache -> pinned memory is a memcpy; one thread does ~5-10 GB/s)
-static bool pread_parallel(int fd, uint8_t *dst, size_t bytes, int64_t off) {
-    auto rd = [fd](uint8_t *d, size_t n, int64_t o) {
-        while (n > 0) {
-            const ssize_t r = pread(fd, d, n, o);
-            if (r <= 0) return false;
-            d += r;
-            o += r;
-            n -= (size_t)r;
+// Read one pipeline chunk into pinned memory with several threads (page cache -> pinned memory is a memcpy; one thread
+// does ~5-10 GB/s).  The chunk is `frames` segments of seg_bytes each, segment k at file offset off0 + k * seg_stride
+// (a contiguous chunk is one segment): the threads share the total byte range evenly, whatever the segment size.
+static bool read_chunk(int fd, uint8_t *dst, int64_t frames, size_t seg_bytes, int64_t off0, int64_t seg_stride) {
+    const size_t total = (size_t)frames * seg_bytes;
+    auto rd = [=](size_t b, size_t e) { // bytes [b, e) of the chunk
+        while (b < e) {
+            const size_t k = b / seg_bytes, in = b - k * seg_bytes;
+            size_t n = std::min(e - b, seg_bytes - in);
+            int64_t o = off0 + (int64_t)k * seg_stride + (int64_t)in;
+            uint8_t *d = dst + b;
+            b += n;
+            while (n > 0) {
+                const ssize_t r = pread(fd, d, n, o);
+                if (r <= 0) return false;
+                d += r;
+                o += r;
+                n -= (size_t)r;
+            }
         }
         return true;
     };
-    if (bytes < ((size_t)4 << 20)) return rd(dst, bytes, off);
+    if (total < ((size_t)4 << 20)) return rd(0, total);
     bool okv[kReaderThreads];
     std::thread th[kReaderThreads];
-    const size_t per = (bytes / kReaderThreads + 4095) & ~(size_t)4095;
+    const size_t per = (total / kReaderThreads + 4095) & ~(size_t)4095;
     for (int t = 0; t < kReaderThreads; ++t) {
-        const size_t b = std::min(bytes, per * t), e = std::min(bytes, per * (t + 1));
+        const size_t lo = std::min(total, per * t), hi = std::min(total, per * (t + 1));
         okv[t] = true;
-        th[t] = std::thread([&, t, b, e] { okv[t] = (e > b) ? rd(dst + b, e - b, off + (int64_t)b) : true; });
+        th[t] = std::thread([&, t, lo, hi] { okv[t] = hi > lo ? rd(lo, hi) : true; });
     }
     bool good = true;
     for (int t = 0; t < kReaderThreads; ++t) {
@@ -309,18 +319,22 @@ static Error ingest_run(const IngestJob &j, float *dst, cudaStream_t s, int dev)
     if (Error e = ingest_streams(dev, st)) return e;
     const bool in_place = (es == 4);
     void *stage[2] = {nullptr, nullptr};
-    if (!in_place)
-        for (int i = 0; i < 2; ++i) AFK_CUDA(cudaMallocAsync(&stage[i], chunk_bytes, s));
-    if (j.fd >= 0)
-        if (Error e = ring_reserve(chunk_bytes)) return e;
+    Error err = ok();
+    if (j.fd >= 0) err = ring_reserve(chunk_bytes);
+    if (err) return err;
     // fork: the two pipeline streams start after everything already queued on s (the allocation of dst and stage)
     cudaEvent_t fork = event_get(), ev_t0 = nullptr, ev_t1 = nullptr;
     cudaEventCreate(&ev_t0);
     cudaEventCreate(&ev_t1);
-    AFK_CUDA(cudaEventRecord(fork, s));
-    AFK_CUDA(cudaEventRecord(ev_t0, s));
-    for (int i = 0; i < 2; ++i) AFK_CUDA(cudaStreamWaitEvent(st[i], fork, 0));
-    Error err = ok();
+    {
+        cudaError_t ce = cudaSuccess;
+        if (!in_place)
+            for (int i = 0; i < 2 && ce == cudaSuccess; ++i) ce = cudaMallocAsync(&stage[i], chunk_bytes, s);
+        if (ce == cudaSuccess) ce = cudaEventRecord(fork, s);
+        if (ce == cudaSuccess) ce = cudaEventRecord(ev_t0, s);
+        for (int i = 0; i < 2 && ce == cudaSuccess; ++i) ce = cudaStreamWaitEvent(st[i], fork, 0);
+        if (ce != cudaSuccess) err = cuda_error(ce, "ingest pipeline set-up"); // falls through to the clean-up below
+    }
     int64_t done = 0;
     for (int c = 0; done < total && !err; ++c) {
         const int b = c & 1;
@@ -336,15 +350,18 @@ static Error ingest_run(const IngestJob &j, float *dst, cudaStream_t s, int dev)
         }
         if (j.fd >= 0) {
             // the pinned buffer is free once the copy issued two chunks ago has drained
-            if (c >= 2) AFK_CUDA(cudaEventSynchronize(t_ring.free_ev[b]));
+            if (c >= 2) {
+                const cudaError_t we = cudaEventSynchronize(t_ring.free_ev[b]);
+                if (we != cudaSuccess) {
+                    err = cuda_error(we, "cudaEventSynchronize(pinned ring)");
+                    break;
+                }
+            }
             const auto r0 = std::chrono::steady_clock::now();
             uint8_t *pin = static_cast<uint8_t *>(t_ring.buf[b]);
-            bool good = true;
-            if (full_frames) good = pread_parallel(j.fd, pin, nbytes, j.file_off + done * es);
-            else
-                for (int64_t k = 0; k < frames && good; ++k)
-                    good = pread_parallel(j.fd, pin + (size_t)k * band_elems * es, (size_t)band_elems * es,
-                                          j.file_off + (((k0 + k) * j.ny + j.y0) * j.nx) * es);
+            const bool good = full_frames ? read_chunk(j.fd, pin, 1, nbytes, j.file_off + done * es, 0)
+                                          : read_chunk(j.fd, pin, frames, (size_t)band_elems * es,
+                                                       j.file_off + ((k0 * j.ny + j.y0) * j.nx) * es, j.ny * j.nx * es);
             t_stats.read_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - r0).count();
             if (!good) {
                 err = make_error(AFK_ERR_FITS, "Unexpected end of file inside the data unit");
