@@ -169,3 +169,95 @@ def test_c5_sharded_bands_equal_whole(gpu, orc, alma):
             np.testing.assert_allclose(got, whole[gpu.SUM_COMPENSATED][y0:y0 + rows], rtol=1.2e-7)
     finally:
         gpu.set_sum_mode(gpu.SUM_COMPENSATED)
+
+
+# ---- SURVEY 8f rows at full size -----------------------------------------------------------------------------------
+
+def test_c3_alma_axis0_operators_sampled_bands(gpu, orc, alma):
+    """variance / stddev / arg maps / fold / centroid / median over the whole 16 GB cube, checked against the oracle on
+    row bands regenerated on the host, plus properties that hold at any size."""
+    nz, ny, nx = ALMA
+    alma.set_axis(2, "WAVE", "Angstrom")
+    wcs = (3621.6, 1.0, 0.83)
+    alma.set_wcs_axis(2, *wcs)
+    var = gpu.call("variance", alma, 0, nz).download()
+    std = gpu.call("stddev", alma, 0, nz).download()
+    arg, peak = (x.download() for x in gpu.call("extract_argmin_max_wavelength", alma, 0, nz, False))
+    lo, hi = (x.download() for x in gpu.call("peak_based_wavelength_range", alma, 0, nz, 5, False))
+    cen = gpu.call("extract_centrobaric_wavelength", alma, 0, nz).download()
+    med = gpu.call("median", alma, 100, 1125).download()   # odd window of 1025 frames
+    mn = gpu.call("extract_argmin_max_wavelength", alma, 0, nz, True)[1].download()
+    # properties: stddev^2 == variance; min <= median <= max; the two index maps are 10 apart; the peak wavelength is the
+    # world coordinate of an integer frame inside the range
+    np.testing.assert_allclose(std.astype(np.float64) ** 2, var, rtol=1e-6)
+    assert np.all(mn <= med) and np.all(med <= peak)
+    assert np.array_equal(hi - lo, np.full_like(hi, 10.0))
+    k = (arg.astype(np.float64) - wcs[0]) / wcs[2]
+    assert np.all(np.abs(k - np.round(k)) < 1e-2) and k.min() >= -0.01 and k.max() <= nz - 1 + 0.01
+    assert np.array_equal(np.round(k), hi - 5.0)
+    for y0 in (0, 513, 1021):
+        band = orc.gen_cube(0xAF1A0003, nz, ny, nx, y0=y0, rows=3)
+        rows = slice(y0, y0 + 3)
+        np.testing.assert_allclose(var[rows], orc.variance_f64(band, 0, nz), rtol=1e-5)
+        assert_bit_equal(arg[rows], orc.argmap(band, 0, nz, 0, False, wcs=wcs), f"C3 argmax rows {y0}")
+        assert_bit_equal(peak[rows], orc.minmax_fold(band, 0, nz, False), f"C3 max fold rows {y0}")
+        assert_bit_equal(lo[rows], orc.argmap(band, 0, nz, -5, False), f"C3 peak range rows {y0}")
+        np.testing.assert_allclose(cen[rows], orc.centroid_f64(band, 0, nz, wcs), rtol=1e-5)
+        assert_bit_equal(med[rows], orc.median(band, 100, 1125), f"C3 median rows {y0}")
+    # sequential mode on the same rows: the reference's own bits (Welford f32 with FMA)
+    gpu.set_sum_mode(gpu.SUM_SEQUENTIAL)
+    try:
+        seq = gpu.call("variance", alma, 0, nz).download()
+    finally:
+        gpu.set_sum_mode(gpu.SUM_COMPENSATED)
+    assert_bit_equal(seq[513:516], orc.variance(orc.gen_cube(0xAF1A0003, nz, ny, nx, y0=513, rows=3), 0, nz), "C3 Welford rows 513..516")
+
+
+def test_c3_alma_extract_wave_checksum_of_checksums(gpu, orc, alma):
+    """Two orthogonal reductions of the same 4 G voxels must agree: the sum over frames of extract_wave(All) equals the
+    sum over pixels of integral (both within 1e-5 of the exact total, positive data); spot frames against numpy."""
+    nz, ny, nx = ALMA
+    wave = gpu.call("extract_wave", alma, gpu.Roi()).download().astype(np.float64)
+    image = gpu.call("integral", alma, 0, nz)[0].download().astype(np.float64)
+    assert wave.shape == (nz,)
+    np.testing.assert_allclose(wave.sum(), image.sum(), rtol=2e-5)
+    for k in (0, 1999, nz - 1):
+        frame = gpu.call("slice_one_frame", alma, k).download().astype(np.float64)
+        np.testing.assert_allclose(wave[k], frame.sum(), rtol=1e-5)
+    # a box region: the waveform template at full size, against the host generator
+    box = [(x, y) for y in range(700, 703) for x in range(100, 164)]
+    got = gpu.call("extract_wave", alma, gpu.Roi(box)).download()
+    band = orc.gen_cube(0xAF1A0003, nz, ny, nx, y0=700, rows=3)
+    want = band[:, :, 100:164].astype(np.float64).sum(axis=(1, 2))
+    np.testing.assert_allclose(got, want, rtol=1e-5)
+
+
+def test_c3_size_ingest_round_trip(gpu, orc):
+    """A 2 GiB BITPIX 16 data unit (1 Gi voxels) through the chunked pipeline: 32 chunks, both streams, staging ring.
+    Property: decode(encode(x)) == x * bscale + bzero for every voxel, checked on the device; samples against the oracle."""
+    n = 1 << 30
+    rng = np.random.default_rng(41)
+    block = rng.integers(-32768, 32768, 1 << 24).astype(">i2")
+    raw = np.tile(block, n // block.size)
+    img = gpu.ingest(raw, gpu.FITS_I16, (1024, 1024, 1024), bscale=0.5, bzero=100.0)
+    want_block = orc.fits_decode(block.tobytes(), 2, block.size, bscale=0.5, bzero=100.0)
+    got = img.download().reshape(-1)
+    for off in (0, 17 * block.size, n - block.size):
+        assert np.array_equal(got[off:off + block.size], want_block)
+    # extremes of the whole decoded cube follow from the encoding
+    mn, mx = gpu.call("image_min_max", img)
+    assert float(mn) == float(want_block.min()) and float(mx) == float(want_block.max())
+
+
+def test_c4_size_display_statistics(gpu, orc):
+    """4096 x 4096: histogram counts sum to the pixel count and match the oracle; vmed / vmad idempotent under re-upload."""
+    rng = np.random.default_rng(42)
+    a = rng.lognormal(0.0, 1.0, (4096, 4096)).astype(np.float32)
+    a[::997, ::13] = np.nan
+    img = gpu.Image.upload(a)
+    vmin, vmax = img.vmin_vmax()
+    counts, _, _ = img.histogram(float(vmin), float(vmax))
+    assert counts.sum() == a.size and np.array_equal(counts, orc.histogram(a, float(vmin), float(vmax))[0])
+    z = img.zscale()
+    zo = orc.zscale(a)
+    assert z[0].tobytes() == zo[0].tobytes() and z[1].tobytes() == zo[1].tobytes()
