@@ -192,7 +192,7 @@ __device__ __forceinline__ void a0_batch(const char *&ptr, size_t stride, int64_
 
 template <class F, int VEC, int U, bool WAVE>
 __global__ void __launch_bounds__(256, 2) axis0_kernel(const Axis0K a) {
-    const int64_t px = ((int64_t)blockIdx.x * 256 + threadIdx.x) * VEC;
+    const int64_t px = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
     if (px >= a.n2) return;
     const int kc = blockIdx.y;
     int64_t k = a.start + (int64_t)kc * a.chunk;
@@ -606,9 +606,16 @@ Axis0Plan axis0_plan(const Axis0Args &a, int sm_count) {
     Axis0Plan pl{};
     const bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0);
     pl.vec = aligned ? 4 : 1;
-    pl.ntiles = (a.n2 + 256 * pl.vec - 1) / (256 * pl.vec);
+    pl.block = 256;
     const int64_t n = a.end - a.start;
     const bool mergeable = a.op == A0_ARGFOLD || a.mode != SUM_SEQUENTIAL;
+    // An order-dependent reduction cannot split the spectral axis: on a small image the only parallelism is the pixels,
+    // so give every pixel its own thread and spread the warps over the SMs (latency-bound chain per pixel either way)
+    if (!mergeable && (a.n2 + 256 * pl.vec - 1) / (256 * pl.vec) < sm_count) {
+        pl.vec = 1;
+        pl.block = a.n2 >= (int64_t)64 * sm_count ? 64 : 32;
+    }
+    pl.ntiles = (a.n2 + (int64_t)pl.block * pl.vec - 1) / ((int64_t)pl.block * pl.vec);
     pl.ksplit = 1;
     const int64_t want = 2 * (int64_t)sm_count;
     if (mergeable && pl.ntiles < want && n >= 32) {
@@ -626,8 +633,8 @@ Axis0Plan axis0_plan(const Axis0Args &a, int sm_count) {
 
 template <class F, bool WAVE> static void a0_go(const Axis0K &k, const Axis0Plan &pl, cudaStream_t s) {
     const dim3 grid((unsigned)pl.ntiles, (unsigned)pl.ksplit);
-    if (pl.vec == 4) axis0_kernel<F, 4, 8, WAVE><<<grid, 256, 0, s>>>(k);
-    else axis0_kernel<F, 1, 16, WAVE><<<grid, 256, 0, s>>>(k);
+    if (pl.vec == 4) axis0_kernel<F, 4, 8, WAVE><<<grid, pl.block, 0, s>>>(k);
+    else axis0_kernel<F, 1, 16, WAVE><<<grid, pl.block, 0, s>>>(k);
     count_launch();
     if (pl.ksplit > 1) {
         axis0_merge_kernel<F><<<(unsigned)((k.n2 + 255) / 256), 256, 0, s>>>(k);

@@ -101,6 +101,7 @@ struct Axis0Args {
 
 struct Axis0Plan {
     int vec;
+    int block; // threads per CTA
     int64_t ntiles;
     int ksplit;
     int64_t chunk;
