@@ -226,7 +226,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -368,7 +368,7 @@ def run_gpu(args):
         }
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
-        print(json.dumps(line), flush=True)
+        emit(line)
     if gather is not None:
         barrier()
         gather.close()
@@ -462,7 +462,27 @@ def run_e2e(args, afk, torch, dist, nz, ny, nx, rank, world, dev):
                               "path": "cube cached as a device handle in the graph; per step: set_constant(end) -> compute -> download 2-D result"}}
 
 
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries loaded below (NCCL prints its version banner to stdout when
+    NCCL_DEBUG is set in the environment) write to file descriptor 1 directly: point fd 1 at stderr for the whole run and
+    keep the real stdout for the final line."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
