@@ -614,9 +614,12 @@ template <int OP> __device__ __forceinline__ float map_one(float u, float v, con
     return u;
 }
 
+// A thread issues U independent 16-byte loads per operand before it computes (U x 2048 threads x 16 B per SM in
+// flight: one load per thread covers only ~2/3 of the HBM latency-bandwidth product on B200).
 template <int OP, bool BINARY>
 __global__ void __launch_bounds__(256) map_kernel(const float *__restrict__ u, const float *__restrict__ v,
                                                    float *__restrict__ out, int64_t n, int vec_ok, MapK k) {
+    constexpr int U = BINARY ? 2 : 4;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
     int64_t done = 0;
@@ -625,15 +628,30 @@ __global__ void __launch_bounds__(256) map_kernel(const float *__restrict__ u, c
         const float4 *u4 = reinterpret_cast<const float4 *>(u);
         const float4 *v4 = reinterpret_cast<const float4 *>(v);
         float4 *o4 = reinterpret_cast<float4 *>(out);
-        for (int64_t i = tid; i < n4; i += nthreads) {
-            float4 x = ld_stream(u4 + i);
-            float4 y = BINARY ? ld_stream(v4 + i) : make_float4(0, 0, 0, 0);
-            float4 r;
-            r.x = map_one<OP>(x.x, y.x, k);
-            r.y = map_one<OP>(x.y, y.y, k);
-            r.z = map_one<OP>(x.z, y.z, k);
-            r.w = map_one<OP>(x.w, y.w, k);
-            o4[i] = r;
+        for (int64_t i = tid; i < n4; i += nthreads * U) {
+            float4 x[U], y[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int64_t idx = i + j * nthreads;
+                x[j] = make_float4(0, 0, 0, 0);
+                y[j] = make_float4(0, 0, 0, 0);
+                if (idx < n4) {
+                    x[j] = ld_stream(u4 + idx);
+                    if (BINARY) y[j] = ld_stream(v4 + idx);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int64_t idx = i + j * nthreads;
+                if (idx < n4) {
+                    float4 r;
+                    r.x = map_one<OP>(x[j].x, y[j].x, k);
+                    r.y = map_one<OP>(x[j].y, y[j].y, k);
+                    r.z = map_one<OP>(x[j].z, y[j].z, k);
+                    r.w = map_one<OP>(x[j].w, y[j].w, k);
+                    o4[idx] = r;
+                }
+            }
         }
         done = n4 << 2;
     }
@@ -808,14 +826,25 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float *__restrict__ i
     const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
     int64_t done = 0;
     if (vec_ok) {
+        constexpr int U = 4; // independent 16-byte loads in flight per thread
         const int64_t n4 = n >> 2;
         const float4 *i4 = reinterpret_cast<const float4 *>(img);
-        for (int64_t i = tid; i < n4; i += nthreads) {
-            float4 x = ld_stream(i4 + i);
-            float e[4] = {x.x, x.y, x.z, x.w};
+        for (int64_t i = tid; i < n4; i += nthreads * U) {
+            float4 x[U];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (e[j] == e[j]) { mn = fminf(mn, e[j]); mx = fmaxf(mx, e[j]); any = true; }
+            for (int j = 0; j < U; ++j) {
+                const int64_t idx = i + j * nthreads;
+                // NaN padding: ignored by the fold below
+                x[j] = idx < n4 ? ld_stream(i4 + idx) : make_float4(__int_as_float(0x7fc00000), __int_as_float(0x7fc00000),
+                                                                     __int_as_float(0x7fc00000), __int_as_float(0x7fc00000));
+            }
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                float e[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (e[q] == e[q]) { mn = fminf(mn, e[q]); mx = fmaxf(mx, e[q]); any = true; }
+            }
         }
         done = n4 << 2;
     }
@@ -838,11 +867,15 @@ cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_
 // ----------------------------------------------------------------------------------------------------
 // K6: down_sampling = decimation (lib.rs:1894-1962): out[z][j][i] = img[z][j*n][i*n]
 // ----------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) downsample_kernel(const float *__restrict__ img, int64_t ny, int64_t nx, int64_t n,
-                                                          float *__restrict__ out, int64_t oy, int64_t ox, int64_t total) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t x = i % ox, t = i / ox, y = t % oy, z = t / oy;
-        out[i] = img[(z * ny + y * n) * nx + x * n];
+// IDX = unsigned when every index fits in 32 bits (the usual case): 64-bit div/mod is ~4x the instructions
+template <typename IDX>
+__global__ void __launch_bounds__(256) downsample_kernel(const float *__restrict__ img, int64_t ny_, int64_t nx_, int64_t n_,
+                                                          float *__restrict__ out, int64_t oy_, int64_t ox_, int64_t total_) {
+    const IDX ny = (IDX)ny_, nx = (IDX)nx_, n = (IDX)n_, oy = (IDX)oy_, ox = (IDX)ox_, total = (IDX)total_;
+    const IDX step = (IDX)gridDim.x * blockDim.x;
+    for (IDX i = (IDX)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+        const IDX t = i / ox, x = i - t * ox, z = t / oy, y = t - z * oy;
+        out[i] = img[(size_t)((z * ny + y * n) * nx + x * n)];
     }
 }
 
@@ -852,7 +885,10 @@ cudaError_t downsample_launch(const float *img, int64_t c, int64_t ny, int64_t n
     if (total <= 0) return cudaSuccess;
     int64_t blocks = (total + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    downsample_kernel<<<(int)blocks, 256, 0, s>>>(img, ny, nx, n, out, oy, ox, total);
+    // 32-bit indices when the input, the output and the grid-stride overshoot all stay below 2^32
+    const bool small = c * ny * nx < (int64_t(1) << 31) && total < (int64_t(1) << 31);
+    if (small) downsample_kernel<unsigned><<<(int)blocks, 256, 0, s>>>(img, ny, nx, n, out, oy, ox, total);
+    else downsample_kernel<int64_t><<<(int)blocks, 256, 0, s>>>(img, ny, nx, n, out, oy, ox, total);
     AFK_COUNT_LAUNCH();
     return cudaGetLastError();
 }
@@ -914,8 +950,11 @@ __global__ void __launch_bounds__(256) colormap_kernel(const float *__restrict__
     const int64_t groups_per_row = (nx + 3) >> 2;
     const int64_t total = ny * groups_per_row;
     const bool row_vec = vec_ok != 0;
+    const bool idx32 = total < (int64_t(1) << 31);
     for (int64_t gi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t y = gi / groups_per_row, x0 = (gi - y * groups_per_row) << 2;
+        // 64-bit division is ~60 instructions; the kernel is issue-bound (profiles/r1_c4_kernels_ncu_full.json)
+        const int64_t y = idx32 ? (int64_t)((unsigned)gi / (unsigned)groups_per_row) : gi / groups_per_row;
+        const int64_t x0 = (gi - y * groups_per_row) << 2;
         const int64_t ys = flip_y ? (ny - 1 - y) : y;
         const int cnt = (int)min((int64_t)4, nx - x0);
         uint32_t px[4];

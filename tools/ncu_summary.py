@@ -85,6 +85,8 @@ def main_grouped(rep, out):
             "warps_active_pct": avg("sm__warps_active.avg.pct_of_peak_sustained_active"),
             "registers_per_thread": val(rs[0], "launch__registers_per_thread"),
             "l2_hit_rate_pct": avg("lts__t_sector_hit_rate.pct"),
+            "issue_active_pct": avg("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+            "warp_instructions": avg("smsp__inst_executed.sum"),
         })
     with open(out + ".json", "w") as f:
         json.dump(summ, f, indent=1)

@@ -78,6 +78,29 @@ elif args.workload == "ingest":  # decode kernel on device-resident raw bytes: B
         afk.k_ingest(raw.device_ptr, afk.FITS_F32, n, dst.device_ptr, bscale=0.5, bzero=1.0)
     for _ in range(args.launches):
         afk.k_ingest(raw.device_ptr, afk.FITS_I16, n, dst.device_ptr, bscale=0.5, bzero=1.0)
+elif args.workload == "c4":  # the 4096^2 display chain (BASELINE configs[3]) + the per-pixel operators, kernel by kernel
+    N = 4096
+    rng = np.random.default_rng(4)
+    img = afk.Image.upload(np.exp(rng.standard_normal((N, N))).astype(np.float32))
+    v = afk.Image.upload(np.exp(rng.standard_normal((N, N))).astype(np.float32))
+    rgba = afk.Image.alloc((N, N))
+    lut = afk.Lut("Flame")
+    lut.set_lims(0.2, 0.3, 0.9)
+    vmin, vmax = afk.call("image_min_max", img)
+    tone = np.arange(256, dtype=np.float32)
+    lmax = float(np.float32(np.log(np.float32(1001.0)) / np.log(np.float32(1000.0))))
+    chain = {"logscale_a": 1000.0, "logscale_vmin": float(vmin), "logscale_vmax": float(vmax), "normalize_min": 0.0,
+             "normalize_max": lmax / 65535.0, "tone_table": tone}
+    for _ in range(args.launches):
+        afk.call("image_min_max", img)
+        afk.colormap_device(img, lut, float(vmin), float(vmax), rgba.device_ptr, channels=4)
+        afk.colormap_device(img, lut, float(vmin), float(vmax), rgba.device_ptr, channels=3)
+        afk.colormap_device(img, lut, 0.0, 65535.0, rgba.device_ptr, channels=4, chain=chain)
+        afk.call("linear_composition", img, v, 0.4, 0.6)
+        afk.call("ratio", img, v)
+        afk.call("convert_to_logscale", img, 1000.0, float(vmin), float(vmax))
+        afk.call("apply_tone_curve", img, afk.ToneCurve(tone))
+        afk.call("down_sampling", img, 2)
 elif args.workload == "stats":
     rng = np.random.default_rng(4)
     img = afk.Image.upload(np.exp(rng.standard_normal((4096, 4096))).astype(np.float32))
