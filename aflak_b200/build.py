@@ -25,6 +25,7 @@ NVCC_FLAGS = [
     "-x", "cu",
     "-shared",
     "-cudart", "static",
+    "-Xlinker", "--no-undefined",  # a missing definition fails the build, not the first dlopen on the GPU box
     "--threads", "0",  # compile the translation units in parallel
 ]
 

@@ -10,6 +10,7 @@
 // (Welford, sequential sums) are never split in SUM_SEQUENTIAL mode.
 //
 // Reference citations are relative to /root/reference/src/.
+#include <cstdlib>
 #include "kernels.h"
 
 #include <cfloat>
@@ -284,7 +285,8 @@ template <bool COMP> __global__ void __launch_bounds__(256) centroid_mask_kernel
 //            staging stores and the per-spectrum loads are bank-conflict free); one warp per spaxel runs a radix select
 //            over key - min(key): the digits cover only the range the spectrum really spans (typically 3 passes of 8
 //            bits, well spread histogram bins).
-//   n beyond shared memory: median_global_kernel re-reads the column from L2 on every pass.
+//   long windows on large images, and any window beyond shared memory: median_stream_kernel (below) streams the cube twice
+//            with coalesced loads instead of staging it.
 // ---------------------------------------------------------------------------------------------------------------
 struct MedianK {
     const float *cube;
@@ -557,37 +559,442 @@ __global__ void __launch_bounds__(256) median_select_kernel(const MedianK a) {
     if (nan && n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
 }
 
-// Ranges that do not fit in shared memory even for one spaxel per CTA: plain 4 x 8-bit radix select with the column
-// re-read on every pass (L2 catches the re-reads of a single spaxel column).
-__global__ void __launch_bounds__(32) median_global_kernel(const MedianK a) {
-    __shared__ unsigned hist[256];
-    const int64_t px = blockIdx.x;
-    const int lane = threadIdx.x;
-    const float *col = a.cube + a.start * a.n2 + px;
-    bool nan = false;
-    auto select = [&](unsigned kth) -> unsigned {
-        unsigned prefix = 0u, mask = 0u, cnt;
-        for (int shift = 24; shift >= 0; shift -= 8) {
-            for (int b = lane; b < 256; b += 32) hist[b] = 0u;
-            __syncwarp();
-            for (int64_t i = lane; i < a.n; i += 32) {
-                const float f = col[i * a.n2];
-                nan |= (f != f);
-                const unsigned key = med_key(f);
-                if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
-            }
-            __syncwarp();
-            const unsigned digit = med_pick_digit(hist, kth, cnt, lane);
-            prefix |= digit << shift;
-            mask |= 255u << shift;
-            __syncwarp();
+// ---------------------------------------------------------------------------------------------------------------
+// Warp-synchronous select on a short list in shared memory (the last phase of median_stream_kernel) -- no atomics, no
+// barriers.  Shared-memory atomics run at about one per clock per SM (the histogram select above spends a clock per
+// voxel and pass on them); compare-and-count in registers is an order of magnitude cheaper per key when the pivots are
+// good, so they come from the data:
+//   round: 32 jittered stratified samples, one per lane, bitonic-sorted across the warp; 7 of them around the sample
+//          median are the pivots.  Count pass: c_j = #(key < p_j) in registers.  The bin (lo, hi) that holds rank r is then
+//          compacted IN PLACE (ballot / popc offsets; every load of a chunk precedes its stores, which land in the
+//          already-read prefix), together with the number of keys equal to lo (they are dropped: a bin made of
+//          duplicates still shrinks) and the smallest key >= hi (the even-n successor).
+//   Rounds repeat on the compacted list (~240 -> ~15 keys) until it fits one key per lane, then it is ranked by counting.
+//   A pivot set that misses the median only makes the next list longer: exactness never depends on the data.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kMedPivots = 7;
+constexpr unsigned kFull = 0xffffffffu;
+
+// ascending bitonic sort of one value per lane
+__device__ __forceinline__ unsigned med_warp_sort(unsigned v, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const unsigned o = __shfl_xor_sync(kFull, v, j);
+            const bool up = ((lane & k) == 0) == ((lane & j) == 0); // keep the smaller one
+            v = up ? min(v, o) : max(v, o);
         }
-        return prefix;
+    }
+    return v;
+}
+
+struct MedState {
+    int m;            // keys in the list
+    unsigned r;       // wanted rank within the list
+    unsigned above;   // smallest key known to sort after every key of the list
+    bool has_above;
+};
+
+// One round on list `keys[0, st.m)`.  Returns true when the answer is known (k_r / k_next set).
+__device__ __forceinline__ bool med_round(unsigned *keys, MedState &st, bool want_next, int lane, unsigned seed, unsigned &k_r, unsigned &k_next) {
+    const int m = st.m;
+    // ---- pivots: stratified sample, one key per lane, jittered so that periodic spectra cannot alias the stride ----
+    const int stride = m >> 5; // m > 32
+    unsigned h = (seed ^ (unsigned)lane * 0x9E3779B9u) * 0x85EBCA6Bu;
+    h ^= h >> 15;
+    const int pos = (int)(((long long)lane * m) >> 5) + (int)(h % (unsigned)stride);
+    const unsigned smp = med_warp_sort(keys[pos], lane);
+    unsigned pv[kMedPivots];
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j) pv[j] = __shfl_sync(kFull, smp, 10 + 2 * j);
+    // ---- count pass ----
+    unsigned c[kMedPivots];
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j) c[j] = 0u;
+    const bool vec = (m >= 256) && ((reinterpret_cast<uintptr_t>(keys) & 15u) == 0);
+    const int nvec = vec ? (m & ~255) : 0; // keys handled 8 per lane
+    for (int base = 0; base < nvec; base += 256) {
+        const uint4 *k4 = reinterpret_cast<const uint4 *>(keys + base);
+        const uint4 v0 = k4[lane], v1 = k4[lane + 32];
+        const unsigned kk[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+#pragma unroll
+            for (int j = 0; j < kMedPivots; ++j) c[j] += kk[u] < pv[j];
+    }
+    for (int i = nvec + lane; i < m; i += 32) {
+        const unsigned key = keys[i];
+#pragma unroll
+        for (int j = 0; j < kMedPivots; ++j) c[j] += key < pv[j];
+    }
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j) c[j] = __reduce_add_sync(kFull, c[j]);
+    // ---- bin of rank r: b = number of pivots with c_j <= r ----
+
+    unsigned below = 0u, lo = 0u, hi = 0u;
+    bool has_lo = false, has_hi = false;
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j) {
+        if (c[j] <= st.r) { below = c[j]; lo = pv[j]; has_lo = true; }
+    }
+#pragma unroll
+    for (int j = kMedPivots - 1; j >= 0; --j) {
+        if (c[j] > st.r) { hi = pv[j]; has_hi = true; }
+    }
+
+    // ---- compaction in place: keep lo < key < hi; count key == lo; min of key >= hi ----
+    unsigned n_eq = 0u, hi_min = kFull, out = 0u;
+    bool hi_any = false;
+    __syncwarp();
+    for (int base = 0; base < m; base += 256) {
+        unsigned kk[8];
+        unsigned valid = 0u;
+        if (base < nvec) {
+            const uint4 *k4 = reinterpret_cast<const uint4 *>(keys + base);
+            const uint4 v0 = k4[lane], v1 = k4[lane + 32];
+            kk[0] = v0.x; kk[1] = v0.y; kk[2] = v0.z; kk[3] = v0.w; kk[4] = v1.x; kk[5] = v1.y; kk[6] = v1.z; kk[7] = v1.w;
+            valid = 0xFFu;
+        } else {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int i = base + u * 32 + lane;
+                kk[u] = 0u;
+                if (i < m) { kk[u] = keys[i]; valid |= 1u << u; }
+            }
+        }
+        __syncwarp(); // every load of this chunk precedes its stores
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const bool ok = (valid >> u) & 1u;
+            const unsigned key = kk[u];
+            const bool ge_hi = ok && has_hi && key >= hi;
+            const bool le_lo = ok && has_lo && key <= lo;
+            if (ok && has_lo && key == lo) ++n_eq;
+            if (ge_hi) { hi_min = min(hi_min, key); hi_any = true; }
+            const bool keep = ok && !ge_hi && !le_lo;
+            const unsigned bal = __ballot_sync(kFull, keep);
+            if (keep) keys[out + __popc(bal & ((1u << lane) - 1u))] = key;
+            out += __popc(bal);
+        }
+    }
+    __syncwarp();
+    n_eq = __reduce_add_sync(kFull, n_eq);
+    if (want_next) {
+        hi_min = __reduce_min_sync(kFull, hi_min);
+        if (__any_sync(kFull, hi_any)) { st.above = hi_min; st.has_above = true; } // keys >= hi sort below every earlier `above`
+    }
+    unsigned r = st.r - below;
+    if (r < n_eq) { // the wanted key is lo itself
+        k_r = lo;
+        if (!want_next || r + 1 < n_eq) { k_next = lo; return true; }
+        // successor: smallest kept key, else `above`
+        unsigned mn = kFull;
+        for (int i = lane; i < (int)out; i += 32) mn = min(mn, keys[i]);
+        mn = __reduce_min_sync(kFull, mn);
+        k_next = out > 0u ? mn : st.above;
+        return true;
+    }
+    st.r = r - n_eq;
+    st.m = (int)out;
+    return false;
+}
+
+// list of at most 32 keys: rank by counting
+__device__ __forceinline__ void med_rank32(const unsigned *keys, const MedState &st, bool want_next, int lane, unsigned &k_r, unsigned &k_next) {
+    const int m = st.m;
+    const unsigned mine = lane < m ? keys[lane] : kFull;
+    unsigned lt = 0u, le = 0u;
+    for (int j = 0; j < m; ++j) {
+        const unsigned o = __shfl_sync(kFull, mine, j);
+        lt += o < mine;
+        le += o <= mine;
+    }
+    const unsigned b0 = __ballot_sync(kFull, lane < m && lt <= st.r && st.r < le);
+    k_r = __shfl_sync(kFull, mine, __ffs(b0) - 1);
+    k_next = k_r;
+    if (!want_next) return;
+    if (st.r + 1 < (unsigned)m) {
+        const unsigned b1 = __ballot_sync(kFull, lane < m && lt <= st.r + 1 && st.r + 1 < le);
+        k_next = __shfl_sync(kFull, mine, __ffs(b1) - 1);
+    } else {
+        k_next = st.above;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// median_stream_kernel: windows longer than 64 frames, any length, any alignment.
+//
+// Staging whole spectra in shared memory limits a CTA to a handful of spaxels, i.e. to 16-32 contiguous bytes per frame:
+// measured 0.75 TB/s for the staging alone on the ALMA cube, whatever the select does afterwards (the memory system
+// is bound by the number of sector requests, not by their bytes).  Here the cube is STREAMED like the other axis-0
+// reductions -- lane = spaxel, a warp reads 128 contiguous bytes of a frame, 16 frames in flight per thread -- and
+// only a small candidate list per spaxel ever lives in shared memory:
+//   A  32 stratified sample frames per spaxel -> sorted by a warp -> 7 pivots around the sample median (registers)
+//   B  stream the window: c_j = #(key < pivot_j) per spaxel (compare + add in registers, no atomics)
+//      -> the bin (lo, hi) that holds the wanted rank; about 1/16 of the keys fall into it
+//   C  stream the window again (largely from L2): append the keys of the bin to the spaxel's list in shared memory (one
+//      shared atomic per APPENDED key), count the keys equal to lo, track the smallest key >= hi (even-n successor)
+//   D  one warp per spaxel finishes on the list with the warp-synchronous rounds of med_round / med_rank32
+// A bin that overflows the list (heavy ties, unlucky pivots) is refined by its warp against the global column with pivots
+// sampled from the bin itself, until it fits: exactness never depends on the data.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kMsPix = 32;            // spaxels per CTA (= lanes)
+constexpr int kMsWarps = 16;          // 2 CTAs x 512 threads x 16 loads in flight = 64 KB per SM
+constexpr int kMsCap = 768;           // candidate slots per spaxel (20 % of an ALMA window: a 4-rank bin of 64 samples overflows 4e-4 of the time)
+constexpr int kMsRow = kMsCap + 1;    // odd row stride: neighbouring spaxels start in different banks
+constexpr int kMsU = 16;              // frames in flight per thread
+constexpr int64_t kMedStreamMinFrames = 2048;        // shorter windows: the shared-memory select is faster
+constexpr int64_t kMedStreamMinPixels = 2 * 148 * 32; // fewer spaxels: not enough 32-spaxel CTAs for two per SM
+
+__device__ __forceinline__ unsigned ms_ld(const float *p) {
+    unsigned r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ unsigned ms_key(unsigned b) { return b ^ ((unsigned)((int)b >> 31) | 0x80000000u); } // == med_key, 2 instructions
+
+struct MsBin { // keys strictly inside (lo, hi) are candidates; sentinels 0 / 0xFFFFFFFF only collide with NaN keys
+    unsigned lo, hi, below;
+    bool has_lo;
+};
+
+// bin of rank r from cumulative counts c_j = #(key < pv_j) (pv ascending)
+__device__ __forceinline__ MsBin ms_pick_bin(const unsigned (&c)[kMedPivots], const unsigned (&pv)[kMedPivots], unsigned r) {
+    MsBin b{0u, kFull, 0u, false};
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j)
+        if (c[j] <= r) { b.lo = pv[j]; b.below = c[j]; b.has_lo = true; }
+#pragma unroll
+    for (int j = kMedPivots - 1; j >= 0; --j)
+        if (c[j] > r) b.hi = pv[j];
+    return b;
+}
+
+// One refinement round of an overflowing bin by a single warp, against the global column (lane = frame).
+// On entry the list holds kMsCap keys of the bin (lo, hi) and r is the rank among the keys strictly inside it.
+// Returns true when the answer is known.
+__device__ bool ms_refine(const float *col, int64_t n2, int n, unsigned *list, unsigned &lo, unsigned &hi, bool &has_lo, unsigned &r,
+                          unsigned &m, unsigned &above, bool want_next, int lane, unsigned seed, unsigned &k_r, unsigned &k_next) {
+    unsigned h = (seed ^ (unsigned)lane * 0x9E3779B9u) * 0x85EBCA6Bu;
+    h ^= h >> 15;
+    const unsigned smp = med_warp_sort(list[lane * (kMsCap / 32) + (h % (kMsCap / 32))], lane);
+    unsigned pv[kMedPivots], c[kMedPivots];
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j) { pv[j] = __shfl_sync(kFull, smp, 10 + 2 * j); c[j] = 0u; }
+    for (int k = lane; k < n; k += 32) {
+        const unsigned key = ms_key(ms_ld(col + (size_t)k * n2));
+        if (key > lo && key < hi) {
+#pragma unroll
+            for (int j = 0; j < kMedPivots; ++j) c[j] += key < pv[j];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kMedPivots; ++j) c[j] = __reduce_add_sync(kFull, c[j]);
+    const MsBin b = ms_pick_bin(c, pv, r);
+    const unsigned nlo = b.has_lo ? b.lo : lo, nhi = b.hi < hi ? b.hi : hi;
+    unsigned n_eq = 0u, hi_min = kFull, out = 0u;
+    __syncwarp();
+    for (int k0 = 0; k0 < n; k0 += 32) {
+        const int k = k0 + lane;
+        const unsigned key = k < n ? ms_key(ms_ld(col + (size_t)k * n2)) : 0u;
+        const bool in_old = k < n && key > lo && key < hi;
+        if (in_old && b.has_lo && key == nlo) ++n_eq;
+        if (in_old && key >= nhi) hi_min = min(hi_min, key);
+        const bool keep = in_old && key > nlo && key < nhi;
+        const unsigned bal = __ballot_sync(kFull, keep);
+        const unsigned at = out + __popc(bal & ((1u << lane) - 1u));
+        if (keep && at < (unsigned)kMsCap) list[at] = key;
+        out += __popc(bal);
+    }
+    __syncwarp();
+    n_eq = __reduce_add_sync(kFull, n_eq);
+    hi_min = __reduce_min_sync(kFull, hi_min);
+    if (hi_min != kFull) above = hi_min;
+    const unsigned rr = r - b.below;
+    if (b.has_lo && rr < n_eq) {
+        k_r = nlo;
+        if (!want_next || rr + 1 < n_eq) { k_next = nlo; return true; }
+        unsigned mn = kFull; // successor of nlo inside the old bin, else `above`
+        for (int k = lane; k < n; k += 32) {
+            const unsigned key = ms_key(ms_ld(col + (size_t)k * n2));
+            if (key > nlo && key < hi) mn = min(mn, key);
+        }
+        mn = __reduce_min_sync(kFull, mn);
+        k_next = mn != kFull ? mn : above;
+        return true;
+    }
+    r = rr - (b.has_lo ? n_eq : 0u);
+    lo = nlo; hi = nhi; has_lo = has_lo || b.has_lo;
+    m = out;
+    return false;
+}
+
+__global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(const MedianK a) {
+    extern __shared__ unsigned s_list[]; // [kMsPix][kMsRow] candidate lists; phases A/B alias samples and per-warp counts onto it
+    __shared__ unsigned s_piv[kMsPix][kMedPivots + 1];
+    __shared__ unsigned s_lo[kMsPix], s_hi[kMsPix], s_below[kMsPix], s_haslo[kMsPix], s_cnt[kMsPix];
+    __shared__ unsigned s_eq[kMsWarps][kMsPix], s_himin[kMsWarps][kMsPix];
+    const int n = (int)a.n;
+    const int tid = threadIdx.x, g = tid >> 5, lane = tid & 31;
+    const int64_t px0 = (int64_t)blockIdx.x * kMsPix;
+    const int64_t mypx = px0 + lane;
+    const bool active = mypx < a.n2;
+    const float *col = a.cube + a.start * a.n2 + (active ? mypx : a.n2 - 1); // inactive lanes read a valid address
+    const unsigned r0 = (unsigned)((n - 1) / 2);
+    const bool even = (n & 1) == 0;
+    bool nan = false;
+    unsigned lo = 0u, hi = kFull;
+    if (tid < kMsPix) { s_cnt[tid] = 0u; s_lo[tid] = 0u; s_hi[tid] = kFull; s_below[tid] = 0u; s_haslo[tid] = 0u; }
+    if (n > kMsCap) {
+        // ---- A: 64 stratified sample frames per spaxel (the same frames for the whole CTA: coalesced) -> pivots ----
+        unsigned *s_smp = s_list; // [kMsPix][65]
+        const int stride = n >> 6; // n > kMsCap >= 64
+        for (int i = g; i < 64; i += kMsWarps) {
+            unsigned h = ((unsigned)blockIdx.x * 0x9E3779B9u + (unsigned)i * 0x85EBCA6Bu) * 0xC2B2AE35u;
+            h ^= h >> 16;
+            const int f = (int)(((long long)i * n) >> 6) + (int)(h % (unsigned)stride);
+            s_smp[lane * 65 + i] = ms_key(ms_ld(col + (size_t)f * a.n2));
+        }
+        __syncthreads();
+        // a warp ranks the 64 samples of a spaxel by counting (ties broken by position); the samples of ranks
+        // 20, 24, .., 44 are the pivots: 4-rank bins (6 % of the keys each), +-3 sigma of the sample median's rank
+        for (int p = g; p < kMsPix; p += kMsWarps) {
+            const unsigned *sp = s_smp + p * 65;
+            const unsigned v0 = sp[lane], v1 = sp[lane + 32];
+            unsigned r0s = 0u, r1s = 0u;
+            for (int i = 0; i < 64; ++i) {
+                const unsigned o = sp[i];
+                r0s += (o < v0) || (o == v0 && i < lane);
+                r1s += (o < v1) || (o == v1 && i < lane + 32);
+            }
+            if (r0s >= 20u && r0s <= 44u && (r0s & 3u) == 0u) s_piv[p][(r0s - 20u) >> 2] = v0;
+            if (r1s >= 20u && r1s <= 44u && (r1s & 3u) == 0u) s_piv[p][(r1s - 20u) >> 2] = v1;
+        }
+        __syncthreads();
+        unsigned pv[kMedPivots], c[kMedPivots];
+#pragma unroll
+        for (int j = 0; j < kMedPivots; ++j) { pv[j] = s_piv[lane][j]; c[j] = 0u; }
+        // ---- B: count (full blocks of kMsU frames unchecked, then the tail) ----
+        int k = g;
+        for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
+            unsigned raw[kMsU];
+#pragma unroll
+            for (int u = 0; u < kMsU; ++u) raw[u] = ms_ld(col + (size_t)(k + u * kMsWarps) * a.n2);
+#pragma unroll
+            for (int u = 0; u < kMsU; ++u) {
+                const unsigned key = ms_key(raw[u]);
+#pragma unroll
+                for (int j = 0; j < kMedPivots; ++j) c[j] += key < pv[j];
+            }
+        }
+        for (; k < n; k += kMsWarps) {
+            const unsigned key = ms_key(ms_ld(col + (size_t)k * a.n2));
+#pragma unroll
+            for (int j = 0; j < kMedPivots; ++j) c[j] += key < pv[j];
+        }
+        unsigned *s_c = s_list; // [kMsWarps][kMsPix][8] (the samples are no longer needed: every warp passed the barrier above)
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < kMedPivots; ++j) s_c[(g * kMsPix + lane) * 8 + j] = c[j];
+        __syncthreads();
+        if (g == 0) {
+#pragma unroll
+            for (int j = 0; j < kMedPivots; ++j) {
+                unsigned t = 0u;
+                for (int w = 0; w < kMsWarps; ++w) t += s_c[(w * kMsPix + lane) * 8 + j];
+                c[j] = t;
+            }
+            const MsBin b = ms_pick_bin(c, pv, r0);
+            s_lo[lane] = b.lo; s_hi[lane] = b.hi; s_below[lane] = b.below; s_haslo[lane] = b.has_lo ? 1u : 0u;
+        }
+        __syncthreads();
+        lo = s_lo[lane]; hi = s_hi[lane];
+    } else {
+        __syncthreads();
+    }
+    // ---- C: collect the bin ----
+    const bool has_lo = s_haslo[lane] != 0u;
+    unsigned n_eq = 0u, hi_min = kFull;
+    const unsigned eq_inc = has_lo ? 1u : 0u;
+    unsigned *row = s_list + lane * kMsRow;
+    auto collect = [&](unsigned rawbits) {
+        const float f = __uint_as_float(rawbits);
+        nan |= (f != f);
+        const unsigned key = ms_key(rawbits);
+        n_eq += (key == lo) ? eq_inc : 0u;
+        hi_min = min(hi_min, key >= hi ? key : kFull);
+        if (key > lo && key < hi) {
+            const unsigned at = atomicAdd(&s_cnt[lane], 1u);
+            if (at < (unsigned)kMsCap) row[at] = key;
+        }
     };
-    const unsigned klo = select((unsigned)((a.n - 1) / 2));
-    const unsigned khi = (a.n & 1) ? klo : select((unsigned)(a.n / 2));
-    if (nan && a.n > 1) atomicMax(a.flag, 1u);
-    if (lane == 0) a.out[px] = med_finish(klo, khi, (a.n & 1) == 0);
+    if (active) {
+        int k = g;
+        for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
+            unsigned raw[kMsU];
+#pragma unroll
+            for (int u = 0; u < kMsU; ++u) raw[u] = ms_ld(col + (size_t)(k + u * kMsWarps) * a.n2);
+#pragma unroll
+            for (int u = 0; u < kMsU; ++u) collect(raw[u]);
+        }
+        for (; k < n; k += kMsWarps) collect(ms_ld(col + (size_t)k * a.n2));
+    }
+    s_eq[g][lane] = n_eq;
+    s_himin[g][lane] = hi_min;
+    __syncthreads();
+    // ---- D: one warp per spaxel ----
+    for (int p = g; p < kMsPix; p += kMsWarps) {
+        const int64_t px = px0 + p;
+        if (px >= a.n2) continue; // warp-uniform
+        unsigned *list = s_list + p * kMsRow;
+        unsigned m = s_cnt[p];
+        unsigned blo = s_lo[p], bhi = s_hi[p];
+        bool bhas_lo = s_haslo[p] != 0u;
+        unsigned eq = lane < kMsWarps ? s_eq[lane][p] : 0u;
+        eq = __reduce_add_sync(kFull, eq);
+        unsigned above = lane < kMsWarps ? s_himin[lane][p] : kFull;
+        above = __reduce_min_sync(kFull, above);
+        unsigned r = r0 - s_below[p];
+        unsigned klo = 0u, khi = 0u;
+        bool done = false;
+        const float *pcol = a.cube + a.start * a.n2 + px;
+        unsigned seed = (unsigned)px * 0x9E3779B9u + 0x7F4A7C15u;
+        if (bhas_lo && r < eq) { // the wanted key is lo itself
+            klo = blo;
+            khi = blo;
+            if (even && !(r + 1 < eq)) {
+                unsigned mn = kFull;
+                if (m <= (unsigned)kMsCap) {
+                    for (int i = lane; i < (int)m; i += 32) mn = min(mn, list[i]);
+                } else {
+                    for (int k = lane; k < n; k += 32) {
+                        const unsigned key = ms_key(ms_ld(pcol + (size_t)k * a.n2));
+                        if (key > blo && key < bhi) mn = min(mn, key);
+                    }
+                }
+                mn = __reduce_min_sync(kFull, mn);
+                khi = mn != kFull ? mn : above;
+            }
+            done = true;
+        } else {
+            if (bhas_lo) r -= eq;
+            while (!done && m > (unsigned)kMsCap) {
+                done = ms_refine(pcol, a.n2, n, list, blo, bhi, bhas_lo, r, m, above, even, lane, seed, klo, khi);
+                seed = seed * 1664525u + 1013904223u;
+            }
+        }
+        if (!done) {
+            MedState st{(int)m, r, above, above != kFull};
+            while (!done && st.m > 32) {
+                done = med_round(list, st, even, lane, seed, klo, khi);
+                seed = seed * 1664525u + 1013904223u;
+            }
+            if (!done) med_rank32(list, st, even, lane, klo, khi);
+        }
+        if (lane == 0) a.out[px] = med_finish(klo, khi, even);
+    }
+    if (nan && n > 1) atomicMax(a.flag, 1u); // a single frame is never compared by the sort
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -699,7 +1106,7 @@ int median_pixels_per_cta(int64_t n2, int64_t n) {
             return best;
         }
     }
-    return fits_once; // 0: not even one spaxel fits -> global variant
+    return fits_once; // 0: not even one spaxel fits -> streaming kernel
 }
 
 cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s) {
@@ -714,9 +1121,21 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
         count_launch();
         return cudaGetLastError();
     }
+    // Long windows on images with enough 32-spaxel tiles to fill the GPU are streamed (two coalesced passes, pivots
+    // prune 15/16 of the keys); so is any window too long for shared memory.  Short windows and small images keep the
+    // shared-memory select (profiles/r1_median_phases.txt).
     const int P = n > (int64_t)(kMedianSmemMax / sizeof(unsigned)) ? 0 : median_pixels_per_cta(n2, n);
-    if (P == 0) {
-        median_global_kernel<<<(unsigned)n2, 32, 0, s>>>(k);
+    if (P == 0 || (n >= kMedStreamMinFrames && n2 >= kMedStreamMinPixels)) {
+        constexpr size_t smem_ms = (size_t)kMsPix * kMsRow * sizeof(unsigned);
+        static bool attr_ms[16] = {};
+        int dev_ms = 0;
+        cudaGetDevice(&dev_ms);
+        if (dev_ms >= 0 && dev_ms < 16 && !attr_ms[dev_ms]) {
+            cudaError_t e = cudaFuncSetAttribute(median_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+            if (e != cudaSuccess) return e;
+            attr_ms[dev_ms] = true;
+        }
+        median_stream_kernel<<<(unsigned)((n2 + kMsPix - 1) / kMsPix), kMsPix * kMsWarps, smem_ms, s>>>(k);
         count_launch();
         return cudaGetLastError();
     }

@@ -151,6 +151,70 @@ def test_median_long_range_and_nan(gpu, orc):
     assert_bit_equal(one, host[7], "median of one frame")
 
 
+def _median_patterns(rng, nz, ny, nx):
+    """Spectra that exercise every branch of the selects: (tag, cube)."""
+    shape = (nz, ny, nx)
+    out = []
+    # smooth noise: the median's bin holds a few dozen to a few hundred keys
+    out.append(("normal", (1.0 + 0.1 * rng.standard_normal(shape)).astype(np.float32)))
+    # heavy outliers stretch the span: equal-width digits put nearly every key into the median's bin
+    h = (1.0 + 1e-3 * rng.standard_normal(shape)).astype(np.float32)
+    h[::97] = 1e30
+    h[5::101] = -1e30
+    out.append(("outliers", h))
+    # more duplicates of the median value than any candidate list holds; the successor lives in a higher bin
+    h = np.full(shape, 3.0, np.float32)
+    k0, k1 = int(0.42 * nz), int(0.9 * nz)
+    h[:k0] = rng.uniform(0.0, 2.9, (k0, ny, nx)).astype(np.float32)
+    h[k1:] = rng.uniform(3.1, 9.0, (nz - k1, ny, nx)).astype(np.float32)
+    out.append(("duplicates", rng.permutation(h, axis=0)))
+    # exactly half below / half above a gap: n even -> the two middles come from different bins
+    h = np.concatenate([rng.uniform(1.0, 1.5, (nz // 2, ny, nx)), rng.uniform(100.0, 200.0, (nz - nz // 2, ny, nx))]).astype(np.float32)
+    out.append(("gap", rng.permutation(h, axis=0)))
+    # neighbouring floats only (span below one radix digit), many ties
+    steps = rng.integers(0, 100, shape).astype(np.uint32)
+    out.append(("tiny span", (np.full(shape, 1.0, np.float32).view(np.uint32) + steps).view(np.float32)))
+    # signed values, zeros of both signs, a sorted ramp along the window (stratified samples are exact quantiles)
+    h = rng.standard_normal(shape).astype(np.float32)
+    h[::9] = 0.0
+    h[4::9] = -0.0
+    out.append(("signed zeros", h))
+    out.append(("ramp", (np.arange(nz, dtype=np.float32)[:, None, None] * np.float32(0.25) + rng.uniform(0, 0.1, (1, ny, nx)).astype(np.float32))))
+    return out
+
+
+def test_median_select_paths(gpu, orc):
+    """Shared-memory select (short windows / small images): candidate bins, ties, successor in another bin, ragged tiles."""
+    rng = np.random.default_rng(0xAF1A0041)
+    for nz, ny, nx in [(301, 16, 16), (1200, 8, 8), (130, 3, 12), (90, 20, 52)]:
+        for tag, host in _median_patterns(rng, nz, ny, nx):
+            cube = gpu.Image.upload(host)
+            for start, end in [(0, nz), (0, nz - 1), (3, nz - 2)]:
+                assert_bit_equal(gpu.call("median", cube, start, end).download(), orc.median(host, start, end), f"{tag} {nz}x{ny}x{nx}[{start},{end})")
+
+
+def test_median_stream_paths(gpu, orc):
+    """Streaming select (windows >= 2048 frames on images of >= 9472 spaxels): the same patterns; 97 x 99 spaxels is not a
+    multiple of the 32-spaxel tile, `duplicates` / `tiny span` end on the equal-to-pivot branch, and the 6001-frame
+    window makes some 4-rank bins overflow the 768-slot list (refinement against the global column)."""
+    rng = np.random.default_rng(0xAF1A0042)
+    nz, ny, nx = 2100, 97, 99
+    for tag, host in _median_patterns(rng, nz, ny, nx):
+        cube = gpu.Image.upload(host)
+        for start, end in [(0, nz), (1, nz), (10, 2060)]:
+            assert_bit_equal(gpu.call("median", cube, start, end).download(), orc.median(host, start, end), f"stream {tag}[{start},{end})")
+    nz = 6001
+    host = (1.0 + 0.1 * rng.standard_normal((nz, ny, nx))).astype(np.float32)
+    host[::5] = -host[::5]
+    cube = gpu.Image.upload(host)
+    for start, end in [(0, nz), (1, nz)]:
+        assert_bit_equal(gpu.call("median", cube, start, end).download(), orc.median(host, start, end), f"stream long[{start},{end})")
+    # NaN anywhere in the window -> the reference panics
+    host[4000, 50, 60] = np.nan
+    e = gpu.get_transform("median").call_results(gpu.Image.upload(host), 0, nz)[0]
+    assert isinstance(e, gpu.AflakError) and e.status == gpu.ERR_PANIC
+
+
 @pytest.mark.parametrize("shape", SHAPES)
 @pytest.mark.parametrize("is_min", [False, True])
 @pytest.mark.parametrize("pathology", [False, True])
