@@ -217,6 +217,17 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
         cudaError_t ce = colormap_launch(a, sm_count(dev), s);
         if (ce != cudaSuccess) { err = cuda_error(ce, "colormap_kernel launch"); break; }
         image_note_read(img, s);
+        if (chain) {
+            // apply_tone_curve indexes its table unchecked (lib.rs:1866): an input above the table panics in the reference.
+            // Same contract as the stand-alone operator: one 4-byte read-back.
+            unsigned hflag = 0;
+            ce = cudaMemcpyAsync(&hflag, flag, sizeof hflag, cudaMemcpyDeviceToHost, s);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+            if (ce != cudaSuccess) { err = cuda_error(ce, "colormap chain flag"); break; }
+            if (hflag)
+                err = make_error(AFK_ERR_PANIC, fmt("index out of bounds: the len is %zu but the index is larger (input above 65535*(1+1/%zu))",
+                                                    (size_t)chain->tone_len, (size_t)chain->tone_len - 1));
+        }
     } while (0);
     if (lut3) cudaFreeAsync(lut3, s);
     if (dtone) cudaFreeAsync(dtone, s);

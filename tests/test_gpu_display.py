@@ -133,6 +133,26 @@ def test_fused_chain_matches_unfused_operators(gpu, orc):
     assert diff.max() <= 2 and (diff.max(axis=2) > 0).mean() < 1e-3, (diff.max(), (diff.max(axis=2) > 0).mean())
 
 
+def test_fused_chain_tone_index_out_of_bounds(gpu, orc):
+    """apply_tone_curve indexes its table unchecked (lib.rs:1866): an input above 65535*(1+1/(len-1)) panics in the
+    reference; the fused chain reports the same error as the stand-alone operator instead of clamping silently."""
+    img = lognormal((64, 64), 26)
+    d = gpu.Image.upload(img)
+    vmin, vmax = gpu.call("image_min_max", d)
+    tone = orc.tone_curve_default()
+    lut = gpu.Lut("Flame")
+    # normalise so that the brightest pixel lands at twice the table range
+    lmax = np.float32(np.log(np.float32(1001.0)) / np.log(np.float32(1000.0)))
+    chain = {"logscale_a": 1000.0, "logscale_vmin": float(vmin), "logscale_vmax": float(vmax), "normalize_min": 0.0,
+             "normalize_max": float(lmax / np.float32(2 * 65535.0)), "tone_table": tone}
+    with pytest.raises(gpu.AflakError) as ei:
+        gpu.colormap(d, lut, vmin=0.0, vmax=65535.0, channels=4, chain=chain)
+    assert ei.value.status == gpu.ERR_PANIC and "index out of bounds" in str(ei.value)
+    nm = gpu.call("normalize_image", gpu.call("convert_to_logscale", d, 1000.0, float(vmin), float(vmax)), 0.0, float(lmax / np.float32(2 * 65535.0)))
+    e = gpu.get_transform("apply_tone_curve").call_results(nm, gpu.ToneCurve(tone))[0]
+    assert isinstance(e, gpu.AflakError) and e.status == gpu.ERR_PANIC
+
+
 def test_colormap_device_buffer(gpu, orc):
     """The headless stand-in for the GL texture: bytes written to a caller-provided device buffer."""
     img = lognormal((40, 64), 25)
