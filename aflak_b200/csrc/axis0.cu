@@ -754,6 +754,11 @@ __device__ __forceinline__ unsigned ms_ld(const float *p) {
 }
 __device__ __forceinline__ unsigned ms_key(unsigned b) { return b ^ ((unsigned)((int)b >> 31) | 0x80000000u); } // == med_key, 2 instructions
 
+// c += (key < pivot) as compare + predicated add: two instructions (the C form compiles to three)
+__device__ __forceinline__ void ms_count(unsigned &c, unsigned key, unsigned pivot) {
+    asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(c) : "r"(key), "r"(pivot));
+}
+
 struct MsBin { // keys strictly inside (lo, hi) are candidates; sentinels 0 / 0xFFFFFFFF only collide with NaN keys
     unsigned lo, hi, below;
     bool has_lo;
@@ -854,19 +859,22 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
             unsigned h = ((unsigned)blockIdx.x * 0x9E3779B9u + (unsigned)i * 0x85EBCA6Bu) * 0xC2B2AE35u;
             h ^= h >> 16;
             const int f = (int)(((long long)i * n) >> 6) + (int)(h % (unsigned)stride);
-            s_smp[lane * 65 + i] = ms_key(ms_ld(col + (size_t)f * a.n2));
+            s_smp[lane * 65 + i] = (ms_key(ms_ld(col + (size_t)f * a.n2)) & ~63u) | (unsigned)i;
         }
         __syncthreads();
-        // a warp ranks the 64 samples of a spaxel by counting (ties broken by position); the samples of ranks
-        // 20, 24, .., 44 are the pivots: 4-rank bins (6 % of the keys each), +-3 sigma of the sample median's rank
+        // a warp ranks the 64 samples of a spaxel by counting.  The low 6 bits of each sample were replaced by its index
+        // when it was stored, so the 64 values are distinct and one compare ranks them; a pivot does not have to be a key
+        // of the spectrum.  Ranks 20, 24, .., 44 are the pivots: 4-rank bins (6 % of the keys each), +-3 sigma of the sample
+        // median's rank.
         for (int p = g; p < kMsPix; p += kMsWarps) {
             const unsigned *sp = s_smp + p * 65;
             const unsigned v0 = sp[lane], v1 = sp[lane + 32];
             unsigned r0s = 0u, r1s = 0u;
+#pragma unroll 8
             for (int i = 0; i < 64; ++i) {
                 const unsigned o = sp[i];
-                r0s += (o < v0) || (o == v0 && i < lane);
-                r1s += (o < v1) || (o == v1 && i < lane + 32);
+                ms_count(r0s, o, v0);
+                ms_count(r1s, o, v1);
             }
             if (r0s >= 20u && r0s <= 44u && (r0s & 3u) == 0u) s_piv[p][(r0s - 20u) >> 2] = v0;
             if (r1s >= 20u && r1s <= 44u && (r1s & 3u) == 0u) s_piv[p][(r1s - 20u) >> 2] = v1;
@@ -876,22 +884,26 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
 #pragma unroll
         for (int j = 0; j < kMedPivots; ++j) { pv[j] = s_piv[lane][j]; c[j] = 0u; }
         // ---- B: count (full blocks of kMsU frames unchecked, then the tail) ----
-        int k = g;
-        for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
-            unsigned raw[kMsU];
+        const size_t wstep = (size_t)kMsWarps * a.n2; // elements between two frames of this warp
+        {
+            const float *p = col + (size_t)g * a.n2;
+            int k = g;
+            for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
+                unsigned raw[kMsU];
 #pragma unroll
-            for (int u = 0; u < kMsU; ++u) raw[u] = ms_ld(col + (size_t)(k + u * kMsWarps) * a.n2);
+                for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p += wstep; }
 #pragma unroll
-            for (int u = 0; u < kMsU; ++u) {
-                const unsigned key = ms_key(raw[u]);
+                for (int u = 0; u < kMsU; ++u) {
+                    const unsigned key = ms_key(raw[u]);
 #pragma unroll
-                for (int j = 0; j < kMedPivots; ++j) c[j] += key < pv[j];
+                    for (int j = 0; j < kMedPivots; ++j) ms_count(c[j], key, pv[j]);
+                }
             }
-        }
-        for (; k < n; k += kMsWarps) {
-            const unsigned key = ms_key(ms_ld(col + (size_t)k * a.n2));
+            for (; k < n; k += kMsWarps, p += wstep) {
+                const unsigned key = ms_key(ms_ld(p));
 #pragma unroll
-            for (int j = 0; j < kMedPivots; ++j) c[j] += key < pv[j];
+                for (int j = 0; j < kMedPivots; ++j) ms_count(c[j], key, pv[j]);
+            }
         }
         unsigned *s_c = s_list; // [kMsWarps][kMsPix][8] (the samples are no longer needed: every warp passed the barrier above)
         __syncthreads();
@@ -914,31 +926,30 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
         __syncthreads();
     }
     // ---- C: collect the bin ----
-    const bool has_lo = s_haslo[lane] != 0u;
     unsigned n_eq = 0u, hi_min = kFull;
-    const unsigned eq_inc = has_lo ? 1u : 0u;
     unsigned *row = s_list + lane * kMsRow;
     auto collect = [&](unsigned rawbits) {
-        const float f = __uint_as_float(rawbits);
-        nan |= (f != f);
         const unsigned key = ms_key(rawbits);
-        n_eq += (key == lo) ? eq_inc : 0u;
-        hi_min = min(hi_min, key >= hi ? key : kFull);
+        nan |= (key - 0x00800000u) > 0xFF000000u; // outside [key(-Inf), key(+Inf)]
+        if (key == lo) ++n_eq;                     // without a lower pivot lo is 0, the key of a NaN: never counted for clean data
+        if (key >= hi) hi_min = min(hi_min, key);
         if (key > lo && key < hi) {
             const unsigned at = atomicAdd(&s_cnt[lane], 1u);
             if (at < (unsigned)kMsCap) row[at] = key;
         }
     };
     if (active) {
+        const size_t wstep = (size_t)kMsWarps * a.n2;
+        const float *p = col + (size_t)g * a.n2;
         int k = g;
         for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
             unsigned raw[kMsU];
 #pragma unroll
-            for (int u = 0; u < kMsU; ++u) raw[u] = ms_ld(col + (size_t)(k + u * kMsWarps) * a.n2);
+            for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p += wstep; }
 #pragma unroll
             for (int u = 0; u < kMsU; ++u) collect(raw[u]);
         }
-        for (; k < n; k += kMsWarps) collect(ms_ld(col + (size_t)k * a.n2));
+        for (; k < n; k += kMsWarps, p += wstep) collect(ms_ld(p));
     }
     s_eq[g][lane] = n_eq;
     s_himin[g][lane] = hi_min;

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <unordered_map>
 
 #include "host.h"
 
@@ -115,15 +116,23 @@ Error current_stream(cudaStream_t *out, int *device) {
     return ok();
 }
 
+// Event pool.  A CUDA event belongs to the device that was current when it was created and can only be recorded on
+// that device's streams, so the free lists are per device (one process may drive several GPUs through afk_set_device).
 static std::mutex g_ev_mu;
-static std::vector<cudaEvent_t> g_ev_pool;
+static std::vector<cudaEvent_t> g_ev_pool[16];
+static std::unordered_map<cudaEvent_t, int> g_ev_device;
 
 cudaEvent_t event_get() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) {
+        cudaGetLastError();
+        return nullptr;
+    }
     {
         std::lock_guard<std::mutex> lk(g_ev_mu);
-        if (!g_ev_pool.empty()) {
-            cudaEvent_t e = g_ev_pool.back();
-            g_ev_pool.pop_back();
+        if (!g_ev_pool[dev].empty()) {
+            cudaEvent_t e = g_ev_pool[dev].back();
+            g_ev_pool[dev].pop_back();
             return e;
         }
     }
@@ -132,13 +141,17 @@ cudaEvent_t event_get() {
         cudaGetLastError();
         return nullptr;
     }
+    std::lock_guard<std::mutex> lk(g_ev_mu);
+    g_ev_device[e] = dev;
     return e;
 }
 
 void event_put(cudaEvent_t e) {
     if (!e) return;
     std::lock_guard<std::mutex> lk(g_ev_mu);
-    g_ev_pool.push_back(e);
+    auto it = g_ev_device.find(e);
+    if (it == g_ev_device.end()) return; // not one of ours
+    g_ev_pool[it->second].push_back(e);
 }
 
 // ---- scratch ---------------------------------------------------------------------------------------------
