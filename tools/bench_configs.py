@@ -206,4 +206,71 @@ for name, nb, fn in [
     ("down_sampling n=2 4096^2", 2, lambda: afk.call("down_sampling", img, 2)),
 ]:
     out.append(entry(name, npx * nb, fn))
-print(json.dumps({"measured_hbm_peak_GBps": PEAK, "entries": out}, indent=1))
+
+# ---------------- the reference's CPU path (oracle port) on this box's host cores, for C1 / C2 / C4 ----------------
+# Threaded the way the reference threads it: reductions are one serial frame-accumulate each (ndarray sum_axis), the
+# sibling nodes of a DAG level run concurrently (rayon::scope), par_iter_mut operators use every core, the LUT mapping
+# runs on the UI thread.  bench.py carries the same comparison for the headline C3 line.
+import threading
+
+import oracle
+
+NCPU = oracle.max_threads()
+
+
+def cpu_best(fn, reps=3):
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        fn()
+        best = min(best, time.perf_counter() - t0)
+    return best * 1e3
+
+
+def concurrently(*fns):
+    res = [None] * len(fns)
+
+    def run(i):
+        res[i] = fns[i]()
+
+    ts = [threading.Thread(target=run, args=(i,)) for i in range(len(fns))]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    return res
+
+
+cpu = []
+hm = oracle.gen_cube(0xAF1A0001, 4563, 74, 74, threads=NCPU)
+cpu.append({"config": "C1 MaNGA integral[0,4563)", "cores": 1, "ms": cpu_best(lambda: oracle.integral(hm, 0, 4563))})
+
+
+def c2_cpu():
+    on, o1, o2 = concurrently(lambda: oracle.average(hm, 3134, 3154), lambda: oracle.average(hm, 3099, 3119), lambda: oracle.average(hm, 3174, 3194))
+    r2, r1 = oracle.ratio_from_bands(3144.0, 3109.0, 3184.0)
+    ew = oracle.equivalent_width(oracle.linear_composition(o1, o2, r2, r1), on, 20.0, 1e10, True)
+    mn, mx = oracle.image_min_max(ew)
+    return oracle.convert_to_logscale(ew, 1000.0, mn, mx)  # 5476 pixels: one core (an OpenMP team costs more than the work)
+
+
+cpu.append({"config": "C2 MaNGA EW template -> min/max -> logscale", "cores": 3, "ms": cpu_best(c2_cpu)})
+rng = np.random.default_rng(4)
+himg = np.exp(rng.standard_normal((N, N))).astype(np.float32)
+table = oracle.lut_build("Flame", lims=(0.2, 0.3, 0.9))
+tone_h = np.arange(256, dtype=np.float32)
+
+
+def c4_cpu():
+    mn, mx = oracle.image_min_max(himg)
+    ls = oracle.convert_to_logscale(himg, 1000.0, mn, mx, threads=NCPU)
+    nm = ((ls - np.float32(0.0)) / np.float32(lmax / 65535.0)).astype(np.float32)
+    tc = oracle.apply_tone_curve(nm, tone_h)
+    return oracle.make_raw_image(tc, 0.0, 65535.0, table, lims=(0.2, 0.3, 0.9), channels=4)
+
+
+cpu.append({"config": "C4 4096^2 chain: min/max, logscale (all cores), normalize, tone curve, colour LUT (serial, UI thread) -> RGBA8",
+            "cores": NCPU, "ms": cpu_best(c4_cpu, reps=2)})
+for e in cpu:
+    print(json.dumps(e), file=sys.stderr, flush=True)
+print(json.dumps({"measured_hbm_peak_GBps": PEAK, "entries": out, "cpu_reference_path": {"kind": "port (oracle/)", "host_threads": NCPU, "entries": cpu}}, indent=1))
