@@ -248,6 +248,31 @@ def build_c3_graph(afk, nz):
     return g, cube, avg, ratio
 
 
+def bind_to_gpu_numa(torch, local):
+    """Pin this rank's host threads (and therefore its first-touch / pinned allocations) to the NUMA node the GPU hangs
+    off: with one rank per GPU the H2D copies of all ranks otherwise cross the socket interconnect.  Best effort."""
+    try:
+        p = torch.cuda.get_device_properties(local)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "cpus": len(cpus)}
+    except Exception:
+        return None
+
+
 def run_gpu(args):
     import torch
 
@@ -262,6 +287,7 @@ def run_gpu(args):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     afk.set_device(local)
+    numa = bind_to_gpu_numa(torch, local) if world > 1 else None  # N=1 keeps every host core for the cpu_baseline leg
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -366,6 +392,8 @@ def run_gpu(args):
                          "frac_of_nominal_8TBs": achieved / 8000.0},
             "e2e": e2e, "gpu_launches": int(launches * world), "clocks": clocks,
         }
+        if numa:
+            line["config"]["host_affinity"] = f"rank 0 bound to NUMA node {numa['numa_node']} ({numa['cpus']} cpus), every rank to its GPU's node"
         if world == 1 and not args.no_cpu:
             line["cpu_baseline"] = cpu_baseline()
         emit(line)
