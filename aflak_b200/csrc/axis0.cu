@@ -740,10 +740,11 @@ __device__ __forceinline__ void med_rank32(const unsigned *keys, const MedState 
 // sampled from the bin itself, until it fits: exactness never depends on the data.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kMsPix = 32;            // spaxels per CTA (= lanes)
-constexpr int kMsWarps = 16;          // 2 CTAs x 512 threads x 16 loads in flight = 64 KB per SM
+constexpr int kMsWarps = 16;          // 2 CTAs x 512 threads x 16 loads in flight = 64 KB per SM (one 1024-thread CTA per SM, whose tile would stay in L2, measured slower: 12.8 vs 11.5 ms)
 constexpr int kMsCap = 768;           // candidate slots per spaxel (20 % of an ALMA window: a 4-rank bin of 64 samples overflows 4e-4 of the time)
 constexpr int kMsRow = kMsCap + 1;    // odd row stride: neighbouring spaxels start in different banks
 constexpr int kMsU = 16;              // frames in flight per thread
+constexpr int64_t kMedStreamWideBins = 4200;         // up to here a 4-rank bin (6 % of the window) fits the list three times over
 constexpr int64_t kMedStreamMinFrames = 2048;        // shorter windows: the shared-memory select is faster
 constexpr int64_t kMedStreamMinPixels = 2 * 148 * 32; // fewer spaxels: not enough 32-spaxel CTAs for two per SM
 
@@ -765,13 +766,13 @@ struct MsBin { // keys strictly inside (lo, hi) are candidates; sentinels 0 / 0x
 };
 
 // bin of rank r from cumulative counts c_j = #(key < pv_j) (pv ascending)
-__device__ __forceinline__ MsBin ms_pick_bin(const unsigned (&c)[kMedPivots], const unsigned (&pv)[kMedPivots], unsigned r) {
+template <int NP> __device__ __forceinline__ MsBin ms_pick_bin(const unsigned (&c)[NP], const unsigned (&pv)[NP], unsigned r) {
     MsBin b{0u, kFull, 0u, false};
 #pragma unroll
-    for (int j = 0; j < kMedPivots; ++j)
+    for (int j = 0; j < NP; ++j)
         if (c[j] <= r) { b.lo = pv[j]; b.below = c[j]; b.has_lo = true; }
 #pragma unroll
-    for (int j = kMedPivots - 1; j >= 0; --j)
+    for (int j = NP - 1; j >= 0; --j)
         if (c[j] > r) b.hi = pv[j];
     return b;
 }
@@ -796,7 +797,7 @@ __device__ bool ms_refine(const float *col, int64_t n2, int n, unsigned *list, u
     }
 #pragma unroll
     for (int j = 0; j < kMedPivots; ++j) c[j] = __reduce_add_sync(kFull, c[j]);
-    const MsBin b = ms_pick_bin(c, pv, r);
+    const MsBin b = ms_pick_bin<kMedPivots>(c, pv, r);
     const unsigned nlo = b.has_lo ? b.lo : lo, nhi = b.hi < hi ? b.hi : hi;
     unsigned n_eq = 0u, hi_min = kFull, out = 0u;
     __syncwarp();
@@ -835,9 +836,12 @@ __device__ bool ms_refine(const float *col, int64_t n2, int n, unsigned *list, u
     return false;
 }
 
+// NP pivots, G sample ranks apart, centred on the sample median: <7, 4> for windows up to ~4200 frames (6 % bins), <15, 2>
+// beyond (3 % bins: a bin must fit the 768-slot list with margin; the pivots must still span +-3 sigma of the median's rank)
+template <int NP, int G>
 __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(const MedianK a) {
     extern __shared__ unsigned s_list[]; // [kMsPix][kMsRow] candidate lists; phases A/B alias samples and per-warp counts onto it
-    __shared__ unsigned s_piv[kMsPix][kMedPivots + 1];
+    __shared__ unsigned s_piv[kMsPix][NP + 1];
     __shared__ unsigned s_lo[kMsPix], s_hi[kMsPix], s_below[kMsPix], s_haslo[kMsPix], s_cnt[kMsPix];
     __shared__ unsigned s_eq[kMsWarps][kMsPix], s_himin[kMsWarps][kMsPix];
     const int n = (int)a.n;
@@ -864,8 +868,7 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
         __syncthreads();
         // a warp ranks the 64 samples of a spaxel by counting.  The low 6 bits of each sample were replaced by its index
         // when it was stored, so the 64 values are distinct and one compare ranks them; a pivot does not have to be a key
-        // of the spectrum.  Ranks 20, 24, .., 44 are the pivots: 4-rank bins (6 % of the keys each), +-3 sigma of the sample
-        // median's rank.
+        // of the spectrum.  The pivots are the samples of ranks 32 + (j - (NP-1)/2) G.
         for (int p = g; p < kMsPix; p += kMsWarps) {
             const unsigned *sp = s_smp + p * 65;
             const unsigned v0 = sp[lane], v1 = sp[lane + 32];
@@ -876,13 +879,14 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
                 ms_count(r0s, o, v0);
                 ms_count(r1s, o, v1);
             }
-            if (r0s >= 20u && r0s <= 44u && (r0s & 3u) == 0u) s_piv[p][(r0s - 20u) >> 2] = v0;
-            if (r1s >= 20u && r1s <= 44u && (r1s & 3u) == 0u) s_piv[p][(r1s - 20u) >> 2] = v1;
+            constexpr unsigned kFirst = 32u - (unsigned)((NP - 1) / 2 * G), kLast = kFirst + (unsigned)((NP - 1) * G);
+            if (r0s >= kFirst && r0s <= kLast && (r0s - kFirst) % G == 0u) s_piv[p][(r0s - kFirst) / G] = v0;
+            if (r1s >= kFirst && r1s <= kLast && (r1s - kFirst) % G == 0u) s_piv[p][(r1s - kFirst) / G] = v1;
         }
         __syncthreads();
-        unsigned pv[kMedPivots], c[kMedPivots];
+        unsigned pv[NP], c[NP];
 #pragma unroll
-        for (int j = 0; j < kMedPivots; ++j) { pv[j] = s_piv[lane][j]; c[j] = 0u; }
+        for (int j = 0; j < NP; ++j) { pv[j] = s_piv[lane][j]; c[j] = 0u; }
         // ---- B: count (full blocks of kMsU frames unchecked, then the tail) ----
         const size_t wstep = (size_t)kMsWarps * a.n2; // elements between two frames of this warp
         {
@@ -896,28 +900,28 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
                 for (int u = 0; u < kMsU; ++u) {
                     const unsigned key = ms_key(raw[u]);
 #pragma unroll
-                    for (int j = 0; j < kMedPivots; ++j) ms_count(c[j], key, pv[j]);
+                    for (int j = 0; j < NP; ++j) ms_count(c[j], key, pv[j]);
                 }
             }
             for (; k < n; k += kMsWarps, p += wstep) {
                 const unsigned key = ms_key(ms_ld(p));
 #pragma unroll
-                for (int j = 0; j < kMedPivots; ++j) ms_count(c[j], key, pv[j]);
+                for (int j = 0; j < NP; ++j) ms_count(c[j], key, pv[j]);
             }
         }
-        unsigned *s_c = s_list; // [kMsWarps][kMsPix][8] (the samples are no longer needed: every warp passed the barrier above)
+        unsigned *s_c = s_list; // [kMsWarps][kMsPix][NP + 1] (the samples are no longer needed: every warp passed the barrier above)
         __syncthreads();
 #pragma unroll
-        for (int j = 0; j < kMedPivots; ++j) s_c[(g * kMsPix + lane) * 8 + j] = c[j];
+        for (int j = 0; j < NP; ++j) s_c[(g * kMsPix + lane) * (NP + 1) + j] = c[j];
         __syncthreads();
         if (g == 0) {
 #pragma unroll
-            for (int j = 0; j < kMedPivots; ++j) {
+            for (int j = 0; j < NP; ++j) {
                 unsigned t = 0u;
-                for (int w = 0; w < kMsWarps; ++w) t += s_c[(w * kMsPix + lane) * 8 + j];
+                for (int w = 0; w < kMsWarps; ++w) t += s_c[(w * kMsPix + lane) * (NP + 1) + j];
                 c[j] = t;
             }
-            const MsBin b = ms_pick_bin(c, pv, r0);
+            const MsBin b = ms_pick_bin<NP>(c, pv, r0);
             s_lo[lane] = b.lo; s_hi[lane] = b.hi; s_below[lane] = b.below; s_haslo[lane] = b.has_lo ? 1u : 0u;
         }
         __syncthreads();
@@ -1142,11 +1146,14 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
         int dev_ms = 0;
         cudaGetDevice(&dev_ms);
         if (dev_ms >= 0 && dev_ms < 16 && !attr_ms[dev_ms]) {
-            cudaError_t e = cudaFuncSetAttribute(median_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+            cudaError_t e = cudaFuncSetAttribute(median_stream_kernel<7, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream_kernel<15, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e != cudaSuccess) return e;
             attr_ms[dev_ms] = true;
         }
-        median_stream_kernel<<<(unsigned)((n2 + kMsPix - 1) / kMsPix), kMsPix * kMsWarps, smem_ms, s>>>(k);
+        const unsigned grid_ms = (unsigned)((n2 + kMsPix - 1) / kMsPix);
+        if (n <= kMedStreamWideBins) median_stream_kernel<7, 4><<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
+        else median_stream_kernel<15, 2><<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
         count_launch();
         return cudaGetLastError();
     }
