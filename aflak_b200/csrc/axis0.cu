@@ -279,8 +279,8 @@ template <bool COMP> __global__ void __launch_bounds__(256) centroid_mask_kernel
 //
 // All variants read the sub-cube from HBM exactly once, staged into shared memory with cp.async (thousands of copies in
 // flight per CTA, no registers held):
-//   n <= 64  median_rank_kernel: a CTA stages [n][128 spaxels] (frame-major, 16-byte copies), then every thread ranks its
-//            own spaxel's column by counting (n^2 shared loads, conflict-free).
+//   n <= 64  median_sort_kernel: lane = spaxel, the column is loaded into registers (coalesced) and sorted by an unrolled
+//            bitonic network.
 //   larger   median_select_kernel: a CTA stages P spaxels transposed to [P][npad] (npad = n padded so that both the
 //            staging stores and the per-spectrum loads are bank-conflict free); one warp per spaxel runs a radix select
 //            over key - min(key): the digits cover only the range the spectrum really spans (typically 3 passes of 8
@@ -310,60 +310,54 @@ __device__ __forceinline__ float med_finish(unsigned klo, unsigned khi, bool eve
     return even ? __fdiv_rn(__fadd_rn(med_unkey(khi), med_unkey(klo)), 2.0f) : med_unkey(klo);
 }
 
-constexpr int kMedRankPixels = 128; // spaxels (= threads) per CTA of the rank kernel
+constexpr int kMedSortPixels = 128; // spaxels (= threads) per CTA of the sorting-network kernel
 constexpr int kMedRankMaxN = 64;
 
-__global__ void __launch_bounds__(kMedRankPixels) median_rank_kernel(const MedianK a) {
-    extern __shared__ __align__(16) unsigned s_keys[]; // [n][128]
-    const int tid = threadIdx.x;
-    const int64_t px0 = (int64_t)blockIdx.x * kMedRankPixels;
-    const int n = (int)a.n;
-    const bool vec = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0);
-    if (vec) {
-        for (int i = tid; i < n * (kMedRankPixels / 4); i += kMedRankPixels) {
-            const int k = i / (kMedRankPixels / 4), j = i % (kMedRankPixels / 4);
-            const int64_t px = px0 + 4 * j;
-            if (px < a.n2) {
-                const unsigned dst = (unsigned)__cvta_generic_to_shared(s_keys + k * kMedRankPixels + 4 * j);
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(a.cube + (a.start + k) * a.n2 + px) : "memory");
-            }
-        }
-    } else {
-        for (int i = tid; i < n * kMedRankPixels; i += kMedRankPixels) {
-            const int k = i / kMedRankPixels, j = i % kMedRankPixels;
-            if (px0 + j < a.n2) {
-                const unsigned dst = (unsigned)__cvta_generic_to_shared(s_keys + i);
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(a.cube + (a.start + k) * a.n2 + px0 + j) : "memory");
-            }
-        }
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
-    const int64_t px = px0 + tid;
+// Windows of at most 64 frames (the template-sized case): lane = spaxel, the whole column lives in registers -- coalesced
+// scalar loads straight from global memory (a warp reads 128 contiguous bytes of a frame, every frame of the window in
+// flight at once), padded with the largest key to the next power of two N, sorted by a fully unrolled bitonic network
+// (N/2 log2 N (log2 N + 1) / 2 compare-exchanges of two instructions each: 672 for N = 64, against 64^2 x 5 for ranking
+// by counting out of shared memory, the first version: 0.51 -> see profiles/r1_axis0_ops.json).
+template <int N>
+__global__ void __launch_bounds__(kMedSortPixels) median_sort_kernel(const MedianK a) {
+    const int64_t px = (int64_t)blockIdx.x * kMedSortPixels + threadIdx.x;
     if (px >= a.n2) return;
-    unsigned *col = s_keys + tid;
+    const int n = (int)a.n;
+    const float *col = a.cube + a.start * a.n2 + px;
+    unsigned key[N];
+#pragma unroll
+    for (int k = 0; k < N; ++k) key[k] = k < n ? __float_as_uint(__ldg(col + (size_t)k * a.n2)) : 0x7FFFFFFFu; // pads map to 0xFFFFFFFF
     bool nan = false;
-    for (int k = 0; k < n; ++k) {
-        const float f = __uint_as_float(col[k * kMedRankPixels]);
-        nan |= (f != f);
-        col[k * kMedRankPixels] = med_key(f);
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        const float f = __uint_as_float(key[k]);
+        nan |= (k < n) && (f != f);
+        key[k] = med_key(f);
     }
     if (nan && n > 1) atomicMax(a.flag, 1u);
-    // the element of rank r is the key with  #(keys < it) <= r < #(keys <= it)
-    const int r_lo = (n - 1) / 2, r_hi = n / 2; // equal when n is odd
-    unsigned klo = 0u, khi = 0u;
-    for (int i = 0; i < n; ++i) {
-        const unsigned ki = col[i * kMedRankPixels];
-        int lt = 0, le = 0;
-#pragma unroll 8
-        for (int j = 0; j < n; ++j) {
-            const unsigned kj = col[j * kMedRankPixels];
-            lt += kj < ki;
-            le += kj <= ki;
+#pragma unroll
+    for (int size = 2; size <= N; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                const int j = i ^ stride;
+                if (j > i) {
+                    const bool up = (i & size) == 0;
+                    const unsigned lo = min(key[i], key[j]), hi = max(key[i], key[j]);
+                    key[i] = up ? lo : hi;
+                    key[j] = up ? hi : lo;
+                }
+            }
         }
-        if (lt <= r_lo && r_lo < le) klo = ki;
-        if (lt <= r_hi && r_hi < le) khi = ki;
+    }
+    // the two middles: compile-time register indices, selected by comparison (a dynamic index would spill the array)
+    const int r_lo = (n - 1) / 2, r_hi = n / 2;
+    unsigned klo = 0u, khi = 0u;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+        if (k == r_lo) klo = key[k];
+        if (k == r_hi) khi = key[k];
     }
     a.out[px] = med_finish(klo, khi, (n & 1) == 0);
 }
@@ -1130,9 +1124,11 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
     if (n < 1 || n > 0x7FFFFFFF || flag == nullptr) return cudaErrorInvalidValue;
     MedianK k{cube, n2, start, n, 0, 0, out, flag};
     if (n <= kMedRankMaxN) {
-        k.P = kMedRankPixels;
-        const size_t smem = (size_t)n * kMedRankPixels * sizeof(unsigned);
-        median_rank_kernel<<<(unsigned)((n2 + kMedRankPixels - 1) / kMedRankPixels), kMedRankPixels, smem, s>>>(k);
+        const unsigned grid = (unsigned)((n2 + kMedSortPixels - 1) / kMedSortPixels);
+        if (n <= 8) median_sort_kernel<8><<<grid, kMedSortPixels, 0, s>>>(k);
+        else if (n <= 16) median_sort_kernel<16><<<grid, kMedSortPixels, 0, s>>>(k);
+        else if (n <= 32) median_sort_kernel<32><<<grid, kMedSortPixels, 0, s>>>(k);
+        else median_sort_kernel<64><<<grid, kMedSortPixels, 0, s>>>(k);
         count_launch();
         return cudaGetLastError();
     }
