@@ -739,7 +739,7 @@ constexpr int kMsCap = 768;           // candidate slots per spaxel (20 % of an 
 constexpr int kMsRow = kMsCap + 1;    // odd row stride: neighbouring spaxels start in different banks
 constexpr int kMsU = 16;              // frames in flight per thread
 constexpr int64_t kMedStreamWideBins = 4200;         // up to here a 4-rank bin (6 % of the window) fits the list three times over
-constexpr int64_t kMedStreamMinFrames = 2048;        // shorter windows: the shared-memory select is faster
+constexpr int64_t kMedStreamMinFrames = 65;          // every window beyond the sorting network, on images large enough (measured 100..3000 frames: profiles/r1_median_phases.txt)
 constexpr int64_t kMedStreamMinPixels = 2 * 148 * 32; // fewer spaxels: not enough 32-spaxel CTAs for two per SM
 
 __device__ __forceinline__ unsigned ms_ld(const float *p) {
@@ -936,7 +936,29 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
             if (at < (unsigned)kMsCap) row[at] = key;
         }
     };
-    if (active) {
+    if (active && n <= kMsCap) {
+        // the whole window fits the list: frame k goes to slot k, nothing to prune, no atomics
+        const size_t wstep = (size_t)kMsWarps * a.n2;
+        const float *p = col + (size_t)g * a.n2;
+        int k = g;
+        for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
+            unsigned raw[kMsU];
+#pragma unroll
+            for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p += wstep; }
+#pragma unroll
+            for (int u = 0; u < kMsU; ++u) {
+                const unsigned key = ms_key(raw[u]);
+                nan |= (key - 0x00800000u) > 0xFF000000u;
+                row[k + u * kMsWarps] = key;
+            }
+        }
+        for (; k < n; k += kMsWarps, p += wstep) {
+            const unsigned key = ms_key(ms_ld(p));
+            nan |= (key - 0x00800000u) > 0xFF000000u;
+            row[k] = key;
+        }
+        if (g == 0) s_cnt[lane] = (unsigned)n;
+    } else if (active) {
         const size_t wstep = (size_t)kMsWarps * a.n2;
         const float *p = col + (size_t)g * a.n2;
         int k = g;
@@ -1136,7 +1158,8 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
     // prune 15/16 of the keys); so is any window too long for shared memory.  Short windows and small images keep the
     // shared-memory select (profiles/r1_median_phases.txt).
     const int P = n > (int64_t)(kMedianSmemMax / sizeof(unsigned)) ? 0 : median_pixels_per_cta(n2, n);
-    if (P == 0 || (n >= kMedStreamMinFrames && n2 >= kMedStreamMinPixels)) {
+    static const int64_t stream_min = getenv("AFK_MEDIAN_STREAM_MIN") ? atoll(getenv("AFK_MEDIAN_STREAM_MIN")) : kMedStreamMinFrames; // tuning knob
+    if (P == 0 || (n >= stream_min && n2 >= kMedStreamMinPixels)) {
         constexpr size_t smem_ms = (size_t)kMsPix * kMsRow * sizeof(unsigned);
         static bool attr_ms[16] = {};
         int dev_ms = 0;
