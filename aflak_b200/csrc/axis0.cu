@@ -279,7 +279,7 @@ template <bool COMP> __global__ void __launch_bounds__(256) centroid_mask_kernel
 //
 // All variants read the sub-cube from HBM exactly once, staged into shared memory with cp.async (thousands of copies in
 // flight per CTA, no registers held):
-//   n <= 64  median_sort_kernel: lane = spaxel, the column is loaded into registers (coalesced) and sorted by an unrolled
+//   n <= 128 median_sort_kernel: lane = spaxel, the column is loaded into registers (coalesced) and sorted by an unrolled
 //            bitonic network.
 //   larger   median_select_kernel: a CTA stages P spaxels transposed to [P][npad] (npad = n padded so that both the
 //            staging stores and the per-spectrum loads are bank-conflict free); one warp per spaxel runs a radix select
@@ -311,9 +311,9 @@ __device__ __forceinline__ float med_finish(unsigned klo, unsigned khi, bool eve
 }
 
 constexpr int kMedSortPixels = 128; // spaxels (= threads) per CTA of the sorting-network kernel
-constexpr int kMedRankMaxN = 64;
+constexpr int kMedRankMaxN = 128;
 
-// Windows of at most 64 frames (the template-sized case): lane = spaxel, the whole column lives in registers -- coalesced
+// Windows of at most 128 frames (the template-sized case): lane = spaxel, the whole column lives in registers -- coalesced
 // scalar loads straight from global memory (a warp reads 128 contiguous bytes of a frame, every frame of the window in
 // flight at once), padded with the largest key to the next power of two N, sorted by a fully unrolled bitonic network
 // (N/2 log2 N (log2 N + 1) / 2 compare-exchanges of two instructions each: 672 for N = 64, against 64^2 x 5 for ranking
@@ -717,7 +717,7 @@ __device__ __forceinline__ void med_rank32(const unsigned *keys, const MedState 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// median_stream_kernel: windows longer than 64 frames, any length, any alignment.
+// median_stream_kernel: windows longer than 128 frames, any length, any alignment.
 //
 // Staging whole spectra in shared memory limits a CTA to a handful of spaxels, i.e. to 16-32 contiguous bytes per frame:
 // measured 0.75 TB/s for the staging alone on the ALMA cube, whatever the select does afterwards (the memory system
@@ -739,7 +739,7 @@ constexpr int kMsCap = 768;           // candidate slots per spaxel (20 % of an 
 constexpr int kMsRow = kMsCap + 1;    // odd row stride: neighbouring spaxels start in different banks
 constexpr int kMsU = 16;              // frames in flight per thread
 constexpr int64_t kMedStreamWideBins = 4200;         // up to here a 4-rank bin (6 % of the window) fits the list three times over
-constexpr int64_t kMedStreamMinFrames = 65;          // every window beyond the sorting network, on images large enough (measured 100..3000 frames: profiles/r1_median_phases.txt)
+constexpr int64_t kMedStreamMinFrames = 129;         // every window beyond the sorting network, on images large enough (measured 100..3000 frames: profiles/r1_median_phases.txt)
 constexpr int64_t kMedStreamMinPixels = 2 * 148 * 32; // fewer spaxels: not enough 32-spaxel CTAs for two per SM
 
 __device__ __forceinline__ unsigned ms_ld(const float *p) {
@@ -1150,7 +1150,8 @@ cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t 
         if (n <= 8) median_sort_kernel<8><<<grid, kMedSortPixels, 0, s>>>(k);
         else if (n <= 16) median_sort_kernel<16><<<grid, kMedSortPixels, 0, s>>>(k);
         else if (n <= 32) median_sort_kernel<32><<<grid, kMedSortPixels, 0, s>>>(k);
-        else median_sort_kernel<64><<<grid, kMedSortPixels, 0, s>>>(k);
+        else if (n <= 64) median_sort_kernel<64><<<grid, kMedSortPixels, 0, s>>>(k);
+        else median_sort_kernel<128><<<grid, kMedSortPixels, 0, s>>>(k);
         count_launch();
         return cudaGetLastError();
     }

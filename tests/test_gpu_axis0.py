@@ -112,8 +112,9 @@ def test_median_bit_exact(gpu, orc, shape):
     host[3::17] = -0.0
     host[4::19] = 1e-40
     cube = gpu.Image.upload(host)
-    # windows <= 64 frames go through the rank-counting kernel, longer ones through the radix select
-    for start, end in [(0, nz), (0, nz - 1), (nz // 3, 2 * nz // 3 + 1), (5, 6), (1, 3), (0, min(nz, 64)), (0, min(nz, 65)), (2, min(nz, 33))]:
+    # windows <= 128 frames go through the sorting-network kernel (N = 8..128), longer ones through the radix select
+    for start, end in [(0, nz), (0, nz - 1), (nz // 3, 2 * nz // 3 + 1), (5, 6), (1, 3), (0, min(nz, 64)), (0, min(nz, 65)), (2, min(nz, 33)),
+                       (0, min(nz, 8)), (1, min(nz, 10)), (0, min(nz, 16)), (0, min(nz, 17)), (0, min(nz, 128)), (0, min(nz, 129)), (3, min(nz, 130))]:
         got = gpu.call("median", cube, start, end).download()
         want = orc.median(host, start, end)
         assert got.shape == (ny, nx)
