@@ -205,8 +205,16 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
             cudaError_t ce = cudaMallocAsync(reinterpret_cast<void **>(&dtone), chain->tone_len * sizeof(float), s);
             if (ce == cudaSuccess) ce = cudaMemcpyAsync(dtone, chain->tone_table, chain->tone_len * sizeof(float), cudaMemcpyHostToDevice, s);
             if (ce != cudaSuccess) { err = cuda_error(ce, "tone table upload"); break; }
-            if ((err = scratch_u32(s, 4, &flag))) break;
+            if ((err = scratch_u32(s, 8, &flag))) break; // [0] tone index flag, [4..6] image_min_max left on the device
             a.chain = 1;
+            if (chain->logscale_vmin != chain->logscale_vmin && chain->logscale_vmax != chain->logscale_vmax) {
+                // NaN, NaN: the chain starts at image_min_max (src/templates.rs: min/max feed convert_to_logscale).  Its result stays
+                // on the device -- no read-back between the two kernels.
+                if ((err = image_wait(img, s))) break;
+                ce = minmax_launch(img->ptr, img->len(), flag + 4, sm_count(dev), s);
+                if (ce != cudaSuccess) { err = cuda_error(ce, "minmax_kernel launch"); break; }
+                a.ls_minmax = flag + 4;
+            }
             a.ls_a = chain->logscale_a; a.ls_min = chain->logscale_vmin; a.ls_max = chain->logscale_vmax;
             a.nm_min = chain->normalize_min; a.nm_max = chain->normalize_max;
             a.tone_table = dtone;

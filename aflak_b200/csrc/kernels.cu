@@ -936,9 +936,17 @@ __device__ __forceinline__ unsigned chain_key(float v, const CmapK &k, unsigned 
 template <bool RGB3, bool CHAIN, int CH>
 __global__ void __launch_bounds__(256) colormap_kernel(const float *__restrict__ img, int64_t ny, int64_t nx,
                                                         const uint32_t *__restrict__ lut, const float *__restrict__ tone,
-                                                        int flip_y, int vec_ok, uint8_t *__restrict__ out, unsigned *oob_flag, CmapK k) {
+                                                        int flip_y, int vec_ok, uint8_t *__restrict__ out, unsigned *oob_flag,
+                                                        const unsigned *__restrict__ ls_minmax, CmapK k) {
     extern __shared__ uint32_t s_color[]; // CHAIN: the packed colour of every tone-table index
     if (CHAIN) {
+        if (ls_minmax != nullptr) {
+            // image_min_max (lib.rs:180-197) left on the device by minmax_kernel: {~key(min), key(max), any}; the operator's
+            // FLT_MAX / -FLT_MAX initial values bound the result
+            const bool any = ls_minmax[2] != 0u;
+            k.ls_min = any ? fminf(3.402823466e38f, key_f32(~ls_minmax[0])) : 3.402823466e38f;
+            k.ls_max = any ? fmaxf(-3.402823466e38f, key_f32(ls_minmax[1])) : -3.402823466e38f;
+        }
         const float ts = (float)(k.tone_len - 1);
         for (int i = threadIdx.x; i < k.tone_len; i += blockDim.x)
             s_color[i] = __ldg(lut + lut_index(tone_value(tone[i], ts), k.vmin[0], k.vmax[0], k.l0[0], k.l1[0], k.l2[0]));
@@ -1032,7 +1040,7 @@ cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s)
     const int vec_ok = (a.nx % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.img) & 15u) == 0) &&
                        ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
     const size_t smem = a.chain ? (size_t)a.tone_len * sizeof(float) : 0;
-#define AFK_CMAP(R, C, CH) colormap_kernel<R, C, CH><<<grid, 256, smem, s>>>(a.img, a.ny, a.nx, a.lut, a.tone_table, a.flip_y, vec_ok, a.out, a.oob_flag, k)
+#define AFK_CMAP(R, C, CH) colormap_kernel<R, C, CH><<<grid, 256, smem, s>>>(a.img, a.ny, a.nx, a.lut, a.tone_table, a.flip_y, vec_ok, a.out, a.oob_flag, a.ls_minmax, k)
     if (a.rgb3) {
         if (a.channels == 4) AFK_CMAP(true, false, 4); else AFK_CMAP(true, false, 3);
     } else if (a.chain) {

@@ -233,6 +233,7 @@ struct ColormapArgs {
     const float *tone_table;
     int tone_len;
     unsigned *oob_flag;
+    const unsigned *ls_minmax; // chain only, may be null: minmax_kernel's result {~key(min), key(max), any} replaces ls_min / ls_max
     uint8_t *out;         // [ny][nx][channels]
 };
 cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s);

@@ -290,7 +290,8 @@ afk_status afk_image_vmed_vmad(const afk_image *img, float *vmed, float *vmad);
 afk_status afk_image_zscale(const afk_image *img, int nsamples, float contrast, int *has_limits, float *z1, float *z2);
 
 typedef struct afk_colormap_chain { /* optional fused upstream chain (BASELINE config 4) */
-    float logscale_a, logscale_vmin, logscale_vmax; /* convert_to_logscale */
+    float logscale_a, logscale_vmin, logscale_vmax; /* convert_to_logscale; vmin = vmax = NaN: use image_min_max of the image
+                                                     * (lib.rs:180-197), computed on the device with no read-back in between */
     float normalize_min, normalize_max;             /* normalize_image */
     const float *tone_table;                        /* apply_tone_curve (host pointer) */
     size_t tone_len;

@@ -123,6 +123,9 @@ def test_fused_chain_matches_unfused_operators(gpu, orc):
              "normalize_max": nmax, "tone_table": tone}
     fused = gpu.colormap(d, lut, vmin=0.0, vmax=65535.0, channels=4, chain=chain)
     assert np.array_equal(fused, unfused), int((fused != unfused).sum())
+    # logscale limits left to the library (NaN, NaN): image_min_max runs on the device and feeds the chain without a read-back
+    auto = gpu.colormap(d, lut, vmin=0.0, vmax=65535.0, channels=4, chain=dict(chain, logscale_vmin=float("nan"), logscale_vmax=float("nan")))
+    assert np.array_equal(auto, unfused), int((auto != unfused).sum())
     # oracle: same chain on the CPU; libm's logf may differ from CUDA's in the last bit, which can move a pixel by one
     # table entry -> allow a channel difference of at most 1 on at most 0.1 % of the pixels
     o = orc.convert_to_logscale(img, a, vmin, vmax)

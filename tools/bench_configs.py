@@ -183,6 +183,9 @@ def c4_full():
 
 
 out.append(entry("C4 full: min/max pass + fused chain -> RGBA8 (12 B/px)", npx * 12, c4_full))
+nan_chain = dict(chain, logscale_vmin=float("nan"), logscale_vmax=float("nan"))
+out.append(entry("C4 full, min/max kept on the device (chain limits = NaN): 2 kernels, 1 read-back (12 B/px)", npx * 12,
+                 lambda: afk.colormap_device(img, lut, 0.0, 65535.0, rgba.device_ptr, channels=4, chain=nan_chain)))
 
 
 def c4_unfused():
