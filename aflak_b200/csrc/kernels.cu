@@ -906,14 +906,22 @@ __device__ __forceinline__ float mtf(float m, float x) {
     return __fdiv_rn(num, den);
 }
 
-// color_at_bounds + color_at (index part), lut.rs:132-149
+// color_at_bounds + color_at (index part), lut.rs:132-149.
+// Two launch-uniform special cases drop divisions without changing the index:
+//   l1 == 0.5 (the default midtone): mtf(0.5, c) = (-0.5 c) / (0 c - 0.5) = c for every c in (0, 1) -- scaling by a power of two is
+//     exact; a denormal c can lose its last bit on the way, but then c * 65535 < 1 and the index is 0 either way;
+//   l0 == 0 and l2 == 1 (the default limits): (x - 0) / (1 - 0) = x exactly.
+// With the reference's default limits (0, 0.5, 1) one IEEE division per pixel is left instead of three.
 __device__ __forceinline__ unsigned lut_index(float val, float vmin, float vmax, float l0, float l1, float l2) {
     float p = val;
     if (p < vmin) p = vmin;       // util::clamp: NaN fails both comparisons and passes through
     else if (p > vmax) p = vmax;
     float x = __fdiv_rn(__fsub_rn(p, vmin), __fsub_rn(vmax, vmin));
-    float c = __fdiv_rn(__fsub_rn(x, l0), __fsub_rn(l2, l0));
-    float i = __fmul_rn(mtf(l1, c), 65535.0f);
+    float c = (l0 == 0.0f && l2 == 1.0f) ? x : __fdiv_rn(__fsub_rn(x, l0), __fsub_rn(l2, l0));
+    float m;
+    if (l1 == 0.5f) m = c >= 1.0f ? 1.0f : (c <= 0.0f ? 0.0f : c);
+    else m = mtf(l1, c);
+    float i = __fmul_rn(m, 65535.0f);
     if (i < 0.0f) i = 0.0f;
     unsigned idx;
     if (!(i > 0.0f)) idx = 0u; // NaN as usize == 0

@@ -34,16 +34,18 @@ def test_make_raw_image_bytes(gpu, orc, shape, gradient, channels):
     assert (gmn, gmx) == (vmin, vmax)
 
 
-@pytest.mark.parametrize("lims", [(0.0, 0.5, 1.0), (0.2, 0.3, 0.9), (0.0, 0.1, 0.5), (0.4, 0.9, 0.6)])
+# (0, 0.5, 1), (l0, 0.5, l2) and (0, l1, 1) take division-free shortcuts in lut_index: same bytes required, denormals included
+@pytest.mark.parametrize("lims", [(0.0, 0.5, 1.0), (0.2, 0.3, 0.9), (0.0, 0.1, 0.5), (0.4, 0.9, 0.6), (0.2, 0.5, 0.9), (0.0, 0.3, 1.0)])
 def test_lims_and_midtone_transfer(gpu, orc, lims):
     img = lognormal((96, 100), 22, nan_frac=0.001)
     img[0, :4] = [np.inf, -np.inf, 0.0, -1.0]
+    img[1, :6] = [1e-40, 3e-45, -0.0, 1.1754944e-38, 1.5e-5, 0.99999994]
     d = gpu.Image.upload(img)
     lut = gpu.Lut("Flame")
     lut.set_lims(*lims)
     eff = lut.lims()  # set_min/set_max clamp against each other (lut.rs:202-236)
     table = orc.lut_build("Flame")  # built with the default lims
-    for vmin, vmax in [(0.1, 5.0), (1.0, 1.0), (2.0, 0.5)]:
+    for vmin, vmax in [(0.1, 5.0), (1.0, 1.0), (2.0, 0.5), (0.0, 1.0), (0.0, 1e-38)]:
         got = gpu.colormap(d, lut, vmin=vmin, vmax=vmax, channels=3)
         want = orc.make_raw_image(img, vmin, vmax, table, lims=eff, channels=3)
         assert np.array_equal(got, want), (lims, vmin, vmax, int((got != want).sum()))

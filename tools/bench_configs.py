@@ -171,7 +171,9 @@ tone = np.arange(256, dtype=np.float32)
 lmax = float(np.float32(np.log(np.float32(1001.0)) / np.log(np.float32(1000.0))))
 chain = {"logscale_a": 1000.0, "logscale_vmin": float(vmin), "logscale_vmax": float(vmax), "normalize_min": 0.0, "normalize_max": lmax / 65535.0, "tone_table": tone}
 out.append(entry("C4 image_min_max 4096^2", npx * 4, lambda: afk.call("image_min_max", img)))
-out.append(entry("C4 colormap RGBA8 (given vmin/vmax)", npx * 8, lambda: afk.colormap_device(img, lut, float(vmin), float(vmax), rgba.device_ptr, channels=4)))
+out.append(entry("C4 colormap RGBA8, limits (0.2, 0.3, 0.9) (given vmin/vmax)", npx * 8, lambda: afk.colormap_device(img, lut, float(vmin), float(vmax), rgba.device_ptr, channels=4)))
+lut_dflt = afk.Lut("Flame")  # the reference's default limits (0, 0.5, 1)
+out.append(entry("C4 colormap RGBA8, default limits (0, 0.5, 1) (given vmin/vmax)", npx * 8, lambda: afk.colormap_device(img, lut_dflt, float(vmin), float(vmax), rgba.device_ptr, channels=4)))
 out.append(entry("C4 colormap RGB8 (given vmin/vmax)", npx * 7, lambda: afk.colormap_device(img, lut, float(vmin), float(vmax), rgba.device_ptr, channels=3)))
 out.append(entry("C4 fused chain logscale->tone->LUT->RGBA8 (given min/max)", npx * 8, lambda: afk.colormap_device(img, lut, 0.0, 65535.0, rgba.device_ptr, channels=4, chain=chain)))
 
