@@ -169,6 +169,7 @@ _sig("afk_get_transform", C.POINTER(afk_transform_desc), C.c_char_p)
 _sig("afk_transform_call", C.c_int, C.POINTER(afk_transform_desc), C.POINTER(C.c_void_p), C.c_size_t, C.POINTER(afk_result), C.c_size_t)
 _sig("afk_set_sum_mode", C.c_int, C.c_int)
 _sig("afk_get_sum_mode", C.c_int)
+_sig("afk_fused_logscale_minmax", C.c_int, _P, C.c_float, C.POINTER(C.c_void_p))
 _sig("afk_fused_average_ratio", C.c_int, _P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p))
 _sig("afk_fused_equivalent_width", C.c_int, _P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
      C.c_float, C.c_float, C.c_int, C.POINTER(C.c_void_p), _fp)
@@ -650,6 +651,12 @@ def call(name, *args):
 def fused_average_ratio(cube, s0, e0, s1, e1):
     out = C.c_void_p()
     _check(lib.afk_fused_average_ratio(cube.handle, s0, e0, s1, e1, C.byref(out)))
+    return Image(out.value)
+
+
+def fused_logscale_minmax(img, a):
+    out = C.c_void_p()
+    _check(lib.afk_fused_logscale_minmax(img.handle, C.c_float(a), C.byref(out)))
     return Image(out.value)
 
 

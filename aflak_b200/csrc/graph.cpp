@@ -170,6 +170,27 @@ static bool try_fused(afk_graph *g, Node *n, std::vector<afk_result> &res) {
         g->calls += 1;
         return true;
     }
+    if (strcmp(name, "convert_to_logscale") == 0) {
+        // convert_to_logscale(x, a, image_min_max(x).0, image_min_max(x).1): the range stays on the device
+        const Edge &ex = n->inputs[0], &emin = n->inputs[2], &emax = n->inputs[3];
+        if (ex.from_t < 0 || emin.from_t < 0 || emin.from_t != emax.from_t || emin.out_i != 0 || emax.out_i != 1) return false;
+        Node *mmn = node_at(g, emin.from_t);
+        if (!mmn || mmn->is_constant || strcmp(mmn->t->name, "image_min_max") != 0) return false;
+        if (mmn->inputs[0].from_t != ex.from_t || mmn->inputs[0].out_i != ex.out_i) return false;
+        const afk_value *av;
+        if (!const_scalar(g, n, 1, AFK_T_FLOAT, &av)) return false;
+        std::vector<afk_result> *src = nullptr;
+        if (compute_node(g, ex.from_t, &src) != AFK_OK || (*src)[ex.out_i].status != AFK_OK) return false;
+        afk_value *xv = (*src)[ex.out_i].value;
+        if (!xv || xv->type != AFK_T_IMAGE) return false;
+        afk_image *o = nullptr;
+        if (afk_fused_logscale_minmax(xv->img, scalar_as_float(av), &o) != AFK_OK) return false;
+        res[0].status = AFK_OK;
+        res[0].value = afk_value_image(o);
+        afk_image_release(o);
+        g->calls += 1;
+        return true;
+    }
     if (strcmp(name, "create_equivalent_width") == 0) {
         // create_equivalent_width(linear_composition(avg(off1), avg(off2), r2, r1), avg(on), fl, max, emission) with
         // (r2, r1) = ratio_from_bands(mid_on, mid_off1, mid_off2)  -- src/templates.rs:143-463

@@ -576,6 +576,7 @@ struct MapK {
     float a, b, c, ln_a;
     int flag0, flag1;
     float d, e;
+    const unsigned *mm; // see MapArgs::bc_minmax
 };
 
 template <int OP> __device__ __forceinline__ float map_one(float u, float v, const MapK &k) {
@@ -620,6 +621,12 @@ template <int OP, bool BINARY>
 __global__ void __launch_bounds__(256) map_kernel(const float *__restrict__ u, const float *__restrict__ v,
                                                    float *__restrict__ out, int64_t n, int vec_ok, MapK k) {
     constexpr int U = BINARY ? 2 : 4;
+    if (OP == MAP_LOGSCALE && k.mm != nullptr) {
+        // image_min_max (lib.rs:180-197) left on the device by minmax_kernel; FLT_MAX / -FLT_MAX are the operator's initial values
+        const bool any = k.mm[2] != 0u;
+        k.b = any ? fminf(3.402823466e38f, key_f32(~k.mm[0])) : 3.402823466e38f;
+        k.c = any ? fmaxf(-3.402823466e38f, key_f32(k.mm[1])) : -3.402823466e38f;
+    }
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
     int64_t done = 0;
@@ -671,7 +678,7 @@ template <int OP, bool BINARY> static void map_go(const MapArgs &a, const MapK &
 
 cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
-    MapK k{a.a, a.b, a.c, 0.0f, a.flag0, a.flag1, a.d, a.e};
+    MapK k{a.a, a.b, a.c, 0.0f, a.flag0, a.flag1, a.d, a.e, a.bc_minmax};
     if (a.op == MAP_LOGSCALE) k.ln_a = logf(a.a); // a.ln(): host libm, same call the reference makes
     auto al = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
     const int vec_ok = al(a.u) && al(a.out) && (a.v == nullptr || al(a.v));

@@ -160,6 +160,7 @@ struct MapArgs {
     int64_t n;
     float *out;
     float d = 0.0f, e = 0.0f; // MAP_HISTTRANS only
+    const unsigned *bc_minmax = nullptr; // MAP_LOGSCALE only: minmax_kernel's device result {~key(min), key(max), any} replaces b, c
 };
 cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s);
 

@@ -1367,6 +1367,45 @@ afk_status afk_fused_average_ratio(const afk_image *cube, int64_t s0, int64_t e0
     return AFK_OK;
 }
 
+afk_status afk_fused_logscale_minmax(const afk_image *img, float a, afk_image **out) {
+    // convert_to_logscale(img, a, image_min_max(img).min, image_min_max(img).max) (src/templates.rs: the tail of the
+    // equivalent-width template): the two floats never visit the host -- minmax_kernel leaves them on the device and the
+    // logscale kernel reads them there.  Same arithmetic as the two operators (lib.rs:180-197, 1598-1611).
+    if (!img || !out) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument"));
+    cudaStream_t s;
+    int dev;
+    if (Error e = current_stream(&s, &dev)) return fail(e);
+    if (Error e = same_device(img, dev)) return fail(e);
+    afk_image *o = nullptr;
+    if (Error e = image_new(img->ndim, img->shape, &o)) return fail(e);
+    unsigned *mm = nullptr;
+    Error err = scratch_u32(s, 4, &mm);
+    do {
+        if (err) break;
+        if ((err = image_wait(img, s))) break;
+        cudaError_t ce = minmax_launch(img->ptr, img->len(), mm, sm_count(dev), s);
+        if (ce == cudaSuccess) {
+            MapArgs m{MAP_LOGSCALE, img->ptr, nullptr, a, 0.0f, 0.0f, 0, 0, img->len(), o->ptr};
+            m.bc_minmax = mm;
+            ce = map_launch(m, sm_count(dev), s);
+        }
+        if (ce != cudaSuccess) {
+            err = cuda_error(ce, "fused logscale launch");
+            break;
+        }
+        image_note_read(img, s);
+        err = image_mark_ready(o, s);
+    } while (0);
+    if (mm) scratch_free(s, mm);
+    if (err) {
+        afk_image_release(o);
+        return fail(err);
+    }
+    meta_clone(img, o); // convert_to_logscale clones its input (lib.rs:1598-1611)
+    *out = o;
+    return AFK_OK;
+}
+
 afk_status afk_fused_equivalent_width(const afk_image *cube, int64_t on_s, int64_t on_e, int64_t off1_s, int64_t off1_e, int64_t off2_s,
                                       int64_t off2_e, float fl, float max, int is_emission, afk_image **out, float minmax[2]) {
     if (!cube || !out) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument"));

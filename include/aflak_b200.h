@@ -249,6 +249,9 @@ int afk_get_sum_mode(void);
  *      reference).  Inputs are borrowed, outputs have refcount 1. ---- */
 /* average(cube,s0,e0) / average(cube,s1,e1)  -- BASELINE config 3 */
 afk_status afk_fused_average_ratio(const afk_image *cube, int64_t s0, int64_t e0, int64_t s1, int64_t e1, afk_image **out);
+/* convert_to_logscale(img, a, min, max) with (min, max) = image_min_max(img) (lib.rs:180-197, 282-290, 1598-1611; the tail of
+ * the equivalent-width template): two kernels, the two floats stay on the device */
+afk_status afk_fused_logscale_minmax(const afk_image *img, float a, afk_image **out);
 /* equivalent-width template (src/templates.rs:143-463): three averages -> ratio_from_bands ->
  * linear_composition -> create_equivalent_width; minmax (may be NULL) receives image_min_max of the result */
 afk_status afk_fused_equivalent_width(const afk_image *cube, int64_t on_s, int64_t on_e, int64_t off1_s, int64_t off1_e,

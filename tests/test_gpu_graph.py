@@ -135,6 +135,43 @@ def test_fused_ew_entry_point_and_minmax(gpu, orc):
     assert "frame count" in ei.value.message
 
 
+def test_fused_logscale_minmax_matches_the_two_operators(gpu, orc):
+    """convert_to_logscale fed by image_min_max of the same image: the fused path keeps the range on the device; same bits as
+    the two operators, including images with NaN / Inf, a constant image (zero range) and an all-NaN image (the operator's
+    FLT_MAX / -FLT_MAX initial values)."""
+    rng = np.random.default_rng(0xAF1A0061)
+    base = np.exp(rng.standard_normal((67, 129))).astype(np.float32)
+    holes = base.copy()
+    holes[::7, ::5] = np.nan
+    holes[3, 4] = np.inf
+    holes[5, 6] = -np.inf
+    for tag, host in [("lognormal", base), ("nan/inf", holes), ("constant", np.full((8, 12), 2.5, np.float32)),
+                      ("all nan", np.full((4, 8), np.nan, np.float32)), ("negative", -base)]:
+        img = gpu.Image.upload(host)
+        mn, mx = gpu.call("image_min_max", img)
+        want = gpu.call("convert_to_logscale", img, 1000.0, float(mn), float(mx)).download()
+        got = gpu.fused_logscale_minmax(img, 1000.0).download()
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)) or (
+            np.array_equal(np.isnan(got), np.isnan(want)) and np.array_equal(got[~np.isnan(got)], want[~np.isnan(want)])), tag
+    # through the evaluator: the pattern is substituted when fusion is on, and the results agree with fusion off
+    outs = []
+    for fusion in (True, False):
+        g = gpu.Graph()
+        g.set_fusion(fusion)
+        c = g.add_constant(gpu.Image.upload(holes))
+        mm = g.add_transform("image_min_max")
+        g.connect(c, 0, mm, 0)
+        ls = g.add_transform("convert_to_logscale")
+        g.connect(c, 0, ls, 0)
+        g.connect(g.add_constant(1000.0), 0, ls, 1)
+        g.connect(mm, 0, ls, 2)
+        g.connect(mm, 1, ls, 3)
+        outs.append((g.compute(ls).download(), g.calls))
+    assert np.array_equal(np.isnan(outs[0][0]), np.isnan(outs[1][0]))
+    assert np.array_equal(outs[0][0][~np.isnan(outs[0][0])], outs[1][0][~np.isnan(outs[1][0])])
+    assert outs[0][1] == 1 and outs[1][1] == 2  # fused: one call; unfused: image_min_max + convert_to_logscale
+
+
 def test_average_ratio_graph_fused_vs_unfused(gpu, orc):
     """BASELINE config 3 on a small cube: average, average, ratio."""
     nz, ny, nx = 128, 64, 96
