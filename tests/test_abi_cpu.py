@@ -275,3 +275,20 @@ def test_compute_entry_points_fail_loudly_without_gpu(afk):
         afk.Image.synthetic(1, 4, 4, 4)
     with pytest.raises(afk.AflakError):
         afk.set_device(0)
+
+
+def test_header_is_plain_c_and_a_c_client_links(afk, tmp_path):
+    """include/aflak_b200.h must be consumable by a C compiler (it is what a Rust `-sys` crate binds): the C99 client of
+    tests/c/ compiles with -Wall -Wextra -Werror, links against the shared library and, without a GPU, stops at its device check."""
+    import subprocess
+
+    from util import build_c_client
+
+    exe = build_c_client(tmp_path)
+    p = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    import aflak_b200
+
+    if aflak_b200.device_count() == 0:
+        assert p.returncode == 77 and "no CUDA device" in p.stderr
+    else:
+        assert p.returncode == 0, p.stderr

@@ -299,3 +299,18 @@ def test_fused_gather_single_rank(gpu, orc):
     ga.wait()
     assert_bit_equal(ga.result_image().download(), orc.ratio(orc.average(host, 0, 50), orc.average(host, 50, 100)))
     ga.close()
+
+
+def test_plain_c_client_of_the_abi(gpu, tmp_path):
+    """The whole boundary from C, the way the Rust binding would drive it (tests/c/abi_client.c): registry walk, `integral` through
+    the descriptor's function pointer with a closed-form answer, the reference's error wording, the evaluator's cache rule."""
+    import json
+    import subprocess
+
+    from util import build_c_client
+
+    p = subprocess.run([build_c_client(tmp_path)], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr + p.stdout
+    assert "abi_client ok" in p.stdout
+    stats = json.loads(p.stdout.splitlines()[0])["c_abi_client"]
+    assert stats["kernel_launches"] > 0

@@ -96,3 +96,18 @@ def fits_hdu_bytes(data_be, cards, primary=True, extname=None):
     data = b"" if data_be is None else data_be.tobytes()
     data += b"\0" * (-len(data) % 2880)
     return hdr + data
+
+
+def build_c_client(tmpdir):
+    """Compile tests/c/abi_client.c (plain C99, only include/aflak_b200.h and the shared library) and return the binary's path."""
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(str(tmpdir), "abi_client")
+    env = dict(os.environ)
+    env.pop("CC", None)
+    subprocess.check_call(["gcc", "-std=c99", "-O2", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(root, "include"),
+                           os.path.join(root, "tests", "c", "abi_client.c"), "-L", os.path.join(root, "aflak_b200"), "-laflak_b200",
+                           "-Wl,-rpath," + os.path.join(root, "aflak_b200"), "-lm", "-o", exe], env=env)
+    return exe
