@@ -6,5 +6,5 @@ timeout 900 python tools/bench_axis0.py > gpurun_out/axis0.json 2> gpurun_out/ax
 python - <<'PY'
 import json
 for e in json.load(open("gpurun_out/axis0.json"))["entries"]:
-    if " median" in e["config"]: print(e["config"][:60], round(e["ms_median"],3), "ms", round(e["GBps"]), "GB/s")
+    if "[0," in e["config"]: print(e["config"][:78], round(e["ms_median"],3), "ms", round(e["GBps"]), "GB/s")
 PY
