@@ -224,6 +224,16 @@ def test_c3_alma_extract_wave_checksum_of_checksums(gpu, orc, alma):
     for k in (0, 1999, nz - 1):
         frame = gpu.call("slice_one_frame", alma, k).download().astype(np.float64)
         np.testing.assert_allclose(wave[k], frame.sum(), rtol=1e-5)
+    # sequential mode: every frame summed in the reference's own order (roi.rs:17-34); sampled frames bit for bit
+    gpu.set_sum_mode(gpu.SUM_SEQUENTIAL)
+    try:
+        seq = gpu.call("extract_wave", alma, gpu.Roi()).download()
+    finally:
+        gpu.set_sum_mode(gpu.SUM_COMPENSATED)
+    for k in (0, 31, 32, 1999, nz - 1):
+        frame = gpu.call("slice_one_frame", alma, k).download()
+        assert_bit_equal(seq[k:k + 1], orc.extract_wave(frame[None]), f"C3 sequential extract_wave frame {k}")
+    np.testing.assert_allclose(seq, wave, rtol=5e-3)  # a million f32 additions in sequence: ~6e-4 off the f64 sum
     # a box region: the waveform template at full size, against the host generator
     box = [(x, y) for y in range(700, 703) for x in range(100, 164)]
     got = gpu.call("extract_wave", alma, gpu.Roi(box)).download()
