@@ -128,7 +128,10 @@ struct afk_value {
     int map_dev_device = -1;
     int map_sliced = -1; // -1 not analysed, 0 None, 1 Some(map_axis, map_start, map_step)
     int map_axis[2] = {0, 0};
-    float map_start[2] = {0, 0}, map_step[2] = {0, 0};
+    float map_start[2] = {0, 0}, map_step[2] = {0, 0};    // lazily built by extract_wave / extrude: device copy of ROI::filter's offsets for a [roi_ny, roi_nx] frame (same mutex)
+    int64_t *roi_dev = nullptr;
+    int roi_dev_device = -1;
+    int64_t roi_ny = -1, roi_nx = -1, roi_count = 0;
 };
 
 namespace afk {

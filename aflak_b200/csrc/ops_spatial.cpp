@@ -259,12 +259,41 @@ static Error roi_offsets(const afk_value *roi, int64_t ny, int64_t nx, bool *who
     return ok();
 }
 
-static Error upload_offsets(const std::vector<int64_t> &h, cudaStream_t s, int64_t **d) {
+// Device copy of the offsets, built once per (Roi value, frame shape, device) and kept with the immutable value like the
+// mesh of slice_3d_to_2d: re-evaluating a node whose region did not change costs no upload and no synchronisation.
+static Error roi_device_offsets(const afk_value *roi, int64_t ny, int64_t nx, int dev, cudaStream_t s, bool *whole_frame, const int64_t **d,
+                                int64_t *count) {
     *d = nullptr;
-    if (h.empty()) return ok();
-    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(d), h.size() * sizeof(int64_t), s));
-    AFK_CUDA(cudaMemcpyAsync(*d, h.data(), h.size() * sizeof(int64_t), cudaMemcpyHostToDevice, s));
-    AFK_CUDA(cudaStreamSynchronize(s)); // `h` is pageable host memory owned by the caller
+    *count = 0;
+    *whole_frame = false;
+    if (roi->roi_all) {
+        std::vector<int64_t> none;
+        Error e = roi_offsets(roi, ny, nx, whole_frame, &none);
+        if (!e) *count = ny * nx;
+        return e;
+    }
+    afk_value *mut = const_cast<afk_value *>(roi);
+    std::lock_guard<std::mutex> lk(mut->map_mu);
+    if (mut->roi_dev_device != dev || mut->roi_ny != ny || mut->roi_nx != nx) {
+        if (mut->roi_dev) cudaFree(mut->roi_dev);
+        mut->roi_dev = nullptr;
+        mut->roi_dev_device = -1;
+        std::vector<int64_t> off;
+        Error e = roi_offsets(roi, ny, nx, whole_frame, &off);
+        if (e) return e;
+        if (!off.empty()) {
+            // from the stream-ordered pool (a plain cudaMalloc costs more than the kernels that follow); `off` is pageable
+            AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&mut->roi_dev), off.size() * sizeof(int64_t), s));
+            AFK_CUDA(cudaMemcpyAsync(mut->roi_dev, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+            AFK_CUDA(cudaStreamSynchronize(s));
+        }
+        mut->roi_count = (int64_t)off.size();
+        mut->roi_ny = ny;
+        mut->roi_nx = nx;
+        mut->roi_dev_device = dev;
+    }
+    *d = mut->roi_dev;
+    *count = mut->roi_count;
     return ok();
 }
 
@@ -276,17 +305,15 @@ AFK_OPX(op_extract_wave) { // lib.rs:376-383, 1147-1169
     OpCtx c;
     if (!e) e = ctx_for(&c, {img});
     afk_image *res = nullptr;
-    int64_t *doff = nullptr;
+    const int64_t *doff = nullptr;
     void *partials = nullptr;
     do {
         if (e) break;
         const int64_t nz = img->shape[0], ny = img->shape[1], nx = img->shape[2];
         bool whole;
-        std::vector<int64_t> off;
-        if ((e = roi_offsets(in[1], ny, nx, &whole, &off))) break;
+        int64_t count;
+        if ((e = roi_device_offsets(in[1], ny, nx, c.dev, c.s, &whole, &doff, &count))) break;
         if ((e = image_new(1, &nz, &res))) break;
-        if ((e = upload_offsets(off, c.s, &doff))) break;
-        const int64_t count = whole ? ny * nx : (int64_t)off.size();
         const int mode = tls().sum_mode;
         cudaError_t ce = cudaSuccess;
         if (count == 0 || (!whole && !doff)) {
@@ -307,7 +334,6 @@ AFK_OPX(op_extract_wave) { // lib.rs:376-383, 1147-1169
         image_note_read(img, c.s);
         e = image_mark_ready(res, c.s);
     } while (0);
-    if (doff) cudaFreeAsync(doff, c.s);
     if (partials) cudaFreeAsync(partials, c.s);
     if (!e) {
         // image.make_slice(&[(2, 0.0, 1.0)], ..): FITS axis 2 (the spectral axis) is the only one kept; unit kept, tag dropped
@@ -326,24 +352,22 @@ AFK_OPX(op_extrude) { // lib.rs:368-375, 1233-1256
     OpCtx c;
     if (!e) e = ctx_for(&c, {img});
     afk_image *res = nullptr;
-    int64_t *doff = nullptr;
+    const int64_t *doff = nullptr;
     do {
         if (e) break;
         const int64_t nz = img->shape[0], ny = img->shape[1], nx = img->shape[2];
         bool whole;
-        std::vector<int64_t> off;
-        if ((e = roi_offsets(in[1], ny, nx, &whole, &off))) break;
+        int64_t pushed;
+        if ((e = roi_device_offsets(in[1], ny, nx, c.dev, c.s, &whole, &doff, &pushed))) break;
         // new_size = (wave_size, roi.datalen()); ROI::All has datalen 0, and skipped pixels leave the vector short:
         // Array::from_shape_vec(..).unwrap() panics unless the lengths agree
         const int64_t datalen = in[1]->roi_all ? 0 : (int64_t)(in[1]->roi_xy.size() / 2);
-        const int64_t pushed = whole ? ny * nx : (int64_t)off.size();
         if (nz * pushed != nz * datalen) {
             e = make_error(AFK_ERR_PANIC, "called `Result::unwrap()` on an `Err` value: ShapeError/OutOfBounds: out of bounds indexing");
             break;
         }
         const int64_t shape[2] = {nz, datalen};
         if ((e = image_new(2, shape, &res))) break;
-        if ((e = upload_offsets(off, c.s, &doff))) break;
         cudaError_t ce = extrude_launch(img->ptr, nz, ny * nx, doff, datalen, res->ptr, sm_count(c.dev), c.s);
         if (ce != cudaSuccess) {
             e = cuda_error(ce, "extrude_kernel");
@@ -352,7 +376,6 @@ AFK_OPX(op_extrude) { // lib.rs:368-375, 1233-1256
         image_note_read(img, c.s);
         e = image_mark_ready(res, c.s);
     } while (0);
-    if (doff) cudaFreeAsync(doff, c.s);
     if (!e) { // from_array(Dimensioned::new(waveimg, unit)): unit kept, nothing else
         res->meta = ImageMeta();
         res->meta.has_unit = img->meta.has_unit;

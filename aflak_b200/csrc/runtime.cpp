@@ -673,6 +673,7 @@ void afk_value_release(afk_value *v) {
         if (v->img) afk_image_release(v->img);
         if (v->fits) afk_fits_release(v->fits);
         if (v->map_dev) cudaFree(v->map_dev);
+        if (v->roi_dev) cudaFree(v->roi_dev);
         delete v;
     }
 }

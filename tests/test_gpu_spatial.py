@@ -69,6 +69,28 @@ def test_extract_wave(gpu, orc, shape):
     assert got.pix2world(2, 3.0) == cube.pix2world(2, 3.0)
 
 
+def test_roi_value_reused_across_frame_shapes(gpu, orc):
+    """A Roi value keeps the device copy of its offsets (ROI::filter depends on the frame shape: roi.rs:25-34); reusing
+    the value on a cube of another shape must rebuild them, and reusing it on the same shape must not change a bit."""
+    px = [(3, 2), (40, 1), (7, 30), (3, 2), (63, 63), (20, 20)]
+    roi = gpu.Value(gpu.Roi(px))
+    for shape in [(12, 64, 64), (12, 64, 64), (9, 32, 48), (12, 64, 64)]:
+        host = orc.gen_cube(0xAF1A0032, *shape)
+        cube = gpu.Image.upload(host)
+        gpu.set_sum_mode(gpu.SUM_SEQUENTIAL)
+        try:
+            seq = gpu.call("extract_wave", cube, roi).download()
+        finally:
+            gpu.set_sum_mode(gpu.SUM_COMPENSATED)
+        assert_bit_equal(seq, orc.extract_wave(host, px), f"reused Roi value on {shape}")
+        inside = [(x, y) for x, y in px if x < shape[2] and y < shape[1]]
+        e = gpu.get_transform("extrude").call_results(cube, roi)[0]
+        if len(inside) == len(px):
+            assert_bit_equal(e.download(), orc.extrude(host, px), f"extrude, reused Roi value on {shape}")
+        else:  # skipped pixels leave the vector short: from_shape_vec(..).unwrap() panics (lib.rs:1233-1256)
+            assert isinstance(e, gpu.AflakError) and e.status == gpu.ERR_PANIC
+
+
 def test_extract_wave_errors(gpu, orc):
     host = orc.gen_cube(0xAF1A0032, 5, 6, 7)
     cube = gpu.Image.upload(host)

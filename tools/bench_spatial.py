@@ -60,8 +60,12 @@ afk.set_sum_mode(afk.SUM_SEQUENTIAL)
 entry("C3 extract_wave ROI::All, sequential (bit-exact) mode", nz * n2 * 4 + nz * 4, lambda: afk.call("extract_wave", cube, afk.Roi()), 3)
 afk.set_sum_mode(afk.SUM_COMPENSATED)
 box = afk.Roi([(x, y) for y in range(500, 532) for x in range(500, 532)])
-entry("C3 extract_wave 32x32-pixel region (interactive waveform)", nz * 1024 * 4 + nz * 4, lambda: afk.call("extract_wave", cube, box), 20)
-entry("C3 extrude 32x32-pixel region", 2 * nz * 1024 * 4, lambda: afk.call("extrude", cube, box), 20)
+entry("C3 extract_wave 32x32-pixel region (interactive waveform), new Roi value per call", nz * 1024 * 4 + nz * 4, lambda: afk.call("extract_wave", cube, box), 20)
+entry("C3 extrude 32x32-pixel region, new Roi value per call", 2 * nz * 1024 * 4, lambda: afk.call("extrude", cube, box), 20)
+boxv = afk.Value(box)  # a constant node of the graph: the value keeps the device copy of its offsets
+entry("C3 extract_wave 32x32-pixel region, Roi value reused (re-evaluation after another input changed)", nz * 1024 * 4 + nz * 4,
+      lambda: afk.call("extract_wave", cube, boxv), 20)
+entry("C3 extrude 32x32-pixel region, Roi value reused", 2 * nz * 1024 * 4, lambda: afk.call("extrude", cube, boxv), 20)
 pv = afk.Value(afk.call("make_plane3d", (0.0, 512.0, 0.0), (0.0, 0.0, 1.0), (1.0, 0.0, 0.0), nx, nz))
 entry("C3 slice_3d_to_2d position-velocity cut (3840 x 1024), mesh value reused", 2 * nz * nx * 4 + nz * nx * 12, lambda: afk.call("slice_3d_to_2d", cube, pv), 10)
 del cube
