@@ -579,10 +579,22 @@ struct MapK {
     const unsigned *mm; // see MapArgs::bc_minmax
 };
 
+// powf(x, e) with a launch-uniform exponent.  The exponents a user actually sets (1 is the default of both slots, -1
+// spells a ratio, 2 a square, 0 switches an input off) have exact closed forms that C99 Annex F fixes for every x, NaN,
+// zeros and infinities included: pow(x, 1) = x, pow(x, 0) = 1, pow(x, -1) = 1/x and pow(x, 2) = x*x correctly rounded
+// (libm's powf is within 1 ulp of them; tier B).  The branch is uniform across the grid; anything else calls powf.
+__device__ __forceinline__ float pow_uniform(float x, float e) {
+    if (e == 1.0f) return x;
+    if (e == -1.0f) return __fdiv_rn(1.0f, x);
+    if (e == 2.0f) return __fmul_rn(x, x);
+    if (e == 0.0f) return 1.0f;
+    return powf(x, e);
+}
+
 template <int OP> __device__ __forceinline__ float map_one(float u, float v, const MapK &k) {
     if (OP == MAP_LINCOMP) return __fadd_rn(__fmul_rn(u, k.a), __fmul_rn(v, k.b));
     if (OP == MAP_RATIO) return __fdiv_rn(u, v);
-    if (OP == MAP_MULTIPLIER) return __fmul_rn(powf(u, k.a), powf(v, k.b));
+    if (OP == MAP_MULTIPLIER) return __fmul_rn(pow_uniform(u, k.a), pow_uniform(v, k.b));
     if (OP == MAP_EW) return ew_value(u, v, k.a, k.b, k.c);
     if (OP == MAP_EMISSION_LINE) {
         float t = __fsub_rn(u, v);

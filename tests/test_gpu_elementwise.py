@@ -109,6 +109,14 @@ def test_logscale_log10_multiplier_within_2ulp(gpu, orc, shape):
         assert_ulp(gpu.call("image_multiplier", du, dv, a, b).download(), orc.image_multiplier(u, v, a, b), 4, f"multiplier {a},{b}")
     # the registry spelling of `ratio`: u^1 * v^-1 equals u/v to within powf accuracy
     assert_ulp(gpu.call("image_multiplier", du, dv, 1.0, -1.0).download(), orc.ratio(u, v), 4, "u^1 v^-1 vs u/v")
+    # exponents with a closed form (1 = the default of both slots, -1, 2, 0) skip powf on the device: same answers as libm's powf
+    # on every special value (C99 F.9.4.4: pow(x, 0) = 1 even for NaN, pow(+-0, -1) = +-Inf, pow(-Inf, 2) = +Inf ...)
+    p, q = images(orc, shape, 16, pathology=True)
+    dp, dq = gpu.Image.upload(p), gpu.Image.upload(q)
+    for a, b in [(1.0, 1.0), (2.0, 0.0), (0.0, -1.0), (-1.0, 2.0), (2.0, 2.0), (1.0, 0.5), (-1.0, -1.0)]:
+        for x, y, dx, dy in ((u, v, du, dv), (p, q, dp, dq)):
+            assert_ulp(gpu.call("image_multiplier", dx, dy, a, b).download(), orc.image_multiplier(x, y, a, b), 4, f"multiplier {a},{b}")
+    assert_bit_equal(gpu.call("image_multiplier", dp, dq, 1.0, 1.0).download(), (p * q).astype(np.float32), "u^1 v^1 is the plain product")
 
 
 def test_logscale_kat_and_nonfinite(gpu):
