@@ -978,15 +978,29 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
     // ---- C: collect the bin ----
     unsigned n_eq = 0u, hi_min = kFull;
     unsigned *row = s_list + lane * kMsRow;
+    const unsigned cnt_addr = (unsigned)__cvta_generic_to_shared(&s_cnt[lane]), row_addr = (unsigned)__cvta_generic_to_shared(row);
     auto collect = [&](unsigned rawbits) {
         const unsigned key = ms_key(rawbits);
-        nan |= (key - 0x00800000u) > 0xFF000000u; // outside [key(-Inf), key(+Inf)]
+        const float xf = __uint_as_float(rawbits);
+        nan |= xf != xf;                           // one FSETP on the raw value
         if (key == lo) ++n_eq;                     // without a lower pivot lo is 0, the key of a NaN: never counted for clean data
         if (key >= hi) hi_min = min(hi_min, key);
-        if (key > lo && key < hi) {
-            const unsigned at = atomicAdd(&s_cnt[lane], 1u);
-            if (at < (unsigned)kMsCap) row[at] = key;
-        }
+        // append, predicated rather than branched (the compiler's version spends a BSSY / BRA / BSYNC triple per key, and in
+        // almost every warp some lane has a key in its bin): slot = atomic counter of the spaxel, stored when below the cap
+        const unsigned inbin = (key > lo && key < hi) ? 1u : 0u;
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p, q;\n\t"
+            ".reg .u32 at, ad;\n\t"
+            "setp.ne.u32 p, %0, 0;\n\t"
+            "@p atom.shared.add.u32 at, [%1], 1;\n\t"
+            "setp.lt.and.u32 q, at, %2, p;\n\t"
+            "mad.lo.u32 ad, at, 4, %3;\n\t"
+            "@q st.shared.u32 [ad], %4;\n\t"
+            "}"
+            :
+            : "r"(inbin), "r"(cnt_addr), "r"((unsigned)kMsCap), "r"(row_addr), "r"(key)
+            : "memory");
     };
     if (active && n <= kMsCap) {
         // the whole window fits the list: frame k goes to slot k, nothing to prune, no atomics
@@ -1011,17 +1025,22 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
         }
         if (g == 0) s_cnt[lane] = (unsigned)n;
     } else if (active) {
+        // Backwards: pass B swept the window upwards, so its last frames are the ones still in L2 (the resident tiles of
+        // all CTAs, 296 x 32 spaxels x n frames, are about the size of L2 for n = 3840).  The list is unordered anyway.
         const size_t wstep = (size_t)kMsWarps * a.n2;
-        const float *p = col + (size_t)g * a.n2;
-        int k = g;
-        for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
+        int i = g < n ? (n - g + kMsWarps - 1) / kMsWarps : 0; // this warp's frames are k = g + j * kMsWarps, j < i
+        const float *p = col + ((size_t)g + (size_t)(i > 0 ? i - 1 : 0) * kMsWarps) * a.n2;
+        for (; i > kMsU; i -= kMsU) { // `>`: the pointer never steps below the warp's first frame
             unsigned raw[kMsU];
 #pragma unroll
-            for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p += wstep; }
+            for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p -= wstep; }
 #pragma unroll
             for (int u = 0; u < kMsU; ++u) collect(raw[u]);
         }
-        for (; k < n; k += kMsWarps, p += wstep) collect(ms_ld(p));
+        for (; i > 0; --i) {
+            collect(ms_ld(p));
+            if (i > 1) p -= wstep;
+        }
     }
     s_eq[g][lane] = n_eq;
     s_himin[g][lane] = hi_min;
