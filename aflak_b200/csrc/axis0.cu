@@ -790,6 +790,7 @@ constexpr int kMsWarps = 16;          // 2 CTAs x 512 threads x 16 loads in flig
 constexpr int kMsCap = 768;           // candidate slots per spaxel (20 % of an ALMA window: a 4-rank bin of 64 samples overflows 4e-4 of the time)
 constexpr int kMsRow = kMsCap + 1;    // odd row stride: neighbouring spaxels start in different banks
 constexpr int kMsU = 16;              // frames in flight per thread
+constexpr int kMsUC = 16;             // ... in the collect pass: 20 -> 10.9 ms, 32 -> 15.3 ms (spills under the 64-register cap); 16 -> 9.8 ms
 constexpr int64_t kMedStreamWideBins = 4200;         // up to here a 4-rank bin (6 % of the window) fits the list three times over
 constexpr int64_t kMedStreamMinFrames = 129;         // every window beyond the sorting network, on images large enough (measured 100..3000 frames: profiles/r1_median_phases.txt)
 constexpr int64_t kMedStreamMinPixels = 2 * 148 * 32; // fewer spaxels: not enough 32-spaxel CTAs for two per SM
@@ -1030,12 +1031,12 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
         const size_t wstep = (size_t)kMsWarps * a.n2;
         int i = g < n ? (n - g + kMsWarps - 1) / kMsWarps : 0; // this warp's frames are k = g + j * kMsWarps, j < i
         const float *p = col + ((size_t)g + (size_t)(i > 0 ? i - 1 : 0) * kMsWarps) * a.n2;
-        for (; i > kMsU; i -= kMsU) { // `>`: the pointer never steps below the warp's first frame
-            unsigned raw[kMsU];
+        for (; i > kMsUC; i -= kMsUC) { // `>`: the pointer never steps below the warp's first frame
+            unsigned raw[kMsUC];
 #pragma unroll
-            for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p -= wstep; }
+            for (int u = 0; u < kMsUC; ++u) { raw[u] = ms_ld(p); p -= wstep; }
 #pragma unroll
-            for (int u = 0; u < kMsU; ++u) collect(raw[u]);
+            for (int u = 0; u < kMsUC; ++u) collect(raw[u]);
         }
         for (; i > 0; --i) {
             collect(ms_ld(p));
