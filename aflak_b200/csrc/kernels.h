@@ -205,12 +205,14 @@ struct StatParams {
 struct StatState {    // device-resident state of one radix select; zero-initialised
     unsigned prefix, mask;
     unsigned long long kth, n, eq_count;
-    unsigned next_key;
+    unsigned above_min;   // smallest key above the 16-bit bucket of the answer; initialise to 0xFFFFFFFF
+    unsigned cand_count;  // keys copied to the candidate buffer (> capacity: the buffer is incomplete)
+    unsigned ticket;      // CTAs that finished the current pass
     int even, error;
     float result;
 };
 cudaError_t stat_select_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, unsigned *hist,
-                               int sm_count, cudaStream_t s);
+                               unsigned *cand, unsigned cand_cap, int sm_count, cudaStream_t s);
 cudaError_t zsample_launch(const float *img, int64_t ny, int64_t nx, int64_t stride, int64_t rows_s, int64_t cols_s, float *out,
                            cudaStream_t s);
 

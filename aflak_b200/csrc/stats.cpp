@@ -51,17 +51,24 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
     cudaStream_t s;
     int dev;
     if (Error e = stats_ctx(img, &s, &dev)) return e;
-    // two select states + one histogram, zeroed
-    const size_t bytes = 2 * sizeof(StatState) + 256 * sizeof(unsigned);
+    // two select states + one histogram (initialised from the host) + the candidate buffer the two selections share
+    const size_t head = 2 * sizeof(StatState) + 256 * sizeof(unsigned);
+    const int64_t n = img->len();
+    const unsigned cand_cap = (unsigned)(n < (int64_t(1) << 22) ? n : (int64_t(1) << 22)); // 4 Mi keys: 25 % of a 4096^2 image in one 16-bit bucket
     char *d = nullptr;
-    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), bytes, s));
+    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), head + (size_t)cand_cap * sizeof(unsigned), s));
     StatState *st = reinterpret_cast<StatState *>(d);
     unsigned *hist = reinterpret_cast<unsigned *>(d + 2 * sizeof(StatState));
-    cudaError_t ce = cudaMemsetAsync(d, 0, bytes, s);
+    unsigned *cand = reinterpret_cast<unsigned *>(d + head);
+    struct { StatState st[2]; unsigned hist[256]; } init;
+    memset(&init, 0, sizeof init);
+    init.st[0].above_min = init.st[1].above_min = 0xFFFFFFFFu;
+    static_assert(sizeof init == 2 * sizeof(StatState) + 256 * sizeof(unsigned), "layout");
+    cudaError_t ce = cudaMemcpyAsync(d, &init, sizeof init, cudaMemcpyHostToDevice, s); // pageable source: staged before the call returns
     StatParams p{vmin, vmax, 0};
-    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, img->len(), p, nullptr, &st[0], hist, sm_count(dev), s);
+    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, n, p, nullptr, &st[0], hist, cand, cand_cap, sm_count(dev), s);
     p.use_vmed = 1;
-    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, img->len(), p, &st[0], &st[1], hist, sm_count(dev), s);
+    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, n, p, &st[0], &st[1], hist, cand, cand_cap, sm_count(dev), s);
     StatState h[2];
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, st, sizeof h, cudaMemcpyDeviceToHost, s);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);

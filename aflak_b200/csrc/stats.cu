@@ -115,48 +115,19 @@ __device__ __forceinline__ bool stat_value(float v, const StatParams &p, float v
     return true;
 }
 
-__global__ void __launch_bounds__(256) stat_hist_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
-                                                         const StatState *state, unsigned *hist, int shift) {
-    __shared__ unsigned s_hist[kHistWarps][256];
-    for (int i = threadIdx.x; i < kHistWarps * 256; i += blockDim.x) (&s_hist[0][0])[i] = 0u;
-    __syncthreads();
-    if (state->error) return;
-    unsigned *my = s_hist[threadIdx.x >> 5];
-    const unsigned prefix = state->prefix, mask = state->mask;
-    const float vmed = p.use_vmed ? prev->result : 0.0f;
-    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
-    RunCounter rc;
-    auto one = [&](float v) {
-        unsigned key;
-        if (stat_value(v, p, vmed, &key) && (key & mask) == prefix) rc.add((key >> shift) & 255u, my);
-    };
-    int64_t done = 0;
-    if ((reinterpret_cast<uintptr_t>(img) & 15u) == 0) {
-        const int64_t n4 = n >> 2;
-        for (int64_t i = tid; i < n4; i += nthreads) {
-            const float4 v = st_ld(reinterpret_cast<const float4 *>(img) + i);
-            one(v.x); one(v.y); one(v.z); one(v.w);
-        }
-        done = n4 << 2;
-    }
-    for (int64_t i = done + tid; i < n; i += nthreads) one(img[i]);
-    rc.flush(my);
-    __syncthreads();
-    for (int b = threadIdx.x; b < 256; b += blockDim.x) {
-        unsigned t = 0u;
-#pragma unroll
-        for (int w = 0; w < kHistWarps; ++w) t += s_hist[w][b];
-        if (t) atomicAdd(&hist[b], t);
-    }
-}
+// Radix select, 8 bits per pass, most significant digit first.  Three passes read the image (digits 31..24, 23..16,
+// 15..8); the third also copies the keys that share the 16-bit prefix found so far -- about 1 % of a typical image -- to a
+// candidate buffer and tracks the smallest key above that bucket, so the last digit, the even-count successor and the final
+// value come from one small single-CTA kernel over the candidates instead of two more passes over the image.  The bin
+// pick that follows each histogram is done by the last CTA to finish (ticket), not by a separate launch.
+// 4 launches and 3 image passes per statistic (were 10 and 5).
 
 // one warp: find the bin holding rank kth among the candidates, narrow the prefix, clear the histogram for the next pass
-__global__ void stat_pick_kernel(StatState *state, unsigned *hist, int shift) {
-    const int lane = threadIdx.x;
+template <bool GLOBAL> __device__ __forceinline__ void stat_pick(StatState *state, unsigned *hist, int shift, int lane) {
     if (state->error) return;
     unsigned long long c[8], tot = 0ull;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { c[j] = hist[lane * 8 + j]; tot += c[j]; }
+    for (int j = 0; j < 8; ++j) { c[j] = GLOBAL ? __ldcg(&hist[lane * 8 + j]) : hist[lane * 8 + j]; tot += c[j]; }
     unsigned long long incl = tot;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -167,11 +138,12 @@ __global__ void stat_pick_kernel(StatState *state, unsigned *hist, int shift) {
     unsigned long long kth = state->kth;
     if (shift == 24) { // first pass: the candidates are all the kept values
         if (total == 0ull) {
+            __syncwarp();
             if (lane == 0) state->error = 1; // "Empty data!" (lims.rs:53, 92)
             return;
         }
         const int even = (total % 2ull) == 0ull;
-        kth = even ? total / 2ull - 1ull : total / 2ull; // data[mid - 1] (then data[mid] via `next`) or data[mid]
+        kth = even ? total / 2ull - 1ull : total / 2ull; // data[mid - 1] (then data[mid] via the successor) or data[mid]
         if (lane == 0) { state->n = total; state->even = even; }
     }
     unsigned long long excl = incl - tot;
@@ -189,57 +161,178 @@ __global__ void stat_pick_kernel(StatState *state, unsigned *hist, int shift) {
     cnt = __shfl_sync(0xffffffffu, cnt, src);
 #pragma unroll
     for (int j = 0; j < 8; ++j) hist[lane * 8 + j] = 0u;
+    __syncwarp(); // every lane has read the old state
     if (lane == 0) {
         state->kth = kth - below;
         state->eq_count = cnt;
         state->prefix |= (unsigned)digit << shift;
         state->mask |= 255u << shift;
-        state->next_key = 0xFFFFFFFFu;
     }
 }
 
-// even count: the upper middle element is the same key when the equal run continues, else the smallest key above it
-__global__ void __launch_bounds__(256) stat_next_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
-                                                         StatState *state) {
-    if (state->error || !state->even || state->kth + 1ull < state->eq_count) return;
-    const unsigned lo = state->prefix;
+constexpr int kStatCandSmem = 4096; // candidates a CTA stages before one reservation in the global buffer
+
+// SHIFT = 24, 16: histogram of the next digit among the keys that match the prefix.  SHIFT = 8: also the candidate copy.
+template <int SHIFT>
+__global__ void __launch_bounds__(256) stat_pass_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
+                                                         StatState *state, unsigned *hist, unsigned *cand, unsigned cand_cap) {
+    __shared__ unsigned s_hist[kHistWarps][256];
+    __shared__ unsigned s_cand[SHIFT == 8 ? kStatCandSmem : 1];
+    __shared__ unsigned s_ccount, s_base, s_last;
+    for (int i = threadIdx.x; i < kHistWarps * 256; i += blockDim.x) (&s_hist[0][0])[i] = 0u;
+    if (threadIdx.x == 0) s_ccount = 0u;
+    __syncthreads();
+    // state->error only changes in the pick of the first pass, which every CTA of the later passes sees complete
+    if (SHIFT != 24 && state->error) return;
+    unsigned *my = s_hist[threadIdx.x >> 5];
+    const unsigned prefix = state->prefix, mask = state->mask;
     const float vmed = p.use_vmed ? prev->result : 0.0f;
-    unsigned m = 0xFFFFFFFFu;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
+    RunCounter rc;
+    unsigned above = 0xFFFFFFFFu;
+    auto one = [&](float v) {
         unsigned key;
-        if (stat_value(img[i], p, vmed, &key) && key > lo && key < m) m = key;
+        if (!stat_value(v, p, vmed, &key)) return;
+        if ((key & mask) == prefix) {
+            rc.add((key >> SHIFT) & 255u, my);
+            if (SHIFT == 8) {
+                const unsigned slot = atomicAdd(&s_ccount, 1u);
+                if (slot < (unsigned)kStatCandSmem) {
+                    s_cand[slot] = key;
+                } else { // a CTA with more candidates than it can stage (long runs of equal values): straight to the buffer
+                    const unsigned at = atomicAdd(&state->cand_count, 1u);
+                    if (at < cand_cap) cand[at] = key;
+                }
+            }
+        } else if (SHIFT == 8 && key > (prefix | 0x0000FFFFu)) {
+            above = min(above, key); // smallest key above the bucket: the successor when the bucket ends at the median
+        }
+    };
+    int64_t done = 0;
+    if ((reinterpret_cast<uintptr_t>(img) & 15u) == 0) {
+        const int64_t n4 = n >> 2;
+        const float4 *src = reinterpret_cast<const float4 *>(img);
+        int64_t i = tid;
+        // four 16-byte loads in flight per thread: with one, 32 resident warps per SM keep only 16 KB in flight and the pass
+        // runs at the latency of L2, not at its bandwidth
+        for (; i + 3 * nthreads < n4; i += 4 * nthreads) {
+            const float4 v0 = st_ld(src + i), v1 = st_ld(src + i + nthreads), v2 = st_ld(src + i + 2 * nthreads), v3 = st_ld(src + i + 3 * nthreads);
+            one(v0.x); one(v0.y); one(v0.z); one(v0.w);
+            one(v1.x); one(v1.y); one(v1.z); one(v1.w);
+            one(v2.x); one(v2.y); one(v2.z); one(v2.w);
+            one(v3.x); one(v3.y); one(v3.z); one(v3.w);
+        }
+        for (; i < n4; i += nthreads) {
+            const float4 v = st_ld(src + i);
+            one(v.x); one(v.y); one(v.z); one(v.w);
+        }
+        done = n4 << 2;
     }
+    for (int64_t i = done + tid; i < n; i += nthreads) one(img[i]);
+    rc.flush(my);
+    if (SHIFT == 8) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((threadIdx.x & 31) == 0 && m != 0xFFFFFFFFu) atomicMin(&state->next_key, m);
+        for (int o = 16; o > 0; o >>= 1) above = min(above, __shfl_xor_sync(0xffffffffu, above, o));
+        if ((threadIdx.x & 31) == 0 && above != 0xFFFFFFFFu) atomicMin(&state->above_min, above);
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < 256; b += blockDim.x) {
+        unsigned t = 0u;
+#pragma unroll
+        for (int w = 0; w < kHistWarps; ++w) t += s_hist[w][b];
+        if (t) atomicAdd(&hist[b], t);
+    }
+    if (SHIFT == 8) {
+        const unsigned staged = min(s_ccount, (unsigned)kStatCandSmem);
+        if (threadIdx.x == 0) s_base = staged ? atomicAdd(&state->cand_count, staged) : 0u;
+        __syncthreads();
+        const unsigned base = s_base;
+        for (unsigned t = threadIdx.x; t < staged; t += blockDim.x)
+            if (base + t < cand_cap) cand[base + t] = s_cand[t]; // past the cap: cand_count > cand_cap tells the last kernel to rescan the image
+    }
+    // the last CTA to get here picks the bin
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&state->ticket, 1u) == gridDim.x - 1u ? 1u : 0u;
+    __syncthreads();
+    if (s_last && threadIdx.x < 32) {
+        __threadfence();
+        stat_pick<true>(state, hist, SHIFT, threadIdx.x);
+        if (threadIdx.x == 0) state->ticket = 0u;
+    }
 }
 
-__global__ void stat_final_kernel(StatState *state) {
+// Last digit, even-count successor and the value, over the candidate buffer (or, when the bucket outgrew the buffer --
+// millions of keys sharing 16 bits, e.g. an image that is half zeros -- over the image again; slower, same answer).
+__global__ void __launch_bounds__(1024) stat_finish_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
+                                                            StatState *state, const unsigned *__restrict__ cand, unsigned cand_cap) {
+    __shared__ unsigned s_hist[256];
+    __shared__ unsigned s_min[32];
     if (state->error) {
-        state->result = __int_as_float(0x7fc00000);
+        if (threadIdx.x == 0) state->result = __int_as_float(0x7fc00000);
         return;
     }
-    const float lo = st_unkey(state->prefix);
-    if (!state->even) { state->result = lo; return; }
-    const float hi = (state->kth + 1ull < state->eq_count) ? lo : st_unkey(state->next_key);
-    state->result = __fdiv_rn(__fadd_rn(hi, lo), 2.0f); // (data[mid] + data[mid - 1]) / 2.0
+    if (threadIdx.x < 256) s_hist[threadIdx.x] = 0u;
+    __syncthreads();
+    const unsigned count = state->cand_count;
+    const bool rescan = count > cand_cap;
+    const int64_t items = rescan ? n : (int64_t)count;
+    const float vmed = p.use_vmed ? prev->result : 0.0f;
+    const unsigned bucket = state->prefix & 0xFFFF0000u;
+    auto key_at = [&](int64_t i, unsigned *key) -> bool {
+        if (!rescan) { *key = cand[i]; return true; }
+        return stat_value(img[i], p, vmed, key) && (*key & 0xFFFF0000u) == bucket;
+    };
+    {
+        const unsigned prefix = state->prefix, mask = state->mask; // 24 bits
+        for (int64_t i = threadIdx.x; i < items; i += blockDim.x) {
+            unsigned key;
+            if (key_at(i, &key) && (key & mask) == prefix) atomicAdd(&s_hist[key & 255u], 1u);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) stat_pick<false>(state, s_hist, 0, threadIdx.x);
+    __syncthreads();
+    const unsigned lo = state->prefix; // the key of data[mid - 1] (even count) or data[mid]
+    float result = st_unkey(lo);
+    if (state->even) { // (data[mid] + data[mid - 1]) / 2.0: the same key when the run of equal keys continues, else the successor
+        unsigned hi = lo;
+        if (!(state->kth + 1ull < state->eq_count)) {
+            unsigned m = 0xFFFFFFFFu;
+            for (int64_t i = threadIdx.x; i < items; i += blockDim.x) {
+                unsigned key;
+                if (key_at(i, &key) && key > lo && key < m) m = key;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if ((threadIdx.x & 31) == 0) s_min[threadIdx.x >> 5] = m;
+            __syncthreads();
+            if (threadIdx.x < 32) {
+                m = s_min[threadIdx.x];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+                hi = min(m, state->above_min); // nothing above it in the bucket: the smallest key of the buckets above
+            }
+        }
+        result = __fdiv_rn(__fadd_rn(st_unkey(hi), st_unkey(lo)), 2.0f);
+    }
+    if (threadIdx.x == 0) state->result = result;
 }
 
-// Enqueues the whole selection for one statistic; `state` must be zero-initialised, `hist` 256 zeroed words.
+// Enqueues the whole selection for one statistic; `state` must be zero-initialised except above_min = 0xFFFFFFFF,
+// `hist` 256 zeroed words, `cand` a buffer of cand_cap keys.
 cudaError_t stat_select_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, unsigned *hist,
-                               int sm_count, cudaStream_t s) {
+                               unsigned *cand, unsigned cand_cap, int sm_count, cudaStream_t s) {
     int64_t need = ((n + 3) / 4 + 255) / 256;
     const int64_t cap = (int64_t)sm_count * 4;
     const int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
-    for (int shift = 24; shift >= 0; shift -= 8) {
-        stat_hist_kernel<<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, shift);
-        count_launch();
-        stat_pick_kernel<<<1, 32, 0, s>>>(state, hist, shift);
-        count_launch();
-    }
-    stat_next_kernel<<<grid, 256, 0, s>>>(img, n, p, prev, state);
+    stat_pass_kernel<24><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
     count_launch();
-    stat_final_kernel<<<1, 1, 0, s>>>(state);
+    stat_pass_kernel<16><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+    count_launch();
+    stat_pass_kernel<8><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+    count_launch();
+    stat_finish_kernel<<<1, 1024, 0, s>>>(img, n, p, prev, state, cand, cand_cap);
     count_launch();
     return cudaGetLastError();
 }
