@@ -201,6 +201,7 @@ cudaError_t histogram_launch(const float *img, int64_t n_per_channel, int channe
 struct StatParams {
     float vmin, vmax; // d = (v - vmin) / (vmax - vmin)
     int use_vmed;     // select over |d - vmed| with vmed read from the previous statistic's state (lims.rs:87)
+    int raw;          // select over the pixel values themselves and normalise the answer (see stat_value); never with use_vmed
 };
 struct StatState {    // device-resident state of one radix select; zero-initialised
     unsigned prefix, mask;

@@ -65,9 +65,12 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
     init.st[0].above_min = init.st[1].above_min = 0xFFFFFFFFu;
     static_assert(sizeof init == 2 * sizeof(StatState) + 256 * sizeof(unsigned), "layout");
     cudaError_t ce = cudaMemcpyAsync(d, &init, sizeof init, cudaMemcpyHostToDevice, s); // pageable source: staged before the call returns
-    StatParams p{vmin, vmax, 0};
+    StatParams p{vmin, vmax, 0, 0};
+    // the median of the normalised values is the normalised median pixel when normalisation is monotone and drops nothing but NaN
+    p.raw = std::isfinite(vmin) && std::isfinite(vmax) && std::isfinite(vmax - vmin) && vmax > vmin;
     if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, n, p, nullptr, &st[0], hist, cand, cand_cap, sm_count(dev), s);
     p.use_vmed = 1;
+    p.raw = 0;
     if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, n, p, &st[0], &st[1], hist, cand, cand_cap, sm_count(dev), s);
     StatState h[2];
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, st, sizeof h, cudaMemcpyDeviceToHost, s);

@@ -107,8 +107,20 @@ __device__ __forceinline__ float st_unkey(unsigned k) {
 
 // the value the reference pushes into `data` before sorting: d = (v - vmin) / (vmax - vmin) (lims.rs:48), or
 // |d - vmed| (lims.rs:87); kept only when neither NaN nor infinite
+// p.raw: d is a monotone function of v (two IEEE operations with a positive divisor), so sorting d is sorting v and
+// data[i] = d(v_sorted[i]); when vmin, vmax and vmax - vmin are finite and vmax > vmin (checked on the host) every
+// non-NaN pixel gives a finite d in [0, 1] and is kept.  The selection then runs on the keys of v -- no division per pixel
+// and pass -- and stat_finish_kernel normalises the one or two pixels it ends on.
+__device__ __forceinline__ float stat_normalise(float v, const StatParams &p) {
+    return __fdiv_rn(__fsub_rn(v, p.vmin), __fsub_rn(p.vmax, p.vmin));
+}
 __device__ __forceinline__ bool stat_value(float v, const StatParams &p, float vmed, unsigned *key) {
-    float d = __fdiv_rn(__fsub_rn(v, p.vmin), __fsub_rn(p.vmax, p.vmin));
+    if (p.raw) {
+        if (v != v) return false;
+        *key = st_key(v);
+        return true;
+    }
+    float d = stat_normalise(v, p);
     if (p.use_vmed) d = fabsf(__fsub_rn(d, vmed));
     if (!(fabsf(d) < __int_as_float(0x7f800000))) return false; // NaN or +-Inf
     *key = st_key(d);
@@ -285,7 +297,18 @@ __global__ void __launch_bounds__(1024) stat_finish_kernel(const float *__restri
     };
     {
         const unsigned prefix = state->prefix, mask = state->mask; // 24 bits
-        for (int64_t i = threadIdx.x; i < items; i += blockDim.x) {
+        int64_t i = threadIdx.x;
+        if (!rescan) { // one CTA: its speed is the number of loads it keeps in flight
+            for (; i + 7 * blockDim.x < items; i += 8 * blockDim.x) {
+                unsigned k8[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) k8[u] = __ldg(cand + i + u * blockDim.x);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if ((k8[u] & mask) == prefix) atomicAdd(&s_hist[k8[u] & 255u], 1u);
+            }
+        }
+        for (; i < items; i += blockDim.x) {
             unsigned key;
             if (key_at(i, &key) && (key & mask) == prefix) atomicAdd(&s_hist[key & 255u], 1u);
         }
@@ -295,11 +318,23 @@ __global__ void __launch_bounds__(1024) stat_finish_kernel(const float *__restri
     __syncthreads();
     const unsigned lo = state->prefix; // the key of data[mid - 1] (even count) or data[mid]
     float result = st_unkey(lo);
+    if (p.raw) result = stat_normalise(result, p);
     if (state->even) { // (data[mid] + data[mid - 1]) / 2.0: the same key when the run of equal keys continues, else the successor
         unsigned hi = lo;
         if (!(state->kth + 1ull < state->eq_count)) {
             unsigned m = 0xFFFFFFFFu;
-            for (int64_t i = threadIdx.x; i < items; i += blockDim.x) {
+            int64_t i = threadIdx.x;
+            if (!rescan) {
+                for (; i + 7 * blockDim.x < items; i += 8 * blockDim.x) {
+                    unsigned k8[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) k8[u] = __ldg(cand + i + u * blockDim.x);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (k8[u] > lo && k8[u] < m) m = k8[u];
+                }
+            }
+            for (; i < items; i += blockDim.x) {
                 unsigned key;
                 if (key_at(i, &key) && key > lo && key < m) m = key;
             }
@@ -314,7 +349,9 @@ __global__ void __launch_bounds__(1024) stat_finish_kernel(const float *__restri
                 hi = min(m, state->above_min); // nothing above it in the bucket: the smallest key of the buckets above
             }
         }
-        result = __fdiv_rn(__fadd_rn(st_unkey(hi), st_unkey(lo)), 2.0f);
+        float a = st_unkey(hi), b = st_unkey(lo);
+        if (p.raw) { a = stat_normalise(a, p); b = stat_normalise(b, p); }
+        result = __fdiv_rn(__fadd_rn(a, b), 2.0f);
     }
     if (threadIdx.x == 0) state->result = result;
 }
