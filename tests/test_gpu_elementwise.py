@@ -116,7 +116,9 @@ def test_logscale_log10_multiplier_within_2ulp(gpu, orc, shape):
     for a, b in [(1.0, 1.0), (2.0, 0.0), (0.0, -1.0), (-1.0, 2.0), (2.0, 2.0), (1.0, 0.5), (-1.0, -1.0)]:
         for x, y, dx, dy in ((u, v, du, dv), (p, q, dp, dq)):
             assert_ulp(gpu.call("image_multiplier", dx, dy, a, b).download(), orc.image_multiplier(x, y, a, b), 4, f"multiplier {a},{b}")
-    assert_bit_equal(gpu.call("image_multiplier", dp, dq, 1.0, 1.0).download(), (p * q).astype(np.float32), "u^1 v^1 is the plain product")
+    with np.errstate(all="ignore"):  # Inf * 0 and overflow are part of the case
+        plain = (p * q).astype(np.float32)
+    assert_bit_equal(gpu.call("image_multiplier", dp, dq, 1.0, 1.0).download(), plain, "u^1 v^1 is the plain product")
 
 
 def test_logscale_kat_and_nonfinite(gpu):
