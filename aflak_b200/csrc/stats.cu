@@ -46,6 +46,31 @@ struct RunCounter {
     }
 };
 
+// The same counter without branches, for the select passes (issue-bound: the branchy form costs ~25 instructions and four
+// branches per key, profiles/r1_stats_ncu_full.json).  `match` = the key takes part; a run that ends is added to its
+// bin by a predicated reduction.  Starts at (bin 0, run 0): the first break adds 0 to bin 0.
+struct RunCounterPred {
+    unsigned bin = 0u, run = 0u;
+    __device__ __forceinline__ void add_if(bool match, unsigned b, unsigned hist_saddr) {
+        const bool brk = match && b != bin;
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "setp.ne.u32 p, %0, 0;\n\t"
+            "@p red.shared.add.u32 [%1], %2;\n\t"
+            "}"
+            :
+            : "r"((unsigned)brk), "r"(hist_saddr + bin * 4u), "r"(run)
+            : "memory");
+        run = brk ? 1u : (match ? run + 1u : run);
+        bin = brk ? b : bin;
+    }
+    __device__ __forceinline__ void flush(unsigned *hist) {
+        if (run) atomicAdd(&hist[bin], run);
+        run = 0u;
+    }
+};
+
 constexpr int kHistWarps = 8;
 
 // counts: [nbins][channels] (bin-major like Vec<[Bin; 3]>), 64-bit
@@ -98,7 +123,7 @@ cudaError_t histogram_launch(const float *img, int64_t n_per_channel, int channe
 // ---- lims::get_vmed_normalized / get_vmad_normalized: exact order statistics by radix select ---------------------------
 __device__ __forceinline__ unsigned st_key(float f) {
     const unsigned b = __float_as_uint(f);
-    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+    return b ^ ((unsigned)((int)b >> 31) | 0x80000000u); // negative: ~b, else b | sign bit -- one shift and one LOP3
 }
 __device__ __forceinline__ float st_unkey(unsigned k) {
     const unsigned b = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
@@ -185,7 +210,7 @@ template <bool GLOBAL> __device__ __forceinline__ void stat_pick(StatState *stat
 constexpr int kStatCandSmem = 4096; // candidates a CTA stages before one reservation in the global buffer
 
 // SHIFT = 24, 16: histogram of the next digit among the keys that match the prefix.  SHIFT = 8: also the candidate copy.
-template <int SHIFT>
+template <int SHIFT, bool RAW>
 __global__ void __launch_bounds__(256) stat_pass_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
                                                          StatState *state, unsigned *hist, unsigned *cand, unsigned cand_cap) {
     __shared__ unsigned s_hist[kHistWarps][256];
@@ -200,14 +225,22 @@ __global__ void __launch_bounds__(256) stat_pass_kernel(const float *__restrict_
     const unsigned prefix = state->prefix, mask = state->mask;
     const float vmed = p.use_vmed ? prev->result : 0.0f;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
-    RunCounter rc;
+    RunCounterPred rc;
+    const unsigned my_saddr = (unsigned)__cvta_generic_to_shared(my);
     unsigned above = 0xFFFFFFFFu;
     auto one = [&](float v) {
-        unsigned key;
-        if (!stat_value(v, p, vmed, &key)) return;
-        if ((key & mask) == prefix) {
-            rc.add((key >> SHIFT) & 255u, my);
-            if (SHIFT == 8) {
+        unsigned key = 0u;
+        bool kept;
+        if (RAW) { // compile-time copy of stat_value's raw branch
+            kept = !(v != v);
+            key = st_key(v);
+        } else {
+            kept = stat_value(v, p, vmed, &key);
+        }
+        const bool match = kept && (key & mask) == prefix;
+        rc.add_if(match, (key >> SHIFT) & 255u, my_saddr);
+        if (SHIFT == 8) {
+            if (match) { // ~1 % of the keys
                 const unsigned slot = atomicAdd(&s_ccount, 1u);
                 if (slot < (unsigned)kStatCandSmem) {
                     s_cand[slot] = key;
@@ -215,9 +248,9 @@ __global__ void __launch_bounds__(256) stat_pass_kernel(const float *__restrict_
                     const unsigned at = atomicAdd(&state->cand_count, 1u);
                     if (at < cand_cap) cand[at] = key;
                 }
+            } else if (kept && key > (prefix | 0x0000FFFFu)) {
+                above = min(above, key); // smallest key above the bucket: the successor when the bucket ends at the median
             }
-        } else if (SHIFT == 8 && key > (prefix | 0x0000FFFFu)) {
-            above = min(above, key); // smallest key above the bucket: the successor when the bucket ends at the median
         }
     };
     int64_t done = 0;
@@ -363,11 +396,17 @@ cudaError_t stat_select_launch(const float *img, int64_t n, const StatParams &p,
     int64_t need = ((n + 3) / 4 + 255) / 256;
     const int64_t cap = (int64_t)sm_count * 4;
     const int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
-    stat_pass_kernel<24><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+    if (p.raw) {
+        stat_pass_kernel<24, true><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+        stat_pass_kernel<16, true><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+        stat_pass_kernel<8, true><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+    } else {
+        stat_pass_kernel<24, false><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+        stat_pass_kernel<16, false><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+        stat_pass_kernel<8, false><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
+    }
     count_launch();
-    stat_pass_kernel<16><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
     count_launch();
-    stat_pass_kernel<8><<<grid, 256, 0, s>>>(img, n, p, prev, state, hist, cand, cand_cap);
     count_launch();
     stat_finish_kernel<<<1, 1024, 0, s>>>(img, n, p, prev, state, cand, cand_cap);
     count_launch();
