@@ -84,20 +84,21 @@ __global__ void __launch_bounds__(256) histogram_kernel(const float *__restrict_
     const int c = blockIdx.y;
     const float *src = img + (size_t)c * n_per_channel;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
-    RunCounter rc;
+    RunCounterPred rc;
+    const unsigned my_saddr = (unsigned)__cvta_generic_to_shared(my);
     int64_t done = 0;
     if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
         const int64_t n4 = n_per_channel >> 2;
         for (int64_t i = tid; i < n4; i += nthreads) {
             const float4 v = st_ld(reinterpret_cast<const float4 *>(src) + i);
-            rc.add(hist_bin(v.x, mn, range, nb_f, nb), my);
-            rc.add(hist_bin(v.y, mn, range, nb_f, nb), my);
-            rc.add(hist_bin(v.z, mn, range, nb_f, nb), my);
-            rc.add(hist_bin(v.w, mn, range, nb_f, nb), my);
+            rc.add_if(true, hist_bin(v.x, mn, range, nb_f, nb), my_saddr);
+            rc.add_if(true, hist_bin(v.y, mn, range, nb_f, nb), my_saddr);
+            rc.add_if(true, hist_bin(v.z, mn, range, nb_f, nb), my_saddr);
+            rc.add_if(true, hist_bin(v.w, mn, range, nb_f, nb), my_saddr);
         }
         done = n4 << 2;
     }
-    for (int64_t i = done + tid; i < n_per_channel; i += nthreads) rc.add(hist_bin(src[i], mn, range, nb_f, nb), my);
+    for (int64_t i = done + tid; i < n_per_channel; i += nthreads) rc.add_if(true, hist_bin(src[i], mn, range, nb_f, nb), my_saddr);
     rc.flush(my);
     __syncthreads();
     for (unsigned b = threadIdx.x; b < nb; b += blockDim.x) {
