@@ -800,6 +800,23 @@ __device__ __forceinline__ unsigned ms_ld(const float *p) {
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
     return r;
 }
+// L2 eviction priorities (a 32-bit load takes them through a cache-hint policy): the count pass marks its lines
+// evict_last -- the collect pass reads them again -- and the collect pass evict_first: last use.
+__device__ __forceinline__ uint64_t ms_policy_keep() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t ms_policy_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ unsigned ms_ld_hint(const float *p, uint64_t pol) {
+    unsigned r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(r) : "l"(p), "l"(pol));
+    return r;
+}
 __device__ __forceinline__ unsigned ms_key(unsigned b) { return b ^ ((unsigned)((int)b >> 31) | 0x80000000u); } // == med_key, 2 instructions
 
 // c += (key < pivot) as compare + predicated add: two instructions (the C form compiles to three)
@@ -937,12 +954,13 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
         // ---- B: count (full blocks of kMsU frames unchecked, then the tail) ----
         const size_t wstep = (size_t)kMsWarps * a.n2; // elements between two frames of this warp
         {
+            const uint64_t pol_keep = ms_policy_keep();
             const float *p = col + (size_t)g * a.n2;
             int k = g;
             for (; k + (kMsU - 1) * kMsWarps < n; k += kMsWarps * kMsU) {
                 unsigned raw[kMsU];
 #pragma unroll
-                for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld(p); p += wstep; }
+                for (int u = 0; u < kMsU; ++u) { raw[u] = ms_ld_hint(p, pol_keep); p += wstep; }
 #pragma unroll
                 for (int u = 0; u < kMsU; ++u) {
                     const unsigned key = ms_key(raw[u]);
@@ -1031,10 +1049,11 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
         const size_t wstep = (size_t)kMsWarps * a.n2;
         int i = g < n ? (n - g + kMsWarps - 1) / kMsWarps : 0; // this warp's frames are k = g + j * kMsWarps, j < i
         const float *p = col + ((size_t)g + (size_t)(i > 0 ? i - 1 : 0) * kMsWarps) * a.n2;
+        const uint64_t pol_last = ms_policy_last();
         for (; i > kMsUC; i -= kMsUC) { // `>`: the pointer never steps below the warp's first frame
             unsigned raw[kMsUC];
 #pragma unroll
-            for (int u = 0; u < kMsUC; ++u) { raw[u] = ms_ld(p); p -= wstep; }
+            for (int u = 0; u < kMsUC; ++u) { raw[u] = ms_ld_hint(p, pol_last); p -= wstep; }
 #pragma unroll
             for (int u = 0; u < kMsUC; ++u) collect(raw[u]);
         }
