@@ -520,7 +520,11 @@ static cudaError_t reduce_dispatch_nw(const ReduceKArgs &k, int grid, cudaStream
 
 template <int VEC, bool COMP>
 static cudaError_t reduce_dispatch_tune(const ReduceKArgs &k, int grid, int kg, cudaStream_t s) {
-    if (kg > 1) return reduce_dispatch_nw<VEC, COMP, 8, kReduceKgCtasPerSm, kReduceKGroups>(k, grid, s);
+    if (kg > 1) { // small images are latency-bound: AFK_REDUCE_KG_UNROLL=16 doubles the loads a warp keeps in flight
+        static const int ukg = env_int("AFK_REDUCE_KG_UNROLL", 8);
+        if (ukg == 16) return reduce_dispatch_nw<VEC, COMP, 16, kReduceKgCtasPerSm, kReduceKGroups>(k, grid, s);
+        return reduce_dispatch_nw<VEC, COMP, 8, kReduceKgCtasPerSm, kReduceKGroups>(k, grid, s);
+    }
     const int u = reduce_tune_unroll(), c = reduce_tune_ctas();
 #define AFK_TUNE(U_, C_) if (u == U_ && c == C_) return reduce_dispatch_nw<VEC, COMP, U_, C_>(k, grid, s)
     AFK_TUNE(8, 4); AFK_TUNE(8, 2); AFK_TUNE(16, 2); AFK_TUNE(16, 3);
