@@ -34,6 +34,7 @@ OK, ERR_IO, ERR_RAWLOADER, ERR_FITS, ERR_UNEXPECTED_INPUT, ERR_SHAPE, ERR_CUDA, 
 (T_INTEGER, T_FLOAT, T_FLOAT2, T_FLOAT3, T_FLOAT3X3, T_STR, T_BOOL, T_FITS, T_IMAGE, T_MAP2DTO3DCOORDS, T_ROI, T_PATHS,
  T_TONECURVE) = range(13)
 SUM_COMPENSATED, SUM_SEQUENTIAL = 0, 1
+SUM_INHERIT = -1
 EPI_SUM, EPI_MEAN, EPI_MEAN_RATIO, EPI_EW = 0, 1, 2, 3
 
 
@@ -169,6 +170,8 @@ _sig("afk_get_transform", C.POINTER(afk_transform_desc), C.c_char_p)
 _sig("afk_transform_call", C.c_int, C.POINTER(afk_transform_desc), C.POINTER(C.c_void_p), C.c_size_t, C.POINTER(afk_result), C.c_size_t)
 _sig("afk_set_sum_mode", C.c_int, C.c_int)
 _sig("afk_get_sum_mode", C.c_int)
+_sig("afk_set_default_sum_mode", C.c_int, C.c_int)
+_sig("afk_trim_pools", C.c_int)
 _sig("afk_fused_logscale_minmax", C.c_int, _P, C.c_float, C.POINTER(C.c_void_p))
 _sig("afk_fused_average_ratio", C.c_int, _P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_void_p))
 _sig("afk_fused_equivalent_width", C.c_int, _P, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
@@ -251,7 +254,20 @@ def launch_count():
 
 
 def set_sum_mode(mode):
+    """Per-thread override of the process-wide default; SUM_INHERIT (-1) removes it."""
     _check(lib.afk_set_sum_mode(mode))
+
+
+def set_default_sum_mode(mode):
+    _check(lib.afk_set_default_sum_mode(mode))
+
+
+def get_sum_mode():
+    return int(lib.afk_get_sum_mode())
+
+
+def trim_pools():
+    _check(lib.afk_trim_pools())
 
 
 def type_name(t):
@@ -669,12 +685,21 @@ def fused_equivalent_width(cube, on, off1, off2, fl, vmax, is_emission, want_min
     return (img, (np.float32(mm[0]), np.float32(mm[1]))) if want_minmax else img
 
 
+def _reduce_params(epilogue, params):
+    """EPI_EW takes exactly (a, b, fl, max, sign); the other epilogues read no params."""
+    if epilogue != EPI_EW:
+        return None
+    if params is None or len(params) != 5:
+        raise ValueError("the equivalent-width epilogue needs exactly 5 params: a, b, fl, max, sign")
+    return (C.c_float * 5)(*params)
+
+
 def k_reduce(cube_ptr, nz, n2, windows, epilogue, out_ptr, params=None, sum_mode=SUM_COMPENSATED):
     """Raw kernel layer: device pointers in, launch on this thread's stream."""
     n = len(windows)
     st = (C.c_int64 * n)(*[w[0] for w in windows])
     en = (C.c_int64 * n)(*[w[1] for w in windows])
-    pr = (C.c_float * 5)(*(list(params) + [0.0] * 5)[:5]) if params is not None else None
+    pr = _reduce_params(epilogue, params)
     _check(lib.afk_k_reduce(C.c_void_p(cube_ptr), nz, n2, n, st, en, epilogue, pr, sum_mode, C.c_void_p(out_ptr)))
 
 
@@ -725,7 +750,7 @@ class Gather:
         n = len(windows)
         st = (C.c_int64 * n)(*[w[0] for w in windows])
         en = (C.c_int64 * n)(*[w[1] for w in windows])
-        pr = (C.c_float * 5)(*(list(params) + [0.0] * 5)[:5]) if params is not None else None
+        pr = _reduce_params(epilogue, params)
         _check(lib.afk_gather_reduce(self._h, C.c_void_p(band_cube_ptr), nz, n, st, en, epilogue, pr, sum_mode))
 
     def wait(self, timeout_s=5.0):

@@ -178,15 +178,27 @@ static Error parse_file(afk_fits *f) {
             int64_t n = 0;
             if (!hdu_int(h, fmt("NAXIS%lld", (long long)a).c_str(), &n) || n < 0) return make_error(AFK_ERR_FITS, "Header without a valid NAXISn");
             h.naxis.push_back(n);
-            count *= n;
+            if (__builtin_mul_overflow(count, n, &count)) return make_error(AFK_ERR_FITS, "Header whose NAXISn product overflows");
         }
+        if (bitpix != 8 && bitpix != 16 && bitpix != 32 && bitpix != 64 && bitpix != -32 && bitpix != -64)
+            return make_error(AFK_ERR_FITS, "Header with an invalid BITPIX");
         int64_t pcount = 0, gcount = 1;
         hdu_int(h, "PCOUNT", &pcount);
         hdu_int(h, "GCOUNT", &gcount);
+        if (pcount < 0 || gcount < 1) return make_error(AFK_ERR_FITS, "Header with a negative PCOUNT or a GCOUNT below 1");
         h.data_offset = off;
-        h.data_bytes = (std::llabs(bitpix) / 8) * gcount * (pcount + count);
-        off += (h.data_bytes + 2879) / 2880 * 2880;
+        // data unit size = |BITPIX|/8 * GCOUNT * (PCOUNT + NAXIS1*...*NAXISn), checked: the header is untrusted input
+        int64_t elems = 0, bytes = 0, padded = 0;
+        if (__builtin_add_overflow(pcount, count, &elems) || __builtin_mul_overflow(elems, gcount, &elems) ||
+            __builtin_mul_overflow(elems, std::llabs(bitpix) / 8, &bytes) || __builtin_add_overflow(bytes, (int64_t)2879, &padded))
+            return make_error(AFK_ERR_FITS, "Header whose data unit size overflows");
+        padded = padded / 2880 * 2880;
+        h.data_bytes = bytes;
+        // a data unit that does not fit in the file ends the HDU list (`off` always advances, so the loop terminates)
+        const bool truncated = bytes > f->file_bytes - off;
+        off += padded;
         f->hdus.push_back(std::move(h));
+        if (truncated) break; // the header stays readable; reading the data unit fails in hdu_job (bounds check there)
     }
     if (f->hdus.empty()) return make_error(AFK_ERR_FITS, "Not a FITS file (shorter than one block)");
     return ok();

@@ -43,13 +43,14 @@ struct ThreadCtx {
     cudaStream_t own[16] = {};
     cudaStream_t external = nullptr;
     std::map<std::pair<int, cudaStream_t>, StreamScratch> scratch;
-    int sum_mode = SUM_COMPENSATED;
+    int sum_mode = SUM_INHERIT; // per-thread override of the process default (afk_set_default_sum_mode)
     bool profile = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
     uint64_t prof_launches = 0;
     std::string last_error;
 };
 ThreadCtx &tls();
+int effective_sum_mode(); // the thread's override, else the process-wide default
 // make sure a device is current and return the stream operators on this thread use
 Error current_stream(cudaStream_t *out, int *device);
 int sm_count(int device);
@@ -84,6 +85,7 @@ struct afk_image {
     size_t bytes = 0;
     bool owned = true;
     bool ipc_peer = false;
+    bool track_readers = false; // borrowed memory whose owner (afk_gather) orders its reuse after recorded readers
     afk_image *parent = nullptr; // a view keeps its parent alive
     int device = 0;
     int ndim = 0;

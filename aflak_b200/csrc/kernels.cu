@@ -425,27 +425,39 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
 }
 
 // Stream-ordered wait of the fused gather: lane i spins until flags[i] >= epoch (epochs are monotonic), with a
-// clock bound so a lost peer turns into an error word instead of a hung GPU.
-__global__ void gather_wait_kernel(const unsigned *flags, int n, unsigned epoch, long long max_cycles, unsigned *err) {
+// clock bound so a lost peer turns into an error word and a NaN band instead of a hung GPU or silently stale pixels.
+__global__ void gather_wait_kernel(const GatherWaitArgs a, long long max_cycles) {
     const int i = threadIdx.x;
-    if (i >= n) return;
-    const long long t0 = clock64();
-    for (;;) {
-        unsigned v;
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
-        if ((int)(v - epoch) >= 0) break;
-        if (clock64() - t0 > max_cycles) {
-            atomicMax(err, 1u + (unsigned)i);
-            break;
+    bool timed_out = false;
+    if (i < a.n) {
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + i) : "memory");
+            if ((int)(v - a.epoch) >= 0) break;
+            if (clock64() - t0 > max_cycles) {
+                atomicMax(a.err, 1u + (unsigned)i);
+                timed_out = true;
+                break;
+            }
+            __nanosleep(200);
         }
-        __nanosleep(200);
+    }
+    unsigned bad = __ballot_sync(0xffffffffu, timed_out);
+    while (bad) { // error path only: the whole warp poisons the band that never arrived
+        const int r = __ffs(bad) - 1;
+        bad &= bad - 1;
+        float *p = a.image + a.band_off[r];
+        for (int64_t j = i; j < a.band_len[r]; j += 32) p[j] = __int_as_float(0x7fc00000);
     }
 }
 
-cudaError_t gather_wait_launch(const unsigned *flags, int n, unsigned epoch, double timeout_s, unsigned *err, cudaStream_t s) {
-    if (n < 1 || n > 32) return cudaErrorInvalidValue;
-    const long long cycles = (long long)(timeout_s * 1.9e9);
-    gather_wait_kernel<<<1, 32, 0, s>>>(flags, n, epoch, cycles, err);
+cudaError_t gather_wait_launch(const GatherWaitArgs &a, double timeout_s, int device, cudaStream_t s) {
+    if (a.n < 1 || a.n > kMaxPeers) return cudaErrorInvalidValue;
+    int khz = 0;
+    if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device) != cudaSuccess || khz <= 0) khz = 1965000;
+    const long long cycles = (long long)(timeout_s * 1e3 * (double)khz);
+    gather_wait_kernel<<<1, 32, 0, s>>>(a, cycles);
     AFK_COUNT_LAUNCH();
     return cudaGetLastError();
 }

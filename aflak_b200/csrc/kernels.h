@@ -23,6 +23,7 @@ enum ReduceEpilogue : int {
 };
 
 enum SumMode : int {
+    SUM_INHERIT = -1,    // host layer only: no per-thread override, use the process default
     SUM_COMPENSATED = 0, // Kahan per thread, f64 combine of split-K partials (<= 1e-5 of the f64 oracle)
     SUM_SEQUENTIAL = 1,  // plain left-to-right f32 in k order, never split: bit-exact with ndarray sum_axis
 };
@@ -71,8 +72,18 @@ struct ReducePlan {
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count);
 cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &plan, const ReduceWorkspace &ws, cudaStream_t s);
 
-// stream-ordered wait until flags[i] >= epoch for i < n (n <= 32); *err gets 1+i of a flag that timed out
-cudaError_t gather_wait_launch(const unsigned *flags, int n, unsigned epoch, double timeout_s, unsigned *err, cudaStream_t s);
+// stream-ordered wait until flags[i] >= epoch for i < n (n <= kMaxPeers).  A flag that times out (bound derived from the
+// device's clock rate) sets *err to 1+i and band i of `image` is overwritten with NaN.
+struct GatherWaitArgs {
+    const unsigned *flags;
+    int n;
+    unsigned epoch;
+    unsigned *err;
+    float *image;               // this rank's copy of the full image of that epoch
+    int64_t band_off[kMaxPeers]; // element offset / length of rank i's band in it
+    int64_t band_len[kMaxPeers];
+};
+cudaError_t gather_wait_launch(const GatherWaitArgs &a, double timeout_s, int device, cudaStream_t s);
 
 // ---- other axis-0 reductions (axis0.cu) --------------------------------------------------------
 enum Axis0Op : int {

@@ -248,7 +248,7 @@ Error op_reduce(const afk_image *cube, int nwin, const int64_t *starts, const in
         a.end[w] = ends[w];
     }
     a.epilogue = epilogue;
-    a.mode = tls().sum_mode;
+    a.mode = effective_sum_mode();
     for (int i = 0; i < 4; ++i) a.p[i] = params ? params[i] : 0.0f;
     a.ew_sign = ew_sign;
     a.out = o->ptr;
@@ -886,7 +886,7 @@ static Error op_axis0(const afk_image *cube, Axis0Args a, const afk_image *m_lo,
             return e;
         }
     }
-    a.mode = tls().sum_mode;
+    a.mode = effective_sum_mode();
     a.cube = cube->ptr;
     a.n2 = cube->frame_len();
     a.nz = cube->shape[0];
@@ -1456,8 +1456,10 @@ afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, con
     }
     a.epilogue = epilogue;
     a.mode = sum_mode;
-    for (int i = 0; i < 4; ++i) a.p[i] = params ? params[i] : 0.0f;
-    a.ew_sign = params ? params[4] : 1.0f;
+    // params are read for EPI_EW only: exactly 5 floats (a, b, fl, max, sign)
+    if (epilogue == EPI_EW && !params) return fail(unexpected("the equivalent-width epilogue needs params[5] = {a, b, fl, max, sign}"));
+    for (int i = 0; i < 4; ++i) a.p[i] = epilogue == EPI_EW ? params[i] : 0.0f;
+    a.ew_sign = epilogue == EPI_EW ? params[4] : 1.0f;
     a.out = out;
     a.minmax = nullptr;
     if (n2 <= 0) return AFK_OK;

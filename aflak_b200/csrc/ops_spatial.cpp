@@ -314,7 +314,7 @@ AFK_OPX(op_extract_wave) { // lib.rs:376-383, 1147-1169
         int64_t count;
         if ((e = roi_device_offsets(in[1], ny, nx, c.dev, c.s, &whole, &doff, &count))) break;
         if ((e = image_new(1, &nz, &res))) break;
-        const int mode = tls().sum_mode;
+        const int mode = effective_sum_mode();
         cudaError_t ce = cudaSuccess;
         if (count == 0 || (!whole && !doff)) {
             ce = cudaMemsetAsync(res->ptr, 0, res->bytes, c.s); // res = 0.0 for every frame

@@ -42,6 +42,12 @@ ThreadCtx &tls() {
     return ctx;
 }
 
+static std::atomic<int> g_default_sum_mode{SUM_COMPENSATED};
+int effective_sum_mode() {
+    const int m = tls().sum_mode;
+    return m == SUM_INHERIT ? g_default_sum_mode.load(std::memory_order_relaxed) : m;
+}
+
 void set_last_error(const std::string &msg) { tls().last_error = msg; }
 
 afk_status fail(const Error &e) {
@@ -201,8 +207,13 @@ bool ImageMeta::meta_equal(const ImageMeta &o) const {
 
 static Error check_shape(int ndim, const int64_t *shape) {
     if (ndim < 0 || ndim > AFK_MAX_NDIM) return make_error(AFK_ERR_SHAPE, fmt("unsupported number of dimensions %d", ndim));
-    for (int i = 0; i < ndim; ++i)
+    int64_t n = 1;
+    for (int i = 0; i < ndim; ++i) {
         if (shape[i] < 0) return make_error(AFK_ERR_SHAPE, "negative dimension");
+        // the element count sizes the allocation and the kernels' index arithmetic: it must not wrap (FITS headers are
+        // untrusted input) and 2^40 elements (4 TiB of f32) is beyond any device
+        if (__builtin_mul_overflow(n, shape[i], &n) || n > (int64_t(1) << 40)) return make_error(AFK_ERR_SHAPE, "image too large");
+    }
     return ok();
 }
 
@@ -254,7 +265,7 @@ Error image_wait(const afk_image *img, cudaStream_t stream) {
 void image_note_read(const afk_image *cimg, cudaStream_t stream) {
     afk_image *img = const_cast<afk_image *>(cimg);
     while (img->parent) img = img->parent; // the allocation belongs to the root
-    if (!img->owned || img->stream == stream) return;
+    if ((!img->owned && !img->track_readers) || img->stream == stream) return;
     cudaEvent_t e = event_get();
     if (!e) return;
     if (cudaEventRecord(e, stream) != cudaSuccess) {
@@ -264,8 +275,19 @@ void image_note_read(const afk_image *cimg, cudaStream_t stream) {
     }
     std::lock_guard<std::mutex> lk(img->mu);
     img->readers.push_back(e);
-    if (img->readers.size() > 64) { // bound the list: the oldest reads are long done once newer ones are enqueued
-        event_put(img->readers.front());
+    if (img->readers.size() > 64) {
+        // bound the list: the owner stream takes over the dependency on the oldest read before its event is recycled,
+        // so the stream-ordered free in image_destroy still comes after every reader (reads may come from many streams)
+        cudaEvent_t old = img->readers.front();
+        if (cudaEventQuery(old) != cudaSuccess) {
+            cudaGetLastError();
+            int prev = -1;
+            cudaGetDevice(&prev);
+            if (prev != img->device) cudaSetDevice(img->device);
+            cudaStreamWaitEvent(img->stream, old, 0);
+            if (prev >= 0 && prev != img->device) cudaSetDevice(prev);
+        }
+        event_put(old);
         img->readers.erase(img->readers.begin());
     }
 }
@@ -357,12 +379,34 @@ int afk_synchronize(void) {
 
 uint64_t afk_launch_count(void) { return launch_count(); }
 
-int afk_set_sum_mode(int mode) {
+// Sum mode: a process-wide default plus a per-thread override.  cake calls operators from arbitrary rayon workers
+// (aflak_cake/src/dst/compute.rs:206-224), so a host that wants the reference's bits sets the default once.
+int afk_set_default_sum_mode(int mode) {
     if (mode != SUM_COMPENSATED && mode != SUM_SEQUENTIAL) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "unknown sum mode"));
+    g_default_sum_mode.store(mode, std::memory_order_relaxed);
+    return AFK_OK;
+}
+int afk_set_sum_mode(int mode) {
+    if (mode != SUM_INHERIT && mode != SUM_COMPENSATED && mode != SUM_SEQUENTIAL) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "unknown sum mode"));
     tls().sum_mode = mode;
     return AFK_OK;
 }
-int afk_get_sum_mode(void) { return tls().sum_mode; }
+int afk_get_sum_mode(void) { return effective_sum_mode(); }
+
+// Return every cached (freed) block of the stream-ordered pools of the current device to the driver.  A host calls this
+// before an allocation that needs nearly the whole device (the 128 GiB cube of BASELINE configs[4] on one GPU).
+int afk_trim_pools(void) {
+    cudaStream_t s;
+    int dev;
+    if (Error e = current_stream(&s, &dev)) return fail(e);
+    cudaError_t ce = cudaDeviceSynchronize();
+    cudaMemPool_t pool;
+    if (ce == cudaSuccess) ce = cudaDeviceGetDefaultMemPool(&pool, dev);
+    if (ce == cudaSuccess) ce = cudaMemPoolTrimTo(pool, 0);
+    if (ce == cudaSuccess && g_big_pool[dev]) ce = cudaMemPoolTrimTo(g_big_pool[dev], 0);
+    if (ce != cudaSuccess) return fail(cuda_error(ce, "afk_trim_pools"));
+    return AFK_OK;
+}
 
 // ---- type ids ---------------------------------------------------------------------------------------------
 static const char *kTypeNames[AFK_T_COUNT] = {"Integer", "Float", "Float2", "Float3", "Float3x3", "Str", "Bool",

@@ -19,7 +19,10 @@ struct afk_gather {
     char *local = nullptr;          // cudaMalloc'ed: [slot 0][slot 1][flags: kMaxPeers u32][done u32][err u32]
     char *peer[afk::kMaxPeers] = {nullptr};
     bool connected = false;
-    unsigned epoch = 0;
+    unsigned epoch = 0;        // last epoch a reduce was enqueued for
+    unsigned waited_epoch = 0; // last epoch a wait was enqueued for
+    cudaStream_t stream = nullptr; // every reduce / wait of this gather is ordered on this stream
+    afk_image *result[2] = {nullptr, nullptr}; // borrowed-memory handles of the two slots (readers on other streams are tracked)
     size_t bytes = 0;
     float *slot(int r, unsigned e) const { return reinterpret_cast<float *>(peer[r]) + (size_t)(e & 1u) * slot_floats; }
     unsigned *flags(int r) const { return reinterpret_cast<unsigned *>(peer[r] + 2 * slot_floats * sizeof(float)); }
@@ -52,6 +55,7 @@ afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx,
     g->world = world;
     g->rank = rank;
     g->device = dev;
+    g->stream = s;
     g->ny = ny_total;
     g->nx = nx;
     for (int r = 0; r < world; ++r) afk_shard_band(ny_total, world, r, &g->y0[r], &g->rows[r]);
@@ -114,6 +118,22 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     int dev;
     if (Error e = current_stream(&s, &dev)) return fail(e);
     if (dev != g->device) return fail(make_error(AFK_ERR_CUDA, "CUDA: gather belongs to another device"));
+    // The two-slot protocol holds only if every reduce is followed by a wait on the same stream before the next reduce:
+    // a peer can then not start step n+2 (which overwrites slot n & 1 here) before this rank has finished step n+1,
+    // which is ordered after this rank's consumers of image n.
+    if (s != g->stream) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_reduce: called on another stream than the gather was created on"));
+    if (g->waited_epoch != g->epoch)
+        return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_reduce: afk_gather_wait has not been called since the previous afk_gather_reduce"));
+    // consumers of the previous image on other streams (operators called on its handle from other threads): this step,
+    // and therefore every peer's next overwrite of that slot, is ordered after them
+    if (afk_image *prev = g->result[g->epoch & 1u]) {
+        std::lock_guard<std::mutex> lk(prev->mu);
+        for (cudaEvent_t e : prev->readers) {
+            cudaStreamWaitEvent(s, e, 0);
+            event_put(e);
+        }
+        prev->readers.clear();
+    }
     const unsigned epoch = ++g->epoch;
     const int64_t band_off = g->y0[g->rank] * g->nx;
     ReduceArgs a{};
@@ -128,8 +148,10 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     }
     a.epilogue = epilogue;
     a.mode = sum_mode;
-    for (int i = 0; i < 4; ++i) a.p[i] = params ? params[i] : 0.0f;
-    a.ew_sign = params ? params[4] : 1.0f;
+    // params are read for EPI_EW only: exactly 5 floats (a, b, fl, max, sign)
+    if (epilogue == EPI_EW && !params) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "the equivalent-width epilogue needs params[5] = {a, b, fl, max, sign}"));
+    for (int i = 0; i < 4; ++i) a.p[i] = epilogue == EPI_EW ? params[i] : 0.0f;
+    a.ew_sign = epilogue == EPI_EW ? params[4] : 1.0f;
     a.out = g->slot(g->rank, epoch) + band_off;
     int k = 0;
     for (int r = 0; r < g->world; ++r)
@@ -141,8 +163,10 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     a.epoch = epoch;
     if (a.n2 <= 0) {
         // an empty band still has to signal: launch a 1-frame plan is impossible, so set the flags from the host side
+        static thread_local unsigned epoch_src[4]; // outlives the (pageable, hence staged at call time) copies
+        epoch_src[epoch & 3u] = epoch;
         for (int r = 0; r < g->world; ++r) {
-            cudaError_t ce = cudaMemcpyAsync(a.signal[r], &g->epoch, sizeof(unsigned), cudaMemcpyHostToDevice, s);
+            cudaError_t ce = cudaMemcpyAsync(a.signal[r], &epoch_src[epoch & 3u], sizeof(unsigned), cudaMemcpyHostToDevice, s);
             if (ce != cudaSuccess) return fail(cuda_error(ce, "signal of an empty band"));
         }
         return AFK_OK;
@@ -172,9 +196,24 @@ afk_status afk_gather_wait(afk_gather *g, float **result, double timeout_s) {
     if (!g) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_gather_wait"));
     cudaStream_t s;
     if (Error e = current_stream(&s, nullptr)) return fail(e);
+    if (s != g->stream) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_wait: called on another stream than the gather was created on"));
+    if (g->epoch == 0) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_wait: no afk_gather_reduce has been enqueued"));
     if (timeout_s <= 0) timeout_s = 5.0;
-    cudaError_t ce = gather_wait_launch(g->flags(g->rank), g->world, g->epoch, timeout_s, g->err(), s);
+    // a band that never arrives is overwritten with NaN in this rank's image (and recorded for afk_gather_check), so stale
+    // data of an older step cannot flow on silently
+    GatherWaitArgs w{};
+    w.flags = g->flags(g->rank);
+    w.n = g->world;
+    w.epoch = g->epoch;
+    w.err = g->err();
+    w.image = g->slot(g->rank, g->epoch);
+    for (int r = 0; r < g->world; ++r) {
+        w.band_off[r] = g->y0[r] * g->nx;
+        w.band_len[r] = g->rows[r] * g->nx;
+    }
+    cudaError_t ce = gather_wait_launch(w, timeout_s, g->device, s);
     if (ce != cudaSuccess) return fail(cuda_error(ce, "gather_wait_kernel launch"));
+    g->waited_epoch = g->epoch;
     if (result) *result = g->slot(g->rank, g->epoch);
     return AFK_OK;
 }
@@ -192,15 +231,29 @@ afk_status afk_gather_check(afk_gather *g) {
     return AFK_OK;
 }
 
+// The handle borrows the slot's memory (never freed through it) and is retained for the caller.  Operators that read it
+// from other streams are recorded on it; the next afk_gather_reduce waits for them (see there).
 afk_image *afk_gather_result_image(afk_gather *g) {
     if (!g) return nullptr;
-    int64_t shape[2] = {g->ny, g->nx};
-    return afk_image_wrap_device(g->slot(g->rank, g->epoch), 2, shape);
+    afk_image *&img = g->result[g->epoch & 1u];
+    if (!img) {
+        int64_t shape[2] = {g->ny, g->nx};
+        img = afk_image_wrap_device(g->slot(g->rank, g->epoch), 2, shape);
+        if (!img) return nullptr;
+        img->track_readers = true;
+    }
+    // ready = everything enqueued on the gather stream so far (the caller has enqueued afk_gather_wait): operators on
+    // other streams wait for it before they read
+    if (fail(image_mark_ready(img, g->stream)) != AFK_OK) return nullptr;
+    afk_image_retain(img);
+    return img;
 }
 
 void afk_gather_destroy(afk_gather *g) {
     if (!g) return;
     cudaDeviceSynchronize();
+    for (afk_image *img : g->result)
+        if (img) afk_image_release(img);
     for (int r = 0; r < g->world; ++r)
         if (r != g->rank && g->peer[r]) cudaIpcCloseMemHandle(g->peer[r]);
     if (g->local) cudaFree(g->local);

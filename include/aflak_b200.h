@@ -241,9 +241,16 @@ afk_status afk_transform_call(const afk_transform_desc *t, const afk_value *cons
                               afk_result *outputs, size_t n_outputs);
 
 /* Reduction arithmetic: 0 = compensated (default; <=1e-5 of the f64 sum), 1 = sequential (bit-exact with the
- * reference's left-to-right f32 sum; slower on small images because it cannot split the spectral axis). */
+ * reference's left-to-right f32 sum; slower on small images because it cannot split the spectral axis).
+ * cake calls operators from arbitrary rayon workers (aflak_cake/src/dst/compute.rs:206-224), so the mode is a
+ * process-wide default (afk_set_default_sum_mode, set once by the host) with an optional per-thread override
+ * (afk_set_sum_mode; -1 removes the override).  afk_get_sum_mode returns the mode in force on the calling thread. */
+int afk_set_default_sum_mode(int mode);
 int afk_set_sum_mode(int mode);
 int afk_get_sum_mode(void);
+/* Return the cached (freed) blocks of the current device's stream-ordered pools to the driver; synchronises the device.
+ * For hosts about to make an allocation that needs nearly the whole device (the 128 GiB cube of BASELINE configs[4]). */
+int afk_trim_pools(void);
 
 /* ---- fused paths the evaluator substitutes for recognised sub-graphs (unfused operators remain the parity
  *      reference).  Inputs are borrowed, outputs have refcount 1. ---- */
@@ -313,7 +320,8 @@ afk_status afk_colormap_rgb_host(const afk_image *img, const afk_lut *const lut[
                                  int flip_y, int channels, uint8_t *out_host);
 
 /* ---- raw kernel layer: device pointers + the thread's stream, no handles (bench.py, multi-GPU bands) ---- */
-/* epilogue: 0 sum, 1 mean, 2 mean0/mean1, 3 EW(params = a,b,fl,max,sign). `out` may be a peer-mapped pointer. */
+/* epilogue: 0 sum, 1 mean, 2 mean0/mean1, 3 EW.  params is read for EW only: exactly 5 floats (a, b, fl, max, sign).
+ * `out` may be a peer-mapped pointer. */
 afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends,
                         int epilogue, const float *params, int sum_mode, float *out);
 /* the ingest decode kernel alone: device raw bytes -> device f32 (out may alias raw for 4-byte formats) */
@@ -335,21 +343,27 @@ int afk_ipc_close(float *peer_ptr);
  *      (world*64 bytes, rank-major), every rank calls afk_gather_connect; then per step afk_gather_reduce (the reduce
  *      kernel stores its band into every rank's full image through peer mappings and publishes an epoch flag) and
  *      afk_gather_wait (stream-ordered one-warp wait for all bands).  Results alternate between two slots, so step
- *      n+1 never overwrites an image a peer may still be reading from step n. ---- */
+ *      n+1 never overwrites an image a peer may still be reading from step n.  The library enforces what that relies
+ *      on: every afk_gather_reduce must be followed by an afk_gather_wait before the next one, both on the stream the
+ *      gather was created on (anything else fails with AFK_ERR_UNEXPECTED_INPUT); operators that read the handle of
+ *      afk_gather_result_image from other streams are recorded and the next reduce is ordered after them.  A band that
+ *      does not arrive within the time-out is overwritten with NaN and reported by afk_gather_check. ---- */
 typedef struct afk_gather afk_gather;
 /* y-band [y0, y0+rows) of `rank`: rows split evenly, the first ny % world ranks get one extra row */
 int afk_shard_band(int64_t ny, int world, int rank, int64_t *y0, int64_t *rows);
 afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx, uint8_t handle_out[64]);
 int afk_gather_connect(afk_gather *g, const uint8_t *handles);
 int afk_gather_band(const afk_gather *g, int rank, int64_t *y0, int64_t *rows);
-/* band_cube: device pointer to this rank's [nz, rows, nx] band; epilogue/params/sum_mode as afk_k_reduce */
+/* band_cube: device pointer to this rank's [nz, rows, nx] band; epilogue/sum_mode as afk_k_reduce; params is read for
+ * epilogue 3 (EW) only and then holds exactly 5 floats (a, b, fl, max, sign) */
 afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, int nwin, const int64_t *starts,
                              const int64_t *ends, int epilogue, const float *params, int sum_mode);
 /* *result = device pointer to this rank's copy of the full [ny_total, nx] image, valid once the stream reaches it */
 afk_status afk_gather_wait(afk_gather *g, float **result, double timeout_s);
 /* host-synchronising: AFK_ERR_CUDA if a wait timed out (a peer's band never arrived) */
 afk_status afk_gather_check(afk_gather *g);
-/* the current full image as a borrowed (non-owning) Image handle, for further operators (LUT, min/max, ...) */
+/* the current full image as an Image handle that borrows the slot's memory (release it like any handle; the pixels are
+ * valid until the second afk_gather_reduce from now), for further operators (LUT, min/max, ...).  Call after afk_gather_wait. */
 afk_image *afk_gather_result_image(afk_gather *g);
 void afk_gather_destroy(afk_gather *g);
 

@@ -292,3 +292,35 @@ def test_header_is_plain_c_and_a_c_client_links(afk, tmp_path):
         assert p.returncode == 77 and "no CUDA device" in p.stderr
     else:
         assert p.returncode == 0, p.stderr
+
+
+def test_sum_mode_is_a_process_default_with_a_thread_override(afk):
+    """cake calls operators from arbitrary rayon workers (aflak_cake/src/dst/compute.rs:206-224): the host sets the mode
+    once for the process; a thread may override it for itself."""
+    import threading
+
+    seen = {}
+
+    def worker(name, override=None):
+        if override is not None:
+            afk.set_sum_mode(override)
+        seen[name] = afk.get_sum_mode()
+
+    assert afk.get_sum_mode() == afk.SUM_COMPENSATED
+    try:
+        afk.set_default_sum_mode(afk.SUM_SEQUENTIAL)
+        assert afk.get_sum_mode() == afk.SUM_SEQUENTIAL  # no override on this thread
+        for name, ov in (("plain", None), ("override", afk.SUM_COMPENSATED)):
+            t = threading.Thread(target=worker, args=(name, ov))
+            t.start()
+            t.join()
+        assert seen == {"plain": afk.SUM_SEQUENTIAL, "override": afk.SUM_COMPENSATED}
+        afk.set_sum_mode(afk.SUM_COMPENSATED)
+        assert afk.get_sum_mode() == afk.SUM_COMPENSATED
+        afk.set_sum_mode(afk.SUM_INHERIT)
+        assert afk.get_sum_mode() == afk.SUM_SEQUENTIAL
+    finally:
+        afk.set_default_sum_mode(afk.SUM_COMPENSATED)
+        afk.set_sum_mode(afk.SUM_INHERIT)
+    with pytest.raises(afk.AflakError):
+        afk.set_default_sum_mode(7)

@@ -103,3 +103,42 @@ def test_oracle_decode_kat(orc):
         a = (rng.normal(0, 1e4, 1000)).astype(dt) if dt[1] == "f" else rng.integers(0, 30000, 1000).astype(dt)
         want = a.astype(np.float32) * np.float32(1.5) + np.float32(-2.0)
         assert np.array_equal(orc.fits_decode(a.tobytes(), fmt, 1000, bscale=1.5, bzero=-2.0), want)
+
+
+def _raw_header(cards):
+    hdr = "".join(cards + ["END".ljust(80)]).encode("ascii")
+    return hdr + b" " * (-len(hdr) % 2880)
+
+
+def test_malformed_headers_are_rejected_not_followed(afk, tmp_path):
+    """FITS headers are untrusted input: a product that wraps int64, a negative PCOUNT / GCOUNT below 1 (which made the
+    parser walk backwards and re-parse the same HDU for ever) and a data unit larger than the file must end as errors or
+    as a short HDU list, never as a tiny buffer under a huge shape."""
+    from util import fits_card
+
+    def open_blob(blob, name):
+        p = tmp_path / name
+        p.write_bytes(blob)
+        return afk.get_transform("open_fits").call_results(afk.Paths([str(p)]), 0)[0]
+
+    head = [fits_card("SIMPLE", True), fits_card("BITPIX", -32), fits_card("NAXIS", 3)]
+    # NAXIS1*NAXIS2*NAXIS3 = 2^66 wraps to 0 in int64
+    e = open_blob(_raw_header(head + [fits_card(f"NAXIS{i}", 1 << 22) for i in (1, 2, 3)]), "wrap.fits")
+    assert isinstance(e, afk.AflakError) and "overflows" in e.message
+    # (|BITPIX|/8) * count overflows although count itself fits
+    e = open_blob(_raw_header(head + [fits_card("NAXIS1", 1 << 31), fits_card("NAXIS2", 1 << 31), fits_card("NAXIS3", 1)]), "wrap2.fits")
+    assert isinstance(e, afk.AflakError) and "overflows" in e.message
+    ext = [fits_card("XTENSION", "IMAGE"), fits_card("BITPIX", 16), fits_card("NAXIS", 1), fits_card("NAXIS1", 4)]
+    prim = fits_hdu_bytes(None, [])
+    for pc, gc in ((-2880, 1), (0, 0), (0, -3)):
+        e = open_blob(prim + _raw_header(ext + [fits_card("PCOUNT", pc), fits_card("GCOUNT", gc)]) + b"\0" * 2880, f"pg{pc}_{gc}.fits")
+        assert isinstance(e, afk.AflakError) and "PCOUNT" in e.message, (pc, gc)
+    e = open_blob(_raw_header([fits_card("SIMPLE", True), fits_card("BITPIX", 12), fits_card("NAXIS", 0)]), "bitpix.fits")
+    assert isinstance(e, afk.AflakError) and "BITPIX" in e.message
+    # a data unit that claims more bytes than the file holds: the header stays readable, the HDU list ends there, and
+    # reading the data fails before any allocation (no GPU needed to see the error)
+    big = _raw_header(head + [fits_card("NAXIS1", 4096), fits_card("NAXIS2", 4096), fits_card("NAXIS3", 4096)]) + b"\0" * 2880
+    f = open_blob(big + fits_hdu_bytes(np.zeros(4, ">f4"), [], primary=False), "truncated.fits")
+    assert isinstance(f, afk.Fits) and len(f) == 1 and f.header("NAXIS3") == "4096"
+    e = afk.get_transform("fits_to_image").call_results(f, 0, "")[0]
+    assert isinstance(e, afk.AflakError) and e.status == afk.ERR_FITS and "end of file" in e.message
