@@ -544,6 +544,25 @@ static cudaError_t reduce_dispatch_tune(const ReduceKArgs &k, int grid, int kg, 
     return reduce_dispatch_nw<VEC, COMP, 8, 3>(k, grid, s);
 }
 
+// mirrors the dispatch below (reduce_dispatch_tune / reduce_dispatch_nw)
+ReduceVariant reduce_variant(const ReduceArgs &a, const ReducePlan &pl) {
+    ReduceVariant v{};
+    v.vec = pl.vec;
+    v.comp = a.mode != SUM_SEQUENTIAL;
+    v.nw = a.nwin;
+    v.kg = v.comp ? pl.kg : 1;
+    if (v.kg > 1) {
+        v.unroll = env_int("AFK_REDUCE_KG_UNROLL", 8) == 16 ? 16 : 8;
+        v.min_blocks = kReduceKgCtasPerSm;
+    } else {
+        const int u = reduce_tune_unroll(), c = reduce_tune_ctas();
+        const bool known = (u == 8 && c == 4) || (u == 8 && c == 2) || (u == 16 && c == 2) || (u == 16 && c == 3);
+        v.unroll = known ? u : 8;
+        v.min_blocks = known ? c : 3;
+    }
+    return v;
+}
+
 cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const ReduceWorkspace &ws, cudaStream_t s) {
     if (a.nwin < 1 || a.nwin > kMaxWindows || pl.grid < 1) return cudaErrorInvalidValue;
     if (ws.partial_bytes < pl.partial_bytes || ws.n_counters < pl.n_counters) return cudaErrorInvalidValue;

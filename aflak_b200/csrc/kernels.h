@@ -70,6 +70,8 @@ struct ReducePlan {
 };
 
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count);
+struct ReduceVariant { int vec, comp, nw, unroll, min_blocks, kg; }; // template arguments reduce_launch instantiates
+ReduceVariant reduce_variant(const ReduceArgs &a, const ReducePlan &plan);
 cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &plan, const ReduceWorkspace &ws, cudaStream_t s);
 
 // stream-ordered wait until flags[i] >= epoch for i < n (n <= kMaxPeers).  A flag that times out (bound derived from the

@@ -1486,4 +1486,29 @@ afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, con
     return AFK_OK;
 }
 
+// Which instantiation and launch shape afk_k_reduce / afk_gather_reduce use for this problem, as text
+// ("reduce_kernel<VEC=4,COMP=1,NW=2,U=8,MINB=3,KG=1> grid=444 block=256 ..."), so that reports name the kernel that ran.
+int afk_k_reduce_describe(const float *cube, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends, int sum_mode,
+                          const float *out, char *buf, size_t cap) {
+    if (!starts || !ends || !buf || cap == 0 || nwin < 1 || nwin > kMaxWindows) return fail(unexpected("bad arguments to afk_k_reduce_describe"));
+    ReduceArgs a{};
+    a.cube = cube;
+    a.n2 = n2;
+    a.nwin = nwin;
+    for (int w = 0; w < nwin; ++w) {
+        a.start[w] = starts[w];
+        a.end[w] = ends[w];
+    }
+    a.mode = sum_mode;
+    a.out = const_cast<float *>(out);
+    cudaStream_t s;
+    int dev;
+    if (Error e = current_stream(&s, &dev)) return fail(e);
+    const ReducePlan pl = reduce_plan(a, sm_count(dev));
+    const ReduceVariant v = reduce_variant(a, pl);
+    snprintf(buf, cap, "reduce_kernel<VEC=%d,COMP=%d,NW=%d,U=%d,MINB=%d,KG=%d> grid=%d block=%d tiles=%lld frames_per_pixel=%lld units_per_cta=%lld",
+             v.vec, v.comp, v.nw, v.unroll, v.min_blocks, v.kg, pl.grid, kReduceBlock, (long long)pl.ntiles, (long long)pl.ktot, (long long)pl.q);
+    return AFK_OK;
+}
+
 } // extern "C"

@@ -324,6 +324,9 @@ afk_status afk_colormap_rgb_host(const afk_image *img, const afk_lut *const lut[
  * `out` may be a peer-mapped pointer. */
 afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends,
                         int epilogue, const float *params, int sum_mode, float *out);
+/* text description of the kernel instantiation and launch shape afk_k_reduce uses for this problem (reports) */
+int afk_k_reduce_describe(const float *cube, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends, int sum_mode,
+                          const float *out, char *buf, size_t cap);
 /* the ingest decode kernel alone: device raw bytes -> device f32 (out may alias raw for 4-byte formats) */
 afk_status afk_k_ingest(const void *device_raw_be, afk_fits_format fmt, int64_t n, int has_blank, int64_t blank, float bscale,
                         float bzero, float *device_out);

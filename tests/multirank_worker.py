@@ -1,0 +1,142 @@
+#!/usr/bin/env python
+"""Worker of tests/test_gpu_multirank.py: run under torchrun, one rank per GPU (also usable by hand:
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 tests/multirank_worker.py)
+
+Every rank reduces its y-band of a global synthetic cube with the fused peer-store gather (aflak_b200/csrc/shard.cpp,
+kernels.cu reduce_kernel epilogue) and then checks ITS copy of the full image against (a) the same cube reduced unsharded on
+its own GPU and (b) the oracle, for the three epilogues x two sum modes, with uneven band splits (ny % world != 0), an empty
+band (ny < world) and enough repetitions to use both result slots and wrap the epoch parity.  Also exercises the sharded
+display path: the min/max exchange and the RGBA band gather.
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import aflak_b200 as afk
+import oracle
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+afk.set_device(local)
+dist.init_process_group("gloo")  # only the 64-byte IPC handles and the verdict cross the process group
+oracle.build()
+
+
+def exchange(h):
+    lst = [None] * world
+    dist.all_gather_object(lst, h)
+    return lst
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def same_bits(a, b):
+    nan = np.isnan(a)
+    return np.array_equal(nan, np.isnan(b)) and np.array_equal(bits(a)[~nan], bits(b)[~nan])
+
+
+SEED = 0xAF1A0005
+failures = []
+# (nz, ny, nx): uneven split; small image (k-split variant of the kernel); an empty band on the last rank(s); vec=1 lanes
+for (nz, ny, nx) in [(96, 257, 128), (64, 74 + 1, 74), (48, max(world - 1, 1), 256), (40, 33, 37)]:
+    g = afk.Gather(world, rank, ny, nx, exchange if world > 1 else None)
+    y0, rows = g.band()
+    assert (y0, rows) == afk.shard_band(ny, world, rank)
+    band = afk.Image.synthetic(SEED, nz, ny, nx, y0=y0, rows=rows) if rows > 0 else afk.Image.alloc((nz, 0, nx))
+    whole = afk.Image.synthetic(SEED, nz, ny, nx)
+    host = oracle.gen_cube(SEED, nz, ny, nx)
+    on, off1, off2 = (nz // 2 - 8, nz // 2 + 8), (4, 16), (nz - 16, nz - 4)
+    z, z1, z2 = [np.float32((a + b) / 2) for a, b in (on, off1, off2)]
+    r1 = np.float32(np.float32(z - z1) / np.float32(z2 - z1))
+    ewp = [float(np.float32(1.0) - r1), float(r1), 20.0, 1e10, -1.0]
+    cases = [("integral", [(0, nz)], afk.EPI_SUM, None), ("average", [(3, nz - 5)], afk.EPI_MEAN, None),
+             ("average/average/ratio", [(0, nz // 2), (nz // 2, nz)], afk.EPI_MEAN_RATIO, None),
+             ("equivalent width", [on, off1, off2], afk.EPI_EW, ewp)]
+    for name, windows, epi, params in cases:
+        for mode in (afk.SUM_SEQUENTIAL, afk.SUM_COMPENSATED):
+            for rep in range(3):  # both result slots, epoch parity wraps
+                g.reduce(band.device_ptr, nz, windows, epi, params, sum_mode=mode)
+                g.wait()
+            got = g.result_image().download()
+            ref = afk.Image.alloc((ny, nx))
+            afk.k_reduce(whole.device_ptr, nz, ny * nx, windows, epi, ref.device_ptr, params, sum_mode=mode)
+            unsharded = ref.download()
+            if epi == afk.EPI_SUM:
+                want = oracle.integral(host, *windows[0])
+            elif epi == afk.EPI_MEAN:
+                want = oracle.average(host, *windows[0])
+            elif epi == afk.EPI_MEAN_RATIO:
+                want = oracle.ratio(oracle.average(host, *windows[0]), oracle.average(host, *windows[1]))
+            else:
+                off = oracle.linear_composition(oracle.average(host, *off1), oracle.average(host, *off2), ewp[0], ewp[1])
+                want = oracle.equivalent_width(off, oracle.average(host, *on), 20.0, 1e10, True)
+            if mode == afk.SUM_SEQUENTIAL:
+                # the sequential sum never splits a pixel: sharded == unsharded == oracle, bit for bit
+                if not same_bits(got, unsharded):
+                    failures.append(f"rank {rank} {(nz, ny, nx)} {name} sequential: sharded != unsharded")
+                if not same_bits(got, want):
+                    failures.append(f"rank {rank} {(nz, ny, nx)} {name} sequential: sharded != oracle")
+            else:
+                # compensated: the split of the spectral axis between CTAs depends on the band shape, so sharded and
+                # unsharded agree to the tier-C tolerance, not bit for bit
+                tol = dict(rtol=2e-4, atol=2e-4) if epi == afk.EPI_EW else dict(rtol=1e-5, atol=0)
+                if not np.allclose(got, want, equal_nan=True, **tol) or not np.allclose(got, unsharded, equal_nan=True, **tol):
+                    failures.append(f"rank {rank} {(nz, ny, nx)} {name} compensated: outside tolerance")
+    g.check()
+    # protocol enforcement: a second reduce without a wait is refused
+    g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM)
+    try:
+        g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM)
+        failures.append(f"rank {rank}: a reduce without a wait in between was accepted")
+    except afk.AflakError as e:
+        if "afk_gather_wait" not in str(e):
+            failures.append(f"rank {rank}: unexpected message {e}")
+    g.wait()
+
+    # ---- sharded display path: min/max exchange + RGBA band gather ----
+    if hasattr(g, "display"):
+        g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM, sum_mode=afk.SUM_SEQUENTIAL)
+        g.wait()
+        lut = afk.Lut("Flame")
+        lut.set_lims(0.2, 0.3, 0.9)
+        for chain in (None, {"logscale_a": 1000.0, "logscale_vmin": float("nan"), "logscale_vmax": float("nan"), "normalize_min": 0.0,
+                             "normalize_max": float(np.float32(np.log(np.float32(1001.0)) / np.log(np.float32(1000.0)))) / 65535.0,
+                             "tone_table": np.arange(256, dtype=np.float32)}):
+            rgba, mn, mx = g.display(lut, channels=4, chain=chain)
+            img = oracle.integral(host, 0, nz)
+            table = oracle.lut_build("Flame")
+            if chain is None:
+                vmin, vmax = oracle.get_vmin(img), oracle.get_vmax(img)
+                want = oracle.make_raw_image(img, vmin, vmax, table, lims=(0.2, 0.3, 0.9), channels=4)
+            else:
+                vmin, vmax = oracle.image_min_max(img)
+                ls = oracle.convert_to_logscale(img, 1000.0, vmin, vmax)
+                nm = ((ls - np.float32(0.0)) / np.float32(chain["normalize_max"])).astype(np.float32)
+                tc = oracle.apply_tone_curve(nm, chain["tone_table"])
+                want = oracle.make_raw_image(tc, 0.0, 65535.0, table, lims=(0.2, 0.3, 0.9), channels=4)
+            if (np.float32(mn), np.float32(mx)) != (np.float32(vmin), np.float32(vmax)):
+                failures.append(f"rank {rank} {(nz, ny, nx)} display: exchanged min/max {(mn, mx)} != {(vmin, vmax)}")
+            if not np.array_equal(rgba.reshape(-1), np.asarray(want).reshape(-1)):
+                failures.append(f"rank {rank} {(nz, ny, nx)} display (chain={chain is not None}): gathered RGBA differs from the oracle")
+    torch.cuda.synchronize()
+    dist.barrier()
+    g.close()
+    del band, whole
+
+allf = [None] * world
+dist.all_gather_object(allf, failures)
+flat = [f for fs in allf for f in fs]
+if rank == 0:
+    for f in flat:
+        print(f, flush=True)
+    print("MULTIRANK", "OK" if not flat else "FAILED", f"world={world}", flush=True)
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(0 if not flat else 1)

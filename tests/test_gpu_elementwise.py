@@ -260,3 +260,42 @@ def test_metadata_rules(gpu, orc):
     assert tc.unit == "" and tc.tag is None and not tc.has_meta                 # from_array(.., Unit::None)
     ct = gpu.call("change_tag", du, "color_image")
     assert ct.tag == "color_image" and ct.unit == "K" and ct.device_ptr == du.device_ptr
+
+
+def test_signed_zeros_are_results_too(gpu, orc):
+    """-0.0 and +0.0 are different bit patterns and the reference's IEEE arithmetic distinguishes them (0 * -1 = -0,
+    -0 + 0 = +0, -0 / x = -0): assert_bit_equal compares raw bits, and every tier-A operator is fed the zero cases."""
+    from util import bits
+
+    z = np.array([0.0, -0.0, 0.0, -0.0, 1.0, -1.0, 0.0, -0.0], np.float32)
+    w = np.array([0.0, 0.0, -0.0, -0.0, 0.0, -0.0, 2.0, -3.0], np.float32)
+    dz, dw = gpu.Image.upload(z), gpu.Image.upload(w)
+    for a, b in [(1.0, 1.0), (-1.0, 1.0), (0.0, 0.0), (-0.0, 2.0), (3.0, -0.0)]:
+        assert_bit_equal(gpu.call("linear_composition", dz, dw, a, b).download(), orc.linear_composition(z, w, a, b), f"lincomp {a} {b}")
+    assert_bit_equal(gpu.call("ratio", dz, dw).download(), orc.ratio(z, w), "ratio")
+    for fl, mx, em in [(20.0, 1e10, True), (20.0, 1e10, False), (0.0, -1.0, True), (-0.0, 0.0, False)]:
+        assert_bit_equal(gpu.call("create_equivalent_width", dz, dw, fl, mx, em).download(), orc.equivalent_width(z, w, fl, mx, em), f"EW {fl} {mx} {em}")
+    neg = gpu.call("negation", dz).download()
+    assert np.array_equal(bits(neg), bits(z) ^ np.uint32(0x80000000))
+    assert_bit_equal(gpu.call("replace_nan_image", dz, -0.0).download(), z)
+    assert_bit_equal(gpu.call("replace_nan_image", gpu.Image.upload(np.array([np.nan, -0.0], np.float32)), -0.0).download(),
+                     np.array([-0.0, -0.0], np.float32))
+    assert_bit_equal(gpu.call("normalize_image", dz, 0.0, 1.0).download(), ((z - np.float32(0.0)) / np.float32(1.0)).astype(np.float32))
+    assert_bit_equal(gpu.call("normalize_image", dz, 0.0, -2.0).download(), ((z - np.float32(0.0)) / np.float32(-2.0)).astype(np.float32))
+    # copies: slice_one_frame and down_sampling move bit patterns
+    cube = np.stack([z.reshape(2, 4), w.reshape(2, 4)])
+    dc = gpu.Image.upload(cube)
+    assert_bit_equal(gpu.call("slice_one_frame", dc, 1).download(), cube[1])
+    assert_bit_equal(gpu.call("down_sampling", dc, 2).download(), cube[:, ::2, ::2])
+    # the sum of frames that are all -0.0 is -0.0 (ndarray sum_axis starts from the first frame, not from +0.0)
+    mz = np.full((5, 3, 4), -0.0, np.float32)
+    mz[:, 0, 0] = [0.0, -0.0, -0.0, -0.0, -0.0]
+    mz[:, 0, 1] = [-0.0, -0.0, 0.0, -0.0, -0.0]
+    dm = gpu.Image.upload(mz)
+    for mode in (gpu.SUM_SEQUENTIAL, gpu.SUM_COMPENSATED):
+        gpu.set_sum_mode(mode)
+        try:
+            assert_bit_equal(gpu.call("integral", dm, 0, 5)[0].download(), orc.integral(mz, 0, 5), f"integral of zeros mode {mode}")
+            assert_bit_equal(gpu.call("average", dm, 1, 5)[0].download(), orc.average(mz, 1, 5), f"average of zeros mode {mode}")
+        finally:
+            gpu.set_sum_mode(gpu.SUM_INHERIT)

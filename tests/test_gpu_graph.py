@@ -298,6 +298,28 @@ def test_fused_gather_single_rank(gpu, orc):
     ga.reduce(cube.device_ptr, nz, [(0, 50), (50, 100)], gpu.EPI_MEAN_RATIO, sum_mode=gpu.SUM_SEQUENTIAL)
     ga.wait()
     assert_bit_equal(ga.result_image().download(), orc.ratio(orc.average(host, 0, 50), orc.average(host, 50, 100)))
+    # the two-slot protocol is enforced, not left to the caller: a reduce needs a wait before the next reduce
+    ga.reduce(cube.device_ptr, nz, [(0, nz)], gpu.EPI_SUM)
+    with pytest.raises(gpu.AflakError, match="afk_gather_wait has not been called"):
+        ga.reduce(cube.device_ptr, nz, [(0, nz)], gpu.EPI_SUM)
+    ga.wait()
+    # EW needs its five parameters; the other epilogues read none
+    with pytest.raises(ValueError):
+        ga.reduce(cube.device_ptr, nz, [(0, 10), (10, 20), (20, 30)], gpu.EPI_EW, [1.0, 0.0, 20.0, 1e10])
+    # a consumer on another thread's stream: recorded on the handle, the next reduce is ordered after it
+    import threading
+
+    img = ga.result_image()
+    box = {}
+    t = threading.Thread(target=lambda: box.update(mm=gpu.call("image_min_max", img)))
+    t.start()
+    t.join()
+    want = orc.integral(host, 0, nz) if gpu.get_sum_mode() == gpu.SUM_SEQUENTIAL else None
+    s64, _ = orc.sum_f64(host, 0, nz)
+    assert abs(float(box["mm"][0]) - s64.min()) <= 1e-5 * abs(s64.min()) and want is None
+    ga.reduce(cube.device_ptr, nz, [(0, nz)], gpu.EPI_SUM)
+    ga.wait()
+    ga.check()
     ga.close()
 
 

@@ -7,16 +7,18 @@ def bits(a):
 
 
 def assert_bit_equal(got, want, what=""):
-    """Tier A: bit-exact, except that -0.0/+0.0 and NaN payloads are compared by value."""
+    """Tier A: bit-exact.  Raw 32-bit patterns are compared on every lane that is not NaN, so -0.0 and +0.0 are different
+    results; NaN lanes must coincide (Rust and CUDA do not promise the same NaN payload or sign for 0/0 or Inf-Inf)."""
     got = np.asarray(got, dtype=np.float32)
     want = np.asarray(want, dtype=np.float32)
     assert got.shape == want.shape, f"{what}: shape {got.shape} != {want.shape}"
     gn, wn = np.isnan(got), np.isnan(want)
     assert np.array_equal(gn, wn), f"{what}: NaN positions differ ({gn.sum()} vs {wn.sum()})"
-    ok = (got == want) | gn
+    ok = (bits(got) == bits(want)) | gn
     if not ok.all():
         i = np.argwhere(~ok)[0]
-        raise AssertionError(f"{what}: {(~ok).sum()} mismatches, first at {tuple(i)}: got {got[tuple(i)]!r} want {want[tuple(i)]!r}")
+        raise AssertionError(f"{what}: {(~ok).sum()} mismatches, first at {tuple(i)}: got {got[tuple(i)]!r} ({bits(got)[tuple(i)]:#010x}) "
+                             f"want {want[tuple(i)]!r} ({bits(want)[tuple(i)]:#010x})")
 
 
 def ulp_diff(got, want):
