@@ -1237,7 +1237,49 @@ int median_pixels_per_cta(int64_t n2, int64_t n) {
     return fits_once; // 0: not even one spaxel fits -> streaming kernel
 }
 
+// The reference sorts with `sort_by(partial_cmp)`: a STABLE sort under which -0.0 == +0.0, so zeros keep their frame order,
+// whereas the select kernels order keys as integers (-0.0 before +0.0).  Only the sign of a zero result can differ, and only
+// when the window holds zeros of both signs.  This pass visits the pixels whose result is zero: with L = #(v < 0) the zeros
+// occupy the sorted ranks L, L+1, ... in frame order, so the middle element(s) are the (mid - L)-th zero(s) of the window.
+__global__ void __launch_bounds__(256) median_zero_fix_kernel(const float *__restrict__ cube, int64_t n2, int64_t start, int64_t n,
+                                                               float *__restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n2) return;
+    if (out[i] != 0.0f) return; // NaN and non-zero results are already final
+    const float *col = cube + start * n2 + i;
+    int64_t less = 0, zeros = 0;
+    for (int64_t k = 0; k < n; ++k) {
+        const float v = col[k * n2];
+        less += v < 0.0f;
+        zeros += v == 0.0f;
+    }
+    const int64_t hi = n / 2 - less, lo = (n % 2 == 1) ? hi : hi - 1; // ranks of the middle element(s) among the zeros
+    if (lo < 0 || hi >= zeros) return; // one of the middles is not a zero: x + (+-0) = x, the result is already exact
+    float zlo = 0.0f, zhi = 0.0f;
+    int64_t seen = 0;
+    for (int64_t k = 0; k < n && seen <= hi; ++k) {
+        const float v = col[k * n2];
+        if (v == 0.0f) {
+            if (seen == lo) zlo = v;
+            if (seen == hi) zhi = v;
+            ++seen;
+        }
+    }
+    out[i] = (n % 2 == 1) ? zhi : __fdiv_rn(__fadd_rn(zhi, zlo), 2.0f);
+}
+
+static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s);
+
 cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s) {
+    if (n2 <= 0) return cudaSuccess;
+    cudaError_t e = median_dispatch(cube, n2, start, end, out, flag, s);
+    if (e != cudaSuccess) return e;
+    median_zero_fix_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(cube, n2, start, end - start, out);
+    count_launch();
+    return cudaGetLastError();
+}
+
+static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s) {
     if (n2 <= 0) return cudaSuccess;
     const int64_t n = end - start;
     if (n < 1 || n > 0x7FFFFFFF || flag == nullptr) return cudaErrorInvalidValue;

@@ -454,8 +454,13 @@ __global__ void gather_wait_kernel(const GatherWaitArgs a, long long max_cycles)
 
 cudaError_t gather_wait_launch(const GatherWaitArgs &a, double timeout_s, int device, cudaStream_t s) {
     if (a.n < 1 || a.n > kMaxPeers) return cudaErrorInvalidValue;
-    int khz = 0;
-    if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device) != cudaSuccess || khz <= 0) khz = 1965000;
+    // cudaDevAttrClockRate is not cached by the runtime (~1 ms per query): ask once per device
+    static std::atomic<int> khz_of[16];
+    int khz = (device >= 0 && device < 16) ? khz_of[device].load(std::memory_order_relaxed) : 0;
+    if (khz <= 0) {
+        if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, device) != cudaSuccess || khz <= 0) khz = 1965000;
+        if (device >= 0 && device < 16) khz_of[device].store(khz, std::memory_order_relaxed);
+    }
     const long long cycles = (long long)(timeout_s * 1e3 * (double)khz);
     gather_wait_kernel<<<1, 32, 0, s>>>(a, cycles);
     AFK_COUNT_LAUNCH();

@@ -61,14 +61,19 @@ def measured_peak():
 
 def ncu_traffic(kernel_label):
     """dram bytes per launch of the reduce kernel from the committed `ncu --set full` capture (profiles/), or None when
-    the capture is of another instantiation than the one that ran."""
+    the capture is of another instantiation than the one that ran (template arguments compared)."""
+    import re
+
+    ran = re.findall(r"=(\d+)", kernel_label.split(">")[0])
     for name in ("r2_reduce_kernel_alma_ncu_full.json", "r1_reduce_kernel_alma_ncu_full.json"):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 d = json.load(f)
-            if d.get("kernel_variant") and d["kernel_variant"] not in kernel_label:
+            captured = re.findall(r"\d+", d["kernel"].split("<")[1].split(">")[0])
+            if captured != ran:
                 continue
-            return {"bytes": float(d["dram_bytes_read"]) + float(d["dram_bytes_write"]), "source": "profiles/" + name}
+            return {"bytes": float(d["dram_bytes_read"]) + float(d["dram_bytes_write"]), "source": "profiles/" + name,
+                    "kernel": d["kernel"]}
         except Exception:
             continue
     return None
@@ -553,7 +558,7 @@ def run_gpu(args):
             "detail": {"sum": "compensated (Kahan) f32", "voxels_per_s": nz * ny * nx * world / (ms_step * 1e-3),
                        "timing": "CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": cx.peak, "unit": "GB/s", "frac": achieved / cx.peak,
-                         "traffic": tr["bytes"] if tr else None, "traffic_source": tr["source"] if tr else None,
+                         "traffic": tr["bytes"] if tr else None, "traffic_source": (tr["source"] + " (" + tr["kernel"] + ")") if tr else None,
                          "kernel": kernel_label, "kernel_ms": k_avg_ms, "launches_timed": k_n,
                          "algorithmic_bytes_per_launch": step_bytes, "peak_source": cx.peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0},
@@ -926,7 +931,14 @@ def run_configs(cx):
     c4["cpu_port"] = {"ms": (time.perf_counter() - t0) * 1e3, "cores": ncpu, "kind": "port",
                       "threading": "logscale on all cores (par_iter_mut), min/max and the LUT mapping serial (UI thread)"}
     got = afk.colormap(img, lut, 0.0, 65535.0, channels=4, chain=nan_chain)
-    c4["parity"] = "ok" if np.array_equal(got.reshape(-1), np.asarray(want).reshape(-1)) else "FAILED"
+    # tier B: the chain calls logf; CUDA's and glibc's differ in the last bit now and then, which moves a pixel by one
+    # tone-table entry.  Same bar as tests/test_gpu_display.py: a channel difference <= 2 on < 0.1 % of the pixels (the
+    # fused chain against the unfused DEVICE operators is byte-exact: tests/test_gpu_display.py)
+    diff = np.abs(got.astype(np.int32) - np.asarray(want).reshape(got.shape).astype(np.int32))
+    frac = float((diff.max(axis=2) > 0).mean())
+    c4["parity"] = "ok" if diff.max() <= 2 and frac < 1e-3 else "FAILED"
+    c4["parity_detail"] = {"pixels_differing_from_cpu_port": frac, "max_channel_difference": int(diff.max()),
+                           "bar": "tier B (logf: CUDA libm vs glibc): <= 2 on < 0.1 % of the pixels; byte-exact against the unfused device operators"}
     out["C4"] = c4
     del img, rgba, flush_buf
     return out

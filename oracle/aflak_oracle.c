@@ -278,12 +278,28 @@ static int cmp_f32(const void *a, const void *b) {
     return (x > y) - (x < y);
 }
 
+/* Rust's slice::sort_by is a STABLE sort (merge sort): elements that compare equal keep their order.  Under partial_cmp
+ * -0.0 == +0.0, so the sign of a zero median depends on the frame order of the zeros; qsort gives no such guarantee.
+ * Bottom-up merge sort taking the right run only when it is strictly smaller. */
+static void stable_sort_f32(float *a, float *tmp, int64_t n) {
+    for (int64_t w = 1; w < n; w *= 2) {
+        for (int64_t lo = 0; lo < n; lo += 2 * w) {
+            int64_t mid = lo + w < n ? lo + w : n, hi = lo + 2 * w < n ? lo + 2 * w : n;
+            int64_t i = lo, j = mid, o = lo;
+            while (i < mid && j < hi) tmp[o++] = (a[j] < a[i]) ? a[j++] : a[i++];
+            while (i < mid) tmp[o++] = a[i++];
+            while (j < hi) tmp[o++] = a[j++];
+        }
+        memcpy(a, tmp, (size_t)n * sizeof(float));
+    }
+}
+
 /* run_median, lib.rs:1340-1372: per pixel sort (partial_cmp().unwrap() panics on NaN), middle or mean of the two middles */
 int orc_median(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t end, float *out) {
     int rc = check_reduce_args(nz, start, end);
     if (rc) return rc;
     int64_t n = end - start;
-    float *vals = (float *)malloc((size_t)n * sizeof(float));
+    float *vals = (float *)malloc((size_t)n * 2 * sizeof(float)), *tmp = vals + n;
     for (int64_t i = 0; i < n2; ++i) {
         for (int64_t k = 0; k < n; ++k) {
             vals[k] = cube[(start + k) * n2 + i];
@@ -293,7 +309,7 @@ int orc_median(const float *cube, int64_t nz, int64_t n2, int64_t start, int64_t
                 return ORC_ERR_PANIC;
             }
         }
-        qsort(vals, (size_t)n, sizeof(float), cmp_f32);
+        stable_sort_f32(vals, tmp, n);
         out[i] = (n % 2 == 1) ? vals[(n - 1) / 2] : (vals[n / 2] + vals[n / 2 - 1]) / 2.0f;
     }
     free(vals);

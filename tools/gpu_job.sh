@@ -8,6 +8,9 @@ for step in "$@"; do
     tests)
       python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit=$?" >> gpurun_out/pytest_gpu.log
       tail -5 gpurun_out/pytest_gpu.log ;;
+    tests_all)
+      python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit=$?" >> gpurun_out/pytest_gpu.log
+      grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/pytest_gpu.log | tail -30 ;;
     bench)
       python bench.py --steps 20 --warmup 5 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err; echo "bench exit=$?"
       tail -3 gpurun_out/bench_n1.err; head -c 1500 gpurun_out/bench_n1.json; echo ;;
