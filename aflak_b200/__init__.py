@@ -189,6 +189,8 @@ _sig("afk_lut_color_at_bounds", None, _P, C.c_float, C.c_float, C.c_float, _u8p)
 _sig("afk_lut_table", None, _P, _u8p)
 _sig("afk_lut_bounds", C.c_size_t, _P, _fp, _u8p, _fp, _u8p, C.c_size_t)
 _sig("afk_image_vmin_vmax", C.c_int, _P, _fp, _fp)
+_sig("afk_set_display_exact", C.c_int, C.c_int)
+_sig("afk_get_display_exact", C.c_int)
 _sig("afk_colormap", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int, C.POINTER(afk_colormap_chain), _P)
 _sig("afk_colormap_host", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int, C.POINTER(afk_colormap_chain), _P)
 _sig("afk_colormap_rgb_host", C.c_int, _P, C.POINTER(C.c_void_p), _fp, _fp, C.c_int, C.c_int, _P)
@@ -857,6 +859,11 @@ def _chain_struct(chain):
     st = afk_colormap_chain(chain["logscale_a"], chain["logscale_vmin"], chain["logscale_vmax"], chain["normalize_min"],
                             chain["normalize_max"], table.ctypes.data_as(_fp), table.size)
     return st, table
+
+
+def set_display_exact(on):
+    """True: every pixel of the display kernels takes the reference's own IEEE sequence (the baseline of the parity tests)."""
+    lib.afk_set_display_exact(int(bool(on)))
 
 
 def colormap(img, lut, vmin=float("nan"), vmax=float("nan"), flip_y=True, channels=4, chain=None):

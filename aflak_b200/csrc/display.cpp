@@ -219,23 +219,16 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
             a.nm_min = chain->normalize_min; a.nm_max = chain->normalize_max;
             a.tone_table = dtone;
             a.tone_len = (int)chain->tone_len;
-            a.oob_flag = flag;
+            // apply_tone_curve indexes its table unchecked (lib.rs:1866): an input above the table panics in the reference.  The
+            // kernel records that in this thread's panic word (mapped host memory, written only when it happens); it is reported
+            // at the next host synchronisation (afk_synchronize, afk_colormap_host) -- no read-back on the steady-state path.
+            if ((err = panic_word_get(dev, &a.oob_flag))) break;
+            tls().panic_tone_len = chain->tone_len;
         }
         if ((err = image_wait(img, s))) break;
         cudaError_t ce = colormap_launch(a, sm_count(dev), s);
         if (ce != cudaSuccess) { err = cuda_error(ce, "colormap_kernel launch"); break; }
         image_note_read(img, s);
-        if (chain) {
-            // apply_tone_curve indexes its table unchecked (lib.rs:1866): an input above the table panics in the reference.
-            // Same contract as the stand-alone operator: one 4-byte read-back.
-            unsigned hflag = 0;
-            ce = cudaMemcpyAsync(&hflag, flag, sizeof hflag, cudaMemcpyDeviceToHost, s);
-            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
-            if (ce != cudaSuccess) { err = cuda_error(ce, "colormap chain flag"); break; }
-            if (hflag)
-                err = make_error(AFK_ERR_PANIC, fmt("index out of bounds: the len is %zu but the index is larger (input above 65535*(1+1/%zu))",
-                                                    (size_t)chain->tone_len, (size_t)chain->tone_len - 1));
-        }
     } while (0);
     if (lut3) cudaFreeAsync(lut3, s);
     if (dtone) cudaFreeAsync(dtone, s);
@@ -260,6 +253,12 @@ static Error resolve_limits(const afk_image *img, float *vmin, float *vmax) {
 using namespace afk;
 
 extern "C" {
+
+int afk_set_display_exact(int on) {
+    set_display_exact(on != 0);
+    return AFK_OK;
+}
+int afk_get_display_exact(void) { return display_exact() ? 1 : 0; }
 
 afk_lut *afk_lut_linear(const float *stop_values, const uint8_t *stop_rgb, size_t n_stops) {
     afk_lut *l = new afk_lut();
@@ -396,6 +395,7 @@ afk_status afk_colormap_host(const afk_image *img, const afk_lut *lut, float vmi
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
         if (ce != cudaSuccess) st = fail(cuda_error(ce, "cudaMemcpyAsync(D2H rgba)"));
     }
+    if (st == AFK_OK && chain) st = fail(panic_word_take(dev)); // the stream is idle: the tone-table check of the chain
     cudaFreeAsync(d, s);
     return st;
 }

@@ -48,12 +48,20 @@ struct ThreadCtx {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
     uint64_t prof_launches = 0;
     std::string last_error;
+    // Deferred reference panics: a word of mapped pinned host memory per device that kernels on this thread's stream set
+    // where the reference would panic (tone-curve index beyond the table).  Read after any host synchronisation.
+    unsigned *panic_word[16] = {};
+    size_t panic_tone_len = 0; // table length of the last chain / tone-curve launch, for the message
 };
 ThreadCtx &tls();
 int effective_sum_mode(); // the thread's override, else the process-wide default
 // make sure a device is current and return the stream operators on this thread use
 Error current_stream(cudaStream_t *out, int *device);
 int sm_count(int device);
+// device-usable pointer (UVA) to this thread's panic word for `device`; the kernel stores 1 to it with a plain store
+Error panic_word_get(int device, unsigned **out);
+// after the stream has been synchronised: the pending panic of this thread on `device` as an error (and clear it), or ok
+Error panic_word_take(int device);
 cudaEvent_t event_get();
 void event_put(cudaEvent_t e);
 

@@ -16,6 +16,19 @@
 namespace afk {
 
 static std::atomic<uint64_t> g_launches{0};
+// Display kernels (tone curve, colour map, fused chain): 0 = fast forms that are proven / guarded to give the reference's
+// indices and bytes (default), 1 = the reference's own IEEE sequence for every pixel (AFK_DISPLAY_EXACT=1, afk_set_display_exact)
+static std::atomic<int> g_display_exact{-1};
+bool display_exact() {
+    int v = g_display_exact.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char *e = getenv("AFK_DISPLAY_EXACT");
+        v = (e && atoi(e) != 0) ? 1 : 0;
+        g_display_exact.store(v, std::memory_order_relaxed);
+    }
+    return v != 0;
+}
+void set_display_exact(bool on) { g_display_exact.store(on ? 1 : 0, std::memory_order_relaxed); }
 uint64_t launch_count() { return g_launches.load(); }
 #define AFK_COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
 void count_launch() { AFK_COUNT_LAUNCH(); }
@@ -823,8 +836,15 @@ cudaError_t color3_launch(int op, const float *img, int64_t n, float beta, float
 // saturate, NaN -> 0.  The value depends on the pixel only through the table index, so the second half (one multiplication
 // and one IEEE division per pixel in the reference) is evaluated once per table entry when a CTA loads the table --
 // the same two roundings on the same inputs, hence the same bits.
+__device__ __forceinline__ float div_uniform(float a, float s, float rs);
+template <bool FAST = false>
 __device__ __forceinline__ unsigned tone_key(float v, int table_len, float ts, unsigned &oob) {
-    float t = __fdiv_rn(__fmul_rn(v, ts), 65535.0f);
+    // FAST: the division by the constant 65535 as div_uniform (exact for |numerator| <= 2^100; a quotient too small for an
+    // exact residual truncates to index 0 either way); anything larger, Inf and NaN take the IEEE division
+    const float num = __fmul_rn(v, ts);
+    float t;
+    if (FAST && fabsf(num) <= 1.2676506e30f) t = div_uniform(num, 65535.0f, (float)(1.0 / 65535.0));
+    else t = __fdiv_rn(num, 65535.0f);
     unsigned key;
     if (!(t > 0.0f)) key = 0u;                    // NaN, negatives, zero
     else if (t >= 4294967296.0f) key = 0xFFFFFFFFu; // saturate
@@ -837,6 +857,7 @@ __device__ __forceinline__ unsigned tone_key(float v, int table_len, float ts, u
 }
 __device__ __forceinline__ float tone_value(float entry, float ts) { return __fdiv_rn(__fmul_rn(65535.0f, entry), ts); }
 
+template <bool FAST>
 __global__ void __launch_bounds__(256) tone_kernel(const float *__restrict__ img, int64_t n, const float *__restrict__ table,
                                                     int table_len, float *__restrict__ out, unsigned *oob_flag, int vec_ok) {
     extern __shared__ float s_table[]; // the OUTPUT value of every table index
@@ -853,16 +874,16 @@ __global__ void __launch_bounds__(256) tone_kernel(const float *__restrict__ img
         float4 *o4 = reinterpret_cast<float4 *>(out);
         for (int64_t i = tid; i < n4; i += nthreads) {
             float4 x = ld_stream(i4 + i), r;
-            r.x = s_table[tone_key(x.x, table_len, ts, oob)];
-            r.y = s_table[tone_key(x.y, table_len, ts, oob)];
-            r.z = s_table[tone_key(x.z, table_len, ts, oob)];
-            r.w = s_table[tone_key(x.w, table_len, ts, oob)];
+            r.x = s_table[tone_key<FAST>(x.x, table_len, ts, oob)];
+            r.y = s_table[tone_key<FAST>(x.y, table_len, ts, oob)];
+            r.z = s_table[tone_key<FAST>(x.z, table_len, ts, oob)];
+            r.w = s_table[tone_key<FAST>(x.w, table_len, ts, oob)];
             o4[i] = r;
         }
         done = n4 << 2;
     }
-    for (int64_t i = done + tid; i < n; i += nthreads) out[i] = s_table[tone_key(img[i], table_len, ts, oob)];
-    if (oob) atomicMax(oob_flag, 1u);
+    for (int64_t i = done + tid; i < n; i += nthreads) out[i] = s_table[tone_key<FAST>(img[i], table_len, ts, oob)];
+    if (oob) *reinterpret_cast<volatile unsigned *>(oob_flag) = 1u; // plain store: the word may be mapped host memory
 }
 
 cudaError_t tone_curve_launch(const float *img, int64_t n, const float *table_dev, int table_len, float *out,
@@ -872,7 +893,8 @@ cudaError_t tone_curve_launch(const float *img, int64_t n, const float *table_de
     auto al = [](const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
     const int vec_ok = al(img) && al(out);
     const int grid = grid_for(vec_ok ? (n + 3) / 4 : n, 256, sm_count, 8);
-    tone_kernel<<<grid, 256, (size_t)table_len * sizeof(float), s>>>(img, n, table_dev, table_len, out, oob_flag, vec_ok);
+    if (display_exact()) tone_kernel<false><<<grid, 256, (size_t)table_len * sizeof(float), s>>>(img, n, table_dev, table_len, out, oob_flag, vec_ok);
+    else tone_kernel<true><<<grid, 256, (size_t)table_len * sizeof(float), s>>>(img, n, table_dev, table_len, out, oob_flag, vec_ok);
     AFK_COUNT_LAUNCH();
     return cudaGetLastError();
 }
@@ -954,7 +976,26 @@ struct CmapK {
     int chain;
     float ls_a, ls_min, ls_max, ls_lna, nm_min, nm_max;
     int tone_len;
+    // plain colour map, launch-uniform divisors with host-checked ranges (see div_uniform): reciprocals of vmax - vmin and l2 - l0
+    int fast_div;
+    float rs_range, rs_lims;
+    // fused chain, guard-band evaluation of the tone index (see chain_key_fast)
+    int fast_chain;
+    float fc_k2, fc_off, fc_delta;
+    unsigned fc_lo_bits, fc_span_bits;
 };
+
+// a / s for a launch-uniform divisor s whose correctly rounded reciprocal rs = RN(1/s) was computed once (on the host in f64:
+// the quotient of two f32 is never within 2^-49 relative of a 25-bit midpoint, so rounding the f64 quotient to f32 is the
+// correctly rounded f32 reciprocal).  Markstein's theorem: with y = RN(1/b) and q0 a faithful quotient, q0 + RN(a - b q0) y
+// rounds to RN(a/b) as long as nothing overflows or underflows -- three instructions instead of the ~12 of div.rn.f32 and its
+// FCHK-guarded fallback.  The CALLER guarantees the range (|a| <= 2^80 and a quotient that is either >= 2^-100 in magnitude or
+// irrelevant below that, e.g. because only a truncated index is taken from it); NaN propagates.
+__device__ __forceinline__ float div_uniform(float a, float s, float rs) {
+    const float q0 = __fmul_rn(a, rs);
+    const float r = __fmaf_rn(-q0, s, a);
+    return __fmaf_rn(r, rs, q0);
+}
 
 // mtf, lut.rs:152-160
 __device__ __forceinline__ float mtf(float m, float x) {
@@ -989,6 +1030,23 @@ __device__ __forceinline__ unsigned lut_index(float val, float vmin, float vmax,
     return idx;
 }
 
+// lut_index with the two launch-uniform divisions done by div_uniform.  Preconditions checked by the host (colormap_launch):
+// vmin < vmax, both finite with a range in [2^-60, 2^60]; 0 <= l0 < l2 <= 1 with l2 - l0 >= 2^-20.  Then p - vmin lies in
+// [0, vmax - vmin] and x in [0, 1]: no overflow, and an x or c so small that the residual underflows gives index 0 either way.
+// A NaN pixel takes index 0 in the reference (clamp passes it through, `NaN as usize` is 0); so does vmin (x = 0, c <= 0, m = 0):
+// the clamp may therefore be the two-instruction fmax/fmin form that maps NaN to vmin.
+__device__ __forceinline__ unsigned lut_index_fast(float val, float vmin, float vmax, float l0, float l1, float l2, float rs_range, float rs_lims) {
+    const float p = fminf(fmaxf(val, vmin), vmax);
+    const float x = div_uniform(__fsub_rn(p, vmin), __fsub_rn(vmax, vmin), rs_range);
+    const float c = (l0 == 0.0f && l2 == 1.0f) ? x : div_uniform(__fsub_rn(x, l0), __fsub_rn(l2, l0), rs_lims);
+    float m;
+    if (l1 == 0.5f) m = fminf(fmaxf(c, 0.0f), 1.0f);
+    else m = mtf(l1, c);
+    const float i = __fmul_rn(m, 65535.0f);
+    unsigned idx = (i > 0.0f) ? (unsigned)i : 0u;
+    return min(idx, 65535u);
+}
+
 // fused chain, per pixel: convert_to_logscale (lib.rs:1598-1611) -> normalize_image (lib.rs:269-273) -> the index half of
 // apply_tone_curve (lib.rs:1858-1871).  Everything downstream of that index -- the tone curve's output value, clamp, the two
 // range divisions, mtf and the colour-table look-up -- is a function of the index alone and is evaluated once per tone-table
@@ -1000,10 +1058,113 @@ __device__ __forceinline__ unsigned chain_key(float v, const CmapK &k, unsigned 
     return tone_key(t, k.tone_len, (float)(k.tone_len - 1), oob);
 }
 
-template <bool RGB3, bool CHAIN, int CH>
+// Guard-band evaluation of chain_key.  Only the INDEX must equal the reference's, not the floats on the way: the index is
+// trunc(kf) of a quantity kf that is, in exact arithmetic, F(t) = ((ln t / ln a - nm_min) / (nm_max - nm_min)) ts / 65535 with
+// t = a d + 1.  The fast path evaluates F with one subtraction, one multiplication by the reciprocal of the range, one FFMA, one
+// MUFU.LG2 and one FFMA (kf' = log2(t') k2 + off), and the host bounds |kf' - kf_reference| by delta (error analysis in
+// chain_fast_setup: every rounding of the reference's nine steps, logf's 1 ulp, lg2.approx's 2^-22 + 1 ulp, the roundings of
+// the constants, doubled).  When kf' is farther than delta from every integer, trunc(kf') IS the reference's index; otherwise
+// -- about 2 delta of the pixels, ~0.1 % -- and for every pixel outside the domain the bound was derived for (kf' outside
+// [lo, hi): t < 1, NaN, Inf, indices at or beyond the end of the table) the reference's own sequence is evaluated.
+// Returns true when the pixel needs the exact path.  Rounding to the nearest integer with the 1.5 * 2^23 trick keeps
+// everything on the FMA pipe (no F2I / I2F).
+__device__ __forceinline__ bool chain_key_fast(float v, float ls_min, float rs, const CmapK &k, unsigned &key) {
+    const float x = __fsub_rn(v, ls_min);
+    const float t = __fmaf_rn(k.ls_a, __fmul_rn(x, rs), 1.0f);
+    float lg;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(t));
+    const float kf = __fmaf_rn(lg, k.fc_k2, k.fc_off);
+    const float y = __fadd_rn(kf, 12582912.0f);          // 1.5 * 2^23: ulp 1, the low mantissa bits hold round(kf)
+    const float df = __fsub_rn(kf, __fsub_rn(y, 12582912.0f)); // signed distance to the nearest integer, exact
+    key = (__float_as_uint(y) & 0x3FFFFFu) - (df < 0.0f ? 1u : 0u);
+    const bool in_domain = (__float_as_uint(kf) - k.fc_lo_bits) < k.fc_span_bits; // lo <= kf < hi for non-negative floats; NaN fails
+    return !in_domain || fabsf(df) < k.fc_delta;
+}
+
+// One group = 4 consecutive pixels of an (input) row: map them to packed colours.
+template <bool RGB3, bool CHAIN, bool VEC>
+__device__ __forceinline__ void colormap_group(const float *__restrict__ img, size_t n2, size_t src_off, int cnt, const uint32_t *__restrict__ lut,
+                                               const uint32_t *s_color, const CmapK &k, bool fast_chain, float fc_rs, unsigned &oob,
+                                               uint32_t (&px)[4]) {
+#pragma unroll
+    for (int c = 0; c < (RGB3 ? 3 : 1); ++c) {
+        const float *src = img + (size_t)c * n2 + src_off;
+        float v[4];
+        if (VEC) {
+            float4 t = ld_stream(reinterpret_cast<const float4 *>(src));
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = j < cnt ? src[j] : 0.0f;
+        }
+        unsigned ckey[4] = {0u, 0u, 0u, 0u};
+        if (CHAIN) {
+            if (fast_chain) {
+                bool slow[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) slow[j] = chain_key_fast(v[j], k.ls_min, fc_rs, k, ckey[j]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (slow[j]) ckey[j] = (v[j] == v[j]) ? chain_key(v[j], k, oob) : 0u; // a NaN pixel takes index 0 (NaN as usize)
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) ckey[j] = chain_key(v[j], k, oob);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t e;
+            if (CHAIN) {
+                e = s_color[ckey[j]];
+            } else {
+                const unsigned idx = (!RGB3 && k.fast_div) ? lut_index_fast(v[j], k.vmin[0], k.vmax[0], k.l0[0], k.l1[0], k.l2[0], k.rs_range, k.rs_lims)
+                                                           : lut_index(v[j], k.vmin[c], k.vmax[c], k.l0[c], k.l1[c], k.l2[c]);
+                e = __ldg(lut + (size_t)c * 65536 + idx);
+            }
+            if (RGB3) {
+                // make_raw_image_rgb (image.rs:66-72): channel c takes component c of its own table
+                const uint32_t comp = (e >> (8 * c)) & 0xFFu;
+                px[j] = (c == 0 ? 0xFF000000u : px[j]) | (comp << (8 * c));
+            } else {
+                px[j] = e;
+            }
+        }
+    }
+}
+
+template <int CH, bool VEC> __device__ __forceinline__ void colormap_store(uint8_t *dst, const uint32_t (&px)[4], int cnt) {
+    if (CH == 4) {
+        if (VEC) {
+            *reinterpret_cast<uint4 *>(dst) = make_uint4(px[0], px[1], px[2], px[3]);
+        } else {
+            for (int j = 0; j < cnt; ++j) {
+                dst[4 * j + 0] = px[j] & 0xFF; dst[4 * j + 1] = (px[j] >> 8) & 0xFF;
+                dst[4 * j + 2] = (px[j] >> 16) & 0xFF; dst[4 * j + 3] = 0xFF;
+            }
+        }
+    } else {
+        if (VEC) {
+            // 4 px = 12 bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+            const uint32_t a0 = px[0] & 0xFFFFFFu, a1 = px[1] & 0xFFFFFFu, a2 = px[2] & 0xFFFFFFu, a3 = px[3] & 0xFFFFFFu;
+            uint32_t *d32 = reinterpret_cast<uint32_t *>(dst);
+            d32[0] = a0 | (a1 << 24);
+            d32[1] = (a1 >> 8) | (a2 << 16);
+            d32[2] = (a2 >> 16) | (a3 << 8);
+        } else {
+            for (int j = 0; j < cnt; ++j) {
+                dst[3 * j + 0] = px[j] & 0xFF; dst[3 * j + 1] = (px[j] >> 8) & 0xFF; dst[3 * j + 2] = (px[j] >> 16) & 0xFF;
+            }
+        }
+    }
+}
+
+// VEC: nx % 4 == 0, 16-byte aligned image and output, fewer than 2^31 pixels -- the case that matters for throughput.  The
+// grid-stride loop then carries (row, group) along by addition instead of dividing the flat index every iteration and uses
+// 32-bit offsets: the loop overhead was ~100 of the ~190 instructions per 4 pixels (profiles/r2_c4_kernels_ncu_full.json).
+template <bool RGB3, bool CHAIN, int CH, bool VEC>
 __global__ void __launch_bounds__(256) colormap_kernel(const float *__restrict__ img, int64_t ny, int64_t nx,
                                                         const uint32_t *__restrict__ lut, const float *__restrict__ tone,
-                                                        int flip_y, int vec_ok, uint8_t *__restrict__ out, unsigned *oob_flag,
+                                                        int flip_y, uint8_t *__restrict__ out, unsigned *oob_flag,
                                                         const unsigned *__restrict__ ls_minmax, CmapK k) {
     extern __shared__ uint32_t s_color[]; // CHAIN: the packed colour of every tone-table index
     if (CHAIN) {
@@ -1019,74 +1180,106 @@ __global__ void __launch_bounds__(256) colormap_kernel(const float *__restrict__
             s_color[i] = __ldg(lut + lut_index(tone_value(tone[i], ts), k.vmin[0], k.vmax[0], k.l0[0], k.l1[0], k.l2[0]));
         __syncthreads();
     }
+    // fast chain: the range is only known here when image_min_max stayed on the device; its reciprocal is one IEEE
+    // reciprocal per thread, and a degenerate range (constant image, Inf) falls back to the exact sequence
+    float fc_rs = 0.0f;
+    bool fast_chain = false;
+    if (CHAIN && k.fast_chain) {
+        const float range = __fsub_rn(k.ls_max, k.ls_min);
+        fast_chain = range >= 7.8886e-31f && range <= 1.2676e30f && fabsf(k.ls_min) <= 1.2676e30f; // 2^-100 .. 2^100
+        fc_rs = __frcp_rn(range);
+    }
     unsigned oob = 0u;
-    const int64_t n2 = ny * nx;
-    const int64_t groups_per_row = (nx + 3) >> 2;
-    const int64_t total = ny * groups_per_row;
-    const bool row_vec = vec_ok != 0;
-    const bool idx32 = total < (int64_t(1) << 31);
-    for (int64_t gi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * blockDim.x) {
-        // 64-bit division is ~60 instructions; the kernel is issue-bound (profiles/r1_c4_kernels_ncu_full.json)
-        const int64_t y = idx32 ? (int64_t)((unsigned)gi / (unsigned)groups_per_row) : gi / groups_per_row;
-        const int64_t x0 = (gi - y * groups_per_row) << 2;
-        const int64_t ys = flip_y ? (ny - 1 - y) : y;
-        const int cnt = (int)min((int64_t)4, nx - x0);
-        uint32_t px[4];
-#pragma unroll
-        for (int c = 0; c < (RGB3 ? 3 : 1); ++c) {
-            const float *src = img + (size_t)c * n2 + ys * nx + x0;
-            float v[4];
-            if (row_vec) {
-                float4 t = ld_stream(reinterpret_cast<const float4 *>(src));
-                v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-            } else {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) v[j] = j < cnt ? src[j] : 0.0f;
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                uint32_t e;
-                if (CHAIN) {
-                    e = s_color[chain_key(v[j], k, oob)];
-                } else {
-                    const unsigned idx = lut_index(v[j], k.vmin[c], k.vmax[c], k.l0[c], k.l1[c], k.l2[c]);
-                    e = __ldg(lut + (size_t)c * 65536 + idx);
-                }
-                if (RGB3) {
-                    // make_raw_image_rgb (image.rs:66-72): channel c takes component c of its own table
-                    const uint32_t comp = (e >> (8 * c)) & 0xFFu;
-                    px[j] = (c == 0 ? 0xFF000000u : px[j]) | (comp << (8 * c));
-                } else {
-                    px[j] = e;
-                }
-            }
+    const size_t n2 = (size_t)(ny * nx);
+    if (VEC) {
+        const unsigned gpr = (unsigned)(nx >> 2), rows = (unsigned)ny, total = rows * gpr;
+        const unsigned stride = gridDim.x * blockDim.x;
+        const unsigned sy = stride / gpr, sx = stride - sy * gpr;
+        unsigned gi = blockIdx.x * blockDim.x + threadIdx.x;
+        unsigned y = gi / gpr, xg = gi - y * gpr;
+        for (; gi < total; gi += stride) {
+            const unsigned ys = flip_y ? rows - 1u - y : y;
+            uint32_t px[4];
+            colormap_group<RGB3, CHAIN, true>(img, n2, (size_t)(ys * (unsigned)nx + (xg << 2)), 4, lut, s_color, k, fast_chain, fc_rs, oob, px);
+            colormap_store<CH, true>(out + (size_t)gi * (4 * CH), px, 4);
+            xg += sx;
+            y += sy;
+            if (xg >= gpr) { xg -= gpr; ++y; }
         }
-        uint8_t *dst = out + (size_t)(y * nx + x0) * CH;
-        if (CH == 4) {
-            if (row_vec) {
-                *reinterpret_cast<uint4 *>(dst) = make_uint4(px[0], px[1], px[2], px[3]);
-            } else {
-                for (int j = 0; j < cnt; ++j) {
-                    dst[4 * j + 0] = px[j] & 0xFF; dst[4 * j + 1] = (px[j] >> 8) & 0xFF;
-                    dst[4 * j + 2] = (px[j] >> 16) & 0xFF; dst[4 * j + 3] = 0xFF;
-                }
-            }
-        } else {
-            if (row_vec) {
-                // 4 px = 12 bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
-                const uint32_t a0 = px[0] & 0xFFFFFFu, a1 = px[1] & 0xFFFFFFu, a2 = px[2] & 0xFFFFFFu, a3 = px[3] & 0xFFFFFFu;
-                uint32_t *d32 = reinterpret_cast<uint32_t *>(dst);
-                d32[0] = a0 | (a1 << 24);
-                d32[1] = (a1 >> 8) | (a2 << 16);
-                d32[2] = (a2 >> 16) | (a3 << 8);
-            } else {
-                for (int j = 0; j < cnt; ++j) {
-                    dst[3 * j + 0] = px[j] & 0xFF; dst[3 * j + 1] = (px[j] >> 8) & 0xFF; dst[3 * j + 2] = (px[j] >> 16) & 0xFF;
-                }
-            }
+    } else {
+        const int64_t groups_per_row = (nx + 3) >> 2;
+        const int64_t total = ny * groups_per_row;
+        for (int64_t gi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gi < total; gi += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t y = gi / groups_per_row;
+            const int64_t x0 = (gi - y * groups_per_row) << 2;
+            const int64_t ys = flip_y ? (ny - 1 - y) : y;
+            const int cnt = (int)min((int64_t)4, nx - x0);
+            uint32_t px[4];
+            colormap_group<RGB3, CHAIN, false>(img, n2, (size_t)(ys * nx + x0), cnt, lut, s_color, k, fast_chain, fc_rs, oob, px);
+            colormap_store<CH, false>(out + (size_t)(y * nx + x0) * CH, px, cnt);
         }
     }
-    if (CHAIN && oob) atomicMax(oob_flag, 1u);
+    if (CHAIN && oob) *reinterpret_cast<volatile unsigned *>(oob_flag) = 1u; // plain store: the word may be mapped host memory
+}
+
+static bool fast_paths_enabled() { return !display_exact(); }
+
+static float f32_reciprocal(float s) { return (float)(1.0 / (double)s); } // correctly rounded, see div_uniform
+
+// plain colour map: are the two launch-uniform divisors in the range div_uniform needs?
+static void lut_fast_setup(const ColormapArgs &a, CmapK &k) {
+    k.fast_div = 0;
+    if (a.rgb3 || a.chain || !fast_paths_enabled()) return;
+    const float vmin = a.vmin[0], vmax = a.vmax[0], l0 = a.lims[0][0], l2 = a.lims[0][2];
+    const float range = vmax - vmin, lr = l2 - l0;
+    if (!(vmin < vmax) || !(fabsf(vmin) <= 1.1529215e18f) || !(fabsf(vmax) <= 1.1529215e18f)) return; // 2^60
+    if (!(range >= 8.6736174e-19f) || !(range <= 1.1529215e18f)) return;                                // 2^-60 .. 2^60
+    if (!(l0 >= 0.0f) || !(l2 <= 1.0f) || !(lr >= 9.5367432e-7f)) return;                                // 2^-20
+    k.fast_div = 1;
+    k.rs_range = f32_reciprocal(range);
+    k.rs_lims = f32_reciprocal(lr);
+}
+
+// fused chain: constants and error bound of chain_key_fast.  Everything below is f64 arithmetic on launch-uniform values.
+static void chain_fast_setup(const ColormapArgs &a, CmapK &k) {
+    k.fast_chain = 0;
+    if (!a.chain || !fast_paths_enabled()) return;
+    const double A = a.ls_a, LNA = k.ls_lna, NMIN = a.nm_min, R = (double)(a.nm_max - a.nm_min);
+    const int len = a.tone_len;
+    if (!(A > 1.0) || !(A <= 1e6) || !(LNA > 0.0) || !(R > 0.0) || !std::isfinite(R) || !std::isfinite(NMIN) || len < 2) return;
+    const double TS = len - 1, C = TS / 65535.0;
+    const double Kd = C / (LNA * R);              // d kf / d ln t
+    const double K2 = Kd * 0.69314718055994530942; // per log2
+    const double OFF = -NMIN / R * C;
+    const double T_HI = 2.0 * (A + 1.0);          // d <= 1 gives t <= a + 1; the domain check is on kf, see hi below
+    const double Lmax = log(T_HI), lgmax = log2(T_HI);
+    const double eps = ldexp(1.0, -24);
+    auto ulp = [](double v) { return ldexp(1.0, (int)floor(log2(fabs(v))) - 23); };
+    // (1) the reference's own roundings after t: logf (1 ulp), / ln a, - nm_min, / range, * ts, / 65535
+    const double Umax = Lmax / LNA, Wmax = Umax + fabs(NMIN), Nmax = Wmax / R, Kmax = Nmax * C;
+    const double e_ref = ulp(Lmax) * Kd + eps * ((Umax + Wmax) / R * C + 3.0 * Kmax);
+    // (2) the fast path after t': lg2.approx (2^-22 on the mantissa's log + the rounding of the sum), the rounding of k2 and off, the FFMA
+    const double e_fast = (ldexp(1.0, -22) + ulp(lgmax)) * fabs(K2) + eps * (lgmax * fabs(K2) + fabs(OFF) + Kmax + fabs(OFF));
+    // (3) t' against the reference's t: x is the same subtraction; d = fl(x / S) against fl(x * RN(1/S)), fl(fl(a d) + 1) against
+    //     fma(a, d', 1): at most 6 half-ulps relative for t >= 1, and d ln t = dt / t
+    const double e_t = Kd * 6.0 * eps;
+    const double delta = 2.0 * (e_ref + e_fast + e_t);
+    if (!(delta < 0.125) || !std::isfinite(delta) || !std::isfinite(K2) || !std::isfinite(OFF)) return;
+    const double lo = OFF > 0.0 ? OFF : 0.0;                       // kf' >= lo implies t' >= 1 (up to the error already in delta)
+    double hi = Kd * Lmax + OFF;                                   // t' <= T_HI
+    if (hi > (double)len - 2.0 * delta) hi = (double)len - 2.0 * delta; // kf' < hi implies the reference's index < len: no out-of-bounds case
+    if (!(hi > lo) || hi >= 4194304.0) return;
+    const float lo_f = (float)lo, hi_f = nextafterf((float)hi, 0.0f);
+    if (!(hi_f > lo_f)) return;
+    unsigned lo_bits, hi_bits;
+    memcpy(&lo_bits, &lo_f, 4);
+    memcpy(&hi_bits, &hi_f, 4);
+    k.fc_k2 = (float)K2;
+    k.fc_off = (float)OFF;
+    k.fc_delta = (float)delta;
+    k.fc_lo_bits = lo_bits;
+    k.fc_span_bits = hi_bits - lo_bits;
+    k.fast_chain = 1;
 }
 
 cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s) {
@@ -1102,12 +1295,18 @@ cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s)
     k.ls_a = a.ls_a; k.ls_min = a.ls_min; k.ls_max = a.ls_max; k.ls_lna = logf(a.ls_a);
     k.nm_min = a.nm_min; k.nm_max = a.nm_max;
     k.tone_len = a.tone_len;
+    lut_fast_setup(a, k);
+    chain_fast_setup(a, k);
     const int64_t groups = a.ny * ((a.nx + 3) / 4);
     const int grid = grid_for(groups, 256, sm_count, 8);
-    const int vec_ok = (a.nx % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.img) & 15u) == 0) &&
-                       ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0);
+    const bool vec = (a.nx % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.img) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(a.out) & 15u) == 0) &&
+                     a.ny * a.nx < (int64_t(1) << 31);
     const size_t smem = a.chain ? (size_t)a.tone_len * sizeof(float) : 0;
-#define AFK_CMAP(R, C, CH) colormap_kernel<R, C, CH><<<grid, 256, smem, s>>>(a.img, a.ny, a.nx, a.lut, a.tone_table, a.flip_y, vec_ok, a.out, a.oob_flag, a.ls_minmax, k)
+#define AFK_CMAP(R, C, CH)                                                                                                                        \
+    do {                                                                                                                                          \
+        if (vec) colormap_kernel<R, C, CH, true><<<grid, 256, smem, s>>>(a.img, a.ny, a.nx, a.lut, a.tone_table, a.flip_y, a.out, a.oob_flag, a.ls_minmax, k);  \
+        else colormap_kernel<R, C, CH, false><<<grid, 256, smem, s>>>(a.img, a.ny, a.nx, a.lut, a.tone_table, a.flip_y, a.out, a.oob_flag, a.ls_minmax, k); \
+    } while (0)
     if (a.rgb3) {
         if (a.channels == 4) AFK_CMAP(true, false, 4); else AFK_CMAP(true, false, 3);
     } else if (a.chain) {

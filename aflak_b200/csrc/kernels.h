@@ -259,6 +259,10 @@ cudaError_t colormap_launch(const ColormapArgs &a, int sm_count, cudaStream_t s)
 cudaError_t gen_cube_launch(uint64_t seed, int64_t nz, int64_t ny, int64_t nx, int64_t y0, int64_t rows, int pathology,
                             float *out, cudaStream_t s);
 
+// display kernels: fast forms (default) or the reference's IEEE sequence for every pixel
+bool display_exact();
+void set_display_exact(bool on);
+
 // number of kernel launches issued by this library since load (bench.py's gpu_launches)
 uint64_t launch_count();
 void count_launch(); // for the other translation units

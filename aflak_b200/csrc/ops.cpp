@@ -638,32 +638,27 @@ AFK_OP(op_apply_tone_curve) {
     afk_image *res = nullptr;
     float *dtab = nullptr;
     unsigned *flag = nullptr;
-    unsigned hflag = 0;
     do {
         if (e) break;
         if ((e = image_new(img->ndim, img->shape, &res))) break;
         if ((e = image_wait(img, s))) break;
-        if ((e = scratch_u32(s, 4, &flag))) break;
+        if ((e = panic_word_get(dev, &flag))) break;
+        tls().panic_tone_len = table.size();
         cudaError_t ce = cudaMallocAsync(reinterpret_cast<void **>(&dtab), table.size() * sizeof(float), s);
         if (ce == cudaSuccess) ce = cudaMemcpyAsync(dtab, table.data(), table.size() * sizeof(float), cudaMemcpyHostToDevice, s);
         if (ce == cudaSuccess) ce = tone_curve_launch(img->ptr, img->len(), dtab, (int)table.size(), res->ptr, flag, sm_count(dev), s);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(&hflag, flag, sizeof hflag, cudaMemcpyDeviceToHost, s);
-        // the index check needs the flag on the host: one 4-byte sync, like the scalar outputs of image_min_max
+        // the operator returns Ok or the reference's panic: the index check needs the kernel to have finished (one stream
+        // synchronisation; the flag itself is a word of mapped host memory, no copy)
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
         if (ce != cudaSuccess) {
             e = cuda_error(ce, "tone_kernel");
             break;
         }
         image_note_read(img, s);
-        if (hflag) {
-            e = make_error(AFK_ERR_PANIC, fmt("index out of bounds: the len is %zu but the index is larger (input above 65535*(1+1/%zu))",
-                                              table.size(), table.size() - 1));
-            break;
-        }
+        if ((e = panic_word_take(dev))) break;
         e = image_mark_ready(res, s);
     } while (0);
     if (dtab) cudaFreeAsync(dtab, s);
-    if (flag) scratch_free(s, flag);
     if (e) {
         if (res) afk_image_release(res);
         set_err(&out[0], e);

@@ -160,6 +160,31 @@ void event_put(cudaEvent_t e) {
     g_ev_pool[it->second].push_back(e);
 }
 
+// ---- deferred panics -------------------------------------------------------------------------------------------
+Error panic_word_get(int device, unsigned **out) {
+    ThreadCtx &c = tls();
+    if (device < 0 || device >= 16) return make_error(AFK_ERR_CUDA, "CUDA: device index out of range");
+    if (!c.panic_word[device]) {
+        void *p = nullptr;
+        AFK_CUDA(cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable));
+        memset(p, 0, 64);
+        c.panic_word[device] = static_cast<unsigned *>(p);
+    }
+    *out = c.panic_word[device];
+    return ok();
+}
+
+Error panic_word_take(int device) {
+    ThreadCtx &c = tls();
+    if (device < 0 || device >= 16 || !c.panic_word[device]) return ok();
+    volatile unsigned *w = c.panic_word[device];
+    if (*w == 0u) return ok();
+    *w = 0u;
+    const size_t len = c.panic_tone_len;
+    return make_error(AFK_ERR_PANIC, fmt("index out of bounds: the len is %zu but the index is larger (input above 65535*(1+1/%zu))", len,
+                                         len > 0 ? len - 1 : 0));
+}
+
 // ---- scratch ---------------------------------------------------------------------------------------------
 Error scratch_u32(cudaStream_t s, size_t n, unsigned **out) {
     void *p = nullptr;
@@ -374,6 +399,8 @@ int afk_synchronize(void) {
     if (Error e = current_stream(&s, nullptr)) return fail(e);
     cudaError_t ce = cudaStreamSynchronize(s);
     if (ce != cudaSuccess) return fail(cuda_error(ce, "cudaStreamSynchronize"));
+    // a display chain enqueued by afk_colormap that ran into the reference's tone-table panic reports it here
+    if (Error e = panic_word_take(tls().device)) return fail(e);
     return AFK_OK;
 }
 

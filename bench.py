@@ -932,13 +932,21 @@ def run_configs(cx):
                       "threading": "logscale on all cores (par_iter_mut), min/max and the LUT mapping serial (UI thread)"}
     got = afk.colormap(img, lut, 0.0, 65535.0, channels=4, chain=nan_chain)
     # tier B: the chain calls logf; CUDA's and glibc's differ in the last bit now and then, which moves a pixel by one
-    # tone-table entry.  Same bar as tests/test_gpu_display.py: a channel difference <= 2 on < 0.1 % of the pixels (the
-    # fused chain against the unfused DEVICE operators is byte-exact: tests/test_gpu_display.py)
+    # tone-table entry (tests/test_gpu_display.py)
     diff = np.abs(got.astype(np.int32) - np.asarray(want).reshape(got.shape).astype(np.int32))
     frac = float((diff.max(axis=2) > 0).mean())
-    c4["parity"] = "ok" if diff.max() <= 2 and frac < 1e-3 else "FAILED"
-    c4["parity_detail"] = {"pixels_differing_from_cpu_port": frac, "max_channel_difference": int(diff.max()),
-                           "bar": "tier B (logf: CUDA libm vs glibc): <= 2 on < 0.1 % of the pixels; byte-exact against the unfused device operators"}
+    gpu_exact = None
+    try:  # the same chain with every pixel on the reference's own IEEE sequence (no guard band, no fast divisions)
+        afk.set_display_exact(True)
+        gpu_exact = afk.colormap(img, lut, 0.0, 65535.0, channels=4, chain=nan_chain)
+    finally:
+        afk.set_display_exact(False)
+    byte_exact = bool(np.array_equal(got, gpu_exact))
+    c4["parity"] = "ok" if byte_exact and frac < 1e-3 else "FAILED"
+    c4["parity_detail"] = {"fast_paths_vs_all_ieee_device_sequence": "byte-exact" if byte_exact else "DIFFERENT",
+                           "pixels_differing_from_cpu_port": frac,
+                           "bar": "byte-exact against the device's all-IEEE sequence; tier B against the CPU port (logf: CUDA libm vs glibc "
+                                  "differ in the last bit now and then, which moves a pixel by one tone-table entry): < 0.1 % of the pixels"}
     out["C4"] = c4
     del img, rgba, flush_buf
     return out

@@ -53,6 +53,8 @@ int afk_set_device(int device);
  * the thread's own stream. */
 int afk_set_stream(void *cuda_stream);
 void *afk_get_stream(void);
+/* waits for this thread's stream; AFK_ERR_PANIC when a display chain enqueued by afk_colormap hit the reference's
+ * tone-table panic since the last synchronisation */
 int afk_synchronize(void);
 /* kernels launched by this library since load (all threads) */
 uint64_t afk_launch_count(void);
@@ -282,6 +284,13 @@ void afk_lut_table(const afk_lut *lut, uint8_t *out_rgb);
 /* bounds() iterator (lut.rs:196-200): writes up to cap pairs, returns the number of pairs */
 size_t afk_lut_bounds(const afk_lut *lut, float *v1, uint8_t *c1, float *v2, uint8_t *c2, size_t cap);
 
+/* The display kernels (apply_tone_curve, colour map, fused chain) replace divisions by launch-uniform divisors with an
+ * exact three-instruction form and evaluate the chain's tone index with a guard band; both give the
+ * reference's indices and bytes.  on = 1 makes every pixel take the reference's own IEEE sequence instead (also
+ * AFK_DISPLAY_EXACT=1 in the environment): the baseline the parity tests compare the fast forms with. */
+int afk_set_display_exact(int on);
+int afk_get_display_exact(void);
+
 /* lims::get_vmin / get_vmax (aflak_plot/src/lims.rs:7-35): NaN-skipping, NaN when every pixel is NaN */
 afk_status afk_image_vmin_vmax(const afk_image *img, float *vmin, float *vmax);
 
@@ -309,7 +318,10 @@ typedef struct afk_colormap_chain { /* optional fused upstream chain (BASELINE c
 
 /* make_raw_image on the vertically flipped image.  vmin/vmax NaN -> computed with afk_image_vmin_vmax.
  * channels: 3 = packed RGB8 (the reference's ClientFormat::U8U8U8), 4 = RGBA8 (A=255).
- * out_device: device buffer of ny*nx*channels bytes (headless stand-in for the GL texture). */
+ * out_device: device buffer of ny*nx*channels bytes (headless stand-in for the GL texture).
+ * Stream-ordered, no host synchronisation.  With a chain, a pixel whose tone-curve index lies beyond the table (the
+ * reference's apply_tone_curve panics there, lib.rs:1866) is mapped with the last table entry and the panic is reported
+ * as AFK_ERR_PANIC by the next afk_synchronize() on this thread (afk_colormap_host reports it itself). */
 afk_status afk_colormap(const afk_image *img, const afk_lut *lut, float vmin, float vmax, int flip_y, int channels,
                         const afk_colormap_chain *chain, uint8_t *out_device);
 /* same, result copied to host memory */

@@ -24,8 +24,8 @@ for step in "$@"; do
       ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_bench.csv \
           python bench.py --steps 5 --warmup 3 --skip cpu > gpurun_out/ncu_launches.log 2>&1; echo "ncu_launches exit=$?" ;;
     ncu_c4)
-      ncu --set full --clock-control none --import-source on -k regex:"colormap_kernel|minmax_kernel|tone_kernel" -c 6 -o gpurun_out/c4_kernels -f \
-          python tools/ncu_target.py --workload lut --launches 2 > gpurun_out/ncu_c4.log 2>&1; echo "ncu_c4 exit=$?" ;;
+      ncu --set full --clock-control none --import-source on -k regex:"colormap_kernel|minmax_kernel|tone_kernel" -c 9 -o gpurun_out/c4_kernels -f \
+          python tools/ncu_target.py --workload c4 --launches 2 > gpurun_out/ncu_c4.log 2>&1; echo "ncu_c4 exit=$?" ;;
     configs)
       python tools/bench_configs.py > gpurun_out/configs.json 2> gpurun_out/configs.err; echo "configs exit=$?"; tail -3 gpurun_out/configs.err ;;
     n2|n4|n8)

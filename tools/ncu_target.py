@@ -45,6 +45,22 @@ elif args.workload == "lut":
     vmin, vmax = img.vmin_vmax()
     for _ in range(args.launches):
         afk.colormap_device(img, lut, float(vmin), float(vmax), outb.device_ptr, channels=4)
+elif args.workload == "c4":  # BASELINE configs[3]: min/max + fused chain, non-default limits; then the plain map and the tone curve
+    rng = np.random.default_rng(4)
+    img = afk.Image.upload(np.exp(rng.standard_normal((4096, 4096))).astype(np.float32))
+    lut = afk.Lut("Flame")
+    lut.set_lims(0.2, 0.3, 0.9)
+    outb = afk.Image.alloc((4096, 4096))
+    lmax = float(np.float32(np.log(np.float32(1001.0)) / np.log(np.float32(1000.0))))
+    chain = {"logscale_a": 1000.0, "logscale_vmin": float("nan"), "logscale_vmax": float("nan"), "normalize_min": 0.0,
+             "normalize_max": lmax / 65535.0, "tone_table": np.arange(256, dtype=np.float32)}
+    vmin, vmax = img.vmin_vmax()
+    scaled = afk.call("normalize_image", img, 0.0, float(vmax) / 65535.0)
+    for _ in range(args.launches):
+        afk.colormap_device(img, lut, 0.0, 65535.0, outb.device_ptr, channels=4, chain=chain)
+        afk.colormap_device(img, lut, float(vmin), float(vmax), outb.device_ptr, channels=4)
+        afk.call("apply_tone_curve", scaled, afk.ToneCurve(np.arange(256, dtype=np.float32)))
+    afk.synchronize()
 elif args.workload == "variance":  # axis0_kernel<VarComp> and <VarSeq> on the ALMA-shape cube
     nz, ny, nx = 3840, 1024, 1024
     cube = afk.Image.synthetic(0xAF1A0003, nz, ny, nx)
