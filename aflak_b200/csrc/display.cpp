@@ -211,9 +211,13 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
                 // NaN, NaN: the chain starts at image_min_max (src/templates.rs: min/max feed convert_to_logscale).  Its result stays
                 // on the device -- no read-back between the two kernels.
                 if ((err = image_wait(img, s))) break;
-                ce = minmax_launch(img->ptr, img->len(), flag + 4, sm_count(dev), s);
-                if (ce != cudaSuccess) { err = cuda_error(ce, "minmax_kernel launch"); break; }
-                a.ls_minmax = flag + 4;
+                if (img->range_valid && img->range) {
+                    a.ls_minmax = img->range; // range memo left by the kernel that wrote the pixels
+                } else {
+                    ce = minmax_launch(img->ptr, img->len(), flag + 4, sm_count(dev), s);
+                    if (ce != cudaSuccess) { err = cuda_error(ce, "minmax_kernel launch"); break; }
+                    a.ls_minmax = flag + 4;
+                }
             }
             a.ls_a = chain->logscale_a; a.ls_min = chain->logscale_vmin; a.ls_max = chain->logscale_vmax;
             a.nm_min = chain->normalize_min; a.nm_max = chain->normalize_max;

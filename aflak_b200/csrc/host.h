@@ -103,6 +103,12 @@ struct afk_image {
     std::mutex mu;
     std::vector<cudaEvent_t> readers; // last reads from other streams, waited on before the memory is freed
     afk::ImageMeta meta;
+    // Range memo: four words {~key(min), key(max), any non-NaN, 0} kept on the device right after the pixels of an image
+    // that image_new allocated.  The kernel that writes the pixels may fill them (range_valid); image_min_max, get_vmin /
+    // get_vmax and the fused consumers then read the range there instead of making a pass over the image.  Images are
+    // immutable values once ready, so a valid memo stays valid.
+    unsigned *range = nullptr;
+    bool range_valid = false;
 
     int64_t len() const {
         int64_t n = 1;

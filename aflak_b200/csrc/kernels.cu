@@ -7,11 +7,16 @@
 // Reference citations are relative to /root/reference/src/.
 #include "kernels.h"
 
+#include <cooperative_groups.h>
+
 #include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
+#include <algorithm>
 
 namespace afk {
 
@@ -102,6 +107,12 @@ struct ReduceKArgs {
     unsigned *sig[kMaxPeers];  // nsig flag words, typically one in every peer's flag array
     int nsig;
     unsigned epoch;
+    // cluster variant (small images): float4 lanes per pixel tile, frame sub-groups per CTA
+    int tile4, jsub;
+    // range memo: the image's {~key(min), key(max), any, 0} left beside the pixels, without atomics on the result and without
+    // a zeroing pass: per-CTA slots + the last CTA to arrive (self-resetting counter) reduces them
+    unsigned *range_out, *range_slots, *range_counter;
+    unsigned long long *trace; // AFK_REDUCE_TRACE=1 (diagnostics): 4 globaltimer stamps per CTA, else nullptr
 };
 
 template <bool COMP> struct Acc {
@@ -214,6 +225,63 @@ __device__ __forceinline__ void block_minmax_flush(float mn, float mx, bool any,
     }
 }
 
+// Range memo of a result image (image_min_max / get_vmin / get_vmax of what this launch wrote, NaN ignored): every CTA
+// leaves its {~key(min), key(max), any} in its own slot; the last CTA to arrive reduces the slots and stores the image's four
+// range words with plain stores.  Nothing has to be zeroed beforehand (the counter resets itself), so a consumer
+// (convert_to_logscale of the template's tail, the display chain, image_min_max itself) finds the range on the device
+// without a min/max pass or a memset.
+__device__ __forceinline__ void block_range_reduce(unsigned &kmn, unsigned &kmx, unsigned &av, unsigned *s_mn, unsigned *s_mx, unsigned *s_any) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+        kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+        av |= __shfl_xor_sync(0xffffffffu, av, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+    if (l == 0) { s_mn[w] = kmn; s_mx[w] = kmx; s_any[w] = av; }
+    __syncthreads();
+    if (w == 0) {
+        kmn = l < nw ? s_mn[l] : 0u;
+        kmx = l < nw ? s_mx[l] : 0u;
+        av = l < nw ? s_any[l] : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+            kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+            av |= __shfl_xor_sync(0xffffffffu, av, o);
+        }
+    }
+}
+__device__ __forceinline__ void block_range_publish(float mn, float mx, bool any, unsigned *slots, unsigned *counter, unsigned *out) {
+    __shared__ unsigned r_mn[32], r_mx[32], r_any[32];
+    __shared__ int r_last;
+    unsigned kmn = any ? ~f32_key(mn) : 0u, kmx = any ? f32_key(mx) : 0u, av = any ? 1u : 0u;
+    block_range_reduce(kmn, kmx, av, r_mn, r_mx, r_any);
+    if (threadIdx.x == 0) {
+        unsigned *sl = slots + (size_t)blockIdx.x * 4;
+        sl[0] = kmn; sl[1] = kmx; sl[2] = av;
+        __threadfence();
+        const unsigned prev = atomicAdd(counter, 1u);
+        r_last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!r_last) return;
+    __threadfence();
+    kmn = 0u; kmx = 0u; av = 0u;
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+        const volatile unsigned *sl = slots + (size_t)i * 4;
+        kmn = max(kmn, sl[0]);
+        kmx = max(kmx, sl[1]);
+        av |= sl[2];
+    }
+    __syncthreads(); // r_mn.. are reused
+    block_range_reduce(kmn, kmx, av, r_mn, r_mx, r_any);
+    if (threadIdx.x == 0) {
+        out[0] = kmn; out[1] = kmx; out[2] = av; out[3] = 0u;
+        *counter = 0u; // self-reset for the next launch
+    }
+}
+
 // create_equivalent_width, lib.rs:1584-1596: four separately rounded steps then the `> max` select
 __device__ __forceinline__ float ew_value(float off, float on, float fl, float mx, float sign) {
     float t = __fsub_rn(off, on);
@@ -254,6 +322,9 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
     // small images, where there are far fewer pixel lanes than threads on the chip).  KG == 8: one warp per group.
     constexpr int LANES = kReduceBlock / KG;
     constexpr int64_t TILE = (int64_t)LANES * VEC;
+    // a dependent elementwise kernel launched with programmatic stream serialization may be scheduled now; it blocks in
+    // griddepcontrol.wait until this grid has completed and its memory is visible
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int tid = threadIdx.x;
     const int lane = tid % LANES, kg = tid / LANES;
     const int64_t g = blockIdx.x;
@@ -420,6 +491,7 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
         u = seg_end;
     }
     if (a.minmax) block_minmax_flush(mm_min, mm_max, mm_any, a.minmax);
+    if (a.range_out) block_range_publish(mm_min, mm_max, mm_any, a.range_slots, a.range_counter, a.range_out);
     if (a.done) {
         // Fused gather epilogue: make this CTA's (peer) stores visible system-wide, count the arrival; the last CTA
         // of the grid publishes the epoch to every destination's flag word with release semantics.
@@ -435,6 +507,179 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
             }
         }
     }
+}
+
+// ----------------------------------------------------------------------------------------------------
+// Small images (MaNGA 74x74x4563: far fewer pixel lanes than threads on the chip): thread-block clusters.
+//
+// One cluster owns one pixel tile of `tile4` float4 lanes at a time; the tile's concatenated window frames are
+// split evenly over the cluster's CTAs, and inside a CTA over `jsub` interleaved frame sub-groups (thread =
+// (lane, sub-group), so a warp's 16-byte loads of one frame are contiguous).  Every thread keeps U independent
+// loads in flight; the remainder is one predicated batch (one memory latency, not log2(U) of them).
+// Merge: sub-groups through shared memory, then the CTAs of the cluster through DISTRIBUTED shared memory --
+// CTA r finishes pixel slice r of the tile from every CTA's partials in rank order (deterministic).  No global
+// scratch, no arrival counters, no fences: this replaces the f64-partials round trip of reduce_kernel, which
+// costs ~8 us of a 33 us launch at this size (tools/c1_probe.cu, profiles/r2_c1_probe.txt).
+// ----------------------------------------------------------------------------------------------------
+namespace cg = cooperative_groups;
+
+__device__ __forceinline__ void cl_stamp(const ReduceKArgs &a, int slot) {
+    if (a.trace && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.trace[(size_t)blockIdx.x * 4 + slot] = t;
+    }
+}
+template <int H> __device__ __forceinline__ void cl_load(float4 (&x)[H], const char *ptr, size_t stride, int64_t n) {
+#pragma unroll
+    for (int u = 0; u < H; ++u)
+        if (u < n) x[u] = ld_stream(reinterpret_cast<const float4 *>(ptr + (size_t)u * stride));
+}
+template <int H> __device__ __forceinline__ void cl_add(Acc<true> (&acc)[4], const float4 (&x)[H], int64_t n) {
+#pragma unroll
+    for (int u = 0; u < H; ++u)
+        if (u < n) {
+            acc_add<true>(acc[0], x[u].x);
+            acc_add<true>(acc[1], x[u].y);
+            acc_add<true>(acc[2], x[u].z);
+            acc_add<true>(acc[3], x[u].w);
+        }
+}
+// the same pixel of every CTA's partial, all remote loads issued before the first add (rank order kept in the sum)
+template <int CS> __device__ __forceinline__ void cl_gather(cg::cluster_group &cl, double2 *part, size_t idx, int C, double &d, float &pl) {
+    for (int c0 = 0; c0 < C; c0 += CS) {
+        double2 v[CS];
+#pragma unroll
+        for (int c = 0; c < CS; ++c)
+            if (c0 + c < C) v[c] = cl.map_shared_rank(part, c0 + c)[idx];
+#pragma unroll
+        for (int c = 0; c < CS; ++c)
+            if (c0 + c < C) {
+                d += v[c].x;
+                pl = __fadd_rn(pl, (float)v[c].y);
+            }
+    }
+}
+
+template <int NW, int U>
+__global__ void __launch_bounds__(kReduceBlock, 2) reduce_cluster_kernel(const ReduceKArgs a) {
+    extern __shared__ __align__(16) unsigned char cl_smem[];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    cg::cluster_group cl = cg::this_cluster();
+    const int C = (int)cl.num_blocks(), rank = (int)cl.block_rank();
+    const int ncl = (int)gridDim.x / C, cid = (int)blockIdx.x / C;
+    const int tid = threadIdx.x;
+    const int li = tid % a.tile4, j = tid / a.tile4;
+    const int tpx = a.tile4 * 4;
+    double2 *part = reinterpret_cast<double2 *>(cl_smem); // [NW][tpx]   this CTA's share of the tile, read by the cluster
+    double2 *comb = part + (size_t)NW * tpx;              // [jsub][NW][tpx]
+    const int64_t kc = (a.ktot + C - 1) / C;
+    const int64_t r0 = (int64_t)rank * kc, r1 = min(a.ktot, r0 + kc);
+    const int64_t n4tot = a.n2 / 4;
+
+    float mm_min = __int_as_float(0x7f800000), mm_max = __int_as_float(0xff800000);
+    bool mm_any = false;
+    cl_stamp(a, 0);
+
+    for (int64_t tile = cid; tile < a.ntiles; tile += ncl) {
+        const int64_t l0 = tile * a.tile4;
+        const int n4 = (int)min((int64_t)a.tile4, n4tot - l0);
+        const bool active = (j < a.jsub) && (li < n4);
+        // every thread leaves its (f64 value, plain f32 sum) per window in shared memory right away: nothing is carried in
+        // registers from one window to the next
+        double2 *mine = (a.jsub > 1 ? comb + (size_t)j * NW * tpx : part) + li * 4;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
+            double dv[4];
+            float pv[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { dv[e] = -0.0; pv[e] = -0.0f; }
+            const int64_t lo = max(r0, a.woff[w]) + j, hi = min(r1, a.woff[w + 1]);
+            if (active && lo < hi) {
+                Acc<true> acc[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc_init<true>(acc[e]);
+                int64_t n = (hi - lo + a.jsub - 1) / a.jsub; // this thread's frames: lo, lo + jsub, ...
+                const size_t stride = (size_t)a.n2 * sizeof(float) * (size_t)a.jsub;
+                const char *ptr = reinterpret_cast<const char *>(a.cube + (a.start[w] + (lo - a.woff[w])) * a.n2 + (l0 + li) * 4);
+                // two half-batches in ping-pong: the loads of the next half are in flight while this half is added
+                constexpr int H = U / 2;
+                float4 xa[H], xb[H];
+                cl_load<H>(xa, ptr, stride, n);
+                while (n > 0) {
+                    cl_load<H>(xb, ptr + (size_t)H * stride, stride, n - H);
+                    cl_add<H>(acc, xa, n);
+                    if (n <= H) break;
+                    cl_load<H>(xa, ptr + (size_t)U * stride, stride, n - U);
+                    cl_add<H>(acc, xb, n - H);
+                    n -= U;
+                    ptr += (size_t)U * stride;
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { dv[e] = acc_value<true>(acc[e]); pv[e] = acc[e].p; }
+            }
+            if (active) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) mine[(size_t)w * tpx + e] = make_double2(dv[e], (double)pv[e]);
+            }
+        }
+        // sub-groups -> this CTA's partial, in sub-group order
+        if (a.jsub > 1) {
+            __syncthreads();
+            cl_stamp(a, 1);
+            if (active && j == 0) {
+#pragma unroll
+                for (int w = 0; w < NW; ++w)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        double d = -0.0;
+                        float pl = -0.0f;
+                        for (int jj = 0; jj < a.jsub; ++jj) {
+                            const double2 v = comb[((size_t)jj * NW + w) * tpx + li * 4 + e];
+                            d += v.x;
+                            pl = __fadd_rn(pl, (float)v.y);
+                        }
+                        part[(size_t)w * tpx + li * 4 + e] = make_double2(d, (double)pl);
+                    }
+            }
+        }
+        cl.sync();
+        cl_stamp(a, 2);
+        // CTA `rank` finishes pixel slice `rank` of the tile from every CTA's partial, in rank order.  tile4 <= 64 lanes
+        // (reduce_plan_cluster), so a slice is at most 256 / C pixels: one pixel per thread.
+        {
+            const int npx = n4 * 4;
+            const int pc = (npx + C - 1) / C;
+            const int q = rank * pc + tid;
+            const bool mine_px = tid < pc && q < npx;
+            float S[NW];
+            if (mine_px) {
+#pragma unroll
+                for (int w = 0; w < NW; ++w) {
+                    double d = -0.0;
+                    float pl = -0.0f;
+                    cl_gather<4>(cl, part, (size_t)w * tpx + q, C, d, pl);
+                    S[w] = finalize_sum(d, pl);
+                }
+            }
+            // the remote partials are in registers: let the other CTAs run ahead (their partials may be overwritten by the
+            // next tile, or their CTA may exit, only after every reader has arrived)
+            asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+            if (mine_px) {
+                const float o = reduce_epilogue<NW>(a, S);
+                if (o == o) {
+                    mm_min = fminf(mm_min, o);
+                    mm_max = fmaxf(mm_max, o);
+                    mm_any = true;
+                }
+                a.out[0][l0 * 4 + q] = o;
+            }
+            asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        }
+        cl_stamp(a, 3);
+    }
+    if (a.minmax) block_minmax_flush(mm_min, mm_max, mm_any, a.minmax);
+    if (a.range_out) block_range_publish(mm_min, mm_max, mm_any, a.range_slots, a.range_counter, a.range_out);
 }
 
 // Stream-ordered wait of the fused gather: lane i spins until flags[i] >= epoch (epochs are monotonic), with a
@@ -490,6 +735,88 @@ static float count_as_f32(int64_t n) {
 
 int reduce_tune_ctas();
 int reduce_tune_kg();
+static int env_int(const char *name, int dflt);
+
+constexpr int kClusterMaxTile4 = 128;                 // float4 lanes per tile (<= kReduceBlock)
+constexpr size_t kClusterMaxSmem = (size_t)(kMaxWindows * kClusterMaxTile4 * 4 + kMaxWindows * kReduceBlock * 4) * sizeof(double2);
+
+template <typename K> static cudaError_t cluster_kernel_attrs(K kernel) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kClusterMaxSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    return e;
+}
+
+// How many clusters of `csize` CTAs the device keeps resident at once (worst-case shared memory); cached per size.
+static int cluster_capacity(int csize) {
+    static std::atomic<int> cache[17];
+    if (csize < 1 || csize > 16) return 0;
+    int v = cache[csize].load(std::memory_order_relaxed);
+    if (v != 0) return v < 0 ? 0 : v;
+    int n = 0;
+    if (cluster_kernel_attrs(reduce_cluster_kernel<1, 16>) == cudaSuccess) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(csize * 64);
+        cfg.blockDim = dim3(kReduceBlock);
+        cfg.dynamicSmemBytes = kClusterMaxSmem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = csize;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        if (cudaOccupancyMaxActiveClusters(&n, reduce_cluster_kernel<1, 16>, &cfg) != cudaSuccess) n = 0;
+    }
+    cudaGetLastError();
+    cache[csize].store(n > 0 ? n : -1, std::memory_order_relaxed);
+    return n;
+}
+
+// AFK_REDUCE_CLUSTER: 0 disables the cluster variant, N = 2|4|8|16 sets the cluster size (default 8).
+static void reduce_plan_cluster(const ReduceArgs &a, ReducePlan &pl) {
+    static const int want = env_int("AFK_REDUCE_CLUSTER", 8);
+    static const int jmax = env_int("AFK_REDUCE_CLUSTER_JMAX", 8);
+    if (want < 1 || a.mode == SUM_SEQUENTIAL) return;
+    // template-sized windows (3 x 20 frames, 1.3 MB) are one load batch either way: the cluster launch and its two
+    // barriers cost more than they save (measured 16.4 vs 14.3 us, profiles/r2_cluster_tuning.jsonl)
+    if (pl.ktot < 128) return;
+    int C = want > 16 ? 16 : want;
+    const int64_t n4tot = a.n2 / 4;
+    int cap = 0;
+    int64_t tile4 = 0;
+    int jsub = 1;
+    for (;; C /= 2) {
+        cap = cluster_capacity(C);
+        if (cap > 0) {
+            const int64_t waves = (n4tot + (int64_t)cap * kClusterMaxTile4 - 1) / ((int64_t)cap * kClusterMaxTile4);
+            tile4 = (n4tot + cap * waves - 1) / (cap * waves);
+            if (tile4 < 1) tile4 = 1;
+            jsub = (int)(kReduceBlock / tile4);
+            if (jsub > jmax) jsub = jmax;
+            if (jsub < 1) jsub = 1;
+            // every (CTA, sub-group) should own at least two frames; otherwise a smaller cluster does the same work
+            if (C == 1 || pl.ktot >= (int64_t)C * jsub * 2) break;
+        }
+        if (C == 1) return; // no cluster launch possible on this device/context: keep the stream-K kernel
+    }
+    // Measured (profiles/r2_cluster_tuning.jsonl): the variant wins while a tile is narrow enough for >= 4 frame sub-groups
+    // per CTA (74x74: 25.0 vs 28.1 us back to back); at 128x128 it ties and at 300x300 the stream-K kernel is 20 % faster.
+    if (C < 4 || tile4 > kReduceBlock / 4) return;
+    const int64_t ntiles = (n4tot + tile4 - 1) / tile4;
+    const int64_t ncl = ntiles < cap ? ntiles : cap;
+    pl.cluster = C;
+    pl.tile4 = (int)tile4;
+    pl.jsub = jsub;
+    pl.cl_unroll = 16;
+    pl.ntiles = ntiles;
+    pl.units = ntiles * pl.ktot;
+    pl.q = (pl.ktot + C - 1) / C;
+    pl.grid = (int)(ncl * C);
+    pl.cl_smem = (size_t)(a.nwin * tile4 * 4 + (jsub > 1 ? (size_t)jsub * a.nwin * tile4 * 4 : 0)) * sizeof(double2);
+    pl.partial_bytes = 0;
+    pl.n_counters = 0;
+}
+
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     ReducePlan pl{};
     bool aligned = (a.n2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.cube) & 15u) == 0) &&
@@ -522,6 +849,12 @@ ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     pl.grid = (int)((pl.units + pl.q - 1) / pl.q);
     pl.partial_bytes = (size_t)pl.grid * 2 * a.nwin * tile * sizeof(double2);
     pl.n_counters = (size_t)pl.ntiles;
+    if (pl.kg > 1 && pl.vec == 4 && a.n_signal == 0 && a.n_extra_out == 0) reduce_plan_cluster(a, pl);
+    // range memo: 4 words per CTA after the partials, one more self-resetting counter after the tile counters
+    pl.range_slot_offset = (pl.partial_bytes + 15) / 16 * 16;
+    pl.partial_bytes = pl.range_slot_offset + (size_t)pl.grid * 4 * sizeof(unsigned);
+    pl.range_counter_index = pl.n_counters;
+    pl.n_counters += 1;
     return pl;
 }
 
@@ -560,6 +893,85 @@ static cudaError_t reduce_dispatch_tune(const ReduceKArgs &k, int grid, int kg, 
     AFK_TUNE(8, 4); AFK_TUNE(8, 2); AFK_TUNE(16, 2); AFK_TUNE(16, 3);
 #undef AFK_TUNE
     return reduce_dispatch_nw<VEC, COMP, 8, 3>(k, grid, s);
+}
+
+// Diagnostics (AFK_REDUCE_TRACE=1): per-CTA globaltimer stamps -> phase durations on stderr.  Synchronises.
+template <typename K> static cudaError_t reduce_cluster_traced(cudaLaunchConfig_t &cfg, K kernel, ReduceKArgs k) {
+    const size_t n = (size_t)cfg.gridDim.x * 4;
+    unsigned long long *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, n * 8);
+    if (e != cudaSuccess) return e;
+    cudaMemset(d, 0, n * 8);
+    k.trace = d;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaEventRecord(e0, cfg.stream);
+    e = cudaLaunchKernelEx(&cfg, kernel, k);
+    cudaEventRecord(e1, cfg.stream);
+    AFK_COUNT_LAUNCH();
+    cudaStreamSynchronize(cfg.stream);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    std::vector<unsigned long long> h(n);
+    cudaMemcpy(h.data(), d, n * 8, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    unsigned long long lo[4], hi[4];
+    for (int sl = 0; sl < 4; ++sl) { lo[sl] = ~0ull; hi[sl] = 0; }
+    for (size_t i = 0; i < n; ++i) {
+        if (!h[i]) continue;
+        lo[i & 3] = std::min(lo[i & 3], h[i]);
+        hi[i & 3] = std::max(hi[i & 3], h[i]);
+    }
+    const double t0 = (double)lo[0];
+    fprintf(stderr, "[afk trace] grid %u events %.2f us | start %.2f..%.2f | stream done %.2f..%.2f | cluster synced %.2f..%.2f | end %.2f..%.2f (us after the first CTA start)\n",
+            cfg.gridDim.x, ms * 1e3, 0.0, (hi[0] - t0) / 1e3, (lo[1] - t0) / 1e3, (hi[1] - t0) / 1e3, (lo[2] - t0) / 1e3, (hi[2] - t0) / 1e3,
+            (lo[3] - t0) / 1e3, (hi[3] - t0) / 1e3);
+    return e;
+}
+
+template <int NW> static cudaError_t reduce_cluster_go(const ReduceKArgs &k, const ReducePlan &pl, cudaStream_t s) {
+    static const cudaError_t attrs = cluster_kernel_attrs(reduce_cluster_kernel<NW, 16>); // once per instantiation
+    if (attrs != cudaSuccess) return attrs;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl.grid);
+    cfg.blockDim = dim3(kReduceBlock);
+    cfg.dynamicSmemBytes = pl.cl_smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)pl.cluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    static const int trace = env_int("AFK_REDUCE_TRACE", 0);
+    if (trace) return reduce_cluster_traced(cfg, reduce_cluster_kernel<NW, 16>, k);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, reduce_cluster_kernel<NW, 16>, k);
+    AFK_COUNT_LAUNCH();
+    return e;
+}
+
+static cudaError_t reduce_cluster_dispatch(const ReduceKArgs &k, const ReducePlan &pl, cudaStream_t s) {
+    switch (k.nwin) {
+    case 1: return reduce_cluster_go<1>(k, pl, s);
+    case 2: return reduce_cluster_go<2>(k, pl, s);
+    case 3: return reduce_cluster_go<3>(k, pl, s);
+    }
+    return cudaErrorInvalidValue;
+}
+
+void reduce_describe(const ReduceArgs &a, const ReducePlan &pl, char *buf, size_t cap) {
+    if (pl.cluster > 0) {
+        snprintf(buf, cap, "reduce_cluster_kernel<NW=%d,U=%d> grid=%d block=%d cluster=%d tiles=%lld lanes_per_tile=%d frame_subgroups=%d frames_per_pixel=%lld frames_per_cta=%lld smem=%zu",
+                 a.nwin, pl.cl_unroll, pl.grid, kReduceBlock, pl.cluster, (long long)pl.ntiles, pl.tile4, pl.jsub, (long long)pl.ktot, (long long)pl.q, pl.cl_smem);
+        return;
+    }
+    const ReduceVariant v = reduce_variant(a, pl);
+    snprintf(buf, cap, "reduce_kernel<VEC=%d,COMP=%d,NW=%d,U=%d,MINB=%d,KG=%d> grid=%d block=%d tiles=%lld frames_per_pixel=%lld units_per_cta=%lld",
+             v.vec, v.comp, v.nw, v.unroll, v.min_blocks, v.kg, pl.grid, kReduceBlock, (long long)pl.ntiles, (long long)pl.ktot, (long long)pl.q);
 }
 
 // mirrors the dispatch below (reduce_dispatch_tune / reduce_dispatch_nw)
@@ -616,8 +1028,17 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
     k.minmax = a.minmax;
     k.partials = static_cast<double2 *>(ws.partials);
     k.counters = ws.counters;
+    k.range_out = a.range_out;
+    k.range_slots = reinterpret_cast<unsigned *>(static_cast<char *>(ws.partials) + pl.range_slot_offset);
+    k.range_counter = ws.counters + pl.range_counter_index;
     const bool comp = a.mode != SUM_SEQUENTIAL;
     if (!comp && pl.kg != 1) return cudaErrorInvalidValue;
+    if (pl.cluster > 0) {
+        if (!comp || pl.vec != 4 || a.n_signal > 0 || a.n_extra_out > 0 || pl.cl_smem > kClusterMaxSmem) return cudaErrorInvalidValue;
+        k.tile4 = pl.tile4;
+        k.jsub = pl.jsub;
+        return reduce_cluster_dispatch(k, pl, s);
+    }
     if (pl.vec == 4) return comp ? reduce_dispatch_tune<4, true>(k, pl.grid, pl.kg, s) : reduce_dispatch_tune<4, false>(k, pl.grid, 1, s);
     return comp ? reduce_dispatch_tune<1, true>(k, pl.grid, pl.kg, s) : reduce_dispatch_tune<1, false>(k, pl.grid, 1, s);
 }
@@ -686,6 +1107,9 @@ template <int OP, bool BINARY>
 __global__ void __launch_bounds__(256) map_kernel(const float *__restrict__ u, const float *__restrict__ v,
                                                    float *__restrict__ out, int64_t n, int vec_ok, MapK k) {
     constexpr int U = BINARY ? 2 : 4;
+    // programmatic dependent launch (map_go): this grid may be scheduled while the kernel before it in the stream drains;
+    // nothing of that kernel's output is touched before this point
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (OP == MAP_LOGSCALE && k.mm != nullptr) {
         // image_min_max (lib.rs:180-197) left on the device by minmax_kernel; FLT_MAX / -FLT_MAX are the operator's initial values
         const bool any = k.mm[2] != 0u;
@@ -737,8 +1161,20 @@ static int grid_for(int64_t work_items, int block, int sm_count, int ctas_per_sm
     return (int)(need < cap ? need : cap);
 }
 
+// AFK_PDL=0 switches programmatic dependent launch off (plain stream order)
+static bool pdl_enabled() { static const int v = env_int("AFK_PDL", 1); return v != 0; }
+
 template <int OP, bool BINARY> static void map_go(const MapArgs &a, const MapK &k, int vec_ok, int grid, cudaStream_t s) {
-    map_kernel<OP, BINARY><<<grid, 256, 0, s>>>(a.u, a.v, a.out, a.n, vec_ok, k);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(256);
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, map_kernel<OP, BINARY>, a.u, a.v, a.out, a.n, vec_ok, k);
 }
 
 cudaError_t map_launch(const MapArgs &a, int sm_count, cudaStream_t s) {

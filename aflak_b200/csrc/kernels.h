@@ -40,6 +40,8 @@ struct ReduceArgs {
     float ew_sign;     // -1 emission, +1 absorption
     float *out;        // [n2] (may be a peer-mapped pointer)
     unsigned *minmax;  // optional: {~key(min), key(max), any-non-NaN} accumulated with atomicMax, or nullptr
+    unsigned *range_out; // optional: the same three words (+ a zero) for the result image, written once by the last CTA -- needs
+                         // no zeroing beforehand (the range memo kept beside an image's pixels)
     // fused gather: the same result is also stored to n_extra_out more buffers (peer-mapped over NVLink),
     // and when the whole grid has stored, `epoch` is written to each signal word (release, system scope).
     int n_extra_out;
@@ -67,11 +69,22 @@ struct ReducePlan {
     int grid;
     size_t partial_bytes;
     size_t n_counters;
+    size_t range_slot_offset;   // byte offset of the per-CTA range slots inside the partials scratch
+    size_t range_counter_index; // index of the range memo's arrival counter
+    // small images in compensated mode: reduce_cluster_kernel (thread-block clusters, merge through distributed shared
+    // memory).  cluster == 0: the stream-K reduce_kernel above.
+    int cluster;         // CTAs per cluster (k split), 0 = not used
+    int tile4;           // float4 lanes per pixel tile
+    int jsub;            // interleaved frame sub-groups per CTA
+    int cl_unroll;       // independent 16-byte loads per thread
+    size_t cl_smem;      // dynamic shared memory per CTA
 };
 
 ReducePlan reduce_plan(const ReduceArgs &a, int sm_count);
 struct ReduceVariant { int vec, comp, nw, unroll, min_blocks, kg; }; // template arguments reduce_launch instantiates
 ReduceVariant reduce_variant(const ReduceArgs &a, const ReducePlan &plan);
+// the kernel instantiation and launch shape of this plan as text (reports name the kernel that ran)
+void reduce_describe(const ReduceArgs &a, const ReducePlan &plan, char *buf, size_t cap);
 cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &plan, const ReduceWorkspace &ws, cudaStream_t s);
 
 // stream-ordered wait until flags[i] >= epoch for i < n (n <= kMaxPeers).  A flag that times out (bound derived from the

@@ -252,6 +252,7 @@ Error op_reduce(const afk_image *cube, int nwin, const int64_t *starts, const in
     for (int i = 0; i < 4; ++i) a.p[i] = params ? params[i] : 0.0f;
     a.ew_sign = ew_sign;
     a.out = o->ptr;
+    a.range_out = o->range; // range memo: a following image_min_max / logscale / display call needs no pass over the image
     Error err = ok();
     unsigned *mm = nullptr;
     do {
@@ -280,6 +281,7 @@ Error op_reduce(const afk_image *cube, int nwin, const int64_t *starts, const in
             break;
         }
         image_note_read(cube, s);
+        o->range_valid = o->range != nullptr;
         if (want_minmax) {
             unsigned h[4];
             ce = cudaMemcpyAsync(h, mm, sizeof h, cudaMemcpyDeviceToHost, s);
@@ -341,13 +343,15 @@ Error op_min_max(const afk_image *img, float *mn, float *mx, bool *any) {
     if (Error e = current_stream(&s, &dev)) return e;
     if (Error e = same_device(img, dev)) return e;
     unsigned *mm = nullptr;
-    if (Error e = scratch_u32(s, 4, &mm)) return e;
+    const bool memo = img->range_valid && img->range; // left by the kernel that wrote the pixels: no pass over the image
+    if (!memo)
+        if (Error e = scratch_u32(s, 4, &mm)) return e;
     Error err = ok();
     unsigned h[4] = {0, 0, 0, 0};
     do {
         if ((err = image_wait(img, s))) break;
-        cudaError_t ce = minmax_launch(img->ptr, img->len(), mm, sm_count(dev), s);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, mm, sizeof h, cudaMemcpyDeviceToHost, s);
+        cudaError_t ce = memo ? cudaSuccess : minmax_launch(img->ptr, img->len(), mm, sm_count(dev), s);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, memo ? img->range : mm, sizeof h, cudaMemcpyDeviceToHost, s);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
         if (ce != cudaSuccess) {
             err = cuda_error(ce, "minmax_kernel");
@@ -1374,14 +1378,15 @@ afk_status afk_fused_logscale_minmax(const afk_image *img, float a, afk_image **
     afk_image *o = nullptr;
     if (Error e = image_new(img->ndim, img->shape, &o)) return fail(e);
     unsigned *mm = nullptr;
-    Error err = scratch_u32(s, 4, &mm);
+    const bool memo = img->range_valid && img->range; // the producer left the range beside the pixels: one launch, not three
+    Error err = memo ? ok() : scratch_u32(s, 4, &mm);
     do {
         if (err) break;
         if ((err = image_wait(img, s))) break;
-        cudaError_t ce = minmax_launch(img->ptr, img->len(), mm, sm_count(dev), s);
+        cudaError_t ce = memo ? cudaSuccess : minmax_launch(img->ptr, img->len(), mm, sm_count(dev), s);
         if (ce == cudaSuccess) {
             MapArgs m{MAP_LOGSCALE, img->ptr, nullptr, a, 0.0f, 0.0f, 0, 0, img->len(), o->ptr};
-            m.bc_minmax = mm;
+            m.bc_minmax = memo ? img->range : mm;
             ce = map_launch(m, sm_count(dev), s);
         }
         if (ce != cudaSuccess) {
@@ -1500,9 +1505,7 @@ int afk_k_reduce_describe(const float *cube, int64_t n2, int nwin, const int64_t
     int dev;
     if (Error e = current_stream(&s, &dev)) return fail(e);
     const ReducePlan pl = reduce_plan(a, sm_count(dev));
-    const ReduceVariant v = reduce_variant(a, pl);
-    snprintf(buf, cap, "reduce_kernel<VEC=%d,COMP=%d,NW=%d,U=%d,MINB=%d,KG=%d> grid=%d block=%d tiles=%lld frames_per_pixel=%lld units_per_cta=%lld",
-             v.vec, v.comp, v.nw, v.unroll, v.min_blocks, v.kg, pl.grid, kReduceBlock, (long long)pl.ntiles, (long long)pl.ktot, (long long)pl.q);
+    reduce_describe(a, pl, buf, cap);
     return AFK_OK;
 }
 

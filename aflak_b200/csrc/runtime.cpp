@@ -267,8 +267,9 @@ Error image_new(int ndim, const int64_t *shape, afk_image **out) {
                 (unsigned long long)(reserved >> 20), (unsigned long long)(used >> 20), (unsigned long long)thr, pool == cur);
     }
     const auto t0 = std::chrono::steady_clock::now();
-    cudaError_t ce = (img->bytes >= kBigAllocBytes && g_big_pool[dev]) ? cudaMallocFromPoolAsync(&p, img->bytes, g_big_pool[dev], s)
-                                                                       : cudaMallocAsync(&p, img->bytes ? img->bytes : 16, s);
+    const size_t data_bytes = (img->bytes + 15) / 16 * 16, alloc_bytes = data_bytes + 16; // + the range memo (host.h)
+    cudaError_t ce = (img->bytes >= kBigAllocBytes && g_big_pool[dev]) ? cudaMallocFromPoolAsync(&p, alloc_bytes, g_big_pool[dev], s)
+                                                                       : cudaMallocAsync(&p, alloc_bytes, s);
     if (trace_enabled() && img->bytes >= ((size_t)64 << 20))
         fprintf(stderr, "[afk] cudaMallocAsync(%zu MiB) took %.2f ms\n", img->bytes >> 20,
                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
@@ -277,6 +278,7 @@ Error image_new(int ndim, const int64_t *shape, afk_image **out) {
         return cuda_error(ce, "cudaMallocAsync(image)");
     }
     img->ptr = static_cast<float *>(p);
+    img->range = reinterpret_cast<unsigned *>(static_cast<char *>(p) + data_bytes);
     img->ready = event_get();
     *out = img;
     return ok();

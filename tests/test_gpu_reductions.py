@@ -164,3 +164,42 @@ def test_float_arguments_are_converted(gpu, orc):
     a = gpu.call("integral", cube, 1.6, 7.4)[0].download()  # -> [2, 7)
     b = gpu.call("integral", cube, 2, 7)[0].download()
     assert_bit_equal(a, b)
+
+
+def test_range_memo_left_by_the_reduce_kernel(gpu, orc):
+    """The kernel that writes a reduction's pixels also leaves image_min_max of them beside the image (the range memo): a
+    following image_min_max / get_vmin / get_vmax launches no kernel and returns the reference's values (lib.rs:180-197,
+    lims.rs:7-35), the fused logscale tail takes one launch; NaN results are ignored, an all-NaN result keeps the
+    operators' initial values.  Covers the stream-K kernel, its small-image variants and the cluster variant."""
+    for shape, win in [((96, 37, 52), (10, 90)), ((300, 74, 74), (0, 300)), ((64, 300, 260), (3, 61)), ((40, 8, 4), (0, 40))]:
+        nz, ny, nx = shape
+        host = orc.gen_cube(0xAF1A0070 + nz, nz, ny, nx, pathology=True)
+        cube = gpu.Image.upload(host)
+        for mode in (gpu.SUM_COMPENSATED, gpu.SUM_SEQUENTIAL):
+            gpu.set_sum_mode(mode)
+            try:
+                for op in ("integral", "average"):
+                    img = gpu.call(op, cube, *win)[0]
+                    got = img.download()
+                    l0 = gpu.launch_count()
+                    mn, mx = gpu.call("image_min_max", img)
+                    vmin, vmax = img.vmin_vmax()
+                    assert gpu.launch_count() == l0, "image_min_max of a reduction result must come from the range memo"
+                    omn, omx = orc.image_min_max(got)
+                    assert (np.float32(mn), np.float32(mx)) == (np.float32(omn), np.float32(omx)), (shape, mode, op)
+                    assert np.float32(vmin) == np.float32(orc.get_vmin(got)) and np.float32(vmax) == np.float32(orc.get_vmax(got))
+                    l0 = gpu.launch_count()
+                    ls = gpu.fused_logscale_minmax(img, 1000.0).download()
+                    assert gpu.launch_count() == l0 + 1
+                    want = gpu.call("convert_to_logscale", img, 1000.0, float(mn), float(mx)).download()
+                    assert np.array_equal(np.isnan(ls), np.isnan(want)) and np.array_equal(ls[~np.isnan(ls)], want[~np.isnan(want)])
+            finally:
+                gpu.set_sum_mode(gpu.SUM_COMPENSATED)
+    # all-NaN result
+    nanc = gpu.Image.upload(np.full((5, 6, 8), np.nan, np.float32))
+    img = gpu.call("integral", nanc, 0, 5)[0]
+    l0 = gpu.launch_count()
+    mn, mx = gpu.call("image_min_max", img)
+    assert gpu.launch_count() == l0
+    omn, omx = orc.image_min_max(img.download())
+    assert (np.float32(mn), np.float32(mx)) == (np.float32(omn), np.float32(omx))
