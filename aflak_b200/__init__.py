@@ -209,6 +209,8 @@ _sig("afk_gather_reduce", C.c_int, _P, _P, C.c_int64, C.c_int, _i64p, _i64p, C.c
 _sig("afk_gather_wait", C.c_int, _P, C.POINTER(C.c_void_p), C.c_double)
 _sig("afk_gather_check", C.c_int, _P)
 _sig("afk_gather_result_image", _P, _P)
+_sig("afk_gather_colormap", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, _P)
+_sig("afk_gather_wait_rgba", C.c_int, _P, C.POINTER(C.c_void_p), C.c_double)
 _sig("afk_gather_destroy", None, _P)
 _sig("afk_graph_new", _P)
 _sig("afk_graph_free", None, _P)
@@ -777,6 +779,28 @@ class Gather:
 
     def result_image(self):
         return Image(lib.afk_gather_result_image(self._h))
+
+    def colormap(self, lut, vmin=float("nan"), vmax=float("nan"), flip_y=True, chain=None):
+        """Colour-map this rank's band of the gathered image and gather the RGBA8 bands on every rank (afk_gather_colormap)."""
+        st, keep = _chain_struct(chain)
+        _check(lib.afk_gather_colormap(self._h, lut.handle, vmin, vmax, int(flip_y), C.byref(st) if st else None))
+        del keep
+
+    def display(self, lut, vmin=float("nan"), vmax=float("nan"), flip_y=True, chain=None):
+        """colormap + wait_rgba + download: this rank's full [ny, nx, 4] uint8 image on the host."""
+        self.colormap(lut, vmin, vmax, flip_y, chain)
+        ptr = self.wait_rgba()
+        if self.ny * self.nx == 0:
+            return np.empty((self.ny, self.nx, 4), dtype=np.uint8)
+        # 4 bytes per pixel: read the byte image back through a borrowed f32 view of the same memory
+        px = Image.wrap_device(ptr, (self.ny, self.nx)).download()
+        return px.view(np.uint8).reshape(self.ny, self.nx, 4)
+
+    def wait_rgba(self, timeout_s=5.0):
+        """Enqueue the wait; returns the device pointer of this rank's full [ny, nx, 4] uint8 image."""
+        p = C.c_void_p()
+        _check(lib.afk_gather_wait_rgba(self._h, C.byref(p), timeout_s))
+        return p.value
 
     def close(self):
         if getattr(self, "_h", None) and lib is not None:

@@ -107,6 +107,8 @@ struct ReduceKArgs {
     unsigned *sig[kMaxPeers];  // nsig flag words, typically one in every peer's flag array
     int nsig;
     unsigned epoch;
+    int n_range_peer;
+    unsigned *range_peer[kMaxPeers - 1];
     // cluster variant (small images): float4 lanes per pixel tile, frame sub-groups per CTA
     int tile4, jsub;
     // range memo: the image's {~key(min), key(max), any, 0} left beside the pixels, without atomics on the result and without
@@ -501,6 +503,15 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
             const unsigned prev = atomicAdd(a.done, 1u);
             if (prev == gridDim.x - 1) {
                 *a.done = 0u; // self-reset for the next launch
+                if (a.range_out) {
+                    // min/max exchange: every CTA has been through block_range_publish, so the band's range words are final
+                    __threadfence();
+                    unsigned rw[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) rw[i] = *reinterpret_cast<volatile unsigned *>(a.range_out + i);
+                    for (int d = 0; d < a.n_range_peer; ++d)
+                        *reinterpret_cast<uint4 *>(a.range_peer[d]) = make_uint4(rw[0], rw[1], rw[2], rw[3]);
+                }
                 __threadfence_system();
                 for (int d = 0; d < a.nsig; ++d)
                     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.sig[d]), "r"(a.epoch) : "memory");
@@ -702,12 +713,59 @@ __global__ void gather_wait_kernel(const GatherWaitArgs a, long long max_cycles)
         }
     }
     unsigned bad = __ballot_sync(0xffffffffu, timed_out);
+    if (a.combined) {
+        // min/max exchange: the bands' ranges arrived before their flags (release / acquire); combine them in the warp
+        unsigned kmn = 0u, kmx = 0u, av = 0u;
+        if (i < a.n && !timed_out) {
+            const volatile unsigned *rp = a.ranges + 4 * i;
+            const uint3 r = make_uint3(rp[0], rp[1], rp[2]);
+            kmn = r.x; kmx = r.y; av = r.z;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+            kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o));
+            av |= __shfl_xor_sync(0xffffffffu, av, o);
+        }
+        if (i == 0) *reinterpret_cast<uint4 *>(a.combined) = make_uint4(kmn, kmx, av, 0u);
+    }
     while (bad) { // error path only: the whole warp poisons the band that never arrived
         const int r = __ffs(bad) - 1;
         bad &= bad - 1;
         float *p = a.image + a.band_off[r];
         for (int64_t j = i; j < a.band_len[r]; j += 32) p[j] = __int_as_float(0x7fc00000);
     }
+}
+
+// Band broadcast: 16-byte words of this rank's band to every peer's copy, then the epoch flags (same arrival protocol as
+// the fused gather of reduce_kernel).
+__global__ void __launch_bounds__(256) band_broadcast_kernel(const BandBroadcastArgs a) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n16; i += stride) {
+        const uint4 v = a.src[i];
+        for (int d = 0; d < a.ndst; ++d) a.dst[d][i] = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned prev = atomicAdd(a.done, 1u);
+        if (prev == gridDim.x - 1) {
+            *a.done = 0u;
+            __threadfence_system();
+            for (int d = 0; d < a.nsig; ++d)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.sig[d]), "r"(a.epoch) : "memory");
+        }
+    }
+}
+
+cudaError_t band_broadcast_launch(const BandBroadcastArgs &a, int sm_count, cudaStream_t s) {
+    if (a.ndst < 0 || a.ndst > kMaxPeers - 1 || a.nsig < 1 || a.nsig > kMaxPeers || !a.done) return cudaErrorInvalidValue;
+    int64_t need = (a.n16 + 255) / 256;
+    if (need < 1) need = 1;
+    const int64_t cap = (int64_t)sm_count * 4;
+    band_broadcast_kernel<<<(int)(need < cap ? need : cap), 256, 0, s>>>(a);
+    AFK_COUNT_LAUNCH();
+    return cudaGetLastError();
 }
 
 cudaError_t gather_wait_launch(const GatherWaitArgs &a, double timeout_s, int device, cudaStream_t s) {
@@ -1025,6 +1083,9 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
     for (int d = 0; d < a.n_signal; ++d) k.sig[d] = a.signal[d];
     k.nsig = a.n_signal;
     k.epoch = a.epoch;
+    if (a.n_range_peer < 0 || a.n_range_peer > kMaxPeers - 1) return cudaErrorInvalidValue;
+    k.n_range_peer = a.n_range_peer;
+    for (int d = 0; d < a.n_range_peer; ++d) k.range_peer[d] = a.range_peer[d];
     k.minmax = a.minmax;
     k.partials = static_cast<double2 *>(ws.partials);
     k.counters = ws.counters;

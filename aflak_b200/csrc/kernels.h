@@ -50,6 +50,10 @@ struct ReduceArgs {
     unsigned *signal[kMaxPeers];
     unsigned *done;    // device counter, zero-initialised, self-resetting; required when n_signal > 0
     unsigned epoch;
+    // sharded min/max exchange: with range_out set, the last CTA also copies the band's four range words to
+    // n_range_peer more places (this rank's entry of every peer's range table) before it signals
+    int n_range_peer;
+    unsigned *range_peer[kMaxPeers - 1];
 };
 
 struct ReduceWorkspace {
@@ -97,8 +101,26 @@ struct GatherWaitArgs {
     float *image;               // this rank's copy of the full image of that epoch
     int64_t band_off[kMaxPeers]; // element offset / length of rank i's band in it
     int64_t band_len[kMaxPeers];
+    // min/max exchange: ranges[i*4 ..] = {~key(min), key(max), any, 0} of band i (arrived with its flag); their combination
+    // is written to combined[0..3] -- the range memo of the gathered image.  Both nullptr when not used.
+    const unsigned *ranges;
+    unsigned *combined;
 };
 cudaError_t gather_wait_launch(const GatherWaitArgs &a, double timeout_s, int device, cudaStream_t s);
+
+// Band broadcast (RGBA bands of the sharded display chain): copy n16 16-byte words of `src` to ndst peer-mapped
+// destinations, then publish `epoch` to nsig flag words (release, system scope) once the whole grid has stored.
+struct BandBroadcastArgs {
+    const uint4 *src;
+    int64_t n16;
+    int ndst;
+    uint4 *dst[kMaxPeers - 1];
+    unsigned *done; // zero-initialised, self-resetting arrival counter
+    int nsig;
+    unsigned *sig[kMaxPeers];
+    unsigned epoch;
+};
+cudaError_t band_broadcast_launch(const BandBroadcastArgs &a, int sm_count, cudaStream_t s);
 
 // ---- other axis-0 reductions (axis0.cu) --------------------------------------------------------
 enum Axis0Op : int {

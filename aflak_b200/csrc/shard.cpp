@@ -16,7 +16,10 @@ struct afk_gather {
     int64_t ny = 0, nx = 0;
     int64_t y0[afk::kMaxPeers] = {0}, rows[afk::kMaxPeers] = {0};
     size_t slot_floats = 0;         // one full image, padded to 256 B
-    char *local = nullptr;          // cudaMalloc'ed: [slot 0][slot 1][flags: kMaxPeers u32][done u32][err u32]
+    // cudaMalloc'ed: [slot 0][slot 1][rgba slot 0][rgba slot 1][control words].  Control words (u32 index):
+    //   0..7 flags | 8 done | 9 err | 16..23 rgba flags | 24 rgba done | 25 rgba err
+    //   32.. range table [2 slots][kMaxPeers][4] (min/max exchange) | 96.. combined range [2 slots][4]
+    char *local = nullptr;
     char *peer[afk::kMaxPeers] = {nullptr};
     bool connected = false;
     unsigned epoch = 0;        // last epoch a reduce was enqueued for
@@ -24,10 +27,21 @@ struct afk_gather {
     cudaStream_t stream = nullptr; // every reduce / wait of this gather is ordered on this stream
     afk_image *result[2] = {nullptr, nullptr}; // borrowed-memory handles of the two slots (readers on other streams are tracked)
     size_t bytes = 0;
+    unsigned rgba_epoch = 0, rgba_waited = 0; // RGBA band gather of the sharded display chain (own flags, own two slots)
+    static constexpr size_t kControlWords = 128;
     float *slot(int r, unsigned e) const { return reinterpret_cast<float *>(peer[r]) + (size_t)(e & 1u) * slot_floats; }
-    unsigned *flags(int r) const { return reinterpret_cast<unsigned *>(peer[r] + 2 * slot_floats * sizeof(float)); }
-    unsigned *done() const { return flags(rank) + afk::kMaxPeers; }
-    unsigned *err() const { return flags(rank) + afk::kMaxPeers + 1; }
+    uint8_t *rgba_slot(int r, unsigned e) const {
+        return reinterpret_cast<uint8_t *>(peer[r]) + (2 + (size_t)(e & 1u)) * slot_floats * sizeof(float);
+    }
+    unsigned *control(int r) const { return reinterpret_cast<unsigned *>(peer[r] + 4 * slot_floats * sizeof(float)); }
+    unsigned *flags(int r) const { return control(r); }
+    unsigned *done() const { return control(rank) + 8; }
+    unsigned *err() const { return control(rank) + 9; }
+    unsigned *rgba_flags(int r) const { return control(r) + 16; }
+    unsigned *rgba_done() const { return control(rank) + 24; }
+    unsigned *rgba_err() const { return control(rank) + 25; }
+    unsigned *range_entry(int r, unsigned e, int of_rank) const { return control(r) + 32 + ((size_t)(e & 1u) * afk::kMaxPeers + of_rank) * 4; }
+    unsigned *combined(unsigned e) const { return control(rank) + 96 + (size_t)(e & 1u) * 4; }
 };
 
 using namespace afk;
@@ -61,7 +75,7 @@ afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx,
     for (int r = 0; r < world; ++r) afk_shard_band(ny_total, world, r, &g->y0[r], &g->rows[r]);
     size_t fl = (size_t)ny_total * (size_t)nx;
     g->slot_floats = (fl + 63) / 64 * 64;
-    g->bytes = 2 * g->slot_floats * sizeof(float) + (kMaxPeers + 8) * sizeof(unsigned);
+    g->bytes = 4 * g->slot_floats * sizeof(float) + afk_gather::kControlWords * sizeof(unsigned);
     void *p = nullptr;
     // cudaMalloc, not the stream-ordered pool: pool memory cannot be exported with cudaIpcGetMemHandle
     cudaError_t ce = cudaMalloc(&p, g->bytes);
@@ -161,10 +175,22 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     a.n_signal = g->world;
     a.done = g->done();
     a.epoch = epoch;
+    // min/max exchange: the band's range, found by the kernel's epilogue, travels with the flag to this rank's
+    // entry of every rank's range table; afk_gather_wait combines the entries into the gathered image's range memo
+    a.range_out = g->range_entry(g->rank, epoch, g->rank);
+    k = 0;
+    for (int r = 0; r < g->world; ++r)
+        if (r != g->rank) a.range_peer[k++] = g->range_entry(r, epoch, g->rank);
+    a.n_range_peer = k;
     if (a.n2 <= 0) {
         // an empty band still has to signal: launch a 1-frame plan is impossible, so set the flags from the host side
+        // (stream order: the zero range entries land before the flags)
         static thread_local unsigned epoch_src[4]; // outlives the (pageable, hence staged at call time) copies
         epoch_src[epoch & 3u] = epoch;
+        for (int r = 0; r < g->world; ++r) {
+            cudaError_t ce = cudaMemsetAsync(g->range_entry(r, epoch, g->rank), 0, 4 * sizeof(unsigned), s);
+            if (ce != cudaSuccess) return fail(cuda_error(ce, "range entry of an empty band"));
+        }
         for (int r = 0; r < g->world; ++r) {
             cudaError_t ce = cudaMemcpyAsync(a.signal[r], &epoch_src[epoch & 3u], sizeof(unsigned), cudaMemcpyHostToDevice, s);
             if (ce != cudaSuccess) return fail(cuda_error(ce, "signal of an empty band"));
@@ -211,6 +237,8 @@ afk_status afk_gather_wait(afk_gather *g, float **result, double timeout_s) {
         w.band_off[r] = g->y0[r] * g->nx;
         w.band_len[r] = g->rows[r] * g->nx;
     }
+    w.ranges = g->range_entry(g->rank, g->epoch, 0);
+    w.combined = g->combined(g->epoch);
     cudaError_t ce = gather_wait_launch(w, timeout_s, g->device, s);
     if (ce != cudaSuccess) return fail(cuda_error(ce, "gather_wait_kernel launch"));
     g->waited_epoch = g->epoch;
@@ -241,12 +269,100 @@ afk_image *afk_gather_result_image(afk_gather *g) {
         img = afk_image_wrap_device(g->slot(g->rank, g->epoch), 2, shape);
         if (!img) return nullptr;
         img->track_readers = true;
+        // the min/max exchange left the whole image's range beside the flags: image_min_max, logscale and the display chain
+        // on this handle make no pass over the 2-D image
+        img->range = g->combined(g->epoch);
     }
+    img->range_valid = true;
     // ready = everything enqueued on the gather stream so far (the caller has enqueued afk_gather_wait): operators on
     // other streams wait for it before they read
     if (fail(image_mark_ready(img, g->stream)) != AFK_OK) return nullptr;
     afk_image_retain(img);
     return img;
+}
+
+// Sharded display chain (aflak_plot/src/imshow/image.rs:20-49): colour-map THIS RANK'S BAND of the gathered image
+// of the current epoch -- limits from the whole image's range memo when vmin / vmax (or the chain's logscale range) are NaN
+// -- and store the RGBA8 band into every rank's copy of the full [ny, nx, 4] byte image, then signal.  1/world of the
+// per-pixel work per GPU; the only traffic is the band's bytes.  Call after afk_gather_wait, on the gather's stream; follow
+// with afk_gather_wait_rgba before the next afk_gather_colormap (same two-slot discipline as the f32 result).
+afk_status afk_gather_colormap(afk_gather *g, const afk_lut *lut, float vmin, float vmax, int flip_y, const afk_colormap_chain *chain) {
+    if (!g || !lut) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_gather_colormap"));
+    cudaStream_t s;
+    int dev;
+    if (Error e = current_stream(&s, &dev)) return fail(e);
+    if (s != g->stream) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_colormap: called on another stream than the gather was created on"));
+    if (g->epoch == 0 || g->waited_epoch != g->epoch)
+        return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_colormap: afk_gather_wait has not been called for the current result"));
+    if (g->rgba_waited != g->rgba_epoch)
+        return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_colormap: afk_gather_wait_rgba has not been called since the previous afk_gather_colormap"));
+    if (g->nx % 4 != 0) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_colormap: the row length must be a multiple of 4 pixels"));
+    const unsigned e2 = ++g->rgba_epoch;
+    const int64_t y0 = g->y0[g->rank], rows = g->rows[g->rank];
+    const int64_t out_row = flip_y ? g->ny - y0 - rows : y0; // a band of input rows is a band of output rows, mirrored
+    const size_t off = (size_t)out_row * (size_t)g->nx * 4;
+    afk_status st = AFK_OK;
+    if (rows > 0) {
+        int64_t shape[2] = {rows, g->nx};
+        afk_image *view = afk_image_wrap_device(g->slot(g->rank, g->epoch) + y0 * g->nx, 2, shape);
+        if (!view) return AFK_ERR_CUDA;
+        view->range = g->combined(g->epoch); // limits are those of the WHOLE image (min/max exchange), not of the band
+        view->range_valid = true;
+        st = afk_colormap(view, lut, vmin, vmax, flip_y, 4, chain, g->rgba_slot(g->rank, e2) + off);
+        afk_image_release(view);
+        if (st != AFK_OK) return st;
+    }
+    unsigned *sig[kMaxPeers];
+    for (int r = 0; r < g->world; ++r) sig[r] = g->rgba_flags(r) + g->rank;
+    if (rows <= 0) {
+        static thread_local unsigned epoch_src[4];
+        epoch_src[e2 & 3u] = e2;
+        for (int r = 0; r < g->world; ++r) {
+            cudaError_t ce = cudaMemcpyAsync(sig[r], &epoch_src[e2 & 3u], sizeof(unsigned), cudaMemcpyHostToDevice, s);
+            if (ce != cudaSuccess) return fail(cuda_error(ce, "signal of an empty RGBA band"));
+        }
+        return AFK_OK;
+    }
+    BandBroadcastArgs b{};
+    b.src = reinterpret_cast<const uint4 *>(g->rgba_slot(g->rank, e2) + off);
+    b.n16 = rows * g->nx * 4 / 16;
+    int k = 0;
+    for (int r = 0; r < g->world; ++r)
+        if (r != g->rank) b.dst[k++] = reinterpret_cast<uint4 *>(g->rgba_slot(r, e2) + off);
+    b.ndst = k;
+    b.done = g->rgba_done();
+    b.nsig = g->world;
+    for (int r = 0; r < g->world; ++r) b.sig[r] = sig[r];
+    b.epoch = e2;
+    cudaError_t ce = band_broadcast_launch(b, sm_count(dev), s);
+    if (ce != cudaSuccess) return fail(cuda_error(ce, "band_broadcast_kernel launch"));
+    return AFK_OK;
+}
+
+// Enqueue the wait for every rank's RGBA band of the current afk_gather_colormap; *rgba = this rank's full [ny, nx, 4]
+// byte image on the device (valid until the second afk_gather_colormap from now).
+afk_status afk_gather_wait_rgba(afk_gather *g, uint8_t **rgba, double timeout_s) {
+    if (!g) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_gather_wait_rgba"));
+    cudaStream_t s;
+    if (Error e = current_stream(&s, nullptr)) return fail(e);
+    if (s != g->stream) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_wait_rgba: called on another stream than the gather was created on"));
+    if (g->rgba_epoch == 0) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_wait_rgba: no afk_gather_colormap has been enqueued"));
+    if (timeout_s <= 0) timeout_s = 5.0;
+    GatherWaitArgs w{};
+    w.flags = g->rgba_flags(g->rank);
+    w.n = g->world;
+    w.epoch = g->rgba_epoch;
+    w.err = g->err();
+    w.image = reinterpret_cast<float *>(g->rgba_slot(g->rank, g->rgba_epoch)); // 4 bytes per pixel: same offsets as the f32 image
+    for (int r = 0; r < g->world; ++r) {
+        w.band_off[r] = g->y0[r] * g->nx; // a band that never arrives is poisoned where its (unflipped) rows would be
+        w.band_len[r] = g->rows[r] * g->nx;
+    }
+    cudaError_t ce = gather_wait_launch(w, timeout_s, g->device, s);
+    if (ce != cudaSuccess) return fail(cuda_error(ce, "gather_wait_kernel launch (RGBA)"));
+    g->rgba_waited = g->rgba_epoch;
+    if (rgba) *rgba = g->rgba_slot(g->rank, g->rgba_epoch);
+    return AFK_OK;
 }
 
 void afk_gather_destroy(afk_gather *g) {

@@ -380,6 +380,17 @@ afk_status afk_gather_check(afk_gather *g);
 /* the current full image as an Image handle that borrows the slot's memory (release it like any handle; the pixels are
  * valid until the second afk_gather_reduce from now), for further operators (LUT, min/max, ...).  Call after afk_gather_wait. */
 afk_image *afk_gather_result_image(afk_gather *g);
+/* Sharded display path.  (1) Min/max exchange: every afk_gather_reduce also finds the range of its band and
+ * sends the two floats with its flag; afk_gather_wait combines them, so the handle returned by afk_gather_result_image
+ * carries the whole image's range and image_min_max (aflak_primitives/src/lib.rs:180-197), convert_to_logscale fed by it
+ * (:1598-1611), get_vmin / get_vmax (aflak_plot/src/lims.rs:7-35) and the colour mapping make no pass over the gathered
+ * image.  (2) RGBA band gather: afk_gather_colormap maps THIS RANK'S BAND of the current gathered image (make_raw_image,
+ * aflak_plot/src/imshow/image.rs:20-49; limits from the whole image when vmin/vmax or the chain's logscale range are NaN)
+ * and stores the RGBA8 band into every rank's full [ny, nx, 4] byte image; afk_gather_wait_rgba enqueues the wait and
+ * returns this rank's copy.  Call order per step: reduce, wait, colormap, wait_rgba, all on the gather's stream.  nx must
+ * be a multiple of 4. */
+afk_status afk_gather_colormap(afk_gather *g, const afk_lut *lut, float vmin, float vmax, int flip_y, const afk_colormap_chain *chain);
+afk_status afk_gather_wait_rgba(afk_gather *g, uint8_t **rgba, double timeout_s);
 void afk_gather_destroy(afk_gather *g);
 
 /* ---- mini evaluator with a device-handle cache: DST::compute + Cache (dst/compute.rs:153-274, cache.rs) ---- */

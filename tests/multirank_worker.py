@@ -101,30 +101,43 @@ for (nz, ny, nx) in [(96, 257, 128), (64, 74 + 1, 74), (48, max(world - 1, 1), 2
     g.wait()
 
     # ---- sharded display path: min/max exchange + RGBA band gather ----
-    if hasattr(g, "display"):
-        g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM, sum_mode=afk.SUM_SEQUENTIAL)
-        g.wait()
+    if nx % 4 == 0:
+        img = oracle.integral(host, 0, nz)
+        ref = afk.Image.alloc((ny, nx))
+        afk.k_reduce(whole.device_ptr, nz, ny * nx, [(0, nz)], afk.EPI_SUM, ref.device_ptr, sum_mode=afk.SUM_SEQUENTIAL)
         lut = afk.Lut("Flame")
         lut.set_lims(0.2, 0.3, 0.9)
-        for chain in (None, {"logscale_a": 1000.0, "logscale_vmin": float("nan"), "logscale_vmax": float("nan"), "normalize_min": 0.0,
-                             "normalize_max": float(np.float32(np.log(np.float32(1001.0)) / np.log(np.float32(1000.0)))) / 65535.0,
-                             "tone_table": np.arange(256, dtype=np.float32)}):
-            rgba, mn, mx = g.display(lut, channels=4, chain=chain)
-            img = oracle.integral(host, 0, nz)
-            table = oracle.lut_build("Flame")
-            if chain is None:
-                vmin, vmax = oracle.get_vmin(img), oracle.get_vmax(img)
-                want = oracle.make_raw_image(img, vmin, vmax, table, lims=(0.2, 0.3, 0.9), channels=4)
-            else:
-                vmin, vmax = oracle.image_min_max(img)
-                ls = oracle.convert_to_logscale(img, 1000.0, vmin, vmax)
-                nm = ((ls - np.float32(0.0)) / np.float32(chain["normalize_max"])).astype(np.float32)
-                tc = oracle.apply_tone_curve(nm, chain["tone_table"])
-                want = oracle.make_raw_image(tc, 0.0, 65535.0, table, lims=(0.2, 0.3, 0.9), channels=4)
-            if (np.float32(mn), np.float32(mx)) != (np.float32(vmin), np.float32(vmax)):
-                failures.append(f"rank {rank} {(nz, ny, nx)} display: exchanged min/max {(mn, mx)} != {(vmin, vmax)}")
-            if not np.array_equal(rgba.reshape(-1), np.asarray(want).reshape(-1)):
-                failures.append(f"rank {rank} {(nz, ny, nx)} display (chain={chain is not None}): gathered RGBA differs from the oracle")
+        table = oracle.lut_build("Flame")
+        tone = oracle.create_curve([(0.0, 0.0), (0.4, 0.7), (1.0, 1.0)])
+        lmax = np.float32(np.log(np.float32(1000.0) + np.float32(1.0)) / np.log(np.float32(1000.0)))
+        chain = {"logscale_a": 1000.0, "logscale_vmin": float("nan"), "logscale_vmax": float("nan"), "normalize_min": 0.0,
+                 "normalize_max": float(lmax / np.float32(65535.0)), "tone_table": tone}
+        for rep in range(3):  # both RGBA slots
+            for flip in (True, False):
+                g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM, sum_mode=afk.SUM_SEQUENTIAL)
+                g.wait()
+                res = g.result_image()
+                l0 = afk.launch_count()
+                mn, mx = afk.call("image_min_max", res)
+                if afk.launch_count() != l0:
+                    failures.append(f"rank {rank} {(nz, ny, nx)}: image_min_max of the gathered image made a pass (no range memo)")
+                if (np.float32(mn), np.float32(mx)) != tuple(np.float32(v) for v in oracle.image_min_max(img)):
+                    failures.append(f"rank {rank} {(nz, ny, nx)}: exchanged min/max {(mn, mx)} != {oracle.image_min_max(img)}")
+                # plain colour map, limits = get_vmin / get_vmax of the WHOLE image (lims.rs:7-35)
+                rgba = g.display(lut, flip_y=flip)
+                # the oracle's make_raw_image includes the vertical flip of image.rs:123-129
+                want = oracle.make_raw_image(img if flip else img[::-1], oracle.get_vmin(img), oracle.get_vmax(img), table,
+                                             lims=(0.2, 0.3, 0.9), channels=4)
+                if not np.array_equal(rgba.reshape(-1), np.asarray(want).reshape(-1)):
+                    bad = np.argwhere((rgba != want).any(axis=2))
+                    failures.append(f"rank {rank} {(nz, ny, nx)} flip={flip}: gathered RGBA differs from the oracle at {len(bad)} pixels, "
+                                    f"rows {sorted(set(bad[:, 0].tolist()))[:8]}, first {bad[0].tolist()} got {rgba[tuple(bad[0])].tolist()} want {want[tuple(bad[0])].tolist()}")
+                # fused chain (BASELINE config 4) on the band, logscale range from the exchange: same bytes as one GPU on the whole image
+                rgba = g.display(lut, vmin=0.0, vmax=65535.0, flip_y=flip, chain=chain)
+                single = afk.colormap(ref, lut, vmin=0.0, vmax=65535.0, flip_y=flip, channels=4, chain=chain)
+                if not np.array_equal(rgba, single):
+                    failures.append(f"rank {rank} {(nz, ny, nx)} flip={flip}: gathered chain RGBA differs from the single-GPU chain")
+        g.check()
     torch.cuda.synchronize()
     dist.barrier()
     g.close()
