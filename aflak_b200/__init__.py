@@ -202,6 +202,7 @@ _sig("afk_ipc_export", C.c_int, _P, _u8p)
 _sig("afk_ipc_open", _P, _u8p)
 _sig("afk_ipc_close", C.c_int, _P)
 _sig("afk_shard_band", C.c_int, C.c_int64, C.c_int, C.c_int, _i64p, _i64p)
+_sig("afk_tone_curve_from_points", C.c_int, _fp, C.c_size_t, _fp, C.c_size_t, C.POINTER(C.c_size_t))
 _sig("afk_gather_create", _P, C.c_int, C.c_int, C.c_int64, C.c_int64, _u8p)
 _sig("afk_gather_connect", C.c_int, _P, _u8p)
 _sig("afk_gather_band", C.c_int, _P, C.c_int, _i64p, _i64p)
@@ -494,6 +495,16 @@ class Map3d:
     def __init__(self, xyz):
         self.xyz = np.ascontiguousarray(xyz, dtype=np.float32)
         assert self.xyz.ndim == 3 and self.xyz.shape[2] == 3
+
+
+def tone_curve_from_points(cp):
+    """UiToneCurve::create_curve (imgui_tone_curve/src/lib.rs:68-158): control points [(x, y), ...] -> table."""
+    xy = np.ascontiguousarray(cp, dtype=np.float32).reshape(-1)
+    n = C.c_size_t()
+    _check(lib.afk_tone_curve_from_points(xy.ctypes.data_as(_fp), xy.size // 2, None, 0, C.byref(n)))
+    out = np.empty(n.value, dtype=np.float32)
+    _check(lib.afk_tone_curve_from_points(xy.ctypes.data_as(_fp), xy.size // 2, out.ctypes.data_as(_fp), out.size, C.byref(n)))
+    return out
 
 
 class ToneCurve:

@@ -5,6 +5,9 @@
 #include <cstring>
 #include <limits>
 
+#include <array>
+#include <algorithm>
+#include <vector>
 #include "host.h"
 
 namespace afk {
@@ -360,6 +363,92 @@ size_t afk_lut_bounds(const afk_lut *l, float *v1, uint8_t *c1, float *v2, uint8
         ++n;
     }
     return n;
+}
+
+// UiToneCurve::create_curve (imgui_tone_curve/src/lib.rs:68-158): the table `arr` of a ToneCurveState from its control
+// points.  GUI-side code in the reference (the widget rebuilds `arr` whenever a point moves); offered here so that a
+// headless host can build the value apply_tone_curve consumes.  Every step is one f32 operation, in the source's order.
+static bool tone_sorted_points(const float *cp_xy, size_t n, std::vector<std::array<float, 2>> &out) {
+    out.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        out[i] = {cp_xy[2 * i], cp_xy[2 * i + 1]};
+        if (out[i][0] != out[i][0]) return false; // partial_cmp(..).unwrap() panics on NaN
+    }
+    std::stable_sort(out.begin(), out.end(), [](const std::array<float, 2> &a, const std::array<float, 2> &b) { return a[0] < b[0]; });
+    return true;
+}
+
+static size_t rust_as_usize(float v) { // `as usize`: saturating, NaN -> 0
+    if (!(v > 0.0f)) return 0;
+    if (v >= 18446744073709551616.0f) return SIZE_MAX;
+    return (size_t)v;
+}
+
+afk_status afk_tone_curve_from_points(const float *cp_xy, size_t n_cp, float *arr_out, size_t cap, size_t *n_out) {
+    if ((!cp_xy && n_cp) || !n_out) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "null argument to afk_tone_curve_from_points"));
+    std::vector<float> ret;
+    std::vector<std::array<float, 2>> cp;
+    if (n_cp == 2) {
+        const float x0 = cp_xy[0], y0 = cp_xy[1], x1 = cp_xy[2], y1 = cp_xy[3];
+        const float slope = (y1 - y0) / (x1 - x0);
+        for (int i = 0; i < 256; ++i) {
+            const float t = (float)i / 256.0f;
+            ret.push_back((t * slope + y0) * 256.0f);
+        }
+    } else if (n_cp == 3) {
+        if (!tone_sorted_points(cp_xy, n_cp, cp)) return fail(make_error(AFK_ERR_PANIC, "called `Option::unwrap()` on a `None` value"));
+        const float x1 = cp[0][0], x2 = cp[1][0], x3 = cp[2][0], y1 = cp[0][1], y2 = cp[1][1], y3 = cp[2][1];
+        const float a = ((y1 - y2) * (x1 - x3) - (y1 - y3) * (x1 - x2)) / ((x1 - x2) * (x1 - x3) * (x2 - x3));
+        const float b = (y1 - y2) / (x1 - x2) - a * (x1 + x2);
+        const float c = y1 - a * x1 * x1 - b * x1;
+        for (int i = 0; i < 256; ++i) {
+            const float t = (float)i / 256.0f;
+            ret.push_back((a * t * t + b * t + c) * 256.0f);
+        }
+    } else if (n_cp > 3) {
+        if (!tone_sorted_points(cp_xy, n_cp, cp)) return fail(make_error(AFK_ERR_PANIC, "called `Option::unwrap()` on a `None` value"));
+        for (size_t counter = 0; counter + 1 < n_cp; ++counter) {
+            if (counter == 0) {
+                const auto p0 = cp[0], p1 = cp[1], p2 = cp[2];
+                const size_t size = rust_as_usize(std::ceil(p1[0] * 256.0f));
+                const float b = p0[1] - 2.0f * p1[1] + p2[1];
+                const float c = -3.0f * p0[1] + 4.0f * p1[1] - p2[1];
+                const float d = 2.0f * p0[1];
+                for (size_t i = 0; i < size; ++i) {
+                    const float t = (float)i / (float)(size - 1);
+                    ret.push_back(((b * t * t) + (c * t) + d) * 128.0f);
+                }
+            } else if (counter == n_cp - 2) {
+                const auto p0 = cp[counter - 1], p1 = cp[counter], p2 = cp[counter + 1];
+                const size_t size = rust_as_usize(std::floor(p2[0] * 256.0f) - std::ceil(p1[0] * 256.0f));
+                const float b = p0[1] - 2.0f * p1[1] + p2[1];
+                const float c = -p0[1] + p2[1];
+                const float d = 2.0f * p1[1];
+                for (size_t i = 0; i < size; ++i) {
+                    const float t = (float)i / (float)(size - 1);
+                    ret.push_back(((b * t * t) + (c * t) + d) * 128.0f);
+                }
+            } else {
+                const auto p0 = cp[counter - 1], p1 = cp[counter], p2 = cp[counter + 1], p3 = cp[counter + 2];
+                const size_t size = rust_as_usize(std::floor(p2[0] * 256.0f) - std::ceil(p1[0] * 256.0f)) + 1;
+                const float a = -p0[1] + 3.0f * p1[1] - 3.0f * p2[1] + p3[1];
+                const float b = 2.0f * p0[1] - 5.0f * p1[1] + 4.0f * p2[1] - p3[1];
+                const float c = -p0[1] + p2[1];
+                const float d = 2.0f * p1[1];
+                for (size_t i = 0; i < size; ++i) {
+                    const float t = (float)i / (float)(size - 1);
+                    ret.push_back(((a * t * t * t) + (b * t * t) + (c * t) + d) * 128.0f);
+                }
+            }
+            if (ret.size() > ((size_t)1 << 24)) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "tone curve table larger than 2^24 entries"));
+        }
+    } // 0 or 1 control points: an empty table
+    *n_out = ret.size();
+    if (arr_out) {
+        if (cap < ret.size()) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, fmt("tone curve table needs %zu entries, the buffer holds %zu", ret.size(), cap)));
+        if (!ret.empty()) memcpy(arr_out, ret.data(), ret.size() * sizeof(float));
+    }
+    return AFK_OK;
 }
 
 afk_status afk_image_vmin_vmax(const afk_image *img, float *vmin, float *vmax) {

@@ -1028,6 +1028,64 @@ def run_c5_strong(cx):
                         "algorithmic_bytes_global": bytes_global, "reduce_kernel_ms_max_over_ranks": kms,
                         "per_gpu_kernel_GBps": per_gpu, "per_gpu_frac_of_measured_peak": per_gpu / cx.peak,
                         "gathered_bytes_over_nvlink": ny * nx * 4 * (world - 1), "parity_sampled_rows": "ok" if ok else "FAILED"}
+    # ---- sharded display chain: min/max exchange + every rank colour-maps its band + RGBA band gather ----
+    lut = afk.Lut("Flame")
+    lut.set_lims(0.2, 0.3, 0.9)
+    tone = oracle.create_curve([(0.0, 0.0), (0.4, 0.7), (1.0, 1.0)])
+    lmax = np.float32(np.log(np.float32(1000.0) + np.float32(1.0)) / np.log(np.float32(1000.0)))
+    chain = {"logscale_a": 1000.0, "logscale_vmin": float("nan"), "logscale_vmax": float("nan"), "normalize_min": 0.0,
+             "normalize_max": float(lmax / np.float32(65535.0)), "tone_table": tone}
+    d_err, memo, mn, mx, res = "", False, float("nan"), float("nan"), None
+    try:  # local work only: the collectives below are reached by every rank whatever happens here
+        g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM, None)
+        g.wait()
+        res = g.result_image()
+        l0 = afk.launch_count()
+        mn, mx = afk.call("image_min_max", res)
+        memo = afk.launch_count() == l0
+        got = g.display(lut, vmin=0.0, vmax=65535.0, chain=chain)
+        single = afk.colormap(res, lut, vmin=0.0, vmax=65535.0, channels=4, chain=chain)  # one GPU, the whole gathered image
+        if not np.array_equal(got, single):
+            d_err = "gathered RGBA differs from the one-GPU chain"
+        elif not memo:
+            d_err = "image_min_max of the gathered image made a pass over it"
+        del got, single
+    except Exception as e:
+        d_err = str(e)[:300]
+    d_ok = cx.all_ok(d_err == "")
+    all_ok &= d_ok
+    disp = {"what": "gathered 4096x4096 integral -> logscale(1000) -> normalize -> tone curve(256) -> Flame LUT -> RGBA8, flip_y: every rank maps its "
+                    "band (range from the min/max exchange, no pass over the image) and stores it into every rank's RGBA image (peer stores)",
+            "parity": "ok" if d_ok else "FAILED", "error": d_err,
+            "parity_how": "every rank's gathered RGBA image == the one-GPU chain on its copy of the gathered image, byte for byte"}
+    if d_ok:
+        for _ in range(warm):
+            g.colormap(lut, 0.0, 65535.0, True, chain)
+            g.wait_rgba()
+        cx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            g.colormap(lut, 0.0, 65535.0, True, chain)
+            g.wait_rgba()
+        e1.record(stream)
+        cx.barrier()
+        t_sharded = e0.elapsed_time(e1) / steps
+        out1 = torch.empty(ny * nx * 4, dtype=torch.uint8, device=cx.dev)
+        for _ in range(warm):
+            afk.colormap_device(res, lut, 0.0, 65535.0, out1.data_ptr(), channels=4, chain=chain)
+        e0.record(stream)
+        for _ in range(steps):
+            afk.colormap_device(res, lut, 0.0, 65535.0, out1.data_ptr(), channels=4, chain=chain)
+        e1.record(stream)
+        e1.synchronize()
+        dms, sms = cx.max_over_ranks(t_sharded, e0.elapsed_time(e1) / steps)
+        disp.update({"ms_per_step_max_over_ranks": dms, "same_chain_on_one_gpu_whole_image_ms": sms,
+                     "rgba_bytes_received_per_rank": ny * nx * 4 * (world - 1) // world,
+                     "image_min_max_from_exchange_without_a_pass": memo, "image_min_max": [float(mn), float(mx)]})
+        del out1
+    base["sharded_display"] = disp
+    del res
     g.check()
     for m in msgs:
         print(m, file=sys.stderr, flush=True)

@@ -185,6 +185,10 @@ afk_value *afk_value_map2dto3d(const float *xyz, int64_t rows, int64_t cols);
 const float *afk_value_get_map(const afk_value *v, int64_t *rows, int64_t *cols);
 /* ToneCurveState: only `arr` is read by operators (imgui_tone_curve/src/lib.rs:10-48); cp = n_cp (x,y) pairs */
 afk_value *afk_value_tone_curve(const float *arr, size_t n, const float *cp_xy, size_t n_cp);
+/* UiToneCurve::create_curve (imgui_tone_curve/src/lib.rs:68-158): the table `arr` the widget builds from n_cp control
+ * points (x,y pairs).  *n_out = number of entries (256 for 2 or 3 points, a spline-dependent count otherwise, 0 for fewer
+ * than 2); arr_out may be NULL to query the size.  A NaN abscissa is the reference's unwrap() panic (AFK_ERR_PANIC). */
+afk_status afk_tone_curve_from_points(const float *cp_xy, size_t n_cp, float *arr_out, size_t cap, size_t *n_out);
 /* DefaultFor::default_for (lib.rs:760-776); NULL for types without a default (Image, Fits, Map2dTo3dCoords) */
 afk_value *afk_value_default_for(afk_type t);
 void afk_value_retain(afk_value *v);

@@ -324,3 +324,31 @@ def test_sum_mode_is_a_process_default_with_a_thread_override(afk):
         afk.set_sum_mode(afk.SUM_INHERIT)
     with pytest.raises(afk.AflakError):
         afk.set_default_sum_mode(7)
+
+
+def test_tone_curve_from_points_host(afk, orc):
+    """afk_tone_curve_from_points restates UiToneCurve::create_curve (imgui_tone_curve/src/lib.rs:68-158) in the product
+    (host code, no device needed): closed forms for 2 and 3 points, the oracle's restatement for the spline cases, the
+    reference's panic for a NaN abscissa."""
+    arr = afk.tone_curve_from_points([(0.0, 0.0), (1.0, 1.0)])
+    assert arr.dtype == np.float32 and np.array_equal(arr, np.arange(256, dtype=np.float32))  # ToneCurveState::default's table
+    arr = afk.tone_curve_from_points([(0.0, 0.25), (0.5, 0.75)])  # slope 1, offset 0.25: (i/256 + 0.25) * 256
+    assert np.array_equal(arr, np.arange(256, dtype=np.float32) + np.float32(64.0))
+    # three points on y = x^2: a = 1, b = c = 0 up to rounding -> (t*t)*256 within a few ulps of the quadratic's own rounding
+    arr = afk.tone_curve_from_points([(0.0, 0.0), (0.5, 0.25), (1.0, 1.0)])
+    t = np.arange(256, dtype=np.float32) / np.float32(256.0)
+    assert np.allclose(arr, t * t * 256.0, rtol=0, atol=1e-4)
+    rng = np.random.default_rng(0xAF1A0090)
+    cases = [[(1.0, 1.0), (0.0, 0.0), (0.3, 0.6)], [(0, 0), (0.25, 0.4), (0.6, 0.5), (1, 1)], [(0, 0), (0.2, 0.1), (0.5, 0.8), (0.7, 0.75), (1, 1)],
+             [(0.0, 0.0)], [(0, 0), (0.5, 0.5), (0.5, 0.6), (1, 1)]]
+    cases += [[(float(x), float(y)) for x, y in rng.random((n, 2))] for n in (3, 4, 5, 6, 9, 12)]
+    for cp in cases:
+        got = afk.tone_curve_from_points(cp)
+        want = np.asarray(orc.create_curve(cp), dtype=np.float32)
+        assert got.shape == want.shape, (cp, got.shape, want.shape)
+        nan = np.isnan(want)
+        assert np.array_equal(np.isnan(got), nan) and np.array_equal(got[~nan].view(np.uint32), want[~nan].view(np.uint32)), cp
+    assert afk.tone_curve_from_points(np.zeros((0, 2), np.float32)).size == 0
+    with pytest.raises(afk.AflakError) as ei:
+        afk.tone_curve_from_points([(0.0, 0.0), (float("nan"), 0.5), (1.0, 1.0)])
+    assert ei.value.status == afk.ERR_PANIC
