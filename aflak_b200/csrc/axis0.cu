@@ -13,6 +13,8 @@
 #include <cstdlib>
 #include "kernels.h"
 
+#include <cstdio>
+
 #include <cfloat>
 #include <cstdint>
 
@@ -348,7 +350,16 @@ struct MedianK {
     int npad;       // words per staged spectrum (select kernel)
     float *out;
     unsigned *flag; // 1: NaN present (reference panics)
+    unsigned long long *trace; // AFK_MEDIAN_TRACE=1 (diagnostics): clock cycles per phase summed over the CTAs, else nullptr
 };
+
+__device__ __forceinline__ void ms_trace(const MedianK &a, int phase, long long &t) {
+    if (a.trace && threadIdx.x == 0) {
+        const long long now = clock64();
+        atomicAdd(a.trace + phase, (unsigned long long)(now - t));
+        t = now;
+    }
+}
 
 __device__ __forceinline__ unsigned med_key(float f) {
     const unsigned b = __float_as_uint(f);
@@ -651,9 +662,14 @@ __device__ __forceinline__ bool med_round(unsigned *keys, MedState &st, bool wan
     h ^= h >> 15;
     const int pos = (int)(((long long)lane * m) >> 5) + (int)(h % (unsigned)stride);
     const unsigned smp = med_warp_sort(keys[pos], lane);
+    // 7 pivots two sample ranks apart, centred on where the wanted rank is expected among the 32 sorted samples (the sample
+    // rank of list rank r has sigma <= 2.8): the bin that holds r is then ~1/16 of the list wherever r lies, not only when
+    // it is near the middle
+    int centre = (int)(((long long)st.r * 32 + m / 2) / m);
+    centre = centre < 6 ? 6 : (centre > 25 ? 25 : centre);
     unsigned pv[kMedPivots];
 #pragma unroll
-    for (int j = 0; j < kMedPivots; ++j) pv[j] = __shfl_sync(kFull, smp, 10 + 2 * j);
+    for (int j = 0; j < kMedPivots; ++j) pv[j] = __shfl_sync(kFull, smp, centre - 6 + 2 * j);
     // ---- count pass ----
     unsigned c[kMedPivots];
 #pragma unroll
@@ -787,7 +803,7 @@ __device__ __forceinline__ void med_rank32(const unsigned *keys, const MedState 
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kMsPix = 32;            // spaxels per CTA (= lanes)
 constexpr int kMsWarps = 16;          // 2 CTAs x 512 threads x 16 loads in flight = 64 KB per SM (one 1024-thread CTA per SM, whose tile would stay in L2, measured slower: 12.8 vs 11.5 ms)
-constexpr int kMsCap = 768;           // candidate slots per spaxel (20 % of an ALMA window: a 4-rank bin of 64 samples overflows 4e-4 of the time)
+constexpr int kMsCap = 800;           // candidate slots per spaxel (20 % of an ALMA window: a 4-rank bin of 64 samples overflows 4e-4 of the time)
 constexpr int kMsRow = kMsCap + 1;    // odd row stride: neighbouring spaxels start in different banks
 constexpr int kMsU = 16;              // frames in flight per thread
 constexpr int kMsUC = 16;             // ... in the collect pass: 20 -> 10.9 ms, 32 -> 15.3 ms (spills under the 64-register cap); 16 -> 9.8 ms
@@ -1120,6 +1136,312 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// median_stream1_kernel (round 2): ONE pass over the window for 768 < n <= 4400 frames (the ALMA window).
+//
+// median_stream_kernel reads the window twice (count, then collect): 8 B per voxel of DRAM traffic and an issue-bound count
+// pass (profiles/r1_median_ncu_full.json).  Here the bracket that will hold the median is fixed BEFORE the stream:
+//   A' 256 stratified sample frames per spaxel (the same frames for the whole CTA: coalesced, 6.7 % of the window), sorted
+//      by a warp as 8 keys per lane (bitonic, 36 compare-exchange steps); lo / hi = the samples of rank 128 -+ 17.  The
+//      sample rank of the true median has sigma ~ 7.7, so the bracket holds it for ~97 % of the spaxels and contains
+//      ~13 % of the window (510 +- 80 keys: overflows the 768-slot list for < 0.1 % of the spaxels);
+//   BC one stream: below += key < lo, count key == lo, track the smallest key >= hi, append lo < key < hi to the spaxel's
+//      list in shared memory -- the collect pass of the two-pass kernel plus one compare;
+//   D  a spaxel whose wanted rank fell outside its bracket (r0 < below or r0 >= below + eq + m) has its outer bin
+//      re-collected from the global column by the WHOLE CTA (all frames in flight at once); then one warp per spaxel finishes
+//      on the list exactly as before, refinement rounds for an overflowing list included: exactness never depends on the
+//      data, only the time of ~3 % of the spaxels.
+// 4.3 B per voxel of DRAM traffic instead of 8, and no count pass.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kMs1HalfWidth = 17;          // bracket = sample ranks 128 -+ 17 of 256
+constexpr int kMs1WingWidth = 40;          // a missed bracket falls back to the wing up to rank 128 -+ 40 (5 sigma)
+constexpr int64_t kMs1MaxFrames = 4400;    // beyond, 15 % of the window no longer fits the list with margin
+constexpr int64_t kMs1MinFrames = 3000;    // below, the two-pass kernel is faster (see median_dispatch)
+
+// ascending bitonic sort of 256 keys held 8 per lane: index = lane * 8 + e
+__device__ __forceinline__ void ms_sort256(unsigned (&v)[8], int lane) {
+#pragma unroll
+    for (int k = 2; k <= 256; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= 8) {
+                const int lj = j >> 3;
+                const bool asc = ((lane << 3) & k) == 0;
+                const bool low = (lane & lj) == 0;
+                const bool take_min = asc == low;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const unsigned o = __shfl_xor_sync(kFull, v[e], lj);
+                    v[e] = take_min ? min(v[e], o) : max(v[e], o);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    if ((e & j) == 0) {
+                        const bool asc = k >= 8 ? (((lane << 3) & k) == 0) : ((e & k) == 0);
+                        const unsigned x = v[e], y = v[e | j];
+                        const unsigned mn = min(x, y), mx = max(x, y);
+                        v[e] = asc ? mn : mx;
+                        v[e | j] = asc ? mx : mn;
+                    }
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream1_kernel(const MedianK a) {
+    extern __shared__ unsigned s_list[]; // [kMsPix][kMsRow] candidate lists; phase A' aliases the samples onto it
+    __shared__ unsigned s_lo[kMsPix], s_hi[kMsPix], s_lo2[kMsPix], s_hi2[kMsPix], s_cnt[kMsPix];
+    __shared__ unsigned s_eq[kMsWarps][kMsPix], s_himin[kMsWarps][kMsPix], s_bel[kMsWarps][kMsPix];
+    const int n = (int)a.n;
+    const int tid = threadIdx.x, g = tid >> 5, lane = tid & 31;
+    const int64_t px0 = (int64_t)blockIdx.x * kMsPix;
+    const int64_t mypx = px0 + lane;
+    const bool active = mypx < a.n2;
+    const float *col = a.cube + a.start * a.n2 + (active ? mypx : a.n2 - 1); // inactive lanes read a valid address
+    const unsigned r0 = (unsigned)((n - 1) / 2);
+    const bool even = (n & 1) == 0;
+    bool nan = false;
+    long long t_tr = a.trace ? clock64() : 0;
+    if (tid < kMsPix) s_cnt[tid] = 0u;
+    // ---- A': 256 stratified sample frames -> bracket ----
+    {
+        unsigned *s_smp = s_list; // [kMsPix][257]
+        const int stride = n >> 8; // n > kMsCap >= 256
+        unsigned raw[256 / kMsWarps]; // this warp's 16 sample frames: all loads in flight before the first store
+#pragma unroll
+        for (int u = 0; u < 256 / kMsWarps; ++u) {
+            const int i = g + u * kMsWarps;
+            unsigned h = ((unsigned)blockIdx.x * 0x9E3779B9u + (unsigned)i * 0x85EBCA6Bu) * 0xC2B2AE35u;
+            h ^= h >> 16;
+            const int f = (int)(((long long)i * n) >> 8) + (int)(h % (unsigned)stride);
+            raw[u] = ms_ld(col + (size_t)f * a.n2);
+        }
+        // the low 8 bits are replaced by the sample's index: the 256 values are distinct, so lo < hi strictly even for a
+        // constant spectrum (a pivot does not have to be a key of the spectrum)
+#pragma unroll
+        for (int u = 0; u < 256 / kMsWarps; ++u) s_smp[lane * 257 + g + u * kMsWarps] = (ms_key(raw[u]) & ~255u) | (unsigned)(g + u * kMsWarps);
+        __syncthreads();
+        ms_trace(a, 0, t_tr);
+        for (int p = g; p < kMsPix; p += kMsWarps) {
+            unsigned v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = s_smp[p * 257 + lane * 8 + e];
+            ms_sort256(v, lane);
+            constexpr int RL = 128 - kMs1HalfWidth, RH = 128 + kMs1HalfWidth, RL2 = 128 - kMs1WingWidth, RH2 = 128 + kMs1WingWidth;
+            const unsigned lo_s = __shfl_sync(kFull, v[RL & 7], RL >> 3), hi_s = __shfl_sync(kFull, v[RH & 7], RH >> 3);
+            const unsigned lo2_s = __shfl_sync(kFull, v[RL2 & 7], RL2 >> 3), hi2_s = __shfl_sync(kFull, v[RH2 & 7], RH2 >> 3);
+            if (lane == 0) { s_lo[p] = lo_s; s_hi[p] = hi_s; s_lo2[p] = lo2_s; s_hi2[p] = hi2_s; }
+        }
+        __syncthreads(); // the samples are dead: the lists may be written
+        ms_trace(a, 1, t_tr);
+    }
+    const unsigned lo = s_lo[lane], hi = s_hi[lane];
+    // ---- BC: one stream over the window ----
+    unsigned n_eq = 0u, hi_min = kFull, below = 0u;
+    unsigned *row = s_list + lane * kMsRow;
+    const unsigned cnt_addr = (unsigned)__cvta_generic_to_shared(&s_cnt[lane]), row_addr = (unsigned)__cvta_generic_to_shared(row);
+    auto collect = [&](unsigned rawbits) {
+        const unsigned key = ms_key(rawbits);
+        const float xf = __uint_as_float(rawbits);
+        nan |= xf != xf;
+        ms_count(below, key, lo);
+        if (key == lo) ++n_eq;
+        if (key >= hi) hi_min = min(hi_min, key);
+        const unsigned inbin = (key > lo && key < hi) ? 1u : 0u;
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p, q;\n\t"
+            ".reg .u32 at, ad;\n\t"
+            "setp.ne.u32 p, %0, 0;\n\t"
+            "@p atom.shared.add.u32 at, [%1], 1;\n\t"
+            "setp.lt.and.u32 q, at, %2, p;\n\t"
+            "mad.lo.u32 ad, at, 4, %3;\n\t"
+            "@q st.shared.u32 [ad], %4;\n\t"
+            "}"
+            :
+            : "r"(inbin), "r"(cnt_addr), "r"((unsigned)kMsCap), "r"(row_addr), "r"(key)
+            : "memory");
+    };
+    if (active) {
+        const size_t wstep = (size_t)kMsWarps * a.n2;
+        const float *p = col + (size_t)g * a.n2;
+        int k = g;
+        for (; k + (kMsUC - 1) * kMsWarps < n; k += kMsWarps * kMsUC) {
+            unsigned raw[kMsUC];
+#pragma unroll
+            for (int u = 0; u < kMsUC; ++u) { raw[u] = ms_ld(p); p += wstep; } // default L2 policy: a re-collect (D1) finds most of the tile still cached
+#pragma unroll
+            for (int u = 0; u < kMsUC; ++u) collect(raw[u]);
+        }
+        for (; k < n; k += kMsWarps, p += wstep) collect(ms_ld(p));
+    }
+    s_eq[g][lane] = n_eq;
+    s_himin[g][lane] = hi_min;
+    s_bel[g][lane] = below;
+    __syncthreads();
+    ms_trace(a, 2, t_tr);
+    // ---- D0: lane = spaxel: does the bracket hold the wanted rank?  If not, the bin becomes the WING next to it, bounded by
+    //      the samples of rank 128 -+ 40 (5 sigma): ~9 % of the window, it fits the list ----
+    __shared__ unsigned s_r[kMsPix], s_eqt[kMsPix], s_abv[kMsPix], s_haslo[kMsPix], s_miss[kMsPix], s_belt[kMsPix];
+    if (g == 0) {
+        unsigned eq = 0u, bel = 0u, above = kFull;
+#pragma unroll
+        for (int w = 0; w < kMsWarps; ++w) { eq += s_eq[w][lane]; bel += s_bel[w][lane]; above = min(above, s_himin[w][lane]); }
+        const unsigned m = s_cnt[lane];
+        unsigned r, miss = 0u;
+        if (r0 < bel) { // below the bracket: (lo2, lo); the rank inside it is known once the wing has been counted
+            s_hi[lane] = lo;
+            s_lo[lane] = s_lo2[lane];
+            r = r0;
+            miss = 1u;
+        } else if (r0 - bel >= eq + m) { // above it: [hi, hi2), hi itself counted as the new `eq`
+            r = r0 - bel - eq - m;
+            s_lo[lane] = hi;
+            s_hi[lane] = s_hi2[lane];
+            miss = 2u;
+        } else {
+            r = r0 - bel;
+        }
+        if (miss) { s_cnt[lane] = 0u; eq = 0u; above = kFull; }
+        s_r[lane] = r; s_eqt[lane] = eq; s_abv[lane] = above; s_haslo[lane] = 1u; s_belt[lane] = bel;
+        s_miss[lane] = active ? miss : 0u;
+        if (a.trace) {
+            if (active && miss) atomicAdd(a.trace + 5, 1ull);
+            if (active && !miss && m > (unsigned)kMsCap) atomicAdd(a.trace + 7, 1ull);
+            if (active) atomicAdd(a.trace + 6, (unsigned long long)m);
+        }
+    }
+    __syncthreads();
+    // ---- D1: the whole CTA re-collects the bin of a spaxel whose bracket missed (every frame of the column in flight at
+    //      once: a few microseconds, where one warp walking the column would stall the CTA for ~100) ----
+    auto recollect = [&]() {
+        for (int p = 0; p < kMsPix; ++p) {
+            if (!s_miss[p]) continue; // CTA-uniform
+            const float *pcol = a.cube + a.start * a.n2 + (px0 + p);
+            const unsigned plo = s_lo[p], phi = s_hi[p];
+            const bool phas = s_haslo[p] != 0u;
+            unsigned *list = s_list + p * kMsRow;
+            unsigned eqc = 0u, hm = kFull;
+            constexpr int kPer = (int)((kMs1MaxFrames + kMsPix * kMsWarps - 1) / (kMsPix * kMsWarps)); // frames per thread
+            unsigned kk[kPer];
+#pragma unroll
+            for (int u = 0; u < kPer; ++u) {
+                const int k = tid + u * kMsPix * kMsWarps;
+                kk[u] = k < n ? ms_key(ms_ld(pcol + (size_t)k * a.n2)) : plo; // plo: counted nowhere below
+            }
+#pragma unroll
+            for (int u = 0; u < kPer; ++u) {
+                const bool valid = tid + u * kMsPix * kMsWarps < n;
+                const unsigned key = kk[u];
+                if (valid && phas && key == plo) ++eqc;
+                if (valid && key >= phi) hm = min(hm, key);
+                // one shared atomic per warp and step, not per key: every append of this loop goes to the same counter
+                const bool keep = valid && key > plo && key < phi;
+                const unsigned bal = __ballot_sync(kFull, keep);
+                if (bal) {
+                    unsigned base = 0u;
+                    if (lane == __ffs(bal) - 1) base = atomicAdd(&s_cnt[p], (unsigned)__popc(bal));
+                    base = __shfl_sync(kFull, base, __ffs(bal) - 1);
+                    const unsigned at = base + __popc(bal & ((1u << lane) - 1u));
+                    if (keep && at < (unsigned)kMsCap) list[at] = key;
+                }
+            }
+            eqc = __reduce_add_sync(kFull, eqc);
+            hm = __reduce_min_sync(kFull, hm);
+            if (lane == 0) {
+                if (eqc) atomicAdd(&s_eqt[p], eqc);
+                if (hm != kFull) atomicMin(&s_abv[p], hm);
+            }
+        }
+    };
+    recollect();
+    __syncthreads();
+    // the wing is counted: rank inside it, or (5 sigma: ~1e-7 of the spaxels) the open bin beyond it
+    if (g == 0) {
+        const unsigned miss = s_miss[lane];
+        unsigned again = 0u;
+        if (miss == 1u) {
+            const unsigned below2 = s_belt[lane] - s_eqt[lane] - s_cnt[lane]; // keys < lo2
+            if (r0 >= below2) {
+                s_r[lane] = r0 - below2;
+            } else {
+                s_hi[lane] = s_lo[lane];
+                s_lo[lane] = 0u;
+                s_haslo[lane] = 0u;
+                s_r[lane] = r0;
+                again = 1u;
+            }
+        } else if (miss == 2u) {
+            const unsigned inside = s_eqt[lane] + s_cnt[lane]; // keys in [hi, hi2)
+            if (s_r[lane] >= inside) {
+                s_r[lane] -= inside;
+                s_lo[lane] = s_hi[lane];
+                s_hi[lane] = kFull;
+                again = 1u;
+            }
+        }
+        if (again) { s_cnt[lane] = 0u; s_eqt[lane] = 0u; s_abv[lane] = kFull; }
+        s_miss[lane] = again;
+    }
+    __syncthreads();
+    recollect();
+    __syncthreads();
+    ms_trace(a, 3, t_tr);
+    // ---- D2: one warp per spaxel ----
+    for (int p = g; p < kMsPix; p += kMsWarps) {
+        const int64_t px = px0 + p;
+        if (px >= a.n2) continue; // warp-uniform
+        unsigned *list = s_list + p * kMsRow;
+        unsigned m = s_cnt[p];
+        unsigned blo = s_lo[p], bhi = s_hi[p];
+        bool bhas_lo = s_haslo[p] != 0u;
+        const unsigned eq = s_eqt[p];
+        unsigned above = s_abv[p];
+        unsigned r = s_r[p];
+        const float *pcol = a.cube + a.start * a.n2 + px;
+        unsigned klo = 0u, khi = 0u;
+        bool done = false;
+        unsigned seed = (unsigned)px * 0x9E3779B9u + 0x7F4A7C15u;
+        if (bhas_lo && r < eq) { // the wanted key is lo itself
+            klo = blo;
+            khi = blo;
+            if (even && !(r + 1 < eq)) {
+                unsigned mn = kFull;
+                if (m <= (unsigned)kMsCap) {
+                    for (int i = lane; i < (int)m; i += 32) mn = min(mn, list[i]);
+                } else {
+                    for (int k = lane; k < n; k += 32) {
+                        const unsigned key = ms_key(ms_ld(pcol + (size_t)k * a.n2));
+                        if (key > blo && key < bhi) mn = min(mn, key);
+                    }
+                }
+                mn = __reduce_min_sync(kFull, mn);
+                khi = mn != kFull ? mn : above;
+            }
+            done = true;
+        } else {
+            if (bhas_lo) r -= eq;
+            while (!done && m > (unsigned)kMsCap) {
+                done = ms_refine(pcol, a.n2, n, list, blo, bhi, bhas_lo, r, m, above, even, lane, seed, klo, khi);
+                seed = seed * 1664525u + 1013904223u;
+            }
+        }
+        if (!done) {
+            MedState st{(int)m, r, above, above != kFull};
+            while (!done && st.m > 32) {
+                done = med_round(list, st, even, lane, seed, klo, khi);
+                seed = seed * 1664525u + 1013904223u;
+            }
+            if (!done) med_rank32(list, st, even, lane, klo, khi);
+        }
+        if (lane == 0) a.out[px] = med_finish(klo, khi, even);
+    }
+    if (a.trace) { __syncthreads(); ms_trace(a, 4, t_tr); }
+    if (nan && n > 1) atomicMax(a.flag, 1u);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------------
 static size_t a0_state_bytes(int op, int mode) {
@@ -1283,7 +1605,7 @@ static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start,
     if (n2 <= 0) return cudaSuccess;
     const int64_t n = end - start;
     if (n < 1 || n > 0x7FFFFFFF || flag == nullptr) return cudaErrorInvalidValue;
-    MedianK k{cube, n2, start, n, 0, 0, out, flag};
+    MedianK k{cube, n2, start, n, 0, 0, out, flag, nullptr};
     if (n <= kMedRankMaxN) {
         const unsigned grid = (unsigned)((n2 + kMedSortPixels - 1) / kMedSortPixels);
         if (n <= 8) median_sort_kernel<8><<<grid, kMedSortPixels, 0, s>>>(k);
@@ -1307,11 +1629,38 @@ static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start,
         if (dev_ms >= 0 && dev_ms < 16 && !attr_ms[dev_ms]) {
             cudaError_t e = cudaFuncSetAttribute(median_stream_kernel<7, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream_kernel<15, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e != cudaSuccess) return e;
             attr_ms[dev_ms] = true;
         }
         const unsigned grid_ms = (unsigned)((n2 + kMsPix - 1) / kMsPix);
-        if (n <= kMedStreamWideBins) median_stream_kernel<7, 4><<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
+        static const int single_pass = getenv("AFK_MEDIAN_SINGLE_PASS") ? atoi(getenv("AFK_MEDIAN_SINGLE_PASS")) : 1; // 0: the two-pass kernel (A/B); 2: from 801 frames
+        // Measured on the ALMA cube (profiles/r2_median_single_pass.json): the one-pass kernel ties with the two-pass kernel at
+        // 3840 frames (9.15 vs 9.06 ms) with half its DRAM traffic, and loses below (2000 frames: 5.7 vs 5.4 ms; 1025: 4.2 vs
+        // 3.5 ms: the 256-sample sort and the re-collects do not shrink with the window) -> used from 3000 frames up.
+        if (single_pass && (n >= kMs1MinFrames || single_pass == 2) && n > kMsCap && n <= kMs1MaxFrames) {
+            static const int trace = getenv("AFK_MEDIAN_TRACE") ? atoi(getenv("AFK_MEDIAN_TRACE")) : 0;
+            if (trace) { // diagnostics: synchronises
+                unsigned long long *d = nullptr, h[8] = {};
+                cudaMalloc(&d, sizeof h);
+                cudaMemset(d, 0, sizeof h);
+                MedianK kt = k;
+                kt.trace = d;
+                median_stream1_kernel<<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(kt);
+                cudaStreamSynchronize(s);
+                cudaMemcpy(h, d, sizeof h, cudaMemcpyDeviceToHost);
+                cudaFree(d);
+                const double tot = (double)(h[0] + h[1] + h[2] + h[3] + h[4]);
+                fprintf(stderr, "[afk median trace] n=%lld CTAs=%u cycles/CTA: sample loads %.0f, sort %.0f, stream %.0f, miss re-collect %.0f, finish %.0f (%.1f%% %.1f%% %.1f%% %.1f%% %.1f%%)\n",
+                        (long long)n, grid_ms, h[0] / (double)grid_ms, h[1] / (double)grid_ms, h[2] / (double)grid_ms, h[3] / (double)grid_ms, h[4] / (double)grid_ms,
+                        100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot);
+                fprintf(stderr, "[afk median trace] spaxels %lld: bracket missed %llu (%.2f%%), list overflowed %llu, mean keys in the bracket %.1f\n", (long long)n2,
+                        h[5], 100.0 * h[5] / (double)n2, h[7], h[6] / (double)n2);
+            } else {
+                median_stream1_kernel<<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
+            }
+        }
+        else if (n <= kMedStreamWideBins) median_stream_kernel<7, 4><<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
         else median_stream_kernel<15, 2><<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
         count_launch();
         return cudaGetLastError();
