@@ -205,6 +205,8 @@ _sig("afk_shard_band", C.c_int, C.c_int64, C.c_int, C.c_int, _i64p, _i64p)
 _sig("afk_tone_curve_from_points", C.c_int, _fp, C.c_size_t, _fp, C.c_size_t, C.POINTER(C.c_size_t))
 _sig("afk_gather_create", _P, C.c_int, C.c_int, C.c_int64, C.c_int64, _u8p)
 _sig("afk_gather_connect", C.c_int, _P, _u8p)
+_sig("afk_gather_bytes", C.c_size_t, C.c_int64, C.c_int64)
+_sig("afk_gather_create_symmetric", _P, C.c_int, C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_void_p), _P)
 _sig("afk_gather_band", C.c_int, _P, C.c_int, _i64p, _i64p)
 _sig("afk_gather_reduce", C.c_int, _P, _P, C.c_int64, C.c_int, _i64p, _i64p, C.c_int, _fp, C.c_int)
 _sig("afk_gather_wait", C.c_int, _P, C.POINTER(C.c_void_p), C.c_double)
@@ -740,6 +742,27 @@ def profile_reduce_read():
 
 
 # ---- spatial sharding + fused gather (one process per GPU) ----------------------------------------------------
+def gather_bytes(ny_total, nx):
+    return int(lib.afk_gather_bytes(ny_total, nx))
+
+
+def symmetric_memory_torch(nbytes, group=None):
+    """Host-side plumbing for Gather(symmetric=...): a zeroed symmetric allocation through torch's symmetric-memory allocator
+    (cuMem + NVLink multicast object + handle exchange over the process group's store).  Returns (peer_ptrs, multicast_ptr,
+    keep_alive); multicast_ptr is 0 where the fabric has no NVLink-SHARP multicast.  Collective: every rank calls it."""
+    import torch
+    import torch.distributed as dist
+    import torch.distributed._symmetric_memory as symm_mem
+
+    group = group or dist.group.WORLD
+    t = symm_mem.empty(int(nbytes), dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+    t.zero_()
+    h = symm_mem.rendezvous(t, group)
+    torch.cuda.synchronize()
+    dist.barrier(group)
+    return [int(p) for p in h.buffer_ptrs], int(h.multicast_ptr), (t, h)
+
+
 def shard_band(ny, world, rank):
     """y-band [y0, y0+rows) of `rank`: pure host arithmetic, usable without a GPU."""
     y0, rows = C.c_int64(), C.c_int64()
@@ -754,12 +777,23 @@ class Gather:
     (e.g. torch.distributed.all_gather_object); only 64 bytes per rank cross it, once.
     """
 
-    def __init__(self, world, rank, ny_total, nx, exchange=None):
+    def __init__(self, world, rank, ny_total, nx, exchange=None, symmetric=None):
+        """symmetric = (peer_ptrs, multicast_ptr, keep_alive): host-supplied symmetric memory of gather_bytes(ny, nx) zeroed
+        bytes per rank (afk_gather_create_symmetric); otherwise the library allocates and `exchange` carries the IPC handles."""
+        self.world, self.rank, self.ny, self.nx = world, rank, ny_total, nx
+        if symmetric is not None:
+            peers, mc, self._keep = symmetric
+            arr = (C.c_void_p * world)(*[C.c_void_p(int(p)) for p in peers])
+            self._h = C.c_void_p(lib.afk_gather_create_symmetric(world, rank, ny_total, nx, arr, C.c_void_p(int(mc) if mc else None)))
+            if not self._h:
+                raise AflakError(ERR_CUDA, lib.afk_last_error().decode())
+            self.multicast = bool(mc)
+            return
+        self.multicast = False
         h = (C.c_uint8 * 64)()
         self._h = C.c_void_p(lib.afk_gather_create(world, rank, ny_total, nx, h))
         if not self._h:
             raise AflakError(ERR_CUDA, lib.afk_last_error().decode())
-        self.world, self.rank, self.ny, self.nx = world, rank, ny_total, nx
         if world > 1:
             if exchange is None:
                 raise ValueError("world > 1 needs an exchange function")

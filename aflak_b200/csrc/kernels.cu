@@ -74,6 +74,13 @@ template <> struct Lane<1> {
     static __device__ __forceinline__ void unpack(const float &v, float (&x)[1]) { x[0] = v; }
     static __device__ __forceinline__ void store(float *p, const float (&x)[1]) { *p = x[0]; }
 };
+// store through an NVLink-SHARP multicast mapping: the switch replicates it into every bound GPU's memory
+__device__ __forceinline__ void mc_store(float *p, const float (&x)[4]) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(x[0]), "f"(x[1]), "f"(x[2]), "f"(x[3]) : "memory");
+}
+__device__ __forceinline__ void mc_store(float *p, const float (&x)[1]) {
+    asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(p), "f"(x[0]) : "memory");
+}
 
 // ----------------------------------------------------------------------------------------------------
 // K1/K2: axis-0 windowed reduction, stream-K decomposition
@@ -109,6 +116,7 @@ struct ReduceKArgs {
     unsigned epoch;
     int n_range_peer;
     unsigned *range_peer[kMaxPeers - 1];
+    int mc; // out[0] is an NVLink multicast mapping: one multimem.st per tile instead of one store per GPU
     // cluster variant (small images): float4 lanes per pixel tile, frame sub-groups per CTA
     int tile4, jsub;
     // range memo: the image's {~key(min), key(max), any, 0} left beside the pixels, without atomics on the result and without
@@ -487,8 +495,12 @@ __global__ void __launch_bounds__(kReduceBlock, MINB) reduce_kernel(const Reduce
                     mm_any = true;
                 }
             }
+            if (a.mc) {
+                mc_store(a.out[0] + px, o);
+            } else {
 #pragma unroll 1
-            for (int d = 0; d < a.nout; ++d) Lane<VEC>::store(a.out[d] + px, o);
+                for (int d = 0; d < a.nout; ++d) Lane<VEC>::store(a.out[d] + px, o);
+            }
         }
         u = seg_end;
     }
@@ -743,7 +755,13 @@ __global__ void __launch_bounds__(256) band_broadcast_kernel(const BandBroadcast
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n16; i += stride) {
         const uint4 v = a.src[i];
-        for (int d = 0; d < a.ndst; ++d) a.dst[d][i] = v;
+        if (a.mc_dst) { // one store through the multicast mapping (bits are copied, not interpreted)
+            asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a.mc_dst + i), "f"(__uint_as_float(v.x)),
+                         "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                         : "memory");
+        } else {
+            for (int d = 0; d < a.ndst; ++d) a.dst[d][i] = v;
+        }
     }
     __threadfence_system();
     __syncthreads();
@@ -907,7 +925,7 @@ ReducePlan reduce_plan(const ReduceArgs &a, int sm_count) {
     pl.grid = (int)((pl.units + pl.q - 1) / pl.q);
     pl.partial_bytes = (size_t)pl.grid * 2 * a.nwin * tile * sizeof(double2);
     pl.n_counters = (size_t)pl.ntiles;
-    if (pl.kg > 1 && pl.vec == 4 && a.n_signal == 0 && a.n_extra_out == 0) reduce_plan_cluster(a, pl);
+    if (pl.kg > 1 && pl.vec == 4 && a.n_signal == 0 && a.n_extra_out == 0 && !a.multicast_out) reduce_plan_cluster(a, pl);
     // range memo: 4 words per CTA after the partials, one more self-resetting counter after the tile counters
     pl.range_slot_offset = (pl.partial_bytes + 15) / 16 * 16;
     pl.partial_bytes = pl.range_slot_offset + (size_t)pl.grid * 4 * sizeof(unsigned);
@@ -1077,6 +1095,8 @@ cudaError_t reduce_launch(const ReduceArgs &a, const ReducePlan &pl, const Reduc
     k.psign = a.ew_sign;
     if (a.n_extra_out < 0 || a.n_extra_out > kMaxPeers - 1 || a.n_signal < 0 || a.n_signal > kMaxPeers) return cudaErrorInvalidValue;
     k.out[0] = a.out;
+    if (a.multicast_out && a.n_extra_out != 0) return cudaErrorInvalidValue;
+    k.mc = a.multicast_out;
     for (int d = 0; d < a.n_extra_out; ++d) k.out[1 + d] = a.extra_out[d];
     k.nout = 1 + a.n_extra_out;
     k.done = a.n_signal > 0 ? a.done : nullptr;

@@ -54,6 +54,9 @@ struct ReduceArgs {
     // n_range_peer more places (this rank's entry of every peer's range table) before it signals
     int n_range_peer;
     unsigned *range_peer[kMaxPeers - 1];
+    // NVLink-SHARP multicast: `out` is a multicast mapping (one multimem.st reaches every GPU's copy, this one included);
+    // n_extra_out must be 0 then.  Flags and range entries stay unicast.
+    int multicast_out;
 };
 
 struct ReduceWorkspace {
@@ -119,6 +122,7 @@ struct BandBroadcastArgs {
     int nsig;
     unsigned *sig[kMaxPeers];
     unsigned epoch;
+    uint4 *mc_dst;  // NVLink-SHARP multicast mapping of the destination (then ndst == 0 and src is the local copy), or nullptr
 };
 cudaError_t band_broadcast_launch(const BandBroadcastArgs &a, int sm_count, cudaStream_t s);
 

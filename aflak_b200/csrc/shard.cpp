@@ -21,6 +21,8 @@ struct afk_gather {
     //   32.. range table [2 slots][kMaxPeers][4] (min/max exchange) | 96.. combined range [2 slots][4]
     char *local = nullptr;
     char *peer[afk::kMaxPeers] = {nullptr};
+    char *mc = nullptr;             // NVLink-SHARP multicast mapping of the same layout (symmetric memory from the host), or nullptr
+    bool owned = true;              // false: the memory belongs to the host (afk_gather_create_symmetric)
     bool connected = false;
     unsigned epoch = 0;        // last epoch a reduce was enqueued for
     unsigned waited_epoch = 0; // last epoch a wait was enqueued for
@@ -42,7 +44,14 @@ struct afk_gather {
     unsigned *rgba_err() const { return control(rank) + 25; }
     unsigned *range_entry(int r, unsigned e, int of_rank) const { return control(r) + 32 + ((size_t)(e & 1u) * afk::kMaxPeers + of_rank) * 4; }
     unsigned *combined(unsigned e) const { return control(rank) + 96 + (size_t)(e & 1u) * 4; }
+    float *mc_slot(unsigned e) const { return reinterpret_cast<float *>(mc) + (size_t)(e & 1u) * slot_floats; }
+    uint8_t *mc_rgba_slot(unsigned e) const { return reinterpret_cast<uint8_t *>(mc) + (2 + (size_t)(e & 1u)) * slot_floats * sizeof(float); }
 };
+
+static size_t gather_slot_floats(int64_t ny_total, int64_t nx) { return ((size_t)ny_total * (size_t)nx + 63) / 64 * 64; }
+static size_t gather_bytes(int64_t ny_total, int64_t nx) {
+    return 4 * gather_slot_floats(ny_total, nx) * sizeof(float) + afk_gather::kControlWords * sizeof(unsigned);
+}
 
 using namespace afk;
 
@@ -73,9 +82,8 @@ afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx,
     g->ny = ny_total;
     g->nx = nx;
     for (int r = 0; r < world; ++r) afk_shard_band(ny_total, world, r, &g->y0[r], &g->rows[r]);
-    size_t fl = (size_t)ny_total * (size_t)nx;
-    g->slot_floats = (fl + 63) / 64 * 64;
-    g->bytes = 4 * g->slot_floats * sizeof(float) + afk_gather::kControlWords * sizeof(unsigned);
+    g->slot_floats = gather_slot_floats(ny_total, nx);
+    g->bytes = gather_bytes(ny_total, nx);
     void *p = nullptr;
     // cudaMalloc, not the stream-ordered pool: pool memory cannot be exported with cudaIpcGetMemHandle
     cudaError_t ce = cudaMalloc(&p, g->bytes);
@@ -92,6 +100,46 @@ afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx,
     g->peer[rank] = g->local;
     memcpy(handle_out, &h, 64);
     if (world == 1) g->connected = true;
+    return g;
+}
+
+size_t afk_gather_bytes(int64_t ny_total, int64_t nx) {
+    if (ny_total < 0 || nx < 0) return 0;
+    return gather_bytes(ny_total, nx);
+}
+
+// The same gather over memory the HOST supplies: a symmetric allocation of afk_gather_bytes() zeroed bytes on every rank,
+// peer_bases[r] = rank r's buffer as mapped in this process (peer_bases[rank] = the local one), multicast_base = an
+// NVLink-SHARP multicast mapping of the same buffers or NULL.  With a multicast mapping the reduce kernel's epilogue emits ONE
+// multimem.st per tile instead of one store per GPU (the switch replicates it), and so does the RGBA band broadcast.
+afk_gather *afk_gather_create_symmetric(int world, int rank, int64_t ny_total, int64_t nx, void *const *peer_bases, void *multicast_base) {
+    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || ny_total < 0 || nx < 0 || !peer_bases) {
+        fail(make_error(AFK_ERR_UNEXPECTED_INPUT, fmt("afk_gather_create_symmetric: world must be 1..%d and 0 <= rank < world", kMaxPeers)));
+        return nullptr;
+    }
+    for (int r = 0; r < world; ++r)
+        if (!peer_bases[r] || (reinterpret_cast<uintptr_t>(peer_bases[r]) & 255u)) {
+            fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_create_symmetric: every peer base must be a non-null, 256-byte aligned device pointer"));
+            return nullptr;
+        }
+    cudaStream_t s;
+    int dev;
+    if (fail(current_stream(&s, &dev)) != AFK_OK) return nullptr;
+    afk_gather *g = new afk_gather();
+    g->world = world;
+    g->rank = rank;
+    g->device = dev;
+    g->stream = s;
+    g->ny = ny_total;
+    g->nx = nx;
+    for (int r = 0; r < world; ++r) afk_shard_band(ny_total, world, r, &g->y0[r], &g->rows[r]);
+    g->slot_floats = gather_slot_floats(ny_total, nx);
+    g->bytes = gather_bytes(ny_total, nx);
+    for (int r = 0; r < world; ++r) g->peer[r] = static_cast<char *>(peer_bases[r]);
+    g->local = g->peer[rank];
+    g->mc = static_cast<char *>(multicast_base);
+    g->owned = false;
+    g->connected = true;
     return g;
 }
 
@@ -166,10 +214,15 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     if (epilogue == EPI_EW && !params) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "the equivalent-width epilogue needs params[5] = {a, b, fl, max, sign}"));
     for (int i = 0; i < 4; ++i) a.p[i] = epilogue == EPI_EW ? params[i] : 0.0f;
     a.ew_sign = epilogue == EPI_EW ? params[4] : 1.0f;
-    a.out = g->slot(g->rank, epoch) + band_off;
     int k = 0;
-    for (int r = 0; r < g->world; ++r)
-        if (r != g->rank) a.extra_out[k++] = g->slot(r, epoch) + band_off;
+    if (g->mc) { // one multicast store reaches every rank's copy, this rank's included
+        a.out = g->mc_slot(epoch) + band_off;
+        a.multicast_out = 1;
+    } else {
+        a.out = g->slot(g->rank, epoch) + band_off;
+        for (int r = 0; r < g->world; ++r)
+            if (r != g->rank) a.extra_out[k++] = g->slot(r, epoch) + band_off;
+    }
     a.n_extra_out = k;
     for (int r = 0; r < g->world; ++r) a.signal[r] = g->flags(r) + g->rank; // my word in rank r's flag array
     a.n_signal = g->world;
@@ -327,8 +380,12 @@ afk_status afk_gather_colormap(afk_gather *g, const afk_lut *lut, float vmin, fl
     b.src = reinterpret_cast<const uint4 *>(g->rgba_slot(g->rank, e2) + off);
     b.n16 = rows * g->nx * 4 / 16;
     int k = 0;
-    for (int r = 0; r < g->world; ++r)
-        if (r != g->rank) b.dst[k++] = reinterpret_cast<uint4 *>(g->rgba_slot(r, e2) + off);
+    if (g->mc) {
+        b.mc_dst = reinterpret_cast<uint4 *>(g->mc_rgba_slot(e2) + off);
+    } else {
+        for (int r = 0; r < g->world; ++r)
+            if (r != g->rank) b.dst[k++] = reinterpret_cast<uint4 *>(g->rgba_slot(r, e2) + off);
+    }
     b.ndst = k;
     b.done = g->rgba_done();
     b.nsig = g->world;
@@ -370,9 +427,11 @@ void afk_gather_destroy(afk_gather *g) {
     cudaDeviceSynchronize();
     for (afk_image *img : g->result)
         if (img) afk_image_release(img);
-    for (int r = 0; r < g->world; ++r)
-        if (r != g->rank && g->peer[r]) cudaIpcCloseMemHandle(g->peer[r]);
-    if (g->local) cudaFree(g->local);
+    if (g->owned) {
+        for (int r = 0; r < g->world; ++r)
+            if (r != g->rank && g->peer[r]) cudaIpcCloseMemHandle(g->peer[r]);
+        if (g->local) cudaFree(g->local);
+    }
     cudaGetLastError();
     delete g;
 }

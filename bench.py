@@ -530,6 +530,12 @@ def run_gpu(args):
         parity, ok = run_gather_parity(cx, gather, cube, nz, ny, nx, windows, out, full)
         failed |= not ok
 
+    # ---- the same step with the gather's stores going through an NVLink-SHARP multicast mapping (A/B, N > 1) ----
+    mc = None
+    if world > 1 and "mc" not in skip:
+        mc, ok = run_gather_multicast(cx, gather, cube, nz, ny, nx, windows, step_bytes, ms_step)
+        failed |= not ok
+
     # ---- e2e: host (pinned) cube -> upload -> operators -> host result ----
     e2e = None
     if "e2e" not in skip:
@@ -566,6 +572,8 @@ def run_gpu(args):
             "gather_parity": parity["status"] if parity else "skipped", "gather_parity_detail": parity,
             "c5_strong": c5,
         }
+        if mc is not None:
+            line["gather_multicast"] = mc
         if configs is not None:
             line["configs"] = configs
         if numa:
@@ -577,6 +585,58 @@ def run_gpu(args):
         dist.barrier()
         dist.destroy_process_group()
     return 1 if failed else 0
+
+
+def run_gather_multicast(cx, gather, cube, nz, ny, nx, windows, step_bytes, ms_p2p):
+    """Headline step with host-supplied symmetric memory (torch's allocator: cuMem + multicast object) whose multicast mapping
+    turns the epilogue's N stores per tile into one multimem.st.  Timed like the headline; the gathered image must equal the
+    peer-store gather's bit for bit (same kernel plan, same arithmetic)."""
+    afk, torch, dist = cx.afk, cx.torch, cx.dist
+    rank, world, stream, args = cx.rank, cx.world, cx.stream, cx.args
+    err, g2 = "", None
+    try:
+        sym = afk.symmetric_memory_torch(afk.gather_bytes(ny * world, nx))
+        g2 = afk.Gather(world, rank, ny * world, nx, symmetric=sym)
+    except Exception as e:
+        err = f"{type(e).__name__}: {str(e)[:200]}"
+    if not cx.all_ok(err == ""):
+        return {"status": "unavailable", "error": err}, True
+    info = {"status": "ok", "multicast_mapping": bool(g2.multicast),
+            "memory": "torch symmetric memory (cuMem + NVLink multicast object), passed to afk_gather_create_symmetric"}
+    for _ in range(args.warmup):
+        g2.reduce(cube.device_ptr, nz, windows, afk.EPI_MEAN_RATIO)
+        g2.wait()
+    cx.barrier()
+    afk.profile_reduce(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        g2.reduce(cube.device_ptr, nz, windows, afk.EPI_MEAN_RATIO)
+        g2.wait()
+    e1.record(stream)
+    cx.barrier()
+    k_ms, k_n = afk.profile_reduce_read()
+    afk.profile_reduce(False)
+    ms, kms = cx.max_over_ranks(e0.elapsed_time(e1) / args.steps, k_ms / max(k_n, 1))
+    # parity: one more step on both gathers, whole image, bit for bit
+    gather.reduce(cube.device_ptr, nz, windows, afk.EPI_MEAN_RATIO)
+    gather.wait()
+    a = gather.result_image().download()
+    g2.reduce(cube.device_ptr, nz, windows, afk.EPI_MEAN_RATIO)
+    g2.wait()
+    b = g2.result_image().download()
+    same = bits_equal(a, b)
+    try:
+        g2.check()
+    except Exception as e:
+        same = False
+        info["error"] = str(e)[:200]
+    ok = cx.all_ok(same)
+    info.update({"ms_per_step": ms, "value_GBps": step_bytes * world / (ms * 1e-3) / 1e9, "reduce_kernel_ms_max_over_ranks": kms,
+                 "peer_store_gather_ms_per_step": ms_p2p, "parity_vs_peer_store_gather": "ok (whole image, bit for bit, every rank)" if ok else "FAILED"})
+    cx.barrier()
+    g2.close()
+    return info, ok
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -1028,6 +1088,42 @@ def run_c5_strong(cx):
                         "algorithmic_bytes_global": bytes_global, "reduce_kernel_ms_max_over_ranks": kms,
                         "per_gpu_kernel_GBps": per_gpu, "per_gpu_frac_of_measured_peak": per_gpu / cx.peak,
                         "gathered_bytes_over_nvlink": ny * nx * 4 * (world - 1), "parity_sampled_rows": "ok" if ok else "FAILED"}
+    # ---- the same cases with the result stored through the NVLink multicast mapping (A/B against the peer stores) ----
+    if world > 1 and "mc" not in [x.strip() for x in cx.args.skip.split(",")]:
+        err, g2 = "", None
+        try:
+            g2 = afk.Gather(world, rank, ny, nx, symmetric=afk.symmetric_memory_torch(afk.gather_bytes(ny, nx)))
+        except Exception as e:
+            err = f"{type(e).__name__}: {str(e)[:200]}"
+        if cx.all_ok(err == ""):
+            mc_ok = True
+            for key, name, windows, epi, params in cases:
+                g.reduce(band.device_ptr, nz, windows, epi, params)
+                g.wait()
+                ref_img = g.result_image().download()
+                for _ in range(warm):
+                    g2.reduce(band.device_ptr, nz, windows, epi, params)
+                    g2.wait()
+                same = bits_equal(ref_img, g2.result_image().download())
+                del ref_img
+                cx.barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(steps):
+                    g2.reduce(band.device_ptr, nz, windows, epi, params)
+                    g2.wait()
+                e1.record(stream)
+                cx.barrier()
+                (ms2,) = cx.max_over_ranks(e0.elapsed_time(e1) / steps)
+                same = cx.all_ok(same)
+                mc_ok &= same
+                entries[key]["multicast_gather"] = {"ms_per_step_max_over_ranks": ms2, "multicast_mapping": bool(g2.multicast),
+                                                    "parity_vs_peer_store_gather": "ok (whole image, bit for bit)" if same else "FAILED"}
+            all_ok &= mc_ok
+            g2.close()
+        else:
+            base["multicast_gather"] = {"status": "unavailable", "error": err}
+
     # ---- sharded display chain: min/max exchange + every rank colour-maps its band + RGBA band gather ----
     lut = afk.Lut("Flame")
     lut.set_lims(0.2, 0.3, 0.9)
@@ -1148,7 +1244,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-store gather (default) or NCCL all_gather")
     ap.add_argument("--e2e-steps", type=int, default=5)
-    ap.add_argument("--skip", default="", help="comma list of blocks to leave out: c5, configs, e2e, cpu, parity")
+    ap.add_argument("--skip", default="", help="comma list of blocks to leave out: c5, configs, e2e, cpu, parity, mc")
     ap.add_argument("--no-cpu", action="store_true", help="same as --skip cpu")
     args = ap.parse_args()
     if args.no_cpu:

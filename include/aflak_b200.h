@@ -372,6 +372,13 @@ typedef struct afk_gather afk_gather;
 int afk_shard_band(int64_t ny, int world, int rank, int64_t *y0, int64_t *rows);
 afk_gather *afk_gather_create(int world, int rank, int64_t ny_total, int64_t nx, uint8_t handle_out[64]);
 int afk_gather_connect(afk_gather *g, const uint8_t *handles);
+/* The same gather over memory the HOST supplies (symmetric allocation: torch symmetric memory, NVSHMEM, or cuMem + a multicast
+ * object): afk_gather_bytes() zeroed bytes on every rank; peer_bases[world] = every rank's buffer as mapped in this process
+ * (peer_bases[rank] is the local one); multicast_base = NVLink-SHARP multicast mapping of the same buffers, or NULL.  With a
+ * multicast mapping the reduce kernel's epilogue and the RGBA band broadcast emit ONE multimem.st per 16 bytes instead of one
+ * store per GPU.  No afk_gather_connect needed; afk_gather_destroy does not free the memory. */
+size_t afk_gather_bytes(int64_t ny_total, int64_t nx);
+afk_gather *afk_gather_create_symmetric(int world, int rank, int64_t ny_total, int64_t nx, void *const *peer_bases, void *multicast_base);
 int afk_gather_band(const afk_gather *g, int rank, int64_t *y0, int64_t *rows);
 /* band_cube: device pointer to this rank's [nz, rows, nx] band; epilogue/sum_mode as afk_k_reduce; params is read for
  * epilogue 3 (EW) only and then holds exactly 5 floats (a, b, fl, max, sign) */

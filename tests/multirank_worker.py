@@ -23,7 +23,9 @@ import oracle
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 afk.set_device(local)
-dist.init_process_group("gloo")  # only the 64-byte IPC handles and the verdict cross the process group
+# only the 64-byte IPC handles and the verdict cross the process group (gloo); the NCCL half exists for torch's symmetric-memory
+# allocator, which supplies the multicast mapping of the second pass
+dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", local))
 oracle.build()
 
 
@@ -44,9 +46,24 @@ def same_bits(a, b):
 
 SEED = 0xAF1A0005
 failures = []
-# (nz, ny, nx): uneven split; small image (k-split variant of the kernel); an empty band on the last rank(s); vec=1 lanes
-for (nz, ny, nx) in [(96, 257, 128), (64, 74 + 1, 74), (48, max(world - 1, 1), 256), (40, 33, 37)]:
-    g = afk.Gather(world, rank, ny, nx, exchange if world > 1 else None)
+notes = []
+# (nz, ny, nx): uneven split; small image (k-split variant of the kernel); an empty band on the last rank(s); vec=1 lanes.
+# Every shape runs twice: library-allocated buffers + CUDA IPC peer stores, then host-supplied symmetric memory whose NVLink
+# multicast mapping (where the fabric has one) turns the epilogue's stores into one multimem.st per tile.
+for memory, (nz, ny, nx) in [(m, s) for m in ("ipc", "symmetric") for s in [(96, 257, 128), (64, 74 + 1, 74), (48, max(world - 1, 1), 256), (40, 33, 37)]]:
+    if memory == "symmetric":
+        if world < 2:
+            continue
+        try:
+            sym = afk.symmetric_memory_torch(afk.gather_bytes(ny, nx))
+        except Exception as e:  # no symmetric-memory support in this torch / driver: say so, the IPC pass above stands
+            notes.append(f"rank {rank}: symmetric memory unavailable ({type(e).__name__}: {str(e)[:120]})")
+            break
+        if not sym[1]:
+            notes.append(f"rank {rank}: no multicast mapping on this fabric; symmetric pass uses unicast peer stores")
+        g = afk.Gather(world, rank, ny, nx, symmetric=sym)
+    else:
+        g = afk.Gather(world, rank, ny, nx, exchange if world > 1 else None)
     y0, rows = g.band()
     assert (y0, rows) == afk.shard_band(ny, world, rank)
     band = afk.Image.synthetic(SEED, nz, ny, nx, y0=y0, rows=rows) if rows > 0 else afk.Image.alloc((nz, 0, nx))
@@ -80,15 +97,15 @@ for (nz, ny, nx) in [(96, 257, 128), (64, 74 + 1, 74), (48, max(world - 1, 1), 2
             if mode == afk.SUM_SEQUENTIAL:
                 # the sequential sum never splits a pixel: sharded == unsharded == oracle, bit for bit
                 if not same_bits(got, unsharded):
-                    failures.append(f"rank {rank} {(nz, ny, nx)} {name} sequential: sharded != unsharded")
+                    failures.append(f"rank {rank} {memory} {(nz, ny, nx)} {name} sequential: sharded != unsharded")
                 if not same_bits(got, want):
-                    failures.append(f"rank {rank} {(nz, ny, nx)} {name} sequential: sharded != oracle")
+                    failures.append(f"rank {rank} {memory} {(nz, ny, nx)} {name} sequential: sharded != oracle")
             else:
                 # compensated: the split of the spectral axis between CTAs depends on the band shape, so sharded and
                 # unsharded agree to the tier-C tolerance, not bit for bit
                 tol = dict(rtol=2e-4, atol=2e-4) if epi == afk.EPI_EW else dict(rtol=1e-5, atol=0)
                 if not np.allclose(got, want, equal_nan=True, **tol) or not np.allclose(got, unsharded, equal_nan=True, **tol):
-                    failures.append(f"rank {rank} {(nz, ny, nx)} {name} compensated: outside tolerance")
+                    failures.append(f"rank {rank} {memory} {(nz, ny, nx)} {name} compensated: outside tolerance")
     g.check()
     # protocol enforcement: a second reduce without a wait is refused
     g.reduce(band.device_ptr, nz, [(0, nz)], afk.EPI_SUM)
@@ -146,9 +163,12 @@ for (nz, ny, nx) in [(96, 257, 128), (64, 74 + 1, 74), (48, max(world - 1, 1), 2
 allf = [None] * world
 dist.all_gather_object(allf, failures)
 flat = [f for fs in allf for f in fs]
+allnotes = [None] * world
+dist.all_gather_object(allnotes, notes)
 if rank == 0:
-    for f in flat:
+    for f in flat + sorted({n for ns in allnotes for n in ns}):
         print(f, flush=True)
+    print("MULTICAST", "used" if world > 1 and not any(ns for ns in allnotes) else "not used", flush=True)
     print("MULTIRANK", "OK" if not flat else "FAILED", f"world={world}", flush=True)
 dist.barrier()
 dist.destroy_process_group()

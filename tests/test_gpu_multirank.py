@@ -24,4 +24,9 @@ def test_two_rank_gather_parity(gpu):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", "29517", os.path.join(ROOT, "tests", "multirank_worker.py")]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env, cwd=ROOT)
+    out_dir = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out_dir):  # evidence for the record: which memory paths ran (IPC peer stores, NVLink multicast)
+        with open(os.path.join(out_dir, "multirank_worker_stdout.txt"), "w") as f:
+            f.write(p.stdout[-8000:])
     assert p.returncode == 0 and f"MULTIRANK OK world={world}" in p.stdout, p.stdout[-4000:] + p.stderr[-4000:]
+    assert "MULTICAST used" in p.stdout or "unavailable" in p.stdout or "no multicast mapping" in p.stdout, p.stdout[-2000:]
