@@ -1442,6 +1442,655 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream1_kernel(co
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// median_stream2_kernel (round 2): the one-pass kernel rebuilt around what its phase trace showed
+// (profiles/r2_median_single_pass.json: stream 51 % of the time at 40 % issue utilisation, finish 19 %, re-collect 16 %,
+// sample sort 10 %; profiles/r2_median_v2_phases.txt for the steps in between).
+//
+// A CTA is 8 warps (2 CTAs = 512 threads per SM, up to 128 registers each).  Thread (warp g, lane) owns the frames
+// g, g+8, g+16, ... of spaxel `lane` ("its" frames, t = 0, 1, ...) and a PRIVATE segment of 100 slots of the spaxel's
+// 800-slot row, in every phase:
+//   S  The samples are part of the stream, not an extra read: the thread's frames t = 0, ss, 2 ss, ... (ss = ceil(frames /
+//      64): ~60 per thread, ~480 per spaxel, stratified over the window) are loaded first and stay in registers.  Each
+//      thread sorts ITS samples with a bitonic network in registers (672 compare-exchanges of two FMNMX, no shuffles, no
+//      shared memory: 1/8 of the instructions of the warp-wide sort of 256 keys per spaxel it replaces, with twice the
+//      samples) and reads the quantiles 0.5 -+ w and 0.5 -+ w2 off its run (interpolated); lo / hi / the wing pivots of the
+//      spaxel are the means of the 8 runs' quantiles.  A pivot does not have to be a value of the spectrum; w is 3 sigma
+//      of that estimator (host side), so the bracket misses ~0.3 % of the spaxels instead of 1.8 % and the list is no longer
+//      than before (12 % of the window).
+//   C  No atomics in the stream: an append is one predicated shared store into the private segment and a pointer bump
+//      (the shared-atomic round trip per key, whose returned slot serialised every step, is gone).  Float compares on the
+//      raw values (x == lo, lo < x < hi, x >= hi; x < lo is what remains): no key transform per voxel, NaNs are caught by
+//      one min.NaN per voxel: 11 instructions per voxel against ~19.  +-0 compare equal, which only matters for the sign
+//      of a zero result -- median_zero_fix_kernel decides that for every kernel of this file.  The sorted samples are
+//      classified from their registers; the other frames are walked column by column (t = j ss + c for c = 1 .. ss-1) in
+//      batches of 16 loads, two batches in ping-pong.
+//   D  As before: a bracket that missed the wanted rank is re-collected by the whole CTA from the wing next to it (or the
+//      open bin beyond when the wing pivot is not distinct); so is a spaxel with an overflowing segment.  A list that
+//      still overflows is refined against the global column.  Exactness never depends on the data.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kM2Warps = 8;
+constexpr int kM2Seg = kMsCap / kM2Warps; // 100 private slots per (warp, spaxel)
+constexpr int kM2Smp = 64;                // samples per thread (at most)
+static_assert(kM2Seg * kM2Warps == kMsCap, "segments tile the row");
+static_assert((size_t)kM2Warps * kM2Smp * kMsPix <= (size_t)kMsPix * kMsRow, "the sorted runs alias the list area");
+
+__device__ __forceinline__ float m2_min_nan(float a, float b) {
+    float r;
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+// ascending bitonic sort of N values in registers (every index is a compile-time constant)
+template <int N> __device__ __forceinline__ void m2_sort_regs(float (&v)[N]) {
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const bool asc = (i & k) == 0;
+                    const float x = v[i], y = v[l];
+                    const float mn = fminf(x, y), mx = fmaxf(x, y);
+                    v[i] = asc ? mn : mx;
+                    v[l] = asc ? mx : mn;
+                }
+            }
+        }
+    }
+}
+
+// quantile q of a sorted run of ms values in shared memory (stride 32 words): linear interpolation between two order
+// statistics at the plotting position q ms - 1/2; infinities never produce a NaN
+__device__ __forceinline__ float m2_run_quantile(const float *run, int ms, float q) {
+    float pos = __fsub_rn(__fmul_rn(q, (float)ms), 0.5f);
+    pos = fminf(fmaxf(pos, 0.0f), (float)(ms - 1));
+    int i0 = (int)pos;
+    if (i0 > ms - 2) i0 = ms - 2;
+    if (i0 < 0) i0 = 0;
+    const float fr = __fsub_rn(pos, (float)i0);
+    const float x = run[i0 * 32], y = run[(ms > 1 ? i0 + 1 : i0) * 32];
+    float v = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, fr), x), __fmul_rn(fr, y));
+    if (v != v) v = fr < 0.5f ? x : y;
+    return v;
+}
+
+template <int kM2U> // loads per batch, two batches in flight
+__global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(const MedianK a, float wq, float wq2) {
+    extern __shared__ unsigned s_list[]; // [kMsPix][kMsRow]: 8 private segments of 100 slots per spaxel; phase S aliases the sorted runs onto it
+    __shared__ float s_q[4][kM2Warps][kMsPix]; // per-run quantiles: lo, hi, wing lo, wing hi
+    __shared__ float s_lo[kMsPix], s_hi[kMsPix];
+    __shared__ unsigned s_cnt[kMsPix];
+    __shared__ unsigned s_seg[kM2Warps][kMsPix], s_eq[kM2Warps][kMsPix], s_bel[kM2Warps][kMsPix];
+    __shared__ float s_hmin[kM2Warps][kMsPix];
+    __shared__ unsigned s_r[kMsPix], s_eqt[kMsPix], s_abv[kMsPix], s_haslo[kMsPix], s_hashi[kMsPix], s_miss[kMsPix], s_belt[kMsPix], s_packed[kMsPix];
+    const int n = (int)a.n;
+    const int tid = threadIdx.x, g = tid >> 5, lane = tid & 31;
+    const int64_t px0 = (int64_t)blockIdx.x * kMsPix;
+    const int64_t mypx = px0 + lane;
+    const bool active = mypx < a.n2;
+    const float *col = a.cube + a.start * a.n2 + (active ? mypx : a.n2 - 1); // inactive lanes do the same work on a valid address
+    const unsigned r0 = (unsigned)((n - 1) / 2);
+    const bool even = (n & 1) == 0;
+    const float kInf = __int_as_float(0x7f800000);
+    if (px0 >= a.n2) return; // the grid is padded to whole clusters
+    long long t_tr = a.trace ? clock64() : 0;
+    // this thread's frames: t = 0 .. mine-1 is frame g + 8 t; samples t = j ss (j < ms <= 64); columns c = 1 .. ss-1 hold the rest
+    const int mine = (n - g + kM2Warps - 1) / kM2Warps;
+    const int ss = (mine + kM2Smp - 1) / kM2Smp;
+    const int ms = (mine + ss - 1) / ss;
+    const size_t tstep = (size_t)kM2Warps * a.n2;   // elements between two of this thread's frames
+    const size_t jstep = tstep * (size_t)ss;        // ... between two entries of a column
+    const float *const tcol = col + (size_t)g * a.n2;
+    float nan_acc = 0.0f;
+    // ---- S: samples -> sorted run -> quantiles -> bracket ----
+    float smp[kM2Smp];
+#pragma unroll
+    for (int j = 0; j < kM2Smp; ++j) {
+        smp[j] = kInf; // pads sort behind the samples: the first ms sorted values are the samples
+        if (j < ms) smp[j] = __uint_as_float(ms_ld(tcol + (size_t)j * jstep));
+    }
+#pragma unroll
+    for (int j = 0; j < kM2Smp; ++j) nan_acc = m2_min_nan(nan_acc, smp[j]);
+    ms_trace(a, 0, t_tr);
+    m2_sort_regs<kM2Smp>(smp);
+    {
+        float *run = reinterpret_cast<float *>(s_list) + (size_t)g * kM2Smp * 32 + lane; // [g][j][lane]: conflict-free
+#pragma unroll
+        for (int j = 0; j < kM2Smp; ++j) run[j * 32] = smp[j];
+        s_q[0][g][lane] = m2_run_quantile(run, ms, 0.5f - wq);
+        s_q[1][g][lane] = m2_run_quantile(run, ms, 0.5f + wq);
+        s_q[2][g][lane] = m2_run_quantile(run, ms, 0.5f - wq2);
+        s_q[3][g][lane] = m2_run_quantile(run, ms, 0.5f + wq2);
+    }
+    __syncthreads(); // the runs are dead: the lists may be written
+    float lo = 0.0f, hi = 0.0f;
+#pragma unroll
+    for (int w = 0; w < kM2Warps; ++w) {
+        lo = __fadd_rn(lo, __fmul_rn(s_q[0][w][lane], 0.125f));
+        hi = __fadd_rn(hi, __fmul_rn(s_q[1][w][lane], 0.125f));
+    }
+    if (lo != lo) lo = s_q[0][0][lane]; // +inf and -inf among the runs
+    if (hi != hi) hi = s_q[1][0][lane];
+    // the classes below must be disjoint: lo < hi strictly.  Tied quantiles: the bracket is everything above lo (the wanted
+    // rank is then almost surely in the `== lo` class); nothing is above +inf.
+    if (!(hi > lo)) hi = (lo == kInf) ? __int_as_float(0x7fc00000) : kInf;
+    ms_trace(a, 1, t_tr);
+    // ---- C: classify.  x == lo, lo < x < hi (appended), x >= hi (counted, smallest kept); x < lo is what remains.
+    //      The stream is bound by the ALU pipe (compares, min/max and integer adds issue at half rate: profiles/
+    //      r2_median_v2_phases.txt), so a voxel costs 7 ALU instructions -- three compares (the third takes !(x >= hi) as a
+    //      predicate operand), two min/max, the list pointer and the load address -- and the two counters are predicated FADDs
+    //      on the FMA pipe (exact: at most 550 frames per thread).  The check against the end of the segment is hoisted out of a
+    //      whole batch. ----
+    float f_eq_cnt = 0.0f, f_ge_cnt = 0.0f;
+    float hi_min = kInf;
+    const unsigned seg0 = (unsigned)__cvta_generic_to_shared(s_list + lane * kMsRow + g * kM2Seg);
+    unsigned wp = seg0; // keeps counting past the segment: D0 sees the overflow
+    const unsigned wend = seg0 + kM2Seg * 4u;
+    auto classify_checked = [&](unsigned rawbits) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred pe, pg, pi, ps;\n\t"
+            ".reg .f32 x;\n\t"
+            "mov.b32 x, %5;\n\t"
+            "setp.eq.f32 pe, x, %6;\n\t"
+            "@pe add.f32 %0, %0, 0f3F800000;\n\t"
+            "setp.ge.f32 pg, x, %7;\n\t"
+            "@pg add.f32 %1, %1, 0f3F800000;\n\t"
+            "@pg min.f32 %2, %2, x;\n\t"
+            "setp.gt.and.f32 pi, x, %6, !pg;\n\t"
+            "setp.lt.and.u32 ps, %4, %8, pi;\n\t"
+            "@ps st.shared.u32 [%4], %5;\n\t"
+            "@pi add.u32 %4, %4, 4;\n\t"
+            "min.NaN.f32 %3, %3, x;\n\t"
+            "}"
+            : "+f"(f_eq_cnt), "+f"(f_ge_cnt), "+f"(hi_min), "+f"(nan_acc), "+r"(wp)
+            : "r"(rawbits), "f"(lo), "f"(hi), "r"(wend)
+            : "memory");
+    };
+    auto classify = [&](unsigned rawbits) { // the caller has checked that 16 / 32 more appends fit the segment
+        asm volatile(
+            "{\n\t"
+            ".reg .pred pe, pg, pi;\n\t"
+            ".reg .f32 x;\n\t"
+            "mov.b32 x, %5;\n\t"
+            "setp.eq.f32 pe, x, %6;\n\t"
+            "@pe add.f32 %0, %0, 0f3F800000;\n\t"
+            "setp.ge.f32 pg, x, %7;\n\t"
+            "@pg add.f32 %1, %1, 0f3F800000;\n\t"
+            "@pg min.f32 %2, %2, x;\n\t"
+            "setp.gt.and.f32 pi, x, %6, !pg;\n\t"
+            "@pi st.shared.u32 [%4], %5;\n\t"
+            "@pi add.u32 %4, %4, 4;\n\t"
+            "min.NaN.f32 %3, %3, x;\n\t"
+            "}"
+            : "+f"(f_eq_cnt), "+f"(f_ge_cnt), "+f"(hi_min), "+f"(nan_acc), "+r"(wp)
+            : "r"(rawbits), "f"(lo), "f"(hi)
+            : "memory");
+    };
+#pragma unroll
+    for (int j = 0; j < kM2Smp; ++j)
+        if (j < ms) classify_checked(__float_as_uint(smp[j]));
+    {
+        // batches never straddle a column; a column's last batch is short (warp-uniform guards)
+        int c = 1, j = 0;
+        int ccnt = c < ss ? (mine - c + ss - 1) / ss : 0;
+        const float *cptr = tcol + tstep; // column c, entry 0
+        auto load = [&](unsigned (&raw)[kM2U], int &nv) {
+            nv = ccnt - j < kM2U ? ccnt - j : kM2U;
+            const float *p = cptr + (size_t)j * jstep;
+            if (nv == kM2U) {
+#pragma unroll
+                for (int u = 0; u < kM2U; ++u) raw[u] = ms_ld(p + (size_t)u * jstep);
+            } else {
+#pragma unroll
+                for (int u = 0; u < kM2U; ++u)
+                    if (u < nv) raw[u] = ms_ld(p + (size_t)u * jstep);
+            }
+            j += kM2U;
+            if (j >= ccnt) {
+                ++c;
+                j = 0;
+                cptr += tstep;
+                ccnt = c < ss ? (mine - c + ss - 1) / ss : 0;
+            }
+        };
+        auto process = [&](const unsigned (&raw)[kM2U], int nv) {
+            if (nv == kM2U && wp + 4u * kM2U <= wend) {
+#pragma unroll
+                for (int u = 0; u < kM2U; ++u) classify(raw[u]);
+            } else {
+#pragma unroll
+                for (int u = 0; u < kM2U; ++u)
+                    if (u < nv) classify_checked(raw[u]);
+            }
+        };
+        unsigned ra[kM2U], rb[kM2U];
+        int na = 0, nb = 0;
+        if (ccnt > 0) load(ra, na);
+        while (na > 0) {
+            nb = 0;
+            if (ccnt > 0) load(rb, nb);
+            process(ra, na);
+            na = 0;
+            if (nb == 0) break;
+            if (ccnt > 0) load(ra, na);
+            process(rb, nb);
+        }
+    }
+    const bool nan = nan_acc != nan_acc;
+    const unsigned cnt = (wp - seg0) >> 2;
+    const unsigned n_eq = (unsigned)f_eq_cnt, n_ge = (unsigned)f_ge_cnt;
+    s_seg[g][lane] = cnt;
+    s_eq[g][lane] = n_eq;
+    s_bel[g][lane] = (unsigned)mine - n_eq - n_ge - cnt; // x < lo (a NaN is in no class: the count is then meaningless, and the flag is set)
+    s_hmin[g][lane] = hi_min;
+    if (tid < kMsPix) { s_lo[tid] = 0.0f; s_hi[tid] = 0.0f; }
+    __syncthreads();
+    ms_trace(a, 2, t_tr);
+    // ---- D0: lane = spaxel: does the bracket hold the wanted rank?  If not, the bin becomes the WING next to it (it fits the
+    //      list), or the open bin beyond when the wing pivot is not distinct from the bracket's ----
+    // s_miss: 0 hit, segmented list; 1 wing below; 2 wing above; 3 hit, but a segment overflowed: same bracket, re-collected
+    //         into a contiguous list; 4 / 5 open bin below / above (final)
+    if (g == 0) {
+        unsigned eq = 0u, bel = 0u, mt = 0u;
+        float hm = kInf, lo2 = 0.0f, hi2 = 0.0f;
+        bool ovf = false;
+#pragma unroll
+        for (int w = 0; w < kM2Warps; ++w) {
+            const unsigned c = s_seg[w][lane];
+            eq += s_eq[w][lane];
+            bel += s_bel[w][lane];
+            hm = fminf(hm, s_hmin[w][lane]);
+            mt += c;
+            ovf |= c > (unsigned)kM2Seg;
+            lo2 = __fadd_rn(lo2, __fmul_rn(s_q[2][w][lane], 0.125f));
+            hi2 = __fadd_rn(hi2, __fmul_rn(s_q[3][w][lane], 0.125f));
+        }
+        unsigned r, miss = 0u, haslo = 1u, hashi = 1u;
+        float blo = lo, bhi = hi;
+        if (r0 < bel) {
+            r = r0;
+            bhi = lo;
+            if (lo2 < lo) { blo = lo2; miss = 1u; }
+            else { haslo = 0u; miss = 4u; }
+        } else if (r0 - bel >= eq + mt) { // above it: [hi, hi2), hi itself counted as the new `eq`
+            r = r0 - bel - eq - mt;
+            blo = hi;
+            if (hi2 > hi) { bhi = hi2; miss = 2u; }
+            else { hashi = 0u; miss = 5u; }
+        } else {
+            r = r0 - bel;
+            // an overflowing segment only matters when the list is needed: not when the answer is lo itself
+            const bool answer_is_lo = r < eq && (!even || r + 1 < eq);
+            if (ovf && !answer_is_lo) miss = 3u;
+            if (ovf && answer_is_lo) mt = 0u;
+            if (bhi != bhi) hashi = 0u; // lo == +inf: nothing above it
+        }
+        unsigned above = med_key(hm);
+        if (miss) { mt = 0u; eq = 0u; above = kFull; }
+        s_lo[lane] = blo; s_hi[lane] = bhi;
+        s_cnt[lane] = mt;
+        s_r[lane] = r; s_eqt[lane] = eq; s_abv[lane] = above; s_haslo[lane] = haslo; s_hashi[lane] = hashi; s_belt[lane] = bel;
+        s_miss[lane] = active ? miss : 0u;
+        s_packed[lane] = (active && miss) || (ovf && !miss) ? 1u : 0u; // the list is contiguous keys already (re-collected), or not needed
+        if (a.trace) {
+            if (active && miss && miss != 3u) atomicAdd(a.trace + 5, 1ull);
+            if (active && miss == 3u) atomicAdd(a.trace + 7, 1ull);
+            if (active && !miss) atomicAdd(a.trace + 6, (unsigned long long)mt);
+        }
+    }
+    __syncthreads();
+    // ---- D1: the whole CTA re-collects the bin of a spaxel whose bracket missed (every frame of the column in flight) ----
+    auto recollect = [&]() {
+        for (int p = 0; p < kMsPix; ++p) {
+            if (!s_miss[p]) continue; // CTA-uniform
+            const float *pcol = a.cube + a.start * a.n2 + (px0 + p);
+            const float plo = s_lo[p], phi = s_hi[p];
+            const bool phas = s_haslo[p] != 0u, phashi = s_hashi[p] != 0u;
+            unsigned *list = s_list + p * kMsRow;
+            unsigned eqc = 0u, hm = kFull;
+            constexpr int kPer = (int)((kMs1MaxFrames + kMsPix * kM2Warps - 1) / (kMsPix * kM2Warps)); // frames per thread
+            unsigned kk[kPer];
+#pragma unroll
+            for (int u = 0; u < kPer; ++u) {
+                const int k = tid + u * kMsPix * kM2Warps;
+                kk[u] = k < n ? ms_ld(pcol + (size_t)k * a.n2) : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < kPer; ++u) {
+                const bool valid = tid + u * kMsPix * kM2Warps < n;
+                const float x = __uint_as_float(kk[u]);
+                const unsigned key = ms_key(kk[u]);
+                if (valid && phas && x == plo) ++eqc;
+                if (valid && phashi && x >= phi) hm = min(hm, key);
+                // one shared atomic per warp and step, not per key: every append of this loop goes to the same counter
+                const bool keep = valid && (!phas || x > plo) && (!phashi || x < phi);
+                const unsigned bal = __ballot_sync(kFull, keep);
+                if (bal) {
+                    unsigned base = 0u;
+                    if (lane == __ffs(bal) - 1) base = atomicAdd(&s_cnt[p], (unsigned)__popc(bal));
+                    base = __shfl_sync(kFull, base, __ffs(bal) - 1);
+                    const unsigned at = base + __popc(bal & ((1u << lane) - 1u));
+                    if (keep && at < (unsigned)kMsCap) list[at] = key;
+                }
+            }
+            eqc = __reduce_add_sync(kFull, eqc);
+            hm = __reduce_min_sync(kFull, hm);
+            if (lane == 0) {
+                if (eqc) atomicAdd(&s_eqt[p], eqc);
+                if (hm != kFull) atomicMin(&s_abv[p], hm);
+            }
+        }
+    };
+    recollect();
+    __syncthreads();
+    // the wing is counted: rank inside it, or (6 sigma) the open bin beyond it
+    if (g == 0) {
+        const unsigned miss = s_miss[lane];
+        unsigned again = 0u;
+        if (miss == 1u) {
+            const unsigned below2 = s_belt[lane] - s_eqt[lane] - s_cnt[lane]; // values < lo2
+            if (r0 >= below2) {
+                s_r[lane] = r0 - below2;
+            } else {
+                s_hi[lane] = s_lo[lane];
+                s_haslo[lane] = 0u;
+                s_r[lane] = r0;
+                again = 4u;
+            }
+        } else if (miss == 2u) {
+            const unsigned inside = s_eqt[lane] + s_cnt[lane]; // values in [hi, hi2)
+            if (s_r[lane] >= inside) {
+                s_r[lane] -= inside;
+                s_lo[lane] = s_hi[lane];
+                s_hashi[lane] = 0u;
+                again = 5u;
+            }
+        }
+        if (again) { s_cnt[lane] = 0u; s_eqt[lane] = 0u; s_abv[lane] = kFull; }
+        s_miss[lane] = again;
+    }
+    __syncthreads();
+    recollect();
+    __syncthreads();
+    ms_trace(a, 3, t_tr);
+    // ---- F: the finish.  The candidates S of a spaxel (values strictly inside its bin) stay where they are, spread over the 8
+    //      private segments, and all 256 threads work on all 32 spaxels at once in the (warp g, lane = spaxel) layout of the
+    //      stream: a round = every thread offers one of its candidates as a pivot; every thread counts its segment against the
+    //      spaxel's 8 sorted pivots (registers, no shuffles), the counts are summed with shared-memory reductions; every thread
+    //      then compacts ITS segment in place to the bin that holds the wanted rank (no data moves between threads).  ~5x
+    //      fewer candidates per round; when <= 32 are left they are gathered and ranked by counting.  One warp per spaxel
+    //      (the earlier finish) had 2 x 8 warps per SM waiting on dependent shuffles and ballots: 56k of 165k cycles per CTA. ----
+    float *const f_pv = &s_q[0][0][0];                                  // [8][32] pivot offers
+    unsigned *const f_c = reinterpret_cast<unsigned *>(&s_q[1][0][0]);  // [2][32][8] pivot counts, two rounds' worth
+    unsigned *const f_k = reinterpret_cast<unsigned *>(&s_q[3][0][0]);  // [8][32] candidates per thread
+    unsigned *const f_mode = s_miss;  // 0 live: klo = S[r] (and khi = S[r+1] or `above`); 1 live: klo is known, khi = min S; 2 done; 3 slow path
+    unsigned *const f_klo = s_haslo, *const f_khi = s_hashi; // results as keys
+    unsigned *const f_eq = s_eqt, *const f_m2 = s_belt;      // per-round sums: candidates equal to the bin's lower pivot, candidates kept
+    float *const seg = reinterpret_cast<float *>(s_list) + lane * kMsRow + g * kM2Seg;
+    unsigned c_own;
+    {
+        // a re-collected list is contiguous keys: view it as segments of raw values (thread g takes [100 g, 100 g + 100))
+        const unsigned m = s_cnt[lane];
+        if (s_packed[lane]) {
+            const unsigned b = (unsigned)(g * kM2Seg);
+            c_own = m <= (unsigned)kMsCap ? (m > b ? min(m - b, (unsigned)kM2Seg) : 0u) : 0u;
+            for (unsigned i = 0; i < c_own; ++i) seg[i] = med_unkey(__float_as_uint(seg[i]));
+        } else {
+            c_own = min(s_seg[g][lane], (unsigned)kM2Seg);
+        }
+    }
+    __syncthreads(); // s_q, s_seg are dead from here on
+    for (int i = tid; i < 2 * kMsPix * 8; i += kMsPix * kM2Warps) f_c[i] = 0u;
+    if (g == 0) {
+        const unsigned m = s_cnt[lane], eq = s_eqt[lane], r = s_r[lane];
+        const bool haslo = s_haslo[lane] != 0u;
+        const unsigned klo_key = med_key(s_lo[lane]);
+        unsigned mode, klo = 0u, khi = 0u, rr = 0u;
+        if (!active) {
+            mode = 2u;
+        } else if (m > (unsigned)kMsCap) {
+            mode = 3u;
+        } else if (haslo && r < eq) { // the wanted value is lo itself
+            klo = klo_key;
+            khi = klo_key;
+            mode = 2u;
+            if (even && !(r + 1 < eq)) { // ... and its successor the smallest candidate, or `above`
+                if (m == 0u) khi = s_abv[lane];
+                else mode = 1u;
+            }
+        } else {
+            rr = r - (haslo ? eq : 0u);
+            mode = 0u;
+            if (rr >= m) { mode = 2u; } // only with NaNs in the window (the flag is set): any value will do
+        }
+        f_mode[lane] = mode;
+        if (mode != 3u) { f_klo[lane] = klo; f_khi[lane] = khi; s_r[lane] = rr; f_eq[lane] = 0u; f_m2[lane] = 0u; }
+    }
+    __syncthreads();
+    unsigned seed = (unsigned)(px0 + lane) * 0x9E3779B9u + (unsigned)g * 0x85EBCA6Bu + 0x7F4A7C15u;
+    for (int round = 0;; ++round) {
+        const unsigned mode = f_mode[lane];
+        const bool big = mode < 2u && s_cnt[lane] > 32u;
+        if (!__syncthreads_or(big ? 1 : 0)) break;
+        unsigned *const cnt_now = f_c + (round & 1) * kMsPix * 8 + lane * 8;
+        // R1: pivot offers
+        seed = seed * 1664525u + 1013904223u;
+        f_pv[g * kMsPix + lane] = (big && c_own > 0u) ? seg[(seed >> 8) % c_own] : __int_as_float(0x7fc00000);
+        __syncthreads();
+        // R2: counts of this segment against the spaxel's sorted pivots (a compare on the ALU pipe + a predicated FADD each)
+        float pv[8];
+        if (big) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                pv[j] = f_pv[j * kMsPix + lane];
+                if (pv[j] != pv[j]) pv[j] = kInf; // no offer: sorts last, counts every finite candidate
+            }
+            m2_sort_regs<8>(pv);
+            float cj[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) cj[j] = 0.0f;
+#pragma unroll 4
+            for (unsigned i = 0; i < c_own; ++i) {
+                const float x = seg[i];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.f32 %0, %0, 0f3F800000;\n\t}" : "+f"(cj[j]) : "f"(x), "f"(pv[j]));
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (cj[j] != 0.0f) atomicAdd(cnt_now + j, (unsigned)cj[j]);
+        }
+        __syncthreads();
+        // R3: the bin that holds the wanted rank; compact this segment to it.  An open side is a NaN bound: `x >= NaN` is
+        // false and `x >u NaN` (greater or unordered) is true, so the loop has no flags.
+        unsigned below_b = 0u;
+        float lo_b = __int_as_float(0x7fc00000), hi_b = __int_as_float(0x7fc00000);
+        if (big) {
+            const unsigned r = mode == 1u ? 0u : s_r[lane];
+            unsigned C[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) C[j] = cnt_now[j];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (C[j] <= r) { below_b = C[j]; lo_b = pv[j]; }
+#pragma unroll
+            for (int j = 7; j >= 0; --j)
+                if (C[j] > r) hi_b = pv[j];
+            float eq_f = 0.0f, ge_f = 0.0f, hmin = kInf;
+            const unsigned w0 = (unsigned)__cvta_generic_to_shared(seg);
+            unsigned wq_ = w0;
+#pragma unroll 4
+            for (unsigned i = 0; i < c_own; ++i) {
+                const float x = seg[i];
+                asm volatile(
+                    "{\n\t"
+                    ".reg .pred pe, pg, pk;\n\t"
+                    "setp.eq.f32 pe, %4, %5;\n\t"
+                    "@pe add.f32 %0, %0, 0f3F800000;\n\t"
+                    "setp.ge.f32 pg, %4, %6;\n\t"
+                    "@pg add.f32 %1, %1, 0f3F800000;\n\t"
+                    "@pg min.f32 %2, %2, %4;\n\t"
+                    "setp.gtu.and.f32 pk, %4, %5, !pg;\n\t"
+                    "@pk st.shared.f32 [%3], %4;\n\t" // at or below slot i: in place
+                    "@pk add.u32 %3, %3, 4;\n\t"
+                    "}"
+                    : "+f"(eq_f), "+f"(ge_f), "+f"(hmin), "+r"(wq_)
+                    : "f"(x), "f"(lo_b), "f"(hi_b)
+                    : "memory");
+            }
+            c_own = (wq_ - w0) >> 2;
+            if (eq_f != 0.0f) atomicAdd(&f_eq[lane], (unsigned)eq_f);
+            if (c_own) atomicAdd(&f_m2[lane], c_own);
+            if (ge_f != 0.0f) atomicMin(&s_abv[lane], med_key(hmin)); // candidates >= hi sort below every earlier `above`
+        }
+        __syncthreads();
+        // R4: lane = spaxel: new rank, or the answer when the rank fell on the lower pivot
+        if (g == 0 && big) {
+            const unsigned eqt = f_eq[lane], m2 = f_m2[lane];
+            const unsigned r = mode == 1u ? 0u : s_r[lane];
+            const unsigned rr = r - below_b;
+            const unsigned pk = med_key(lo_b);
+            const bool has_lo_b = lo_b == lo_b;
+            if (has_lo_b && rr < eqt) {
+                if (mode == 1u) {
+                    f_khi[lane] = pk;
+                    f_mode[lane] = 2u;
+                } else {
+                    f_klo[lane] = pk;
+                    f_khi[lane] = pk;
+                    f_mode[lane] = 2u;
+                    if (even && !(rr + 1 < eqt)) {
+                        if (m2 == 0u) f_khi[lane] = s_abv[lane];
+                        else { f_mode[lane] = 1u; s_r[lane] = 0u; }
+                    }
+                }
+            } else {
+                s_r[lane] = rr - (has_lo_b ? eqt : 0u);
+            }
+            s_cnt[lane] = m2;
+            f_eq[lane] = 0u;
+            f_m2[lane] = 0u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) cnt_now[j] = 0u; // next used two rounds from now
+        }
+        __syncthreads();
+    }
+    // at most 32 candidates per live spaxel: gather them at the front of the row and rank them by counting, still in the
+    // (warp g, lane = spaxel) layout: thread g ranks the candidates g, g + 8, g + 16, g + 24 of its spaxel against all of them
+    f_k[g * kMsPix + lane] = c_own;
+    __syncthreads();
+    {
+        const unsigned mode = f_mode[lane];
+        if (mode < 2u && c_own > 0u && g > 0) {
+            unsigned off = 0u;
+            for (int w = 0; w < g; ++w) off += f_k[w * kMsPix + lane];
+            // segment 0 starts at the front and stays; the others land behind its <= 32 candidates
+            float *row = reinterpret_cast<float *>(s_list) + lane * kMsRow;
+            for (unsigned i = 0; i < c_own; ++i) row[off + i] = seg[i];
+        }
+        if (g == 0 && mode == 0u && even && s_r[lane] + 1u >= s_cnt[lane]) f_khi[lane] = s_abv[lane]; // the successor is beyond S
+    }
+    __syncthreads();
+    {
+        const unsigned mode = f_mode[lane];
+        const unsigned m = s_cnt[lane];
+        if (mode < 2u && m > 0u) {
+            const float *row = reinterpret_cast<const float *>(s_list) + lane * kMsRow;
+            const unsigned r = mode == 1u ? 0u : s_r[lane];
+            float xc[4], lt[4], le[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const unsigned i = (unsigned)g + 8u * k;
+                xc[k] = row[i < m ? i : 0u];
+                lt[k] = 0.0f;
+                le[k] = 0.0f;
+            }
+            for (unsigned j = 0; j < m; ++j) {
+                const float y = row[j];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.f32 %0, %0, 0f3F800000;\n\t}" : "+f"(lt[k]) : "f"(y), "f"(xc[k]));
+                    asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t@p add.f32 %0, %0, 0f3F800000;\n\t}" : "+f"(le[k]) : "f"(y), "f"(xc[k]));
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if ((unsigned)g + 8u * k >= m) continue;
+                const unsigned l = (unsigned)lt[k], h = (unsigned)le[k];
+                const unsigned key = med_key(xc[k]);
+                // equal candidates write the same value (a zero of either sign: median_zero_fix_kernel decides)
+                if (mode == 1u) {
+                    if (l == 0u) f_khi[lane] = key;
+                } else {
+                    if (l <= r && r < h) f_klo[lane] = key;
+                    if (l <= r + 1u && r + 1u < h) f_khi[lane] = key;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (g == 0 && active && f_mode[lane] != 3u) a.out[mypx] = med_finish(f_klo[lane], f_khi[lane], even);
+    for (int p = g; p < kMsPix; p += kM2Warps) {
+        const int64_t px = px0 + p;
+        if (px >= a.n2) continue; // warp-uniform
+        const unsigned mode = f_mode[p];
+        if (mode != 3u) continue;
+        unsigned *list = s_list + p * kMsRow;
+        unsigned klo = 0u, khi = 0u;
+        {
+            // the re-collected bin did not fit the list (heavy ties next to the median, or a tied bracket): refine it against
+            // the global column until it does, then the warp-wide rounds
+            unsigned m = s_cnt[p];
+            const float flo = s_lo[p], fhi = s_hi[p];
+            bool bhas_lo = s_haslo[p] != 0u;
+            // bounds as keys, consistent with the float compares: values > (+-)0 are the keys above +0.0, values < (+-)0 the keys below -0.0
+            unsigned blo = bhas_lo ? med_key(flo == 0.0f ? 0.0f : flo) : 0u;
+            unsigned bhi = s_hashi[p] != 0u ? med_key(fhi == 0.0f ? -0.0f : fhi) : kFull;
+            const unsigned eq = s_eqt[p];
+            unsigned above = s_abv[p];
+            unsigned r = s_r[p];
+            const float *pcol = a.cube + a.start * a.n2 + px;
+            bool done = false;
+            unsigned sd = (unsigned)px * 0x9E3779B9u + 0x7F4A7C15u;
+            if (bhas_lo && r < eq) { // the wanted value is lo itself
+                klo = blo;
+                khi = blo;
+                if (even && !(r + 1 < eq)) {
+                    unsigned mn = kFull;
+                    for (int k = lane; k < n; k += 32) {
+                        const unsigned key = ms_key(ms_ld(pcol + (size_t)k * a.n2));
+                        if (key > blo && key < bhi) mn = min(mn, key);
+                    }
+                    mn = __reduce_min_sync(kFull, mn);
+                    khi = mn != kFull ? mn : above;
+                }
+                done = true;
+            } else {
+                if (bhas_lo) r -= eq;
+                while (!done && m > (unsigned)kMsCap) {
+                    done = ms_refine(pcol, a.n2, n, list, blo, bhi, bhas_lo, r, m, above, even, lane, sd, klo, khi);
+                    sd = sd * 1664525u + 1013904223u;
+                }
+            }
+            if (!done) {
+                MedState st{(int)m, r, above, above != kFull};
+                while (!done && st.m > 32) {
+                    done = med_round(list, st, even, lane, sd, klo, khi);
+                    sd = sd * 1664525u + 1013904223u;
+                }
+                if (!done) med_rank32(list, st, even, lane, klo, khi);
+            }
+        }
+        if (lane == 0) a.out[px] = med_finish(klo, khi, even);
+    }
+    if (a.trace) { __syncthreads(); ms_trace(a, 4, t_tr); }
+    if (nan && n > 1) atomicMax(a.flag, 1u);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------------
 static size_t a0_state_bytes(int op, int mode) {
@@ -1630,34 +2279,70 @@ static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start,
             cudaError_t e = cudaFuncSetAttribute(median_stream_kernel<7, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream_kernel<15, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e != cudaSuccess) return e;
             attr_ms[dev_ms] = true;
         }
         const unsigned grid_ms = (unsigned)((n2 + kMsPix - 1) / kMsPix);
         static const int single_pass = getenv("AFK_MEDIAN_SINGLE_PASS") ? atoi(getenv("AFK_MEDIAN_SINGLE_PASS")) : 1; // 0: the two-pass kernel (A/B); 2: from 801 frames
+        static const int64_t one_pass_min = getenv("AFK_MEDIAN_ONEPASS_MIN") ? atoll(getenv("AFK_MEDIAN_ONEPASS_MIN")) : kMs1MinFrames;
         // Measured on the ALMA cube (profiles/r2_median_single_pass.json): the one-pass kernel ties with the two-pass kernel at
         // 3840 frames (9.15 vs 9.06 ms) with half its DRAM traffic, and loses below (2000 frames: 5.7 vs 5.4 ms; 1025: 4.2 vs
         // 3.5 ms: the 256-sample sort and the re-collects do not shrink with the window) -> used from 3000 frames up.
-        if (single_pass && (n >= kMs1MinFrames || single_pass == 2) && n > kMsCap && n <= kMs1MaxFrames) {
+        if (single_pass && (n >= one_pass_min || single_pass == 2) && n > kMsCap && n <= kMs1MaxFrames) {
             static const int trace = getenv("AFK_MEDIAN_TRACE") ? atoi(getenv("AFK_MEDIAN_TRACE")) : 0;
+            // AFK_MEDIAN_ONEPASS_V=1: the first one-pass kernel (shared atomics, 16 warps) for A/B
+            static const int version = getenv("AFK_MEDIAN_ONEPASS_V") ? atoi(getenv("AFK_MEDIAN_ONEPASS_V")) : 2;
+            // half-widths of the bracket and of the wing in quantile units: z sigma of the sample quantile near the median,
+            // sigma = 1/2 sqrt((1 - M/n) / M) with M ~ n / ceil(n / 512) samples per spaxel (AFK_MEDIAN_Z, default 3; wing 2 z + 1)
+            static const double z = getenv("AFK_MEDIAN_Z") ? atof(getenv("AFK_MEDIAN_Z")) : 3.0;
+            const int64_t mine = (n + kM2Warps - 1) / kM2Warps, ssamp = (mine + kM2Smp - 1) / kM2Smp;
+            const double msamp = (double)kM2Warps * (double)((mine + ssamp - 1) / ssamp);
+            const double sigma_q = 0.5 * std::sqrt(std::max(0.0, 1.0 - msamp / (double)n) / msamp) + 0.25 / msamp;
+            const float wq = (float)std::min(0.2, z * sigma_q), wq2 = (float)std::min(0.45, (2.0 * z + 1.0) * sigma_q);
+            const unsigned block = version == 1 ? kMsPix * kMsWarps : kMsPix * kM2Warps;
+            MedianK kt = k;
+            unsigned long long *d = nullptr, h[8] = {};
             if (trace) { // diagnostics: synchronises
-                unsigned long long *d = nullptr, h[8] = {};
                 cudaMalloc(&d, sizeof h);
                 cudaMemset(d, 0, sizeof h);
-                MedianK kt = k;
                 kt.trace = d;
-                median_stream1_kernel<<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(kt);
+            }
+            if (version == 1) median_stream1_kernel<<<grid_ms, block, smem_ms, s>>>(kt);
+            else {
+                // Thread-block clusters for DRAM locality, not for shared memory: a CTA reads 128 contiguous bytes of a frame at a
+                // time; the CTAs of a cluster start together on neighbouring SMs and walk adjacent tiles in step, so the memory
+                // system sees 128 B x cluster-size contiguous requests close in time (AFK_MEDIAN_CLUSTER = 1|2|4|8)
+                static const int cl = getenv("AFK_MEDIAN_CLUSTER") ? atoi(getenv("AFK_MEDIAN_CLUSTER")) : 2;
+                const unsigned csize = (cl == 2 || cl == 4 || cl == 8) ? (unsigned)cl : 1u;
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3((grid_ms + csize - 1) / csize * csize);
+                cfg.blockDim = dim3(block);
+                cfg.dynamicSmemBytes = smem_ms;
+                cfg.stream = s;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = csize;
+                at[0].val.clusterDim.y = 1;
+                at[0].val.clusterDim.z = 1;
+                cfg.attrs = at;
+                cfg.numAttrs = 1;
+                static const int batch = getenv("AFK_MEDIAN_U") ? atoi(getenv("AFK_MEDIAN_U")) : 16;
+                const cudaError_t le = batch == 32 ? cudaLaunchKernelEx(&cfg, median_stream2_kernel<32>, kt, wq, wq2)
+                                                   : cudaLaunchKernelEx(&cfg, median_stream2_kernel<16>, kt, wq, wq2);
+                if (le != cudaSuccess) return le;
+            }
+            if (trace) {
                 cudaStreamSynchronize(s);
                 cudaMemcpy(h, d, sizeof h, cudaMemcpyDeviceToHost);
                 cudaFree(d);
                 const double tot = (double)(h[0] + h[1] + h[2] + h[3] + h[4]);
-                fprintf(stderr, "[afk median trace] n=%lld CTAs=%u cycles/CTA: sample loads %.0f, sort %.0f, stream %.0f, miss re-collect %.0f, finish %.0f (%.1f%% %.1f%% %.1f%% %.1f%% %.1f%%)\n",
-                        (long long)n, grid_ms, h[0] / (double)grid_ms, h[1] / (double)grid_ms, h[2] / (double)grid_ms, h[3] / (double)grid_ms, h[4] / (double)grid_ms,
+                fprintf(stderr, "[afk median trace] one-pass v%d n=%lld CTAs=%u cycles/CTA: sample loads %.0f, sort %.0f, stream %.0f, miss re-collect %.0f, finish %.0f (%.1f%% %.1f%% %.1f%% %.1f%% %.1f%%)\n",
+                        version, (long long)n, grid_ms, h[0] / (double)grid_ms, h[1] / (double)grid_ms, h[2] / (double)grid_ms, h[3] / (double)grid_ms, h[4] / (double)grid_ms,
                         100 * h[0] / tot, 100 * h[1] / tot, 100 * h[2] / tot, 100 * h[3] / tot, 100 * h[4] / tot);
                 fprintf(stderr, "[afk median trace] spaxels %lld: bracket missed %llu (%.2f%%), list overflowed %llu, mean keys in the bracket %.1f\n", (long long)n2,
                         h[5], 100.0 * h[5] / (double)n2, h[7], h[6] / (double)n2);
-            } else {
-                median_stream1_kernel<<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);
             }
         }
         else if (n <= kMedStreamWideBins) median_stream_kernel<7, 4><<<grid_ms, kMsPix * kMsWarps, smem_ms, s>>>(k);

@@ -173,7 +173,6 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
     uint32_t *lut3 = nullptr;
     Error err = ok();
     float *dtone = nullptr;
-    unsigned *flag = nullptr;
     do {
         if (rgb3) {
             // three tables side by side
@@ -205,10 +204,30 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
                 err = make_error(AFK_ERR_UNEXPECTED_INPUT, "bad tone table in colormap chain");
                 break;
             }
-            cudaError_t ce = cudaMallocAsync(reinterpret_cast<void **>(&dtone), chain->tone_len * sizeof(float), s);
-            if (ce == cudaSuccess) ce = cudaMemcpyAsync(dtone, chain->tone_table, chain->tone_len * sizeof(float), cudaMemcpyHostToDevice, s);
-            if (ce != cudaSuccess) { err = cuda_error(ce, "tone table upload"); break; }
-            if ((err = scratch_u32(s, 8, &flag))) break; // [0] tone index flag, [4..6] image_min_max left on the device
+            // The table is a GUI value that changes when the user drags a control point, not per frame: keep the last one
+            // uploaded on this stream and compare (1 KiB memcmp) instead of an allocation + upload + free per call.
+            StreamScratch &sc = tls().scratch[std::make_pair(dev, s)];
+            const bool same = sc.tone_dev && sc.tone_host.size() == chain->tone_len &&
+                              memcmp(sc.tone_host.data(), chain->tone_table, chain->tone_len * sizeof(float)) == 0;
+            if (!same) {
+                cudaError_t ce = cudaSuccess;
+                sc.tone_host.clear(); // not valid until the copy below has been enqueued
+                if (sc.tone_cap < chain->tone_len) {
+                    if (sc.tone_dev) cudaFreeAsync(sc.tone_dev, s);
+                    sc.tone_dev = nullptr;
+                    sc.tone_cap = 0;
+                    const size_t cap = chain->tone_len < 1024 ? 1024 : chain->tone_len;
+                    ce = cudaMallocAsync(reinterpret_cast<void **>(&sc.tone_dev), cap * sizeof(float), s);
+                    if (ce == cudaSuccess) sc.tone_cap = cap;
+                    else sc.tone_dev = nullptr;
+                }
+                // pageable source: the call returns once the entries are staged, and kernels enqueued earlier on `s` that
+                // read the previous table finish before the copy runs (stream order)
+                if (ce == cudaSuccess) ce = cudaMemcpyAsync(sc.tone_dev, chain->tone_table, chain->tone_len * sizeof(float), cudaMemcpyHostToDevice, s);
+                if (ce != cudaSuccess) { err = cuda_error(ce, "tone table upload"); break; }
+                sc.tone_host.assign(chain->tone_table, chain->tone_table + chain->tone_len);
+            }
+            dtone = sc.tone_dev;
             a.chain = 1;
             if (chain->logscale_vmin != chain->logscale_vmin && chain->logscale_vmax != chain->logscale_vmax) {
                 // NaN, NaN: the chain starts at image_min_max (src/templates.rs: min/max feed convert_to_logscale).  Its result stays
@@ -217,9 +236,14 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
                 if (img->range_valid && img->range) {
                     a.ls_minmax = img->range; // range memo left by the kernel that wrote the pixels
                 } else {
-                    ce = minmax_launch(img->ptr, img->len(), flag + 4, sm_count(dev), s);
+                    if (!sc.minmax_words) {
+                        cudaError_t ce = cudaMallocAsync(reinterpret_cast<void **>(&sc.minmax_words), 4 * sizeof(unsigned), s);
+                        if (ce != cudaSuccess) { sc.minmax_words = nullptr; err = cuda_error(ce, "cudaMallocAsync(min/max words)"); break; }
+                    }
+                    cudaError_t ce = cudaMemsetAsync(sc.minmax_words, 0, 4 * sizeof(unsigned), s);
+                    if (ce == cudaSuccess) ce = minmax_launch(img->ptr, img->len(), sc.minmax_words, sm_count(dev), s);
                     if (ce != cudaSuccess) { err = cuda_error(ce, "minmax_kernel launch"); break; }
-                    a.ls_minmax = flag + 4;
+                    a.ls_minmax = sc.minmax_words;
                 }
             }
             a.ls_a = chain->logscale_a; a.ls_min = chain->logscale_vmin; a.ls_max = chain->logscale_vmax;
@@ -238,8 +262,6 @@ static Error colormap_run(const afk_image *img, const afk_lut *const *luts, int 
         image_note_read(img, s);
     } while (0);
     if (lut3) cudaFreeAsync(lut3, s);
-    if (dtone) cudaFreeAsync(dtone, s);
-    if (flag) scratch_free(s, flag);
     return err;
 }
 

@@ -36,6 +36,12 @@ afk_status fail(const Error &e); // records the message for afk_last_error(), re
 // ---- per-thread execution context -----------------------------------------------------------------
 struct StreamScratch {
     ReduceWorkspace ws{nullptr, 0, nullptr, 0};
+    // display chain: the last tone table uploaded on this stream (re-used while the host passes the same entries) and the
+    // three words image_min_max leaves on the device for the chain kernel.  Stream ordered, owned by the calling thread.
+    float *tone_dev = nullptr;
+    size_t tone_cap = 0;
+    std::vector<float> tone_host;
+    unsigned *minmax_words = nullptr;
 };
 
 struct ThreadCtx {

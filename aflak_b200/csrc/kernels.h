@@ -163,7 +163,9 @@ Axis0Plan axis0_plan(const Axis0Args &a, int sm_count);
 // partials: >= plan.partial_bytes of device scratch (may be nullptr when 0); flag: one zero-initialised word that is
 // set where the reference would panic (A0_CENTROID_MASK ranges outside the cube)
 cudaError_t axis0_launch(const Axis0Args &a, const Axis0Plan &plan, void *partials, unsigned *flag, cudaStream_t s);
-// run_median (lib.rs:1340-1372); *flag is set when a NaN is met (the reference panics)
+// run_median (lib.rs:1340-1372); flag: kMedianScratchWords zero-initialised words; flag[0] is set when a NaN is met (the
+// reference panics), the rest is per-SM arrival counters of the one-pass kernel's staggered first wave
+constexpr size_t kMedianScratchWords = 1 + 256;
 cudaError_t median_launch(const float *cube, int64_t n2, int64_t start, int64_t end, float *out, unsigned *flag, cudaStream_t s);
 
 // ---- FITS data unit -> f32 (ingest.cu) ----------------------------------------------------------

@@ -903,7 +903,7 @@ static Error op_axis0(const afk_image *cube, Axis0Args a, const afk_image *m_lo,
         if (m_hi && (err = image_wait(m_hi, s))) break;
         cudaError_t ce = cudaSuccess;
         if (a.op == A0_MEDIAN_OP) {
-            if ((err = scratch_u32(s, 1, &flag))) break;
+            if ((err = scratch_u32(s, kMedianScratchWords, &flag))) break;
             ce = median_launch(a.cube, a.n2, a.start, a.end, a.out, flag, s);
         } else {
             Axis0Plan plan = a.op == A0_CENTROID_MASK ? Axis0Plan{1, 256, 0, 1, 0, 0} : axis0_plan(a, sm_count(dev));

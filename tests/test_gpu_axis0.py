@@ -218,6 +218,57 @@ def test_median_stream_paths(gpu, orc):
     assert isinstance(e, gpu.AflakError) and e.status == gpu.ERR_PANIC
 
 
+def _median_one_pass_patterns(rng, nz, ny, nx):
+    """The patterns above plus the ones that stress a bracket taken from 256 samples: constant spectra (every sample equal:
+    the bracket collapses onto the `== lo` class), blank spaxels (all zeros, both signs), two-valued spectra (lo and hi a
+    gap apart), a median sitting on +inf, and a spectrum whose upper half is one repeated value (no sample above lo)."""
+    out = _median_patterns(rng, nz, ny, nx)
+    shape = (nz, ny, nx)
+    h = (1.0 + 0.1 * rng.standard_normal(shape)).astype(np.float32)
+    h[:, : ny // 3, :] = np.float32(2.5)            # constant spaxels
+    h[:, ny // 3 : ny // 2, :] = 0.0                # blank spaxels ...
+    h[::2, ny // 3 : ny // 2, ::2] = -0.0           # ... with zeros of both signs
+    out.append(("constant and blank spaxels", h))
+    h = np.where(rng.random(shape) < 0.5, np.float32(1.0), np.float32(7.0)).astype(np.float32)
+    out.append(("two values", h))
+    h = (1.0 + 0.1 * rng.standard_normal(shape)).astype(np.float32)
+    h[rng.random(shape) < 0.55] = np.inf
+    out.append(("median on +inf", h))
+    h = rng.uniform(0.0, 1.0, shape).astype(np.float32)
+    h[rng.random(shape) < 0.52] = np.float32(1.0)
+    out.append(("upper half tied", h))
+    return out
+
+
+def test_median_one_pass_paths(gpu, orc):
+    """One-pass streaming select (median_stream2_kernel: 3000..4400 frames on images of >= 9472 spaxels): bracket from 256
+    samples, private list segments, wing / open-bin re-collects, refinement of an overflowing list.  Even and odd windows."""
+    rng = np.random.default_rng(0xAF1A0043)
+    ny, nx = 97, 99
+    for nz in (3001, 4400):
+        for tag, host in _median_one_pass_patterns(rng, nz, ny, nx):
+            cube = gpu.Image.upload(host)
+            for start, end in [(0, nz), (1, nz)] if nz < 4400 else [(0, nz)]:
+                assert_bit_equal(gpu.call("median", cube, start, end).download(), orc.median(host, start, end), f"one-pass {tag} {nz}[{start},{end})")
+            del cube
+    host = (1.0 + 0.1 * rng.standard_normal((3200, ny, nx))).astype(np.float32)
+    host[1234, 50, 60] = np.nan
+    e = gpu.get_transform("median").call_results(gpu.Image.upload(host), 0, 3200)[0]
+    assert isinstance(e, gpu.AflakError) and e.status == gpu.ERR_PANIC
+
+
+def test_median_one_pass_short_windows_subprocess():
+    """The same kernel forced onto windows from 801 frames (AFK_MEDIAN_SINGLE_PASS=2; the switch is read once per process)."""
+    import os
+    import subprocess
+    import sys
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, AFK_MEDIAN_SINGLE_PASS="2")
+    r = subprocess.run([sys.executable, os.path.join(here, "median_onepass_worker.py")], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 @pytest.mark.parametrize("shape", SHAPES)
 @pytest.mark.parametrize("is_min", [False, True])
 @pytest.mark.parametrize("pathology", [False, True])
