@@ -1516,7 +1516,7 @@ __device__ __forceinline__ float m2_run_quantile(const float *run, int ms, float
     return v;
 }
 
-template <int kM2U> // loads per batch, two batches in flight
+template <int SS> // sample stride: a thread's frames t = 0, SS, 2 SS, ... are its samples; compile-time so that a batch is whole blocks of SS - 1 frames
 __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(const MedianK a, float wq, float wq2) {
     extern __shared__ unsigned s_list[]; // [kMsPix][kMsRow]: 8 private segments of 100 slots per spaxel; phase S aliases the sorted runs onto it
     __shared__ float s_q[4][kM2Warps][kMsPix]; // per-run quantiles: lo, hi, wing lo, wing hi
@@ -1536,20 +1536,31 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
     const float kInf = __int_as_float(0x7f800000);
     if (px0 >= a.n2) return; // the grid is padded to whole clusters
     long long t_tr = a.trace ? clock64() : 0;
-    // this thread's frames: t = 0 .. mine-1 is frame g + 8 t; samples t = j ss (j < ms <= 64); columns c = 1 .. ss-1 hold the rest
+    // this thread's frames: t = 0 .. mine-1 is frame g + 8 t, in blocks of SS: the first frame of block j (t = j SS) is a sample
+    // (j < ms <= 64: the host picks SS), its other SS - 1 frames are streamed
     const int mine = (n - g + kM2Warps - 1) / kM2Warps;
-    const int ss = (mine + kM2Smp - 1) / kM2Smp;
-    const int ms = (mine + ss - 1) / ss;
+    const int ms = (mine + SS - 1) / SS;
     const size_t tstep = (size_t)kM2Warps * a.n2;   // elements between two of this thread's frames
-    const size_t jstep = tstep * (size_t)ss;        // ... between two entries of a column
     const float *const tcol = col + (size_t)g * a.n2;
     float nan_acc = 0.0f;
     // ---- S: samples -> sorted run -> quantiles -> bracket ----
     float smp[kM2Smp];
+    {
+        const float *sp = tcol;
 #pragma unroll
-    for (int j = 0; j < kM2Smp; ++j) {
-        smp[j] = kInf; // pads sort behind the samples: the first ms sorted values are the samples
-        if (j < ms) smp[j] = __uint_as_float(ms_ld(tcol + (size_t)j * jstep));
+        for (int j0 = 0; j0 < kM2Smp; j0 += 16) {
+            if (j0 + 16 <= ms) {
+#pragma unroll
+                for (int j = j0; j < j0 + 16; ++j) { smp[j] = __uint_as_float(ms_ld(sp)); sp += (size_t)SS * tstep; }
+            } else {
+#pragma unroll
+                for (int j = j0; j < j0 + 16; ++j) {
+                    smp[j] = kInf; // pads sort behind the samples: the first ms sorted values are the samples
+                    if (j < ms) smp[j] = __uint_as_float(ms_ld(sp));
+                    sp += (size_t)SS * tstep;
+                }
+            }
+        }
     }
 #pragma unroll
     for (int j = 0; j < kM2Smp; ++j) nan_acc = m2_min_nan(nan_acc, smp[j]);
@@ -1630,53 +1641,75 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
             : "memory");
     };
 #pragma unroll
-    for (int j = 0; j < kM2Smp; ++j)
-        if (j < ms) classify_checked(__float_as_uint(smp[j]));
+    for (int j0 = 0; j0 < kM2Smp; j0 += 16) { // the sorted samples, from their registers
+        if (j0 + 16 <= ms && wp + 4u * 16u <= wend) {
+#pragma unroll
+            for (int j = j0; j < j0 + 16; ++j) classify(__float_as_uint(smp[j]));
+        } else {
+#pragma unroll
+            for (int j = j0; j < j0 + 16; ++j)
+                if (j < ms) classify_checked(__float_as_uint(smp[j]));
+        }
+    }
+    // the segment starts with this thread's samples of the bracket, in ascending order (they were classified sorted): the first
+    // round of the finish picks its pivots there
+    const unsigned ks = min((wp - seg0) >> 2, (unsigned)kM2Seg);
     {
-        // batches never straddle a column; a column's last batch is short (warp-uniform guards)
-        int c = 1, j = 0;
-        int ccnt = c < ss ? (mine - c + ss - 1) / ss : 0;
-        const float *cptr = tcol + tstep; // column c, entry 0
-        auto load = [&](unsigned (&raw)[kM2U], int &nv) {
-            nv = ccnt - j < kM2U ? ccnt - j : kM2U;
-            const float *p = cptr + (size_t)j * jstep;
-            if (nv == kM2U) {
+        // the other frames: a batch is kNB whole blocks (kBatch = kNB (SS - 1) ~ 16 loads, every address one 64-bit add from the
+        // last), two batches in ping-pong; the last blocks, which may be cut by the end of the window, are one guarded batch
+        constexpr int kMem = SS - 1;
+        constexpr int kNB = (16 + kMem / 2) / kMem;
+        constexpr int kBatch = kNB * kMem;
+        const int nfb = mine / SS;     // blocks with all their frames inside the window
+        int left = nfb / kNB;          // full batches
+        const float *p = tcol + tstep; // block 0, frame 1
+        auto load = [&](unsigned (&raw)[kBatch]) {
 #pragma unroll
-                for (int u = 0; u < kM2U; ++u) raw[u] = ms_ld(p + (size_t)u * jstep);
-            } else {
+            for (int b = 0; b < kNB; ++b) {
 #pragma unroll
-                for (int u = 0; u < kM2U; ++u)
-                    if (u < nv) raw[u] = ms_ld(p + (size_t)u * jstep);
-            }
-            j += kM2U;
-            if (j >= ccnt) {
-                ++c;
-                j = 0;
-                cptr += tstep;
-                ccnt = c < ss ? (mine - c + ss - 1) / ss : 0;
+                for (int c = 0; c < kMem; ++c) {
+                    raw[b * kMem + c] = ms_ld(p);
+                    p += c == kMem - 1 ? 2 * tstep : tstep; // over the next block's sample
+                }
             }
         };
-        auto process = [&](const unsigned (&raw)[kM2U], int nv) {
-            if (nv == kM2U && wp + 4u * kM2U <= wend) {
+        auto process = [&](const unsigned (&raw)[kBatch]) {
+            if (wp + 4u * kBatch <= wend) {
 #pragma unroll
-                for (int u = 0; u < kM2U; ++u) classify(raw[u]);
+                for (int u = 0; u < kBatch; ++u) classify(raw[u]);
             } else {
 #pragma unroll
-                for (int u = 0; u < kM2U; ++u)
-                    if (u < nv) classify_checked(raw[u]);
+                for (int u = 0; u < kBatch; ++u) classify_checked(raw[u]);
             }
         };
-        unsigned ra[kM2U], rb[kM2U];
-        int na = 0, nb = 0;
-        if (ccnt > 0) load(ra, na);
-        while (na > 0) {
-            nb = 0;
-            if (ccnt > 0) load(rb, nb);
-            process(ra, na);
-            na = 0;
-            if (nb == 0) break;
-            if (ccnt > 0) load(ra, na);
-            process(rb, nb);
+        const int t_tail = (left * kNB) * SS; // first frame of the first block that is not part of a full batch
+        unsigned ra[kBatch], rb[kBatch];
+        if (left > 0) load(ra);
+        while (left > 0) {
+            if (left > 1) load(rb);
+            process(ra);
+            if (--left == 0) break;
+            if (left > 1) load(ra);
+            process(rb);
+            --left;
+        }
+        // tail: at most kNB blocks (the last one possibly short), all loads in flight at once
+        unsigned rt[kBatch + kMem];
+        const float *q = tcol + (size_t)t_tail * tstep;
+#pragma unroll
+        for (int b = 0; b < kNB + 1; ++b) {
+#pragma unroll
+            for (int c = 0; c < kMem; ++c) {
+                const int t = t_tail + b * SS + 1 + c;
+                rt[b * kMem + c] = 0u;
+                if (t < mine) rt[b * kMem + c] = ms_ld(q + (size_t)(b * SS + 1 + c) * tstep);
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < kNB + 1; ++b) {
+#pragma unroll
+            for (int c = 0; c < kMem; ++c)
+                if (t_tail + b * SS + 1 + c < mine) classify_checked(rt[b * kMem + c]);
         }
     }
     const bool nan = nan_acc != nan_acc;
@@ -1741,7 +1774,8 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
             if (active && !miss) atomicAdd(a.trace + 6, (unsigned long long)mt);
         }
     }
-    __syncthreads();
+    // most CTAs have nothing to re-collect: one barrier that also carries the vote
+    const bool any_miss = __syncthreads_or(g == 0 && s_miss[lane] != 0u) != 0;
     // ---- D1: the whole CTA re-collects the bin of a spaxel whose bracket missed (every frame of the column in flight) ----
     auto recollect = [&]() {
         for (int p = 0; p < kMsPix; ++p) {
@@ -1784,37 +1818,39 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
             }
         }
     };
-    recollect();
-    __syncthreads();
-    // the wing is counted: rank inside it, or (6 sigma) the open bin beyond it
-    if (g == 0) {
-        const unsigned miss = s_miss[lane];
-        unsigned again = 0u;
-        if (miss == 1u) {
-            const unsigned below2 = s_belt[lane] - s_eqt[lane] - s_cnt[lane]; // values < lo2
-            if (r0 >= below2) {
-                s_r[lane] = r0 - below2;
-            } else {
-                s_hi[lane] = s_lo[lane];
-                s_haslo[lane] = 0u;
-                s_r[lane] = r0;
-                again = 4u;
+    if (any_miss) {
+        recollect();
+        __syncthreads();
+        // the wing is counted: rank inside it, or (6 sigma) the open bin beyond it
+        if (g == 0) {
+            const unsigned miss = s_miss[lane];
+            unsigned again = 0u;
+            if (miss == 1u) {
+                const unsigned below2 = s_belt[lane] - s_eqt[lane] - s_cnt[lane]; // values < lo2
+                if (r0 >= below2) {
+                    s_r[lane] = r0 - below2;
+                } else {
+                    s_hi[lane] = s_lo[lane];
+                    s_haslo[lane] = 0u;
+                    s_r[lane] = r0;
+                    again = 4u;
+                }
+            } else if (miss == 2u) {
+                const unsigned inside = s_eqt[lane] + s_cnt[lane]; // values in [hi, hi2)
+                if (s_r[lane] >= inside) {
+                    s_r[lane] -= inside;
+                    s_lo[lane] = s_hi[lane];
+                    s_hashi[lane] = 0u;
+                    again = 5u;
+                }
             }
-        } else if (miss == 2u) {
-            const unsigned inside = s_eqt[lane] + s_cnt[lane]; // values in [hi, hi2)
-            if (s_r[lane] >= inside) {
-                s_r[lane] -= inside;
-                s_lo[lane] = s_hi[lane];
-                s_hashi[lane] = 0u;
-                again = 5u;
-            }
+            if (again) { s_cnt[lane] = 0u; s_eqt[lane] = 0u; s_abv[lane] = kFull; }
+            s_miss[lane] = again;
         }
-        if (again) { s_cnt[lane] = 0u; s_eqt[lane] = 0u; s_abv[lane] = kFull; }
-        s_miss[lane] = again;
+        __syncthreads();
+        recollect();
+        __syncthreads();
     }
-    __syncthreads();
-    recollect();
-    __syncthreads();
     ms_trace(a, 3, t_tr);
     // ---- F: the finish.  The candidates S of a spaxel (values strictly inside its bin) stay where they are, spread over the 8
     //      private segments, and all 256 threads work on all 32 spaxels at once in the (warp g, lane = spaxel) layout of the
@@ -1876,28 +1912,61 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
         const bool big = mode < 2u && s_cnt[lane] > 32u;
         if (!__syncthreads_or(big ? 1 : 0)) break;
         unsigned *const cnt_now = f_c + (round & 1) * kMsPix * 8 + lane * 8;
-        // R1: pivot offers
+        // R1: pivot offers.  Round 0: 4 pivots (the even warps offer), each the sample of the thread's sorted prefix at the
+        // wanted rank's quantile -- 4 estimates of the wanted value, close together, so the bin between two of them is small
+        // (~70 of ~500 candidates) at half the compares of 8 pivots.  Later rounds: 8 pivots, one random candidate per thread.
+        const int np = round == 0 ? 4 : 8;
         seed = seed * 1664525u + 1013904223u;
-        f_pv[g * kMsPix + lane] = (big && c_own > 0u) ? seg[(seed >> 8) % c_own] : __int_as_float(0x7fc00000);
+        {
+            float offer = __int_as_float(0x7fc00000);
+            if (big && c_own > 0u) {
+                unsigned idx = (seed >> 8) % c_own;
+                if (round == 0 && ks > 0u && !s_packed[lane]) {
+                    const float phi = __fdividef((float)(mode == 1u ? 0u : s_r[lane]) + 0.5f, (float)s_cnt[lane]);
+                    idx = min(min(ks, c_own) - 1u, (unsigned)(phi * (float)ks));
+                }
+                offer = seg[idx];
+            }
+            f_pv[g * kMsPix + lane] = offer;
+        }
         __syncthreads();
         // R2: counts of this segment against the spaxel's sorted pivots (a compare on the ALU pipe + a predicated FADD each)
         float pv[8];
         if (big) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                pv[j] = f_pv[j * kMsPix + lane];
-                if (pv[j] != pv[j]) pv[j] = kInf; // no offer: sorts last, counts every finite candidate
-            }
-            m2_sort_regs<8>(pv);
             float cj[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) cj[j] = 0.0f;
-#pragma unroll 4
-            for (unsigned i = 0; i < c_own; ++i) {
-                const float x = seg[i];
+            for (int j = 0; j < 8; ++j) { cj[j] = 0.0f; pv[j] = kInf; }
+            if (round == 0) {
+                float p4[4];
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.f32 %0, %0, 0f3F800000;\n\t}" : "+f"(cj[j]) : "f"(x), "f"(pv[j]));
+                for (int j = 0; j < 4; ++j) {
+                    p4[j] = f_pv[2 * j * kMsPix + lane];
+                    if (p4[j] != p4[j]) p4[j] = kInf; // no offer: sorts last, counts every finite candidate
+                }
+                m2_sort_regs<4>(p4);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) pv[j] = p4[j];
+#pragma unroll 4
+                for (unsigned i = 0; i < c_own; ++i) {
+                    const float x = seg[i];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.f32 %0, %0, 0f3F800000;\n\t}" : "+f"(cj[j]) : "f"(x), "f"(pv[j]));
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    pv[j] = f_pv[j * kMsPix + lane];
+                    if (pv[j] != pv[j]) pv[j] = kInf;
+                }
+                m2_sort_regs<8>(pv);
+#pragma unroll 4
+                for (unsigned i = 0; i < c_own; ++i) {
+                    const float x = seg[i];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        asm("{\n\t.reg .pred p;\n\tsetp.lt.f32 p, %1, %2;\n\t@p add.f32 %0, %0, 0f3F800000;\n\t}" : "+f"(cj[j]) : "f"(x), "f"(pv[j]));
+                }
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j)
@@ -1915,10 +1984,10 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
             for (int j = 0; j < 8; ++j) C[j] = cnt_now[j];
 #pragma unroll
             for (int j = 0; j < 8; ++j)
-                if (C[j] <= r) { below_b = C[j]; lo_b = pv[j]; }
+                if (j < np && C[j] <= r) { below_b = C[j]; lo_b = pv[j]; }
 #pragma unroll
             for (int j = 7; j >= 0; --j)
-                if (C[j] > r) hi_b = pv[j];
+                if (j < np && C[j] > r) hi_b = pv[j];
             float eq_f = 0.0f, ge_f = 0.0f, hmin = kInf;
             const unsigned w0 = (unsigned)__cvta_generic_to_shared(seg);
             unsigned wq_ = w0;
@@ -2279,17 +2348,18 @@ static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start,
             cudaError_t e = cudaFuncSetAttribute(median_stream_kernel<7, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream_kernel<15, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms);
+#define AFK_M2_ATTR(SS_) if (e == cudaSuccess) e = cudaFuncSetAttribute(median_stream2_kernel<SS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ms)
+            AFK_M2_ATTR(2); AFK_M2_ATTR(3); AFK_M2_ATTR(4); AFK_M2_ATTR(5); AFK_M2_ATTR(6); AFK_M2_ATTR(7); AFK_M2_ATTR(8); AFK_M2_ATTR(9);
+#undef AFK_M2_ATTR
             if (e != cudaSuccess) return e;
             attr_ms[dev_ms] = true;
         }
         const unsigned grid_ms = (unsigned)((n2 + kMsPix - 1) / kMsPix);
         static const int single_pass = getenv("AFK_MEDIAN_SINGLE_PASS") ? atoi(getenv("AFK_MEDIAN_SINGLE_PASS")) : 1; // 0: the two-pass kernel (A/B); 2: from 801 frames
-        static const int64_t one_pass_min = getenv("AFK_MEDIAN_ONEPASS_MIN") ? atoll(getenv("AFK_MEDIAN_ONEPASS_MIN")) : kMs1MinFrames;
-        // Measured on the ALMA cube (profiles/r2_median_single_pass.json): the one-pass kernel ties with the two-pass kernel at
-        // 3840 frames (9.15 vs 9.06 ms) with half its DRAM traffic, and loses below (2000 frames: 5.7 vs 5.4 ms; 1025: 4.2 vs
-        // 3.5 ms: the 256-sample sort and the re-collects do not shrink with the window) -> used from 3000 frames up.
+        static const int64_t one_pass_min = getenv("AFK_MEDIAN_ONEPASS_MIN") ? atoll(getenv("AFK_MEDIAN_ONEPASS_MIN")) : kMsCap + 1;
+        // Measured on the ALMA cube (profiles/r2_median_one_pass_v2.json): the rebuilt one-pass kernel beats the two-pass kernel on
+        // every window its 800-slot rows allow (1025 frames: 3.05 vs 3.48 ms, 2000: 3.81 vs 5.39, 3840: 6.0 vs 9.1) -> used from
+        // 801 frames up (AFK_MEDIAN_ONEPASS_MIN moves the switch, AFK_MEDIAN_SINGLE_PASS=0 selects the two-pass kernel).
         if (single_pass && (n >= one_pass_min || single_pass == 2) && n > kMsCap && n <= kMs1MaxFrames) {
             static const int trace = getenv("AFK_MEDIAN_TRACE") ? atoi(getenv("AFK_MEDIAN_TRACE")) : 0;
             // AFK_MEDIAN_ONEPASS_V=1: the first one-pass kernel (shared atomics, 16 warps) for A/B
@@ -2328,9 +2398,12 @@ static cudaError_t median_dispatch(const float *cube, int64_t n2, int64_t start,
                 at[0].val.clusterDim.z = 1;
                 cfg.attrs = at;
                 cfg.numAttrs = 1;
-                static const int batch = getenv("AFK_MEDIAN_U") ? atoi(getenv("AFK_MEDIAN_U")) : 16;
-                const cudaError_t le = batch == 32 ? cudaLaunchKernelEx(&cfg, median_stream2_kernel<32>, kt, wq, wq2)
-                                                   : cudaLaunchKernelEx(&cfg, median_stream2_kernel<16>, kt, wq, wq2);
+                cudaError_t le = cudaErrorInvalidValue;
+                switch ((int)ssamp) { // the sample stride is a template parameter: whole blocks of SS - 1 streamed frames per batch
+#define AFK_M2_GO(SS_) case SS_: le = cudaLaunchKernelEx(&cfg, median_stream2_kernel<SS_>, kt, wq, wq2); break
+                    AFK_M2_GO(2); AFK_M2_GO(3); AFK_M2_GO(4); AFK_M2_GO(5); AFK_M2_GO(6); AFK_M2_GO(7); AFK_M2_GO(8); AFK_M2_GO(9);
+#undef AFK_M2_GO
+                }
                 if (le != cudaSuccess) return le;
             }
             if (trace) {

@@ -18,7 +18,7 @@ gpu.set_device(0)
 rng = np.random.default_rng(0xAF1A0044)
 ny, nx = 97, 99
 bad = 0
-for nz in (801, 1300, 2100):
+for nz in (801, 1300, 1700, 2100):
     for tag, host in _median_one_pass_patterns(rng, nz, ny, nx):
         cube = gpu.Image.upload(host)
         for start, end in [(0, nz), (0, nz - 1)] if nz > 801 else [(0, nz)]:
