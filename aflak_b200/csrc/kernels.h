@@ -268,6 +268,21 @@ struct StatState {    // device-resident state of one radix select; zero-initial
 };
 cudaError_t stat_select_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, unsigned *hist,
                                unsigned *cand, unsigned cand_cap, int sm_count, cudaStream_t s);
+struct StatBracket {  // device-resident state of the one-pass (sample-bracketed) select; zero-initialised
+    unsigned lo, hi;      // inclusive key bracket from the sample
+    int shift;            // bin = (key - lo) >> shift, < 2048
+    unsigned above_min;   // smallest kept key above hi; initialise to 0xFFFFFFFF
+    unsigned next_min;    // smallest candidate in a bin above the chosen one; initialise to 0xFFFFFFFF
+    unsigned cand_count, bin_cand_count, bin;
+    unsigned ticket, ticket2;
+    int even, error, fallback;
+    unsigned pad;
+    unsigned long long n, below, in_count, rank_in_bin, bin_count;
+};
+constexpr unsigned kStatBracketBins = 2048, kStatBracketBinBuf = 8192;
+constexpr int64_t kStatBracketMinPixels = (int64_t)1 << 20; // below, the three radix passes are as fast (launch-bound)
+cudaError_t stat_bracket_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, StatBracket *br,
+                                unsigned *hist, unsigned *cand, unsigned cand_cap, unsigned *binbuf, int sm_count, cudaStream_t s);
 cudaError_t zsample_launch(const float *img, int64_t ny, int64_t nx, int64_t stride, int64_t rows_s, int64_t cols_s, float *out,
                            cudaStream_t s);
 

@@ -5,8 +5,11 @@
 // line fit works on <= ~1000 samples and stays on the host, restated step by step in f32.
 #include <algorithm>
 #include <cmath>
+#include <cstddef>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <vector>
 
 #include "host.h"
 
@@ -51,30 +54,75 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
     cudaStream_t s;
     int dev;
     if (Error e = stats_ctx(img, &s, &dev)) return e;
-    // two select states + one histogram (initialised from the host) + the candidate buffer the two selections share
-    const size_t head = 2 * sizeof(StatState) + 256 * sizeof(unsigned);
+    // device block: the states of both selections (one-pass bracket select and radix select), their histograms, the small
+    // buffers of the bracket finish, then the candidate buffer the selections share (they run one after the other)
+    struct Head {
+        StatState sel[2];     // results of the one-pass select (vmed, vmad)
+        StatState radix[2];   // radix select: the path for small images and the fallback
+        StatBracket br[2];
+        unsigned hist_radix[256];
+        unsigned hist_br[2][kStatBracketBins];
+        unsigned binbuf[2][kStatBracketBinBuf];
+    };
+    const size_t head = (offsetof(Head, binbuf) + 15) / 16 * 16; // initialised from the host up to here
     const int64_t n = img->len();
-    const unsigned cand_cap = (unsigned)(n < (int64_t(1) << 22) ? n : (int64_t(1) << 22)); // 4 Mi keys: 25 % of a 4096^2 image in one 16-bit bucket
+    const unsigned cand_cap = (unsigned)(n < (int64_t(1) << 22) ? n : (int64_t(1) << 22)); // 4 Mi keys: 25 % of a 4096^2 image
     char *d = nullptr;
-    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), head + (size_t)cand_cap * sizeof(unsigned), s));
-    StatState *st = reinterpret_cast<StatState *>(d);
-    unsigned *hist = reinterpret_cast<unsigned *>(d + 2 * sizeof(StatState));
-    unsigned *cand = reinterpret_cast<unsigned *>(d + head);
-    struct { StatState st[2]; unsigned hist[256]; } init;
-    memset(&init, 0, sizeof init);
-    init.st[0].above_min = init.st[1].above_min = 0xFFFFFFFFu;
-    static_assert(sizeof init == 2 * sizeof(StatState) + 256 * sizeof(unsigned), "layout");
-    cudaError_t ce = cudaMemcpyAsync(d, &init, sizeof init, cudaMemcpyHostToDevice, s); // pageable source: staged before the call returns
+    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), sizeof(Head) + (size_t)cand_cap * sizeof(unsigned), s));
+    Head *hd = reinterpret_cast<Head *>(d);
+    unsigned *cand = reinterpret_cast<unsigned *>(d + sizeof(Head));
+    static const std::vector<char> init_block = [head] {
+        std::vector<char> b(head, 0);
+        Head *h0 = reinterpret_cast<Head *>(b.data()); // only the fields below `binbuf` are touched
+        for (int i = 0; i < 2; ++i) {
+            h0->sel[i].above_min = h0->radix[i].above_min = 0xFFFFFFFFu;
+            h0->br[i].above_min = h0->br[i].next_min = 0xFFFFFFFFu;
+        }
+        return b;
+    }();
+    cudaError_t ce = cudaMemcpyAsync(d, init_block.data(), head, cudaMemcpyHostToDevice, s); // pageable source: staged before the call returns
     StatParams p{vmin, vmax, 0, 0};
     // the median of the normalised values is the normalised median pixel when normalisation is monotone and drops nothing but NaN
-    p.raw = std::isfinite(vmin) && std::isfinite(vmax) && std::isfinite(vmax - vmin) && vmax > vmin;
-    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, n, p, nullptr, &st[0], hist, cand, cand_cap, sm_count(dev), s);
-    p.use_vmed = 1;
-    p.raw = 0;
-    if (ce == cudaSuccess) ce = stat_select_launch(img->ptr, n, p, &st[0], &st[1], hist, cand, cand_cap, sm_count(dev), s);
+    const int raw = std::isfinite(vmin) && std::isfinite(vmax) && std::isfinite(vmax - vmin) && vmax > vmin;
+    const int sms = sm_count(dev);
+    static const int one_pass_env = getenv("AFK_STATS_ONE_PASS") ? atoi(getenv("AFK_STATS_ONE_PASS")) : 1; // 0: radix select only (A/B)
+    const bool one_pass = one_pass_env != 0 && n >= kStatBracketMinPixels;
     StatState h[2];
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, st, sizeof h, cudaMemcpyDeviceToHost, s);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    StatBracket hb[2];
+    memset(hb, 0, sizeof hb);
+    auto radix = [&](int which, const StatState *prev) { // which: 0 vmed, 1 vmad
+        StatParams q = p;
+        q.use_vmed = which;
+        q.raw = which == 0 ? raw : 0;
+        return stat_select_launch(img->ptr, n, q, prev, &hd->radix[which], hd->hist_radix, cand, cand_cap, sms, s);
+    };
+    if (one_pass) {
+        StatParams q = p;
+        q.raw = raw;
+        if (ce == cudaSuccess) ce = stat_bracket_launch(img->ptr, n, q, nullptr, &hd->sel[0], &hd->br[0], hd->hist_br[0], cand, cand_cap, hd->binbuf[0], sms, s);
+        q.use_vmed = 1;
+        q.raw = 0;
+        if (ce == cudaSuccess) ce = stat_bracket_launch(img->ptr, n, q, &hd->sel[0], &hd->sel[1], &hd->br[1], hd->hist_br[1], cand, cand_cap, hd->binbuf[1], sms, s);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, hd->sel, sizeof h, cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(hb, hd->br, sizeof hb, cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        // a bracket that missed the wanted rank (about one image in 16000) or could not hold its keys (heavy ties): the radix select
+        if (ce == cudaSuccess && hb[0].fallback) {
+            ce = radix(0, nullptr);
+            if (ce == cudaSuccess) ce = radix(1, &hd->radix[0]);
+            if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, hd->radix, sizeof h, cudaMemcpyDeviceToHost, s);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        } else if (ce == cudaSuccess && !h[0].error && hb[1].fallback) {
+            ce = radix(1, &hd->sel[0]);
+            if (ce == cudaSuccess) ce = cudaMemcpyAsync(&h[1], &hd->radix[1], sizeof h[1], cudaMemcpyDeviceToHost, s);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        }
+    } else {
+        if (ce == cudaSuccess) ce = radix(0, nullptr);
+        if (ce == cudaSuccess) ce = radix(1, &hd->radix[0]);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, hd->radix, sizeof h, cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    }
     cudaFreeAsync(d, s);
     if (ce != cudaSuccess) return cuda_error(ce, "stat_select");
     image_note_read(img, s);

@@ -9,6 +9,8 @@
 // passes; every pass is a streaming read with shared-memory privatised histograms.
 #include "kernels.h"
 
+#include <cstdlib>
+
 #include <cstdint>
 
 namespace afk {
@@ -410,6 +412,402 @@ cudaError_t stat_select_launch(const float *img, int64_t n, const StatParams &p,
     count_launch();
     count_launch();
     stat_finish_kernel<<<1, 1024, 0, s>>>(img, n, p, prev, state, cand, cand_cap);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// ---- the same order statistics in ONE pass over the image (round 2) -----------------------------------------------------
+// The radix select above reads the image three times per statistic because each pass only learns 8 bits of the answer.  For
+// images of a megapixel and more a SAMPLE says where the answer is before the first pass:
+//   stat_sample_kernel          one CTA sorts the keys of 4096 jittered stratified pixels (bitonic sort in shared memory, ~3 us)
+//                               and brackets the wanted rank: [lo, hi] = the sample keys of rank mid -+ 4 sigma -- the bracket
+//                               holds ~6 % of the image and misses the rank about once in 16000 images;
+//   stat_bracket_pass_kernel    the ONE pass: counts the kept keys and the keys below lo, histograms the keys of the bracket
+//                               over 2048 equal-width bins, copies them to the candidate buffer, tracks the smallest key above
+//                               hi; the last CTA to finish (ticket) picks the bin that holds the rank;
+//   stat_bracket_finish_kernel  a few CTAs filter the candidates down to that bin (~500 keys); the last one sorts them in
+//                               shared memory and writes the value (and the even-count successor).
+// Exactness never depends on the sample: a bracket that misses the rank, a candidate buffer or a bin that overflows (heavy
+// ties) sets `fallback`, and the host runs the radix select.  2 launches + 1 image pass per statistic instead of 3 passes.
+// ---------------------------------------------------------------------------------------------------------------------------
+constexpr int kBrSample = 4096;
+constexpr int kBrBins = 2048;
+constexpr int kBrBinBuf = 8192; // keys of the chosen bin the finish can sort in shared memory
+
+// the key of rank `rank` among the keys the CTA sees through key_at(i), i < count (registers or shared memory): radix select,
+// 8 bits per step.  Every thread of the CTA calls it.  s_hist: one 256-bin histogram PER WARP (the keys of an image share
+// their leading bits: on one shared histogram the first steps put thousands of atomics on a single address; private to a warp,
+// a conflict costs at most the 32 lanes of one instruction), s_pick: 2 words.
+template <class KeyAt>
+__device__ unsigned stat_cta_select(KeyAt key_at, unsigned count, unsigned rank, unsigned *s_hist, unsigned *s_pick) {
+    unsigned prefix = 0u, mask = 0u;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = tid; i < nwarp * 256; i += blockDim.x) s_hist[i] = 0u;
+        __syncthreads();
+        for (unsigned i = tid; i < count; i += blockDim.x) {
+            const unsigned key = key_at(i);
+            if ((key & mask) == prefix) atomicAdd(&s_hist[warp * 256 + ((key >> shift) & 255u)], 1u);
+        }
+        __syncthreads();
+        if (tid < 256) { // bin tid summed over the warps, left in the first histogram
+            unsigned t = 0u;
+            for (int w = 0; w < nwarp; ++w) t += s_hist[w * 256 + tid];
+            s_hist[tid] = t;
+        }
+        __syncthreads();
+        if (tid < 32) {
+            unsigned c[8], tot = 0u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { c[j] = s_hist[lane * 8 + j]; tot += c[j]; }
+            unsigned incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            unsigned excl = incl - tot;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (rank >= excl && rank < excl + c[j]) { s_pick[0] = (unsigned)(lane * 8 + j); s_pick[1] = rank - excl; } // one lane, one j
+                excl += c[j];
+            }
+        }
+        __syncthreads();
+        prefix |= s_pick[0] << shift;
+        mask |= 255u << shift;
+        rank = s_pick[1];
+    }
+    return prefix;
+}
+
+__global__ void __launch_bounds__(1024) stat_sample_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
+                                                            StatBracket *br) {
+    __shared__ unsigned s_hist[32 * 256], s_pick[2], s_ms;
+    const int tid = threadIdx.x;
+    const float vmed = p.use_vmed ? prev->result : 0.0f;
+    const int64_t stride = n / kBrSample; // n >= kBrSample (host)
+    if (tid == 0) s_ms = 0u;
+    __syncthreads();
+    unsigned k[kBrSample / 1024];
+    float v[kBrSample / 1024];
+#pragma unroll
+    for (int u = 0; u < kBrSample / 1024; ++u) {
+        const int j = tid + u * 1024;
+        unsigned h = ((unsigned)j * 0x9E3779B9u + 0x7F4A7C15u) * 0x85EBCA6Bu;
+        h ^= h >> 15;
+        v[u] = img[(int64_t)j * stride + (int64_t)(h % (unsigned)(stride < 0x7FFFFFFF ? stride : 0x7FFFFFFF))];
+    }
+    unsigned kept = 0u;
+#pragma unroll
+    for (int u = 0; u < kBrSample / 1024; ++u) {
+        k[u] = 0xFFFFFFFFu; // a dropped sample (NaN, infinite normalised value): ranks last; no kept value has this key
+        unsigned k2;
+        if (stat_value(v[u], p, vmed, &k2)) { k[u] = k2; ++kept; }
+    }
+    kept = __reduce_add_sync(0xffffffffu, kept);
+    if ((tid & 31) == 0 && kept) atomicAdd(&s_ms, kept);
+    __syncthreads();
+    const int ms = (int)s_ms;
+    unsigned lo = 0u, hi = 0xFFFFFFFEu;
+    if (ms >= 64) { // CTA-uniform
+        const int mid = ms / 2;
+        const int w = (int)(2.0f * sqrtf((float)ms)) + 2; // 4 sigma of the sample rank of the image's median (sigma = sqrt(ms) / 2)
+        auto mine = [&](unsigned i) { // key i lives in thread i % 1024, register i / 1024: the select visits i = tid, tid + 1024, ...
+            const unsigned u = i >> 10;
+            return u == 0u ? k[0] : (u == 1u ? k[1] : (u == 2u ? k[2] : k[3]));
+        };
+        static_assert(kBrSample / 1024 == 4, "mine() unpacks 4 registers");
+        if (mid - w >= 0) lo = stat_cta_select(mine, (unsigned)kBrSample, (unsigned)(mid - w), s_hist, s_pick);
+        if (mid + w <= ms - 1) hi = stat_cta_select(mine, (unsigned)kBrSample, (unsigned)(mid + w), s_hist, s_pick);
+    }
+    if (tid == 0) {
+        const unsigned span = hi - lo;
+        const int bits = 32 - __clz(span | 1u);
+        br->lo = lo;
+        br->hi = hi;
+        br->shift = bits > 11 ? bits - 11 : 0; // (span >> shift) < 2048
+    }
+}
+
+constexpr int kBrPriv = 16; // candidates a thread stages privately (it meets ~7); more go straight to the buffer
+
+template <bool RAW>
+__global__ void __launch_bounds__(256) stat_bracket_pass_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
+                                                                 StatBracket *br, unsigned *hist, unsigned *cand, unsigned cand_cap) {
+    __shared__ unsigned s_hist[kBrBins];
+    __shared__ unsigned s_priv[kBrPriv][256]; // slot-major: a warp's appends hit 32 banks
+    __shared__ unsigned s_last;
+    __shared__ unsigned long long s_n, s_below;
+    for (int i = threadIdx.x; i < kBrBins; i += blockDim.x) s_hist[i] = 0u;
+    if (threadIdx.x == 0) { s_n = 0ull; s_below = 0ull; }
+    __syncthreads();
+    const unsigned lo = br->lo, hi = br->hi;
+    const int shift = br->shift;
+    const bool collect = lo != hi; // one key value in the bracket: its count is all the finish needs
+    const float vmed = p.use_vmed ? prev->result : 0.0f;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
+    unsigned above = 0xFFFFFFFFu, n_kept = 0u, n_below = 0u, pc = 0u;
+    const unsigned hist_saddr = (unsigned)__cvta_generic_to_shared(s_hist);
+    const unsigned priv_saddr = (unsigned)__cvta_generic_to_shared(&s_priv[0][threadIdx.x]);
+    // No shared atomic with a result in the loop (a returned slot serialises every step): the bracket's keys (~6 %) go to a
+    // private column of shared memory, the histogram takes a predicated reduction.
+    auto one = [&](float v) {
+        unsigned key = 0u;
+        bool kept;
+        if (RAW) {
+            kept = !(v != v);
+            key = st_key(v);
+        } else {
+            kept = stat_value(v, p, vmed, &key);
+        }
+        n_kept += kept ? 1u : 0u;
+        const bool lt = kept && key < lo, gt = kept && key > hi;
+        n_below += lt ? 1u : 0u;
+        if (gt) above = min(above, key);
+        const unsigned in = (kept && !lt && !gt) ? 1u : 0u;
+        const unsigned stage = (in && collect && pc < (unsigned)kBrPriv) ? 1u : 0u;
+        // predicated, no branch: the bracket's keys are sparse in every thread's stream but present in nearly every warp step
+        asm volatile(
+            "{\n\t"
+            ".reg .pred pi, ps;\n\t"
+            "setp.ne.u32 pi, %0, 0;\n\t"
+            "setp.ne.u32 ps, %1, 0;\n\t"
+            "@pi red.shared.add.u32 [%2], 1;\n\t"
+            "@ps st.shared.u32 [%3], %4;\n\t"
+            "}"
+            :
+            : "r"(in), "r"(stage), "r"(hist_saddr + (((key - lo) >> shift) << 2)), "r"(priv_saddr + pc * (256u * 4u)), "r"(key)
+            : "memory");
+        if (in && collect && !stage) { // a thread with more than 16 candidates: rare
+            const unsigned at = atomicAdd(&br->cand_count, 1u);
+            if (at < cand_cap) cand[at] = key;
+        }
+        pc += (in && collect) ? 1u : 0u;
+    };
+    int64_t done = 0;
+    if ((reinterpret_cast<uintptr_t>(img) & 15u) == 0) {
+        const int64_t n4 = n >> 2;
+        const float4 *src = reinterpret_cast<const float4 *>(img);
+        int64_t i = tid;
+        for (; i + 3 * nthreads < n4; i += 4 * nthreads) {
+            const float4 v0 = st_ld(src + i), v1 = st_ld(src + i + nthreads), v2 = st_ld(src + i + 2 * nthreads), v3 = st_ld(src + i + 3 * nthreads);
+            one(v0.x); one(v0.y); one(v0.z); one(v0.w);
+            one(v1.x); one(v1.y); one(v1.z); one(v1.w);
+            one(v2.x); one(v2.y); one(v2.z); one(v2.w);
+            one(v3.x); one(v3.y); one(v3.z); one(v3.w);
+        }
+        for (; i < n4; i += nthreads) {
+            const float4 v = st_ld(src + i);
+            one(v.x); one(v.y); one(v.z); one(v.w);
+        }
+        done = n4 << 2;
+    }
+    for (int64_t i = done + tid; i < n; i += nthreads) one(img[i]);
+    {
+        // this warp's staged candidates -> the buffer: one reservation per warp
+        const int lane = threadIdx.x & 31;
+        const unsigned mine = min(pc, (unsigned)kBrPriv);
+        unsigned incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const unsigned wtot = __shfl_sync(0xffffffffu, incl, 31);
+        unsigned base = 0u;
+        if (lane == 31 && wtot) base = atomicAdd(&br->cand_count, wtot);
+        base = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
+        for (unsigned i = 0; i < mine; ++i)
+            if (base + i < cand_cap) cand[base + i] = s_priv[i][threadIdx.x];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        above = min(above, __shfl_xor_sync(0xffffffffu, above, o));
+        n_kept += __shfl_xor_sync(0xffffffffu, n_kept, o);
+        n_below += __shfl_xor_sync(0xffffffffu, n_below, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (above != 0xFFFFFFFFu) atomicMin(&br->above_min, above);
+        atomicAdd(&s_n, (unsigned long long)n_kept);
+        atomicAdd(&s_below, (unsigned long long)n_below);
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < kBrBins; b += blockDim.x)
+        if (s_hist[b]) atomicAdd(&hist[b], s_hist[b]);
+    if (threadIdx.x == 0) {
+        atomicAdd(&br->n, s_n);
+        atomicAdd(&br->below, s_below);
+    }
+    // the last CTA to get here picks the bin
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&br->ticket, 1u) == gridDim.x - 1u ? 1u : 0u;
+    __syncthreads();
+    if (!s_last || threadIdx.x >= 32) return;
+    __threadfence();
+    const int lane = threadIdx.x;
+    const unsigned long long total = *reinterpret_cast<volatile unsigned long long *>(&br->n);
+    const unsigned long long below = *reinterpret_cast<volatile unsigned long long *>(&br->below);
+    if (total == 0ull) {
+        if (lane == 0) br->error = 1; // "Empty data!" (lims.rs:53, 92)
+        return;
+    }
+    const int even = (total % 2ull) == 0ull;
+    const unsigned long long kth = even ? total / 2ull - 1ull : total / 2ull;
+    constexpr int kPer = kBrBins / 32;
+    unsigned hc[kPer]; // all loads in flight at once
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) hc[j] = __ldcg(&hist[j * 32 + lane]); // bin j * 32 + lane: coalesced
+    // lane-major order for the scan: bin b = lane * kPer + j  <->  loaded as hist[j * 32 + lane]; transpose through shared memory
+    __shared__ unsigned s_bins[kBrBins];
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) s_bins[j * 32 + lane] = hc[j];
+    __syncwarp();
+    unsigned long long tot = 0ull;
+    for (int j = 0; j < kPer; ++j) tot += s_bins[lane * kPer + j];
+    unsigned long long incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    const unsigned long long in_count = __shfl_sync(0xffffffffu, incl, 31);
+    const unsigned ccount = *reinterpret_cast<volatile unsigned *>(&br->cand_count);
+    const bool collected = br->lo != br->hi;
+    // the rank must fall inside the bracket, and its candidates must all be in the buffer
+    const bool ok = kth >= below && kth < below + in_count && (!collected || (ccount <= cand_cap && (unsigned long long)ccount == in_count));
+    if (!ok) {
+        if (lane == 0) { br->fallback = 1; br->even = even; }
+        return;
+    }
+    const unsigned long long want = kth - below;
+    unsigned long long excl = incl - tot;
+    int bin = -1;
+    unsigned long long rank_in = 0ull, bcount = 0ull;
+    for (int j = 0; j < kPer; ++j) {
+        const unsigned long long c = s_bins[lane * kPer + j];
+        if (bin < 0 && want < excl + c) { bin = lane * kPer + j; rank_in = want - excl; bcount = c; }
+        excl += c;
+    }
+    const unsigned ballot = __ballot_sync(0xffffffffu, bin >= 0);
+    const int src = __ffs(ballot) - 1;
+    bin = __shfl_sync(0xffffffffu, bin, src);
+    rank_in = __shfl_sync(0xffffffffu, rank_in, src);
+    bcount = __shfl_sync(0xffffffffu, bcount, src);
+    if (lane == 0) {
+        br->bin = (unsigned)bin;
+        br->rank_in_bin = rank_in;
+        br->bin_count = bcount;
+        br->even = even;
+        br->in_count = in_count;
+        if (collected && bcount > (unsigned long long)(kBrBinBuf - 16 * 256)) br->fallback = 1; // heavy ties in one bin (the finish keeps 16 histograms behind the keys)
+    }
+}
+
+// grid of a few CTAs over the candidates; the last one to finish sorts the chosen bin's keys and writes the result
+__global__ void __launch_bounds__(512) stat_bracket_finish_kernel(StatParams p, StatBracket *br, StatState *state, const unsigned *__restrict__ cand,
+                                                                    unsigned *binbuf) {
+    __shared__ unsigned s_key[kBrBinBuf];
+    __shared__ unsigned s_last;
+    const int tid = threadIdx.x;
+    if (br->error || br->fallback) {
+        if (blockIdx.x == 0 && tid == 0) {
+            state->error = br->error;
+            state->result = __int_as_float(0x7fc00000);
+        }
+        return;
+    }
+    const unsigned lo = br->lo, hi = br->hi;
+    const int shift = br->shift;
+    const unsigned bin = br->bin;
+    const int even = br->even;
+    unsigned klo, khi;
+    if (lo == hi) { // one key value in the bracket
+        if (blockIdx.x != 0) return;
+        klo = lo;
+        khi = (br->rank_in_bin + 1ull < br->bin_count) ? lo : br->above_min;
+    } else {
+        const unsigned count = br->cand_count;
+        unsigned next = 0xFFFFFFFFu;
+        const unsigned nthr = gridDim.x * blockDim.x;
+        for (unsigned i0 = blockIdx.x * blockDim.x + tid; i0 < count; i0 += 8u * nthr) { // 8 loads in flight per thread
+            unsigned k8[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) k8[u] = i0 + u * nthr < count ? __ldg(cand + i0 + u * nthr) : lo + (bin << shift); // filler: in no bin above, dropped below
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                if (!(i0 + u * nthr < count)) continue;
+                const unsigned key = k8[u];
+                const unsigned b = (key - lo) >> shift;
+                if (b == bin) {
+                    const unsigned at = atomicAdd(&br->bin_cand_count, 1u);
+                    if (at < (unsigned)kBrBinBuf) binbuf[at] = key;
+                } else if (b > bin) {
+                    next = min(next, key);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) next = min(next, __shfl_xor_sync(0xffffffffu, next, o));
+        if ((tid & 31) == 0 && next != 0xFFFFFFFFu) atomicMin(&br->next_min, next);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_last = atomicAdd(&br->ticket2, 1u) == gridDim.x - 1u ? 1u : 0u;
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        const unsigned c = *reinterpret_cast<volatile unsigned *>(&br->bin_cand_count); // == bin_count <= kBrBinBuf
+        const unsigned r = (unsigned)br->rank_in_bin;
+        unsigned *const s_hist = s_key + kBrBinBuf - 16 * 256; // 16 warp histograms at the end of the key area (c <= kBrBinBuf - 4096 is checked by the pass)
+        __shared__ unsigned s_pick[2], s_cnt_le, s_succ;
+        for (unsigned i = tid; i < c; i += blockDim.x) s_key[i] = __ldcg(binbuf + i);
+        if (tid == 0) { s_cnt_le = 0u; s_succ = 0xFFFFFFFFu; }
+        __syncthreads();
+        klo = stat_cta_select([&](unsigned i) { return s_key[i]; }, c, r, s_hist, s_pick);
+        khi = klo;
+        if (even) { // data[mid]: the same key when the run of equal keys continues, else the smallest key above it
+            unsigned le = 0u, succ = 0xFFFFFFFFu;
+            for (unsigned i = tid; i < c; i += blockDim.x) {
+                const unsigned key = s_key[i];
+                le += key <= klo ? 1u : 0u;
+                if (key > klo) succ = min(succ, key);
+            }
+            le = __reduce_add_sync(0xffffffffu, le);
+            succ = __reduce_min_sync(0xffffffffu, succ);
+            if ((tid & 31) == 0) {
+                if (le) atomicAdd(&s_cnt_le, le);
+                if (succ != 0xFFFFFFFFu) atomicMin(&s_succ, succ);
+            }
+            __syncthreads();
+            if (!(r + 1u < s_cnt_le)) {
+                khi = s_succ;
+                if (khi == 0xFFFFFFFFu) khi = min(*reinterpret_cast<volatile unsigned *>(&br->next_min), br->above_min); // the next bin's smallest key, or the smallest key above the bracket
+            }
+        }
+    }
+    if (tid == 0) {
+        float a = st_unkey(khi), b = st_unkey(klo);
+        if (p.raw) { a = stat_normalise(a, p); b = stat_normalise(b, p); }
+        state->result = even ? __fdiv_rn(__fadd_rn(a, b), 2.0f) : b;
+        state->error = 0;
+    }
+}
+
+// Enqueues the one-pass selection; `br` zero-initialised except above_min = next_min = 0xFFFFFFFF, `hist` kBrBins zeroed words,
+// `cand` cand_cap keys, `binbuf` kBrBinBuf keys.  state->result is valid unless br->fallback (then run stat_select_launch).
+cudaError_t stat_bracket_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, StatBracket *br,
+                                unsigned *hist, unsigned *cand, unsigned cand_cap, unsigned *binbuf, int sm_count, cudaStream_t s) {
+    if (n < kBrSample) return cudaErrorInvalidValue;
+    stat_sample_kernel<<<1, 1024, 0, s>>>(img, n, p, prev, br);
+    count_launch();
+    int64_t need = ((n + 3) / 4 + 255) / 256;
+    const int64_t cap = (int64_t)sm_count * 4;
+    const int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
+    if (p.raw) stat_bracket_pass_kernel<true><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+    else stat_bracket_pass_kernel<false><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+    count_launch();
+    stat_bracket_finish_kernel<<<128, 512, 0, s>>>(p, br, state, cand, binbuf);
     count_launch();
     return cudaGetLastError();
 }

@@ -85,6 +85,44 @@ def test_vmed_vmad_full_size_c4(gpu, orc):
     assert got[0] == np.float32(vmed) and got[1] == np.float32(vmad)
 
 
+def big_images():
+    """Megapixel images: vmed / vmad take the one-pass (sample-bracketed) select; the patterns stress its bracket, its bins and
+    its fall-back to the radix select."""
+    rng = np.random.default_rng(24)
+    a = rng.normal(100.0, 15.0, (1024, 1024)).astype(np.float32)
+    yield "normal 1024x1024, even count", a.copy()
+    a[::37, ::11] = np.nan
+    a[5, 5] = 0.0
+    yield "normal with NaN (odd or even kept count)", a.copy()
+    a[7, 7] = np.nan
+    yield "normal with one more NaN (the other parity)", a.copy()
+    yield "quantised 1200x1000 (heavy ties: one key value in the bracket)", np.round(rng.normal(0, 3, (1200, 1000))).astype(np.float32)
+    yield "quantised, wide (several tied values in the bracket)", np.round(rng.normal(0, 300, (1100, 1000))).astype(np.float32)
+    b = rng.lognormal(0.0, 1.0, (1500, 1100)).astype(np.float32)
+    b[rng.random(b.shape) < 0.3] = 0.0
+    yield "30 % zeros + lognormal", b
+    yield "two values", np.where(rng.random((1024, 1100)) < 0.5, np.float32(1.0), np.float32(7.0)).astype(np.float32)
+    yield "ramp (sorted image)", np.arange(1024 * 1024, dtype=np.float32).reshape(1024, 1024) * np.float32(0.37)
+    c = rng.uniform(-1.0, 1.0, (1024, 1024)).astype(np.float32)
+    c[0, 0] = -1e30
+    c[0, 1] = 1e30
+    yield "outliers stretch the range (all normalised values within a few ulps)", c
+    d = rng.normal(0.0, 1.0, (1025, 1023)).astype(np.float32)
+    d[d > 0.0] = np.float32(0.5)  # the upper half is one value: the median sits at the edge of a huge tie
+    yield "upper half tied", d
+
+
+def test_vmed_vmad_one_pass_bit_exact(gpu, orc):
+    for name, a in big_images():
+        want = orc.vmed_vmad(a)
+        got = gpu.Image.upload(a).vmed_vmad()
+        assert got[0].tobytes() == want[0].tobytes() and got[1].tobytes() == want[1].tobytes(), f"{name}: {got} != {want}"
+    for a in [np.full((1024, 1024), 2.0, np.float32), np.full((1024, 1030), np.nan, np.float32)]:
+        with pytest.raises(gpu.AflakError) as e:
+            gpu.Image.upload(a).vmed_vmad()
+        assert e.value.status == gpu.ERR_UNEXPECTED_INPUT and "Empty data!, med" in str(e.value)
+
+
 def test_vmed_vmad_errors(gpu, orc):
     for a in [np.full((5, 5), 2.0, np.float32), np.full((3, 3), np.nan, np.float32)]:
         with pytest.raises(gpu.AflakError) as e:
