@@ -195,6 +195,7 @@ _sig("afk_colormap", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int, C.
 _sig("afk_colormap_host", C.c_int, _P, _P, C.c_float, C.c_float, C.c_int, C.c_int, C.POINTER(afk_colormap_chain), _P)
 _sig("afk_colormap_rgb_host", C.c_int, _P, C.POINTER(C.c_void_p), _fp, _fp, C.c_int, C.c_int, _P)
 _sig("afk_k_reduce", C.c_int, _P, C.c_int64, C.c_int64, C.c_int, _i64p, _i64p, C.c_int, _fp, C.c_int, _P)
+_sig("afk_k_reduce_static", C.c_int, _P, C.c_int64, C.c_int64, C.c_int, _i64p, _i64p, C.c_int, _fp, C.c_int, _P, _P)
 _sig("afk_k_reduce_describe", C.c_int, _P, C.c_int64, C.c_int, _i64p, _i64p, C.c_int, _P, C.c_char_p, C.c_size_t)
 _sig("afk_profile_reduce", C.c_int, C.c_int)
 _sig("afk_profile_reduce_read", C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_uint64))
@@ -719,6 +720,17 @@ def k_reduce(cube_ptr, nz, n2, windows, epilogue, out_ptr, params=None, sum_mode
     en = (C.c_int64 * n)(*[w[1] for w in windows])
     pr = _reduce_params(epilogue, params)
     _check(lib.afk_k_reduce(C.c_void_p(cube_ptr), nz, n2, n, st, en, epilogue, pr, sum_mode, C.c_void_p(out_ptr)))
+
+
+def k_reduce_static(cube_ptr, nz, n2, windows, epilogue, out_ptr, params=None, sum_mode=SUM_COMPENSATED, stream=None):
+    """k_reduce without any allocation: the split-K scratch is a static __device__ array of the library (afk_k_reduce_static).
+    stream: a cudaStream_t handle (None = the legacy default stream)."""
+    n = len(windows)
+    st = (C.c_int64 * n)(*[w[0] for w in windows])
+    en = (C.c_int64 * n)(*[w[1] for w in windows])
+    pr = _reduce_params(epilogue, params)
+    _check(lib.afk_k_reduce_static(C.c_void_p(cube_ptr), nz, n2, n, st, en, epilogue, pr, sum_mode, C.c_void_p(out_ptr),
+                                   C.c_void_p(stream) if stream else None))
 
 
 def k_reduce_describe(cube_ptr, n2, windows, out_ptr, sum_mode=SUM_COMPENSATED):

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libaflak_b200.so")
 STAMP = LIB + ".stamp"
-SOURCES = ["kernels.cu", "axis0.cu", "ingest.cu", "stats.cu", "spatial.cu", "fits.cpp", "stats.cpp", "ops_spatial.cpp", "runtime.cpp", "ops.cpp", "display.cpp", "graph.cpp", "shard.cpp"]
+SOURCES = ["kernels.cu", "noalloc.cu", "axis0.cu", "ingest.cu", "stats.cu", "spatial.cu", "fits.cpp", "stats.cpp", "ops_spatial.cpp", "runtime.cpp", "ops.cpp", "display.cpp", "graph.cpp", "shard.cpp"]
 HEADERS = ["kernels.h", "host.h", os.path.join("..", "..", "include", "aflak_b200.h")]
 
 NVCC_FLAGS = [

@@ -340,6 +340,17 @@ afk_status afk_colormap_rgb_host(const afk_image *img, const afk_lut *const lut[
  * `out` may be a peer-mapped pointer. */
 afk_status afk_k_reduce(const float *cube, int64_t nz, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends,
                         int epilogue, const float *params, int sum_mode, float *out);
+/* afk_k_reduce for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Same arguments, arithmetic, kernels and
+ * bits as afk_k_reduce, but the split-K scratch (f64 partials + arrival counters) lives in a file-scope __device__ array of
+ * 32.25 MiB that every GPU holds from library load to exit; the call performs no cudaMalloc / cudaFree / pool allocation.
+ * cuda_stream: the cudaStream_t to launch on (NULL = the legacy default stream); `cube` and `out` must be ready on it.
+ * Limits: a launch plan that needs more than 32 MiB of partials or more than 65536 arrival counters (e.g. the three-window
+ * EW epilogue on images of a megapixel and more) is rejected with AFK_ERR_UNEXPECTED_INPUT -- use afk_k_reduce there.
+ * All calls on one device share the array: calls that overlap on the GPU race (serialise them); the counters are cleared
+ * on the stream in every call.  The first call on a device resolves the array's address: make it outside a capture. */
+afk_status afk_k_reduce_static(const float *cube, int64_t nz, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends,
+                               int epilogue, const float *params, int sum_mode, float *out, void *cuda_stream);
 /* text description of the kernel instantiation and launch shape afk_k_reduce uses for this problem (reports) */
 int afk_k_reduce_describe(const float *cube, int64_t n2, int nwin, const int64_t *starts, const int64_t *ends, int sum_mode,
                           const float *out, char *buf, size_t cap);
