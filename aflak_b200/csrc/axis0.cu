@@ -1155,7 +1155,6 @@ __global__ void __launch_bounds__(kMsPix * kMsWarps, 2) median_stream_kernel(con
 constexpr int kMs1HalfWidth = 17;          // bracket = sample ranks 128 -+ 17 of 256
 constexpr int kMs1WingWidth = 40;          // a missed bracket falls back to the wing up to rank 128 -+ 40 (5 sigma)
 constexpr int64_t kMs1MaxFrames = 4400;    // beyond, 15 % of the window no longer fits the list with margin
-constexpr int64_t kMs1MinFrames = 3000;    // below, the two-pass kernel is faster (see median_dispatch)
 
 // ascending bitonic sort of 256 keys held 8 per lane: index = lane * 8 + e
 __device__ __forceinline__ void ms_sort256(unsigned (&v)[8], int lane) {
@@ -1523,7 +1522,6 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
     __shared__ float s_lo[kMsPix], s_hi[kMsPix];
     __shared__ unsigned s_cnt[kMsPix];
     __shared__ unsigned s_seg[kM2Warps][kMsPix], s_eq[kM2Warps][kMsPix], s_bel[kM2Warps][kMsPix];
-    __shared__ float s_hmin[kM2Warps][kMsPix];
     __shared__ unsigned s_r[kMsPix], s_eqt[kMsPix], s_abv[kMsPix], s_haslo[kMsPix], s_hashi[kMsPix], s_miss[kMsPix], s_belt[kMsPix], s_packed[kMsPix];
     const int n = (int)a.n;
     const int tid = threadIdx.x, g = tid >> 5, lane = tid & 31;
@@ -1588,14 +1586,18 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
     // rank is then almost surely in the `== lo` class); nothing is above +inf.
     if (!(hi > lo)) hi = (lo == kInf) ? __int_as_float(0x7fc00000) : kInf;
     ms_trace(a, 1, t_tr);
-    // ---- C: classify.  x == lo, lo < x < hi (appended), x >= hi (counted, smallest kept); x < lo is what remains.
+    // ---- C: classify.  x == lo, lo < x < hi (appended), x >= hi (counted); x < lo is what remains.
     //      The stream is bound by the ALU pipe (compares, min/max and integer adds issue at half rate: profiles/
-    //      r2_median_v2_phases.txt), so a voxel costs 7 ALU instructions -- three compares (the third takes !(x >= hi) as a
-    //      predicate operand), two min/max, the list pointer and the load address -- and the two counters are predicated FADDs
-    //      on the FMA pipe (exact: at most 550 frames per thread).  The check against the end of the segment is hoisted out of a
-    //      whole batch. ----
+    //      r2_median_v2_phases.txt), so a voxel costs 5 ALU instructions on the fast path -- three compares (the third takes
+    //      !(x >= hi) as a predicate operand), the list pointer and the load address -- and the two counters are predicated FADDs
+    //      on the FMA pipe (exact: at most 550 frames per thread).  Two things the stream no longer does per voxel:
+    //        * NaN detection: the third compare is "greater or unordered", so a NaN is APPENDED to the segment (the fast path
+    //          has room for a whole batch by construction) and found when the thread scans its <= 100 slots after the stream;
+    //          the checked path (segment nearly full, batch tails) keeps its min.NaN.  A CTA that saw a NaN sets the flag and
+    //          stops: a candidate list never holds a NaN.
+    //        * the smallest value >= hi (the even-count successor when the wanted rank is the bracket's last key): that is one
+    //          spaxel in thousands, known in D0 from the counts, and served by the re-collect. ----
     float f_eq_cnt = 0.0f, f_ge_cnt = 0.0f;
-    float hi_min = kInf;
     const unsigned seg0 = (unsigned)__cvta_generic_to_shared(s_list + lane * kMsRow + g * kM2Seg);
     unsigned wp = seg0; // keeps counting past the segment: D0 sees the overflow
     const unsigned wend = seg0 + kM2Seg * 4u;
@@ -1604,39 +1606,36 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
             "{\n\t"
             ".reg .pred pe, pg, pi, ps;\n\t"
             ".reg .f32 x;\n\t"
-            "mov.b32 x, %5;\n\t"
-            "setp.eq.f32 pe, x, %6;\n\t"
+            "mov.b32 x, %4;\n\t"
+            "setp.eq.f32 pe, x, %5;\n\t"
             "@pe add.f32 %0, %0, 0f3F800000;\n\t"
-            "setp.ge.f32 pg, x, %7;\n\t"
+            "setp.ge.f32 pg, x, %6;\n\t"
             "@pg add.f32 %1, %1, 0f3F800000;\n\t"
-            "@pg min.f32 %2, %2, x;\n\t"
-            "setp.gt.and.f32 pi, x, %6, !pg;\n\t"
-            "setp.lt.and.u32 ps, %4, %8, pi;\n\t"
-            "@ps st.shared.u32 [%4], %5;\n\t"
-            "@pi add.u32 %4, %4, 4;\n\t"
-            "min.NaN.f32 %3, %3, x;\n\t"
+            "setp.gt.and.f32 pi, x, %5, !pg;\n\t"
+            "setp.lt.and.u32 ps, %3, %7, pi;\n\t"
+            "@ps st.shared.u32 [%3], %4;\n\t"
+            "@pi add.u32 %3, %3, 4;\n\t"
+            "min.NaN.f32 %2, %2, x;\n\t"
             "}"
-            : "+f"(f_eq_cnt), "+f"(f_ge_cnt), "+f"(hi_min), "+f"(nan_acc), "+r"(wp)
+            : "+f"(f_eq_cnt), "+f"(f_ge_cnt), "+f"(nan_acc), "+r"(wp)
             : "r"(rawbits), "f"(lo), "f"(hi), "r"(wend)
             : "memory");
     };
-    auto classify = [&](unsigned rawbits) { // the caller has checked that 16 / 32 more appends fit the segment
+    auto classify = [&](unsigned rawbits) { // the caller has checked that 16 more appends fit the segment
         asm volatile(
             "{\n\t"
             ".reg .pred pe, pg, pi;\n\t"
             ".reg .f32 x;\n\t"
-            "mov.b32 x, %5;\n\t"
-            "setp.eq.f32 pe, x, %6;\n\t"
+            "mov.b32 x, %3;\n\t"
+            "setp.eq.f32 pe, x, %4;\n\t"
             "@pe add.f32 %0, %0, 0f3F800000;\n\t"
-            "setp.ge.f32 pg, x, %7;\n\t"
+            "setp.ge.f32 pg, x, %5;\n\t"
             "@pg add.f32 %1, %1, 0f3F800000;\n\t"
-            "@pg min.f32 %2, %2, x;\n\t"
-            "setp.gt.and.f32 pi, x, %6, !pg;\n\t"
-            "@pi st.shared.u32 [%4], %5;\n\t"
-            "@pi add.u32 %4, %4, 4;\n\t"
-            "min.NaN.f32 %3, %3, x;\n\t"
+            "setp.gtu.and.f32 pi, x, %4, !pg;\n\t" // greater or unordered: a NaN goes to the list
+            "@pi st.shared.u32 [%2], %3;\n\t"
+            "@pi add.u32 %2, %2, 4;\n\t"
             "}"
-            : "+f"(f_eq_cnt), "+f"(f_ge_cnt), "+f"(hi_min), "+f"(nan_acc), "+r"(wp)
+            : "+f"(f_eq_cnt), "+f"(f_ge_cnt), "+r"(wp)
             : "r"(rawbits), "f"(lo), "f"(hi)
             : "memory");
     };
@@ -1712,15 +1711,25 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
                 if (t_tail + b * SS + 1 + c < mine) classify_checked(rt[b * kMem + c]);
         }
     }
-    const bool nan = nan_acc != nan_acc;
     const unsigned cnt = (wp - seg0) >> 2;
+    {
+        // NaNs the fast path appended: this thread's own stores, no barrier needed
+        const float *own = reinterpret_cast<const float *>(s_list + lane * kMsRow + g * kM2Seg);
+        const unsigned c = min(cnt, (unsigned)kM2Seg);
+        for (unsigned i = 0; i < c; ++i) nan_acc = m2_min_nan(nan_acc, own[i]);
+    }
+    const bool nan = nan_acc != nan_acc;
     const unsigned n_eq = (unsigned)f_eq_cnt, n_ge = (unsigned)f_ge_cnt;
     s_seg[g][lane] = cnt;
     s_eq[g][lane] = n_eq;
-    s_bel[g][lane] = (unsigned)mine - n_eq - n_ge - cnt; // x < lo (a NaN is in no class: the count is then meaningless, and the flag is set)
-    s_hmin[g][lane] = hi_min;
+    s_bel[g][lane] = (unsigned)mine - n_eq - n_ge - cnt; // x < lo
     if (tid < kMsPix) { s_lo[tid] = 0.0f; s_hi[tid] = 0.0f; }
-    __syncthreads();
+    // a NaN anywhere in the tile: the reference panics (the host reports it), the tile's results do not matter -- and no list may
+    // hold a NaN when the finish runs (its rounds would never drop it)
+    if (__syncthreads_or(nan && active)) {
+        if (nan && active && n > 1) atomicMax(a.flag, 1u);
+        return;
+    }
     ms_trace(a, 2, t_tr);
     // ---- D0: lane = spaxel: does the bracket hold the wanted rank?  If not, the bin becomes the WING next to it (it fits the
     //      list), or the open bin beyond when the wing pivot is not distinct from the bracket's ----
@@ -1728,14 +1737,13 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
     //         into a contiguous list; 4 / 5 open bin below / above (final)
     if (g == 0) {
         unsigned eq = 0u, bel = 0u, mt = 0u;
-        float hm = kInf, lo2 = 0.0f, hi2 = 0.0f;
+        float lo2 = 0.0f, hi2 = 0.0f;
         bool ovf = false;
 #pragma unroll
         for (int w = 0; w < kM2Warps; ++w) {
             const unsigned c = s_seg[w][lane];
             eq += s_eq[w][lane];
             bel += s_bel[w][lane];
-            hm = fminf(hm, s_hmin[w][lane]);
             mt += c;
             ovf |= c > (unsigned)kM2Seg;
             lo2 = __fadd_rn(lo2, __fmul_rn(s_q[2][w][lane], 0.125f));
@@ -1757,12 +1765,15 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
             r = r0 - bel;
             // an overflowing segment only matters when the list is needed: not when the answer is lo itself
             const bool answer_is_lo = r < eq && (!even || r + 1 < eq);
-            if (ovf && !answer_is_lo) miss = 3u;
-            if (ovf && answer_is_lo) mt = 0u;
+            // even count and the wanted rank is the last value below hi: its successor is the smallest value >= hi, which the
+            // stream does not track -- the re-collect of the same bracket finds it
+            const bool need_above = even && r0 + 1u == bel + eq + mt;
+            if ((ovf && !answer_is_lo) || need_above) miss = 3u;
+            if (ovf && answer_is_lo && !need_above) mt = 0u;
             if (bhi != bhi) hashi = 0u; // lo == +inf: nothing above it
         }
-        unsigned above = med_key(hm);
-        if (miss) { mt = 0u; eq = 0u; above = kFull; }
+        unsigned above = kFull; // becomes known when the finish drops candidates above a pivot, or through the re-collect
+        if (miss) { mt = 0u; eq = 0u; }
         s_lo[lane] = blo; s_hi[lane] = bhi;
         s_cnt[lane] = mt;
         s_r[lane] = r; s_eqt[lane] = eq; s_abv[lane] = above; s_haslo[lane] = haslo; s_hashi[lane] = hashi; s_belt[lane] = bel;
@@ -1907,7 +1918,7 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
     }
     __syncthreads();
     unsigned seed = (unsigned)(px0 + lane) * 0x9E3779B9u + (unsigned)g * 0x85EBCA6Bu + 0x7F4A7C15u;
-    for (int round = 0;; ++round) {
+    for (int round = 0; round < 64; ++round) { // random pivots shrink a list ~5x per round: 64 is never reached; a guard against a hang, not a limit
         const unsigned mode = f_mode[lane];
         const bool big = mode < 2u && s_cnt[lane] > 32u;
         if (!__syncthreads_or(big ? 1 : 0)) break;
@@ -2156,7 +2167,6 @@ __global__ void __launch_bounds__(kMsPix * kM2Warps, 2) median_stream2_kernel(co
         if (lane == 0) a.out[px] = med_finish(klo, khi, even);
     }
     if (a.trace) { __syncthreads(); ms_trace(a, 4, t_tr); }
-    if (nan && n > 1) atomicMax(a.flag, 1u);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -1,5 +1,7 @@
 """Worker of test_median_one_pass_short_windows_subprocess: the one-pass median kernel on windows of 801..2100 frames
-(the process is started with AFK_MEDIAN_SINGLE_PASS=2).  Exit status 0 = every pattern bit-exact against the oracle."""
+(the process is started with AFK_MEDIAN_SINGLE_PASS=2; MEDIAN_WORKER_NZ picks the window lengths, AFK_MEDIAN_Z the bracket's
+half-width in sigmas: 0.5 makes most brackets miss or end on the wanted rank -- wing / open-bin re-collects and the even-count
+successor above the bracket).  Exit status 0 = every pattern bit-exact against the oracle."""
 import os
 import sys
 
@@ -18,7 +20,7 @@ gpu.set_device(0)
 rng = np.random.default_rng(0xAF1A0044)
 ny, nx = 97, 99
 bad = 0
-for nz in (801, 1300, 1700, 2100):
+for nz in [int(x) for x in os.environ.get("MEDIAN_WORKER_NZ", "801,1300,1700,2100").split(",")]:
     for tag, host in _median_one_pass_patterns(rng, nz, ny, nx):
         cube = gpu.Image.upload(host)
         for start, end in [(0, nz), (0, nz - 1)] if nz > 801 else [(0, nz)]:

@@ -267,6 +267,10 @@ def test_median_one_pass_short_windows_subprocess():
     env = dict(os.environ, AFK_MEDIAN_SINGLE_PASS="2")
     r = subprocess.run([sys.executable, os.path.join(here, "median_onepass_worker.py")], env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    # a bracket of +-0.5 sigma instead of +-3: most spaxels miss it or end on its last key (re-collect paths, successor above the bracket)
+    env = dict(os.environ, AFK_MEDIAN_SINGLE_PASS="2", AFK_MEDIAN_Z="0.5", MEDIAN_WORKER_NZ="1300,2100")
+    r = subprocess.run([sys.executable, os.path.join(here, "median_onepass_worker.py")], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 @pytest.mark.parametrize("shape", SHAPES)
