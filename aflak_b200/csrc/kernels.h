@@ -256,6 +256,7 @@ struct StatParams {
     float vmin, vmax; // d = (v - vmin) / (vmax - vmin)
     int use_vmed;     // select over |d - vmed| with vmed read from the previous statistic's state (lims.rs:87)
     int raw;          // select over the pixel values themselves and normalise the answer (see stat_value); never with use_vmed
+    const unsigned *mm; // one-pass select only, may be null: device words {~key(min), key(max), any} that replace vmin / vmax / raw
 };
 struct StatState {    // device-resident state of one radix select; zero-initialised
     unsigned prefix, mask;

@@ -48,12 +48,19 @@ static Error histogram_run(const afk_image *img, int channels, int nbins, float 
 
 static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
     if (img->len() == 0) return make_error(AFK_ERR_UNEXPECTED_INPUT, "Could not get vmed from normalized image"); // get_vmax/get_vmin fail
-    float vmin, vmax;
-    bool any;
-    if (Error e = op_min_max(img, &vmin, &vmax, &any)) return e;
     cudaStream_t s;
     int dev;
     if (Error e = stats_ctx(img, &s, &dev)) return e;
+    const int64_t n = img->len();
+    static const int one_pass_env = getenv("AFK_STATS_ONE_PASS") ? atoi(getenv("AFK_STATS_ONE_PASS")) : 1; // 0: radix select only (A/B)
+    const bool one_pass = one_pass_env != 0 && n >= kStatBracketMinPixels;
+    // get_vmin / get_vmax (lims.rs:7-35).  The radix select needs them on the host before its first launch; the one-pass select
+    // leaves them on the device (its kernels decode the words and decide the raw-key shortcut themselves: stat_resolve), so the
+    // whole chain has ONE host synchronisation, at its end.
+    float vmin = 0.0f, vmax = 0.0f;
+    bool any = false;
+    if (!one_pass)
+        if (Error e = op_min_max(img, &vmin, &vmax, &any)) return e;
     // device block: the states of both selections (one-pass bracket select and radix select), their histograms, the small
     // buffers of the bracket finish, then the candidate buffer the selections share (they run one after the other)
     struct Head {
@@ -61,11 +68,11 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
         StatState radix[2];   // radix select: the path for small images and the fallback
         StatBracket br[2];
         unsigned hist_radix[256];
+        unsigned mm[4];       // minmax_kernel's words for the one-pass select (when the image carries no range memo)
         unsigned hist_br[2][kStatBracketBins];
         unsigned binbuf[2][kStatBracketBinBuf];
     };
     const size_t head = (offsetof(Head, binbuf) + 15) / 16 * 16; // initialised from the host up to here
-    const int64_t n = img->len();
     const unsigned cand_cap = (unsigned)(n < (int64_t(1) << 22) ? n : (int64_t(1) << 22)); // 4 Mi keys: 25 % of a 4096^2 image
     char *d = nullptr;
     AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), sizeof(Head) + (size_t)cand_cap * sizeof(unsigned), s));
@@ -81,31 +88,33 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
         return b;
     }();
     cudaError_t ce = cudaMemcpyAsync(d, init_block.data(), head, cudaMemcpyHostToDevice, s); // pageable source: staged before the call returns
-    StatParams p{vmin, vmax, 0, 0};
-    // the median of the normalised values is the normalised median pixel when normalisation is monotone and drops nothing but NaN
-    const int raw = std::isfinite(vmin) && std::isfinite(vmax) && std::isfinite(vmax - vmin) && vmax > vmin;
     const int sms = sm_count(dev);
-    static const int one_pass_env = getenv("AFK_STATS_ONE_PASS") ? atoi(getenv("AFK_STATS_ONE_PASS")) : 1; // 0: radix select only (A/B)
-    const bool one_pass = one_pass_env != 0 && n >= kStatBracketMinPixels;
     StatState h[2];
     StatBracket hb[2];
     memset(hb, 0, sizeof hb);
-    auto radix = [&](int which, const StatState *prev) { // which: 0 vmed, 1 vmad
-        StatParams q = p;
-        q.use_vmed = which;
-        q.raw = which == 0 ? raw : 0;
+    auto radix = [&](int which, const StatState *prev) { // which: 0 vmed, 1 vmad; vmin / vmax are on the host by now
+        StatParams q{vmin, vmax, which, 0, nullptr};
+        // the median of the normalised values is the normalised median pixel when normalisation is monotone and drops nothing but NaN
+        q.raw = which == 0 && std::isfinite(vmin) && std::isfinite(vmax) && std::isfinite(vmax - vmin) && vmax > vmin;
         return stat_select_launch(img->ptr, n, q, prev, &hd->radix[which], hd->hist_radix, cand, cand_cap, sms, s);
     };
     if (one_pass) {
-        StatParams q = p;
-        q.raw = raw;
+        const bool memo = img->range_valid && img->range; // left by the kernel that wrote the pixels: no pass over the image
+        const unsigned *mm = memo ? img->range : hd->mm;
+        if (ce == cudaSuccess && !memo) ce = minmax_launch(img->ptr, n, hd->mm, sms, s);
+        StatParams q{0.0f, 0.0f, 0, 0, mm};
         if (ce == cudaSuccess) ce = stat_bracket_launch(img->ptr, n, q, nullptr, &hd->sel[0], &hd->br[0], hd->hist_br[0], cand, cand_cap, hd->binbuf[0], sms, s);
         q.use_vmed = 1;
-        q.raw = 0;
         if (ce == cudaSuccess) ce = stat_bracket_launch(img->ptr, n, q, &hd->sel[0], &hd->sel[1], &hd->br[1], hd->hist_br[1], cand, cand_cap, hd->binbuf[1], sms, s);
+        unsigned hm[4] = {0, 0, 0, 0};
         if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, hd->sel, sizeof h, cudaMemcpyDeviceToHost, s);
         if (ce == cudaSuccess) ce = cudaMemcpyAsync(hb, hd->br, sizeof hb, cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(hm, mm, sizeof hm, cudaMemcpyDeviceToHost, s);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        // the limits as op_min_max reports them, for the fall-back below
+        any = hm[2] != 0;
+        vmin = any ? minmax_decode_min(hm[0]) : std::numeric_limits<float>::quiet_NaN();
+        vmax = any ? minmax_decode_max(hm[1]) : std::numeric_limits<float>::quiet_NaN();
         // a bracket that missed the wanted rank (about one image in 16000) or could not hold its keys (heavy ties): the radix select
         if (ce == cudaSuccess && hb[0].fallback) {
             ce = radix(0, nullptr);

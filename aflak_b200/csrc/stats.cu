@@ -438,25 +438,28 @@ constexpr int kBrBinBuf = 8192; // keys of the chosen bin the finish can sort in
 // 8 bits per step.  Every thread of the CTA calls it.  s_hist: one 256-bin histogram PER WARP (the keys of an image share
 // their leading bits: on one shared histogram the first steps put thousands of atomics on a single address; private to a warp,
 // a conflict costs at most the 32 lanes of one instruction), s_pick: 2 words.
+// A GROUP of threads (gsize of them, a multiple of 32 and at least 256; gtid = index in the group) runs the select on named
+// barrier `bar`, so two groups of one CTA can select two ranks at the same time.  s_hist: min(warps of the group, 8) x 256 words.
 template <class KeyAt>
-__device__ unsigned stat_cta_select(KeyAt key_at, unsigned count, unsigned rank, unsigned *s_hist, unsigned *s_pick) {
+__device__ unsigned stat_group_select(KeyAt key_at, unsigned count, unsigned rank, unsigned *s_hist, unsigned *s_pick, int gtid, int gsize, int bar) {
     unsigned prefix = 0u, mask = 0u;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+    const int lane = gtid & 31, nwarp = gsize >> 5, nh = nwarp < 8 ? nwarp : 8, mine = (gtid >> 5) % nh;
+    auto sync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(gsize) : "memory"); };
     for (int shift = 24; shift >= 0; shift -= 8) {
-        for (int i = tid; i < nwarp * 256; i += blockDim.x) s_hist[i] = 0u;
-        __syncthreads();
-        for (unsigned i = tid; i < count; i += blockDim.x) {
+        for (int i = gtid; i < nh * 256; i += gsize) s_hist[i] = 0u;
+        sync();
+        for (unsigned i = gtid; i < count; i += gsize) {
             const unsigned key = key_at(i);
-            if ((key & mask) == prefix) atomicAdd(&s_hist[warp * 256 + ((key >> shift) & 255u)], 1u);
+            if ((key & mask) == prefix) atomicAdd(&s_hist[mine * 256 + ((key >> shift) & 255u)], 1u);
         }
-        __syncthreads();
-        if (tid < 256) { // bin tid summed over the warps, left in the first histogram
+        sync();
+        if (gtid < 256) { // bin gtid summed over the private histograms, left in the first one
             unsigned t = 0u;
-            for (int w = 0; w < nwarp; ++w) t += s_hist[w * 256 + tid];
-            s_hist[tid] = t;
+            for (int w = 0; w < nh; ++w) t += s_hist[w * 256 + gtid];
+            s_hist[gtid] = t;
         }
-        __syncthreads();
-        if (tid < 32) {
+        sync();
+        if (gtid < 32) {
             unsigned c[8], tot = 0u;
 #pragma unroll
             for (int j = 0; j < 8; ++j) { c[j] = s_hist[lane * 8 + j]; tot += c[j]; }
@@ -473,23 +476,42 @@ __device__ unsigned stat_cta_select(KeyAt key_at, unsigned count, unsigned rank,
                 excl += c[j];
             }
         }
-        __syncthreads();
+        sync();
         prefix |= s_pick[0] << shift;
         mask |= 255u << shift;
         rank = s_pick[1];
     }
     return prefix;
 }
+// the whole CTA as one group (barrier 0 with every thread is __syncthreads)
+template <class KeyAt>
+__device__ unsigned stat_cta_select(KeyAt key_at, unsigned count, unsigned rank, unsigned *s_hist, unsigned *s_pick) {
+    return stat_group_select(key_at, count, rank, s_hist, s_pick, (int)threadIdx.x, (int)blockDim.x, 0);
+}
+
+// Limits that stayed on the device (p.mm = the three words minmax_kernel / a reduction's range memo leave: {~key(min), key(max),
+// any non-NaN}): decode them and decide the raw-key shortcut here, exactly as the host does for limits it has read back
+// (op_min_max, vmed_vmad_run).  The chain then needs no read-back before its last kernel.
+__device__ __forceinline__ void stat_resolve(StatParams &p) {
+    if (!p.mm) return;
+    const unsigned a = __ldcg(p.mm + 0), b = __ldcg(p.mm + 1), any = __ldcg(p.mm + 2);
+    const float qnan = __int_as_float(0x7fc00000), inf = __int_as_float(0x7f800000);
+    p.vmin = any ? st_unkey(~a) : qnan;
+    p.vmax = any ? st_unkey(b) : qnan;
+    const float r = __fsub_rn(p.vmax, p.vmin);
+    p.raw = (!p.use_vmed && fabsf(p.vmin) < inf && fabsf(p.vmax) < inf && fabsf(r) < inf && p.vmax > p.vmin) ? 1 : 0;
+}
 
 __global__ void __launch_bounds__(1024) stat_sample_kernel(const float *__restrict__ img, int64_t n, StatParams p, const StatState *prev,
                                                             StatBracket *br) {
-    __shared__ unsigned s_hist[32 * 256], s_pick[2], s_ms;
+    __shared__ unsigned s_key[kBrSample];
+    __shared__ unsigned s_hist[2][8 * 256], s_pick[2][2], s_res[2], s_ms;
     const int tid = threadIdx.x;
+    stat_resolve(p);
     const float vmed = p.use_vmed ? prev->result : 0.0f;
     const int64_t stride = n / kBrSample; // n >= kBrSample (host)
-    if (tid == 0) s_ms = 0u;
+    if (tid == 0) { s_ms = 0u; s_res[0] = 0u; s_res[1] = 0xFFFFFFFEu; }
     __syncthreads();
-    unsigned k[kBrSample / 1024];
     float v[kBrSample / 1024];
 #pragma unroll
     for (int u = 0; u < kBrSample / 1024; ++u) {
@@ -501,27 +523,28 @@ __global__ void __launch_bounds__(1024) stat_sample_kernel(const float *__restri
     unsigned kept = 0u;
 #pragma unroll
     for (int u = 0; u < kBrSample / 1024; ++u) {
-        k[u] = 0xFFFFFFFFu; // a dropped sample (NaN, infinite normalised value): ranks last; no kept value has this key
-        unsigned k2;
-        if (stat_value(v[u], p, vmed, &k2)) { k[u] = k2; ++kept; }
+        unsigned key = 0xFFFFFFFFu, k2; // a dropped sample (NaN, infinite normalised value): ranks last; no kept value has this key
+        if (stat_value(v[u], p, vmed, &k2)) { key = k2; ++kept; }
+        s_key[tid + u * 1024] = key;
     }
     kept = __reduce_add_sync(0xffffffffu, kept);
     if ((tid & 31) == 0 && kept) atomicAdd(&s_ms, kept);
     __syncthreads();
     const int ms = (int)s_ms;
-    unsigned lo = 0u, hi = 0xFFFFFFFEu;
     if (ms >= 64) { // CTA-uniform
         const int mid = ms / 2;
         const int w = (int)(2.0f * sqrtf((float)ms)) + 2; // 4 sigma of the sample rank of the image's median (sigma = sqrt(ms) / 2)
-        auto mine = [&](unsigned i) { // key i lives in thread i % 1024, register i / 1024: the select visits i = tid, tid + 1024, ...
-            const unsigned u = i >> 10;
-            return u == 0u ? k[0] : (u == 1u ? k[1] : (u == 2u ? k[2] : k[3]));
-        };
-        static_assert(kBrSample / 1024 == 4, "mine() unpacks 4 registers");
-        if (mid - w >= 0) lo = stat_cta_select(mine, (unsigned)kBrSample, (unsigned)(mid - w), s_hist, s_pick);
-        if (mid + w <= ms - 1) hi = stat_cta_select(mine, (unsigned)kBrSample, (unsigned)(mid + w), s_hist, s_pick);
+        // the two halves of the CTA select the two ranks at the same time, each over all the keys, on its own named barrier
+        const int grp = tid >> 9, gtid = tid & 511;
+        const int rank = grp == 0 ? mid - w : mid + w;
+        if (rank >= 0 && rank <= ms - 1) { // uniform within a group
+            const unsigned key = stat_group_select([&](unsigned i) { return s_key[i]; }, (unsigned)kBrSample, (unsigned)rank, s_hist[grp], s_pick[grp], gtid, 512, 1 + grp);
+            if (gtid == 0) s_res[grp] = key;
+        }
     }
+    __syncthreads();
     if (tid == 0) {
+        const unsigned lo = s_res[0], hi = s_res[1];
         const unsigned span = hi - lo;
         const int bits = 32 - __clz(span | 1u);
         br->lo = lo;
@@ -542,6 +565,9 @@ __global__ void __launch_bounds__(256) stat_bracket_pass_kernel(const float *__r
     for (int i = threadIdx.x; i < kBrBins; i += blockDim.x) s_hist[i] = 0u;
     if (threadIdx.x == 0) { s_n = 0ull; s_below = 0ull; }
     __syncthreads();
+    stat_resolve(p);
+    // limits decided on the device: both instantiations are launched, the one whose case it is not leaves before touching anything
+    if (p.mm && RAW != (p.raw != 0)) return;
     const unsigned lo = br->lo, hi = br->hi;
     const int shift = br->shift;
     const bool collect = lo != hi; // one key value in the bracket: its count is all the finish needs
@@ -711,6 +737,7 @@ __global__ void __launch_bounds__(512) stat_bracket_finish_kernel(StatParams p, 
     __shared__ unsigned s_key[kBrBinBuf];
     __shared__ unsigned s_last;
     const int tid = threadIdx.x;
+    stat_resolve(p);
     if (br->error || br->fallback) {
         if (blockIdx.x == 0 && tid == 0) {
             state->error = br->error;
@@ -804,8 +831,15 @@ cudaError_t stat_bracket_launch(const float *img, int64_t n, const StatParams &p
     int64_t need = ((n + 3) / 4 + 255) / 256;
     const int64_t cap = (int64_t)sm_count * 4;
     const int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
-    if (p.raw) stat_bracket_pass_kernel<true><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
-    else stat_bracket_pass_kernel<false><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+    if (p.mm && !p.use_vmed) { // raw keys or normalised values is decided on the device (stat_resolve): one of the two returns at once
+        stat_bracket_pass_kernel<true><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+        stat_bracket_pass_kernel<false><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+        count_launch();
+    } else if (p.raw && !p.mm) {
+        stat_bracket_pass_kernel<true><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+    } else {
+        stat_bracket_pass_kernel<false><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
+    }
     count_launch();
     stat_bracket_finish_kernel<<<128, 512, 0, s>>>(p, br, state, cand, binbuf);
     count_launch();
