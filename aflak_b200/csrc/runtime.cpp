@@ -202,13 +202,19 @@ Error reduce_workspace(const ReducePlan &plan, int device, cudaStream_t stream, 
     StreamScratch &sc = tls().scratch[std::make_pair(device, stream)];
     ReduceWorkspace &ws = sc.ws;
     if (ws.partial_bytes < plan.partial_bytes) {
-        if (ws.partials) AFK_CUDA(cudaFreeAsync(ws.partials, stream));
+        void *old = ws.partials; // forget the block before anything can fail: a failed allocation must not leave a freed pointer behind
+        ws.partials = nullptr;
+        ws.partial_bytes = 0;
+        if (old) AFK_CUDA(cudaFreeAsync(old, stream));
         size_t want = plan.partial_bytes + plan.partial_bytes / 4;
         AFK_CUDA(cudaMallocAsync(&ws.partials, want, stream));
         ws.partial_bytes = want;
     }
     if (ws.n_counters < plan.n_counters) {
-        if (ws.counters) AFK_CUDA(cudaFreeAsync(ws.counters, stream));
+        void *old = ws.counters;
+        ws.counters = nullptr;
+        ws.n_counters = 0;
+        if (old) AFK_CUDA(cudaFreeAsync(old, stream));
         size_t want = plan.n_counters * 2 + 64;
         void *p = nullptr;
         AFK_CUDA(cudaMallocAsync(&p, want * sizeof(unsigned), stream));
@@ -511,10 +517,11 @@ afk_image *afk_image_upload(const float *host, int ndim, const int64_t *shape) {
 }
 
 afk_image *afk_image_wrap_device(float *device_ptr, int ndim, const int64_t *shape) {
-    if (ndim < 0 || ndim > AFK_MAX_NDIM || !device_ptr) {
+    if (ndim < 0 || ndim > AFK_MAX_NDIM || !device_ptr || (ndim > 0 && !shape)) {
         fail(make_error(AFK_ERR_SHAPE, "bad arguments to afk_image_wrap_device"));
         return nullptr;
     }
+    if (fail(check_shape(ndim, shape)) != AFK_OK) return nullptr; // negative or overflowing extents: the kernels index with the product
     cudaStream_t s;
     int dev;
     if (fail(current_stream(&s, &dev)) != AFK_OK) return nullptr;

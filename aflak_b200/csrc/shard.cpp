@@ -186,18 +186,8 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     if (s != g->stream) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_reduce: called on another stream than the gather was created on"));
     if (g->waited_epoch != g->epoch)
         return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_reduce: afk_gather_wait has not been called since the previous afk_gather_reduce"));
-    // consumers of the previous image on other streams (operators called on its handle from other threads): this step,
-    // and therefore every peer's next overwrite of that slot, is ordered after them
-    if (afk_image *prev = g->result[g->epoch & 1u]) {
-        std::lock_guard<std::mutex> lk(prev->mu);
-        for (cudaEvent_t e : prev->readers) {
-            cudaStreamWaitEvent(s, e, 0);
-            event_put(e);
-        }
-        prev->readers.clear();
-    }
-    const unsigned epoch = ++g->epoch;
-    const int64_t band_off = g->y0[g->rank] * g->nx;
+    // every argument check comes before the epoch moves: a rejected call must leave the protocol where it was (a bumped epoch
+    // with nothing enqueued would make the next reduce fail and every peer's wait time out)
     ReduceArgs a{};
     a.cube = band_cube;
     a.n2 = g->rows[g->rank] * g->nx;
@@ -214,6 +204,18 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     if (epilogue == EPI_EW && !params) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "the equivalent-width epilogue needs params[5] = {a, b, fl, max, sign}"));
     for (int i = 0; i < 4; ++i) a.p[i] = epilogue == EPI_EW ? params[i] : 0.0f;
     a.ew_sign = epilogue == EPI_EW ? params[4] : 1.0f;
+    // consumers of the previous image on other streams (operators called on its handle from other threads): this step,
+    // and therefore every peer's next overwrite of that slot, is ordered after them
+    if (afk_image *prev = g->result[g->epoch & 1u]) {
+        std::lock_guard<std::mutex> lk(prev->mu);
+        for (cudaEvent_t e : prev->readers) {
+            cudaStreamWaitEvent(s, e, 0);
+            event_put(e);
+        }
+        prev->readers.clear();
+    }
+    const unsigned epoch = ++g->epoch;
+    const int64_t band_off = g->y0[g->rank] * g->nx;
     int k = 0;
     if (g->mc) { // one multicast store reaches every rank's copy, this rank's included
         a.out = g->mc_slot(epoch) + band_off;
@@ -252,7 +254,10 @@ afk_status afk_gather_reduce(afk_gather *g, const float *band_cube, int64_t nz, 
     }
     ReducePlan plan = reduce_plan(a, sm_count(dev));
     ReduceWorkspace ws;
-    if (Error e = reduce_workspace(plan, dev, s, &ws)) return fail(e);
+    if (Error e = reduce_workspace(plan, dev, s, &ws)) {
+        --g->epoch; // nothing has been enqueued for this epoch
+        return fail(e);
+    }
     ThreadCtx &c = tls();
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (c.profile) {
@@ -350,7 +355,7 @@ afk_status afk_gather_colormap(afk_gather *g, const afk_lut *lut, float vmin, fl
     if (g->rgba_waited != g->rgba_epoch)
         return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_colormap: afk_gather_wait_rgba has not been called since the previous afk_gather_colormap"));
     if (g->nx % 4 != 0) return fail(make_error(AFK_ERR_UNEXPECTED_INPUT, "afk_gather_colormap: the row length must be a multiple of 4 pixels"));
-    const unsigned e2 = ++g->rgba_epoch;
+    const unsigned e2 = g->rgba_epoch + 1; // committed below, once the band has been mapped: a rejected call leaves the protocol where it was
     const int64_t y0 = g->y0[g->rank], rows = g->rows[g->rank];
     const int64_t out_row = flip_y ? g->ny - y0 - rows : y0; // a band of input rows is a band of output rows, mirrored
     const size_t off = (size_t)out_row * (size_t)g->nx * 4;
@@ -365,6 +370,7 @@ afk_status afk_gather_colormap(afk_gather *g, const afk_lut *lut, float vmin, fl
         afk_image_release(view);
         if (st != AFK_OK) return st;
     }
+    g->rgba_epoch = e2;
     unsigned *sig[kMaxPeers];
     for (int r = 0; r < g->world; ++r) sig[r] = g->rgba_flags(r) + g->rank;
     if (rows <= 0) {

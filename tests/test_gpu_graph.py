@@ -306,6 +306,16 @@ def test_fused_gather_single_rank(gpu, orc):
     # EW needs its five parameters; the other epilogues read none
     with pytest.raises(ValueError):
         ga.reduce(cube.device_ptr, nz, [(0, 10), (10, 20), (20, 30)], gpu.EPI_EW, [1.0, 0.0, 20.0, 1e10])
+    # a rejected call leaves the protocol where it was: the epoch only moves once the arguments have passed, so the next
+    # reduce is accepted (no "wait has not been called") and its wait finds its own flag (no time-out, no NaN band)
+    with pytest.raises(gpu.AflakError, match="Expected 0 <= start < end"):
+        ga.reduce(cube.device_ptr, nz, [(10, nz + 1)], gpu.EPI_SUM)
+    with pytest.raises(gpu.AflakError, match="Expected 0 <= start < end"):
+        ga.reduce(cube.device_ptr, nz, [(7, 7)], gpu.EPI_SUM)
+    ga.reduce(cube.device_ptr, nz, [(5, 25)], gpu.EPI_SUM, sum_mode=gpu.SUM_SEQUENTIAL)
+    ga.wait(timeout_s=2.0)
+    ga.check()
+    assert_bit_equal(ga.result_image().download(), orc.integral(host, 5, 25), "reduce after two rejected calls")
     # a consumer on another thread's stream: recorded on the handle, the next reduce is ordered after it
     import threading
 
