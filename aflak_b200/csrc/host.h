@@ -42,6 +42,7 @@ struct StreamScratch {
     size_t tone_cap = 0;
     std::vector<float> tone_host;
     unsigned *minmax_words = nullptr;
+    unsigned *minmax_self = nullptr; // op_min_max: four self-resetting words (minmax_launch_readback), zeroed once
 };
 
 struct ThreadCtx {
@@ -58,7 +59,13 @@ struct ThreadCtx {
     // where the reference would panic (tone-curve index beyond the table).  Read after any host synchronisation.
     unsigned *panic_word[16] = {};
     size_t panic_tone_len = 0; // table length of the last chain / tone-curve launch, for the message
+    // One page of mapped pinned host memory per thread for the few words an operator reads back (limits, order statistics):
+    // an asynchronous copy into it (or a kernel's own store) plus ONE stream synchronisation, instead of one synchronising
+    // pageable copy per value.  Only valid between the enqueue and the synchronisation of one operator call on this thread.
+    char *readback = nullptr;
 };
+constexpr size_t kReadbackBytes = 4096;
+Error readback_page(char **out);
 ThreadCtx &tls();
 int effective_sum_mode(); // the thread's override, else the process-wide default
 // make sure a device is current and return the stream operators on this thread use

@@ -1419,7 +1419,10 @@ cudaError_t tone_curve_launch(const float *img, int64_t n, const float *table_de
 // ----------------------------------------------------------------------------------------------------
 // K4: min/max ignoring NaN (image_min_max lib.rs:180-197; lims::get_vmin/get_vmax lims.rs:7-35)
 // ----------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) minmax_kernel(const float *__restrict__ img, int64_t n, unsigned *result, int vec_ok) {
+// host_out (may be null): mapped pinned host words.  The last CTA to flush (ticket = result[3]) stores the three final words
+// there with plain stores -- the host needs a stream synchronisation and no copy -- and returns result[0..3] to zero, so the
+// same four device words serve the next launch on the stream without a memset.
+__global__ void __launch_bounds__(256) minmax_kernel(const float *__restrict__ img, int64_t n, unsigned *result, int vec_ok, unsigned *host_out) {
     // running values start at +-Inf so that +-Inf inputs are seen; the FLT_MAX init of image_min_max is applied
     // by the host when it decodes the result
     float mn = __int_as_float(0x7f800000), mx = __int_as_float(0xff800000);
@@ -1445,15 +1448,39 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float *__restrict__ i
         if (e == e) { mn = fminf(mn, e); mx = fmaxf(mx, e); any = true; }
     }
     block_minmax_flush(mn, mx, any, result);
+    if (host_out && threadIdx.x == 0) { // thread 0 issued this CTA's three atomics
+        __threadfence();
+        if (atomicAdd(result + 3, 1u) == gridDim.x - 1u) {
+            __threadfence();
+            const unsigned a = __ldcg(result + 0), b = __ldcg(result + 1), c = __ldcg(result + 2);
+            volatile unsigned *h = host_out;
+            h[0] = a;
+            h[1] = b;
+            h[2] = c;
+            result[0] = 0u;
+            result[1] = 0u;
+            result[2] = 0u;
+            result[3] = 0u;
+        }
+    }
 }
 
-cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_count, cudaStream_t s) {
+static cudaError_t minmax_go(const float *img, int64_t n, unsigned *result, unsigned *host_out, int sm_count, cudaStream_t s) {
     if (n <= 0) return cudaSuccess;
     const int vec_ok = (reinterpret_cast<uintptr_t>(img) & 15u) == 0;
     const int grid = grid_for(vec_ok ? (n + 3) / 4 : n, 256 * 4, sm_count, 8);
-    minmax_kernel<<<grid, 256, 0, s>>>(img, n, result, vec_ok);
+    minmax_kernel<<<grid, 256, 0, s>>>(img, n, result, vec_ok, host_out);
     AFK_COUNT_LAUNCH();
     return cudaGetLastError();
+}
+cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_count, cudaStream_t s) {
+    return minmax_go(img, n, result, nullptr, sm_count, s);
+}
+// words4: four device words that are zero when the launch starts and zero again when it ends (self-resetting; word 3 is the
+// ticket); host_out: three mapped pinned host words that hold {~key(min), key(max), any} once the stream is synchronised
+cudaError_t minmax_launch_readback(const float *img, int64_t n, unsigned *words4, unsigned *host_out, int sm_count, cudaStream_t s) {
+    if (!words4 || !host_out) return cudaErrorInvalidValue;
+    return minmax_go(img, n, words4, host_out, sm_count, s);
 }
 
 // ----------------------------------------------------------------------------------------------------

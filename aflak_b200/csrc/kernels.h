@@ -245,6 +245,8 @@ cudaError_t slice3d_launch(const float *cube, int64_t d0, int64_t d1, int64_t d2
 // ---- min/max (K4) -------------------------------------------------------------
 // result[0] = ~key(min), result[1] = key(max), result[2] = number-of-non-NaN > 0 ; all via atomicMax, zero-init.
 cudaError_t minmax_launch(const float *img, int64_t n, unsigned *result, int sm_count, cudaStream_t s);
+// the same with the read-back folded in: see minmax_kernel (kernels.cu)
+cudaError_t minmax_launch_readback(const float *img, int64_t n, unsigned *words4, unsigned *host_out, int sm_count, cudaStream_t s);
 float minmax_decode_min(unsigned inv_key);
 float minmax_decode_max(unsigned key);
 

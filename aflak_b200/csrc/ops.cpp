@@ -342,28 +342,39 @@ Error op_min_max(const afk_image *img, float *mn, float *mx, bool *any) {
     int dev;
     if (Error e = current_stream(&s, &dev)) return e;
     if (Error e = same_device(img, dev)) return e;
-    unsigned *mm = nullptr;
+    // The three words {~key(min), key(max), any} reach the host through this thread's mapped read-back page: the kernel's last
+    // CTA stores them there itself (or one asynchronous copy does, when the image carries a range memo), so the call is one
+    // launch and one stream synchronisation -- no allocation, memset or copy around the kernel.
+    char *page = nullptr;
+    if (Error e = readback_page(&page)) return e;
+    volatile unsigned *h = reinterpret_cast<volatile unsigned *>(page + 512);
     const bool memo = img->range_valid && img->range; // left by the kernel that wrote the pixels: no pass over the image
-    if (!memo)
-        if (Error e = scratch_u32(s, 4, &mm)) return e;
-    Error err = ok();
-    unsigned h[4] = {0, 0, 0, 0};
-    do {
-        if ((err = image_wait(img, s))) break;
-        cudaError_t ce = memo ? cudaSuccess : minmax_launch(img->ptr, img->len(), mm, sm_count(dev), s);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, memo ? img->range : mm, sizeof h, cudaMemcpyDeviceToHost, s);
-        if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
-        if (ce != cudaSuccess) {
-            err = cuda_error(ce, "minmax_kernel");
-            break;
+    h[0] = h[1] = h[2] = 0u; // an empty image launches nothing
+    if (Error e = image_wait(img, s)) return e;
+    cudaError_t ce = cudaSuccess;
+    StreamScratch &sc = tls().scratch[std::make_pair(dev, s)];
+    if (memo) {
+        ce = cudaMemcpyAsync(page + 512, img->range, 3 * sizeof(unsigned), cudaMemcpyDeviceToHost, s);
+    } else if (img->len() > 0) {
+        if (!sc.minmax_self) {
+            ce = cudaMallocAsync(reinterpret_cast<void **>(&sc.minmax_self), 4 * sizeof(unsigned), s);
+            if (ce == cudaSuccess) ce = cudaMemsetAsync(sc.minmax_self, 0, 4 * sizeof(unsigned), s);
+            else sc.minmax_self = nullptr;
         }
-        image_note_read(img, s);
-    } while (0);
-    scratch_free(s, mm);
-    if (err) return err;
-    *any = h[2] != 0;
-    *mn = *any ? minmax_decode_min(h[0]) : std::numeric_limits<float>::quiet_NaN();
-    *mx = *any ? minmax_decode_max(h[1]) : std::numeric_limits<float>::quiet_NaN();
+        if (ce == cudaSuccess) ce = minmax_launch_readback(img->ptr, img->len(), sc.minmax_self, reinterpret_cast<unsigned *>(page + 512), sm_count(dev), s);
+    }
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) {
+        // the words may not have been returned to zero: start from a fresh block next time
+        if (sc.minmax_self) cudaFreeAsync(sc.minmax_self, s);
+        sc.minmax_self = nullptr;
+        return cuda_error(ce, "minmax_kernel");
+    }
+    image_note_read(img, s);
+    const unsigned h0 = h[0], h1 = h[1], h2 = h[2];
+    *any = h2 != 0;
+    *mn = *any ? minmax_decode_min(h0) : std::numeric_limits<float>::quiet_NaN();
+    *mx = *any ? minmax_decode_max(h1) : std::numeric_limits<float>::quiet_NaN();
     return ok();
 }
 

@@ -185,6 +185,19 @@ Error panic_word_take(int device) {
                                          len > 0 ? len - 1 : 0));
 }
 
+// ---- read-back page --------------------------------------------------------------------------------------------
+Error readback_page(char **out) {
+    ThreadCtx &c = tls();
+    if (!c.readback) {
+        void *p = nullptr;
+        AFK_CUDA(cudaHostAlloc(&p, kReadbackBytes, cudaHostAllocMapped | cudaHostAllocPortable));
+        memset(p, 0, kReadbackBytes);
+        c.readback = static_cast<char *>(p);
+    }
+    *out = c.readback;
+    return ok();
+}
+
 // ---- scratch ---------------------------------------------------------------------------------------------
 Error scratch_u32(cudaStream_t s, size_t n, unsigned **out) {
     void *p = nullptr;

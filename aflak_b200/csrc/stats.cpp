@@ -64,11 +64,13 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
     // device block: the states of both selections (one-pass bracket select and radix select), their histograms, the small
     // buffers of the bracket finish, then the candidate buffer the selections share (they run one after the other)
     struct Head {
+        // read back in ONE copy at the end of the one-pass chain (sel, br, mm are contiguous): a pageable read-back is a host
+        // synchronisation of its own, three of them cost ~15 us of a ~200 us chain
         StatState sel[2];     // results of the one-pass select (vmed, vmad)
-        StatState radix[2];   // radix select: the path for small images and the fallback
         StatBracket br[2];
-        unsigned hist_radix[256];
         unsigned mm[4];       // minmax_kernel's words for the one-pass select (when the image carries no range memo)
+        StatState radix[2];   // radix select: the path for small images and the fallback
+        unsigned hist_radix[256];
         unsigned hist_br[2][kStatBracketBins];
         unsigned binbuf[2][kStatBracketBinBuf];
     };
@@ -107,10 +109,26 @@ static Error vmed_vmad_run(const afk_image *img, float *vmed, float *vmad) {
         q.use_vmed = 1;
         if (ce == cudaSuccess) ce = stat_bracket_launch(img->ptr, n, q, &hd->sel[0], &hd->sel[1], &hd->br[1], hd->hist_br[1], cand, cand_cap, hd->binbuf[1], sms, s);
         unsigned hm[4] = {0, 0, 0, 0};
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(h, hd->sel, sizeof h, cudaMemcpyDeviceToHost, s);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(hb, hd->br, sizeof hb, cudaMemcpyDeviceToHost, s);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(hm, mm, sizeof hm, cudaMemcpyDeviceToHost, s);
+        // one asynchronous copy into this thread's pinned read-back page (plus the memo's words when the limits came from the
+        // image's range memo), one synchronisation
+        constexpr size_t kOut = offsetof(Head, mm) + sizeof(hd->mm);
+        static_assert(offsetof(Head, sel) == 0 && offsetof(Head, br) == sizeof(StatState) * 2 && offsetof(Head, mm) == offsetof(Head, br) + sizeof(StatBracket) * 2,
+                      "sel, br, mm are contiguous at the start of the block");
+        static_assert(kOut + 16 <= kReadbackBytes, "fits the read-back page");
+        char *rb = nullptr;
+        if (ce == cudaSuccess)
+            if (Error e = readback_page(&rb)) {
+                cudaFreeAsync(d, s);
+                return e;
+            }
+        if (ce == cudaSuccess) ce = cudaMemcpyAsync(rb, d, kOut, cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess && memo) ce = cudaMemcpyAsync(rb + kOut, mm, sizeof hm, cudaMemcpyDeviceToHost, s);
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+        if (ce == cudaSuccess) {
+            memcpy(h, rb + offsetof(Head, sel), sizeof h);
+            memcpy(hb, rb + offsetof(Head, br), sizeof hb);
+            memcpy(hm, memo ? rb + kOut : rb + offsetof(Head, mm), sizeof hm);
+        }
         // the limits as op_min_max reports them, for the fall-back below
         any = hm[2] != 0;
         vmin = any ? minmax_decode_min(hm[0]) : std::numeric_limits<float>::quiet_NaN();

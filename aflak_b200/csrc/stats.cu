@@ -9,6 +9,7 @@
 // passes; every pass is a streaming read with shared-memory privatised histograms.
 #include "kernels.h"
 
+#include <cstdio>
 #include <cstdlib>
 
 #include <cstdint>
@@ -826,8 +827,15 @@ __global__ void __launch_bounds__(512) stat_bracket_finish_kernel(StatParams p, 
 cudaError_t stat_bracket_launch(const float *img, int64_t n, const StatParams &p, const StatState *prev, StatState *state, StatBracket *br,
                                 unsigned *hist, unsigned *cand, unsigned cand_cap, unsigned *binbuf, int sm_count, cudaStream_t s) {
     if (n < kBrSample) return cudaErrorInvalidValue;
+    static const bool dbg = getenv("AFK_STATS_DEBUG") != nullptr; // synchronise after every launch and say which one failed
+    auto stage = [&](const char *what) {
+        if (!dbg) return;
+        const cudaError_t e = cudaStreamSynchronize(s);
+        fprintf(stderr, "[afk stats] %s (use_vmed %d): %s\n", what, p.use_vmed, cudaGetErrorString(e));
+    };
     stat_sample_kernel<<<1, 1024, 0, s>>>(img, n, p, prev, br);
     count_launch();
+    stage("stat_sample_kernel");
     int64_t need = ((n + 3) / 4 + 255) / 256;
     const int64_t cap = (int64_t)sm_count * 4;
     const int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
@@ -841,8 +849,13 @@ cudaError_t stat_bracket_launch(const float *img, int64_t n, const StatParams &p
         stat_bracket_pass_kernel<false><<<grid, 256, 0, s>>>(img, n, p, prev, br, hist, cand, cand_cap);
     }
     count_launch();
+    stage("stat_bracket_pass_kernel");
+    // (One kernel that branches on p.raw between the two instantiations of the stream was tried in round 2 and dropped: inlined
+    // side by side, the PTX nvcc 12.9 emits for the non-RAW copy lacks the `key > hi` term of the bracket test, and the
+    // histogram reduction then lands outside shared memory.  Two launches, one of which returns at once, cost ~6 us.)
     stat_bracket_finish_kernel<<<128, 512, 0, s>>>(p, br, state, cand, binbuf);
     count_launch();
+    stage("stat_bracket_finish_kernel");
     return cudaGetLastError();
 }
 

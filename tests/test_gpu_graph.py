@@ -316,6 +316,8 @@ def test_fused_gather_single_rank(gpu, orc):
     ga.wait(timeout_s=2.0)
     ga.check()
     assert_bit_equal(ga.result_image().download(), orc.integral(host, 5, 25), "reduce after two rejected calls")
+    ga.reduce(cube.device_ptr, nz, [(0, nz)], gpu.EPI_SUM)
+    ga.wait()
     # a consumer on another thread's stream: recorded on the handle, the next reduce is ordered after it
     import threading
 

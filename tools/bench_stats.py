@@ -66,7 +66,7 @@ def entry(name, passes, fn):
 
 entry("vmin/vmax (lims::get_vmin, get_vmax)", 1, lambda: img.vmin_vmax())
 entry("histogram 100 bins (hist::histogram)", 1, lambda: img.histogram(vmin, vmax))
-entry("vmed + vmad (lims::get_vmed_normalized, get_vmad_normalized): 1 min/max + 2 x (3 digit passes over the image + 1 single-CTA finish over the candidates)", 7, lambda: img.vmed_vmad())
+entry("vmed + vmad (lims::get_vmed_normalized, get_vmad_normalized): 1 min/max pass + 2 x (sample kernel, ONE bracket pass over the image, finish over the candidates); one read-back", 3, lambda: img.vmed_vmad())
 entry("zscale(1000, 0.25)", 0, lambda: img.zscale(1000, 0.25))
 
 
