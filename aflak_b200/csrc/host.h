@@ -43,7 +43,9 @@ struct StreamScratch {
     std::vector<float> tone_host;
     unsigned *minmax_words = nullptr;
     unsigned *minmax_self = nullptr; // op_min_max: four self-resetting words (minmax_launch_readback), zeroed once
+    unsigned long long *hist_self = nullptr; // histogram_run: kHistSelfEntries self-resetting counts + the ticket word, zeroed once
 };
+constexpr size_t kHistSelfEntries = 768; // 256 bins x 3 channels (hist.rs:36-66)
 
 struct ThreadCtx {
     int device = -1;
@@ -64,7 +66,7 @@ struct ThreadCtx {
     // pageable copy per value.  Only valid between the enqueue and the synchronisation of one operator call on this thread.
     char *readback = nullptr;
 };
-constexpr size_t kReadbackBytes = 4096;
+constexpr size_t kReadbackBytes = 8192; // [0, 512) order statistics | [512, 1024) min/max | [1024, 8192) histogram counts, zscale samples
 Error readback_page(char **out);
 ThreadCtx &tls();
 int effective_sum_mode(); // the thread's override, else the process-wide default

@@ -252,8 +252,11 @@ float minmax_decode_max(unsigned key);
 
 // ---- display statistics (stats.cu) ----------------------------------------------------------------
 // hist::histogram / histogram_color (aflak_plot/src/imshow/hist.rs:10-66): counts_dev is [nbins][channels] u64, zeroed
+// ticket_dev / host_out: both null, or a zeroed device word and mapped pinned host memory for the counts -- the kernel's last
+// CTA then stores the counts there and returns counts_dev and the ticket to zero (no memset before the next launch, no copy)
 cudaError_t histogram_launch(const float *img, int64_t n_per_channel, int channels, float mn, float mx, int nbins,
-                             unsigned long long *counts_dev, int sm_count, cudaStream_t s);
+                             unsigned long long *counts_dev, int sm_count, cudaStream_t s, unsigned *ticket_dev = nullptr,
+                             unsigned long long *host_out = nullptr);
 struct StatParams {
     float vmin, vmax; // d = (v - vmin) / (vmax - vmin)
     int use_vmed;     // select over |d - vmed| with vmed read from the previous statistic's state (lims.rs:87)

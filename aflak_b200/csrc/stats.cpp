@@ -27,15 +27,32 @@ static Error histogram_run(const afk_image *img, int channels, int nbins, float 
     int dev;
     if (Error e = stats_ctx(img, &s, &dev)) return e;
     const int64_t n_per = img->len() / channels;
-    const size_t bytes = (size_t)nbins * channels * sizeof(unsigned long long);
-    unsigned long long *d = nullptr;
-    AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), bytes, s));
-    cudaError_t ce = cudaMemsetAsync(d, 0, bytes, s);
-    if (ce == cudaSuccess) ce = histogram_launch(img->ptr, n_per, channels, vmin, vmax, nbins, d, sm_count(dev), s);
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(counts, d, bytes, cudaMemcpyDeviceToHost, s);
+    const size_t entries = (size_t)nbins * channels, bytes = entries * sizeof(unsigned long long);
+    if (entries > kHistSelfEntries) return make_error(AFK_ERR_UNEXPECTED_INPUT, "histogram: too many bins");
+    // The counts reach the host through this thread's mapped read-back page: the kernel's last CTA stores them there and
+    // returns the device block to zero, so the call is one launch and one synchronisation (no allocation, memset or copy).
+    char *page = nullptr;
+    if (Error e = readback_page(&page)) return e;
+    unsigned long long *host_out = reinterpret_cast<unsigned long long *>(page + 1024);
+    memset(host_out, 0, bytes); // an empty image launches nothing
+    StreamScratch &sc = tls().scratch[std::make_pair(dev, s)];
+    cudaError_t ce = cudaSuccess;
+    if (!sc.hist_self) {
+        const size_t block = (kHistSelfEntries + 2) * sizeof(unsigned long long); // counts, then the ticket word
+        ce = cudaMallocAsync(reinterpret_cast<void **>(&sc.hist_self), block, s);
+        if (ce == cudaSuccess) ce = cudaMemsetAsync(sc.hist_self, 0, block, s);
+        else sc.hist_self = nullptr;
+    }
+    if (ce == cudaSuccess)
+        ce = histogram_launch(img->ptr, n_per, channels, vmin, vmax, nbins, sc.hist_self, sm_count(dev), s,
+                              reinterpret_cast<unsigned *>(sc.hist_self + kHistSelfEntries), host_out);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
-    cudaFreeAsync(d, s);
-    if (ce != cudaSuccess) return cuda_error(ce, "histogram_kernel");
+    if (ce != cudaSuccess) {
+        if (sc.hist_self) cudaFreeAsync(sc.hist_self, s); // the block may not have been returned to zero
+        sc.hist_self = nullptr;
+        return cuda_error(ce, "histogram_kernel");
+    }
+    memcpy(counts, host_out, bytes);
     image_note_read(img, s);
     // Bin { start: min + i as f32 * size, end: min + (i + 1) as f32 * size } with size = (max - min) / NB (hist.rs:16-23)
     const float size = (vmax - vmin) / (float)nbins;
@@ -263,12 +280,23 @@ static Error zscale_run(const afk_image *img, int nsamples, float contrast, int 
         cudaStream_t s;
         int dev;
         if (Error e = stats_ctx(img, &s, &dev)) return e;
-        float *d = nullptr;
-        AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), grid.size() * sizeof(float), s));
-        cudaError_t ce = zsample_launch(img->ptr, nc, nl, stride, rows_s, cols_s, d, s);
-        if (ce == cudaSuccess) ce = cudaMemcpyAsync(grid.data(), d, grid.size() * sizeof(float), cudaMemcpyDeviceToHost, s);
-        if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
-        cudaFreeAsync(d, s);
+        cudaError_t ce;
+        if (grid.size() * sizeof(float) <= kReadbackBytes - 1024) {
+            // the usual ~1000 samples: the kernel stores them straight into this thread's mapped read-back page (one launch,
+            // one synchronisation; no allocation or copy)
+            char *page = nullptr;
+            if (Error e = readback_page(&page)) return e;
+            ce = zsample_launch(img->ptr, nc, nl, stride, rows_s, cols_s, reinterpret_cast<float *>(page + 1024), s);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+            if (ce == cudaSuccess) memcpy(grid.data(), page + 1024, grid.size() * sizeof(float));
+        } else {
+            float *d = nullptr;
+            AFK_CUDA(cudaMallocAsync(reinterpret_cast<void **>(&d), grid.size() * sizeof(float), s));
+            ce = zsample_launch(img->ptr, nc, nl, stride, rows_s, cols_s, d, s);
+            if (ce == cudaSuccess) ce = cudaMemcpyAsync(grid.data(), d, grid.size() * sizeof(float), cudaMemcpyDeviceToHost, s);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+            cudaFreeAsync(d, s);
+        }
         if (ce != cudaSuccess) return cuda_error(ce, "zsample_kernel");
         image_note_read(img, s);
         for (float v : grid)

@@ -77,8 +77,12 @@ struct RunCounterPred {
 constexpr int kHistWarps = 8;
 
 // counts: [nbins][channels] (bin-major like Vec<[Bin; 3]>), 64-bit
+// host_out (may be null, then ticket is unused): mapped pinned host memory for the [nb][channels] counts.  The last CTA of the
+// grid (ticket) copies the finished counts there with plain stores and returns counts[] and the ticket to zero, so that the
+// same device block serves the next launch on the stream without a memset and the host needs no copy, only a synchronisation.
 __global__ void __launch_bounds__(256) histogram_kernel(const float *__restrict__ img, int64_t n_per_channel, int channels, float mn,
-                                                         float mx, unsigned nb, unsigned long long *counts) {
+                                                         float mx, unsigned nb, unsigned long long *counts, unsigned *ticket,
+                                                         unsigned long long *host_out) {
     extern __shared__ unsigned s_hist[]; // [kHistWarps][nb]
     for (unsigned i = threadIdx.x; i < kHistWarps * nb; i += blockDim.x) s_hist[i] = 0u;
     __syncthreads();
@@ -110,16 +114,33 @@ __global__ void __launch_bounds__(256) histogram_kernel(const float *__restrict_
         for (int w = 0; w < kHistWarps; ++w) t += s_hist[w * nb + b];
         if (t) atomicAdd(&counts[(size_t)b * channels + c], (unsigned long long)t);
     }
+    if (host_out) {
+        __shared__ unsigned s_last;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1u ? 1u : 0u;
+        __syncthreads();
+        if (s_last) {
+            __threadfence();
+            const unsigned total = nb * (unsigned)channels;
+            for (unsigned i = threadIdx.x; i < total; i += blockDim.x) {
+                *reinterpret_cast<volatile unsigned long long *>(host_out + i) = __ldcg(&counts[i]);
+                counts[i] = 0ull;
+            }
+            if (threadIdx.x == 0) *ticket = 0u;
+        }
+    }
 }
 
 cudaError_t histogram_launch(const float *img, int64_t n_per_channel, int channels, float mn, float mx, int nbins,
-                             unsigned long long *counts_dev, int sm_count, cudaStream_t s) {
+                             unsigned long long *counts_dev, int sm_count, cudaStream_t s, unsigned *ticket_dev, unsigned long long *host_out) {
+    if ((ticket_dev == nullptr) != (host_out == nullptr)) return cudaErrorInvalidValue;
     if (n_per_channel <= 0) return cudaSuccess;
     if (nbins < 1 || nbins > 1024 || channels < 1 || channels > 3) return cudaErrorInvalidValue;
     int64_t need = ((n_per_channel + 3) / 4 + 255) / 256;
     const int64_t cap = (int64_t)sm_count * 4;
     const dim3 grid((unsigned)(need < 1 ? 1 : (need < cap ? need : cap)), (unsigned)channels);
-    histogram_kernel<<<grid, 256, (size_t)kHistWarps * nbins * sizeof(unsigned), s>>>(img, n_per_channel, channels, mn, mx, (unsigned)nbins, counts_dev);
+    histogram_kernel<<<grid, 256, (size_t)kHistWarps * nbins * sizeof(unsigned), s>>>(img, n_per_channel, channels, mn, mx, (unsigned)nbins, counts_dev, ticket_dev, host_out);
     count_launch();
     return cudaGetLastError();
 }
@@ -563,12 +584,13 @@ __global__ void __launch_bounds__(256) stat_bracket_pass_kernel(const float *__r
     __shared__ unsigned s_priv[kBrPriv][256]; // slot-major: a warp's appends hit 32 banks
     __shared__ unsigned s_last;
     __shared__ unsigned long long s_n, s_below;
+    stat_resolve(p);
+    // limits decided on the device: both instantiations are launched, the one whose case it is not leaves before touching anything
+    // (grid-uniform, ahead of the first barrier: its CTAs retire at once)
+    if (p.mm && RAW != (p.raw != 0)) return;
     for (int i = threadIdx.x; i < kBrBins; i += blockDim.x) s_hist[i] = 0u;
     if (threadIdx.x == 0) { s_n = 0ull; s_below = 0ull; }
     __syncthreads();
-    stat_resolve(p);
-    // limits decided on the device: both instantiations are launched, the one whose case it is not leaves before touching anything
-    if (p.mm && RAW != (p.raw != 0)) return;
     const unsigned lo = br->lo, hi = br->hi;
     const int shift = br->shift;
     const bool collect = lo != hi; // one key value in the bracket: its count is all the finish needs
