@@ -596,43 +596,55 @@ __global__ void __launch_bounds__(256) stat_bracket_pass_kernel(const float *__r
     const bool collect = lo != hi; // one key value in the bracket: its count is all the finish needs
     const float vmed = p.use_vmed ? prev->result : 0.0f;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
-    unsigned above = 0xFFFFFFFFu, n_kept = 0u, n_below = 0u, pc = 0u;
+    unsigned above = 0xFFFFFFFFu, n_seen = 0u, n_drop = 0u, n_below = 0u, pc = 0u;
     const unsigned hist_saddr = (unsigned)__cvta_generic_to_shared(s_hist);
     const unsigned priv_saddr = (unsigned)__cvta_generic_to_shared(&s_priv[0][threadIdx.x]);
-    // No shared atomic with a result in the loop (a returned slot serialises every step): the bracket's keys (~6 %) go to a
-    // private column of shared memory, the histogram takes a predicated reduction.
+    const unsigned span = hi - lo;
+    // The common case -- a kept key outside the bracket, 94 % of the pixels -- is kept short: key, one subtraction, three compares,
+    // two predicated updates, one branch (14 instructions on raw keys).  Measured with ncu in round 2 (profiles/
+    // r2_stats_one_pass_ncu_before.json -> r2_stats_one_pass_ncu.json): 41 -> 34.6 instructions per pixel on raw keys, 63 -> 48 on
+    // normalised values; the normalised pass went from 54.2 to 46.6 us, the raw pass stayed at 40 us with 59 % of its issue
+    // slots busy -- that one waits on its loads and branches (32 warps per SM), not on issue.  A dropped value (NaN, infinite
+    // normalised value) leaves at once and is counted; the kept count is what is left of the pixels seen.
+    // Only a bracket key (key - lo <= hi - lo: the subtraction wraps beyond the span for a key below lo) takes the histogram
+    // reduction and the private staging column -- no shared atomic with a result anywhere (a returned slot serialises).
     auto one = [&](float v) {
         unsigned key = 0u;
         bool kept;
         if (RAW) {
             kept = !(v != v);
             key = st_key(v);
-        } else {
-            kept = stat_value(v, p, vmed, &key);
+        } else { // stat_value without its run-time p.raw case: this instantiation only runs on normalised values
+            float d = stat_normalise(v, p);
+            if (p.use_vmed) d = fabsf(__fsub_rn(d, vmed));
+            kept = fabsf(d) < __int_as_float(0x7f800000); // neither NaN nor infinite
+            key = st_key(d);
         }
-        n_kept += kept ? 1u : 0u;
-        const bool lt = kept && key < lo, gt = kept && key > hi;
-        n_below += lt ? 1u : 0u;
-        if (gt) above = min(above, key);
-        const unsigned in = (kept && !lt && !gt) ? 1u : 0u;
-        const unsigned stage = (in && collect && pc < (unsigned)kBrPriv) ? 1u : 0u;
-        // predicated, no branch: the bracket's keys are sparse in every thread's stream but present in nearly every warp step
-        asm volatile(
-            "{\n\t"
-            ".reg .pred pi, ps;\n\t"
-            "setp.ne.u32 pi, %0, 0;\n\t"
-            "setp.ne.u32 ps, %1, 0;\n\t"
-            "@pi red.shared.add.u32 [%2], 1;\n\t"
-            "@ps st.shared.u32 [%3], %4;\n\t"
+        if (!kept) {
+            ++n_drop;
+            return;
+        }
+        const unsigned d = key - lo;
+        asm("{\n\t"
+            ".reg .pred q;\n\t"
+            "setp.lt.u32 q, %1, %2;\n\t"
+            "@q add.u32 %0, %0, 1;\n\t"
             "}"
-            :
-            : "r"(in), "r"(stage), "r"(hist_saddr + (((key - lo) >> shift) << 2)), "r"(priv_saddr + pc * (256u * 4u)), "r"(key)
-            : "memory");
-        if (in && collect && !stage) { // a thread with more than 16 candidates: rare
-            const unsigned at = atomicAdd(&br->cand_count, 1u);
-            if (at < cand_cap) cand[at] = key;
+            : "+r"(n_below)
+            : "r"(key), "r"(lo));
+        if (key > hi) above = min(above, key);
+        if (d <= span) {
+            asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(hist_saddr + ((d >> shift) << 2)) : "memory");
+            if (collect) {
+                if (pc < (unsigned)kBrPriv) {
+                    asm volatile("st.shared.u32 [%0], %1;" ::"r"(priv_saddr + pc * (256u * 4u)), "r"(key) : "memory");
+                } else { // a thread with more than 16 candidates: rare
+                    const unsigned at = atomicAdd(&br->cand_count, 1u);
+                    if (at < cand_cap) cand[at] = key;
+                }
+                ++pc;
+            }
         }
-        pc += (in && collect) ? 1u : 0u;
     };
     int64_t done = 0;
     if ((reinterpret_cast<uintptr_t>(img) & 15u) == 0) {
@@ -645,14 +657,20 @@ __global__ void __launch_bounds__(256) stat_bracket_pass_kernel(const float *__r
             one(v1.x); one(v1.y); one(v1.z); one(v1.w);
             one(v2.x); one(v2.y); one(v2.z); one(v2.w);
             one(v3.x); one(v3.y); one(v3.z); one(v3.w);
+            n_seen += 16u;
         }
         for (; i < n4; i += nthreads) {
             const float4 v = st_ld(src + i);
             one(v.x); one(v.y); one(v.z); one(v.w);
+            n_seen += 4u;
         }
         done = n4 << 2;
     }
-    for (int64_t i = done + tid; i < n; i += nthreads) one(img[i]);
+    for (int64_t i = done + tid; i < n; i += nthreads) {
+        one(img[i]);
+        n_seen += 1u;
+    }
+    unsigned n_kept = n_seen - n_drop;
     {
         // this warp's staged candidates -> the buffer: one reservation per warp
         const int lane = threadIdx.x & 31;

@@ -110,6 +110,12 @@ def big_images():
     d = rng.normal(0.0, 1.0, (1025, 1023)).astype(np.float32)
     d[d > 0.0] = np.float32(0.5)  # the upper half is one value: the median sits at the edge of a huge tie
     yield "upper half tied", d
+    e = rng.normal(10.0, 2.0, (1024, 1024)).astype(np.float32)
+    e[3, 3] = np.inf  # vmax = +Inf: no raw-key shortcut, every finite pixel normalises to 0, the Inf pixel to NaN (dropped)
+    yield "one +Inf pixel (infinite range: one key value in the bracket, normalised path for both statistics)", e
+    f = rng.normal(0.0, 1.0, (1024, 1024)).astype(np.float32)
+    f[::2, :] = np.nan  # half of every warp's stream is dropped
+    yield "every other row NaN", f
 
 
 def test_vmed_vmad_one_pass_bit_exact(gpu, orc):
