@@ -1007,6 +1007,28 @@ def run_configs(cx):
                            "pixels_differing_from_cpu_port": frac,
                            "bar": "byte-exact against the device's all-IEEE sequence; tier B against the CPU port (logf: CUDA libm vs glibc "
                                   "differ in the last bit now and then, which moves a pixel by one tone-table entry): < 0.1 % of the pixels"}
+    # the display statistics aflak_plot computes for the same image (hist.rs:10-66, lims.rs:37-106, zscale.rs:45-242);
+    # guarded: a failure here is recorded, it does not take the headline down
+    try:
+        st = {}
+        fvmin, fvmax = float(vmin), float(vmax)
+        st["histogram_100_bins"] = entry("hist::histogram, 100 bins (incl. the read-back of the counts)", npx * 4, lambda: img.histogram(fvmin, fvmax))
+        st["vmed_vmad"] = entry("lims::get_vmed_normalized + get_vmad_normalized: exact order statistics, one min/max pass + one bracket "
+                                "pass per statistic (the reference sorts the image twice)", npx * 12, lambda: img.vmed_vmad())
+        st["zscale_1000_0.25"] = entry("Image::zscale(1000, 0.25): strided sample on the device, line fit on the host", 0, lambda: img.zscale(1000, 0.25),
+                                       cold=False)
+        t0 = time.perf_counter()
+        want_stats = oracle.vmed_vmad(himg)
+        st["cpu_port"] = {"vmed_vmad_ms": (time.perf_counter() - t0) * 1e3, "cores": 1, "kind": "port", "threading": "two full sorts on the UI thread"}
+        got_stats = img.vmed_vmad()
+        exact = got_stats[0].tobytes() == want_stats[0].tobytes() and got_stats[1].tobytes() == want_stats[1].tobytes()
+        st["parity"] = "ok" if exact else "FAILED"
+        st["parity_how"] = "vmed and vmad bit for bit against the oracle's two sorts"
+        c4["display_statistics"] = st
+        if not exact:
+            c4["parity"] = "FAILED"
+    except Exception as e:  # noqa: BLE001
+        c4["display_statistics"] = {"error": repr(e)[:300]}
     out["C4"] = c4
     del img, rgba, flush_buf
     return out
