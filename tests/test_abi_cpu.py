@@ -277,6 +277,22 @@ def test_compute_entry_points_fail_loudly_without_gpu(afk):
         afk.set_device(0)
 
 
+def test_wrap_device_validates_its_shape_before_anything_else(afk):
+    """afk_image_wrap_device takes extents from the caller: negative or overflowing ones are refused (the kernels index with
+    their product) -- checked before the device is touched, so this runs without a GPU."""
+    import ctypes as C
+
+    fake = C.c_void_p(0x1000)  # never dereferenced
+    for shape in ([4, -1], [1 << 40, 1 << 40], [-5]):
+        sh = (C.c_int64 * len(shape))(*shape)
+        assert not afk.lib.afk_image_wrap_device(fake, len(shape), sh), shape
+        msg = afk.lib.afk_last_error().decode()
+        assert "negative dimension" in msg or "image too large" in msg, msg
+    assert not afk.lib.afk_image_wrap_device(fake, 2, None)
+    assert "bad arguments" in afk.lib.afk_last_error().decode()
+    assert not afk.lib.afk_image_wrap_device(None, 0, None)
+
+
 def test_header_is_plain_c_and_a_c_client_links(afk, tmp_path):
     """include/aflak_b200.h must be consumable by a C compiler (it is what a Rust `-sys` crate binds): the C99 client of
     tests/c/ compiles with -Wall -Wextra -Werror, links against the shared library and, without a GPU, stops at its device check."""
